@@ -66,7 +66,8 @@ def fit_scaler(params, data):
 
 def _swish(x):
     # fc.py:21  x * sigmoid(x)
-    return x * (1.0 / (1.0 + np.exp(-x)))
+    with np.errstate(over="ignore"):
+        return x * (1.0 / (1.0 + np.exp(-x)))
 
 
 def _softplus(x):
@@ -139,3 +140,35 @@ class OracleModel:
             assert len(self.forced_inds) == batch_size
             return np.asarray(self.forced_inds)
         return np.random.choice(self._model_inds, size=batch_size)
+
+
+def scale_weights(params, gain):
+    """Multiply every weight tensor by ``gain`` (test helper: the init law makes activations
+    shrink layer by layer; a gain of 2-4 gives O(1) activations so GEMM errors are visible)."""
+    params['weights'] = [w * np.float32(gain) for w in params['weights']]
+    if 'var_weights' in params:
+        params['var_weights'] = params['var_weights'] * np.float32(gain)
+    return params
+
+
+def synthetic_case(domain, B, seed=0, gain=3.0, separate_mean_var=True, bias_std=0.1):
+    """Seeded synthetic D4RL-shaped case shared by the golden generator, tests and bench
+    (SURVEY.md 8(d)): params (reference init law x gain), start obs, per-step actions."""
+    shapes = {'halfcheetah': (17, 6), 'hopper': (11, 3), 'walker2d': (17, 6), 'ant': (27, 8),
+              'humanoid': (45, 17)}
+    obs_dim, act_dim = shapes[domain]
+    p = init_params(obs_dim, act_dim, seed=seed, separate_mean_var=separate_mean_var, bias_std=bias_std)
+    scale_weights(p, gain)
+    rng = np.random.RandomState(seed + 1)
+    obs = rng.standard_normal((B, obs_dim)).astype(np.float32)
+    if domain == 'hopper':
+        obs *= 0.05; obs[:, 0] += 1.25
+    elif domain == 'walker2d':
+        obs *= 0.05; obs[:, 0] += 1.25
+    elif domain == 'ant':
+        obs *= 0.05; obs[:, 0] += 0.6
+    elif domain == 'humanoid':
+        obs *= 0.05; obs[:, 0] += 1.4
+    act = np.tanh(rng.standard_normal((B, act_dim))).astype(np.float32)
+    fit_scaler(p, np.concatenate([obs, act], -1))
+    return p, obs, act

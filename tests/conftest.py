@@ -1,0 +1,16 @@
+import os, sys
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = os.path.join(ROOT, 'tests', 'golden')
+
+
+def pytest_configure(config):
+    config.addinivalue_line('markers', 'gpu: needs a CUDA device (run on the B200 box with -m gpu)')
+
+
+def golden_files(prefix):
+    return sorted(os.path.join(GOLDEN, f) for f in os.listdir(GOLDEN) if f.startswith(prefix) and f.endswith('.npz'))
