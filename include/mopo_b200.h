@@ -1,0 +1,175 @@
+/* mopo_b200 -- C ABI of the B200-native MOPO model-rollout hot path.
+ *
+ * Plain pointers and sizes only (no torch types).  Every entry point returns 0 on
+ * success or a negative MOPO_E* code; mopo_last_error() gives the message for the
+ * calling thread.  All device work is enqueued on the caller's `stream`
+ * (a cudaStream_t passed as void*; NULL = legacy default stream); calls on one handle
+ * are stream-ordered and non-reentrant (SURVEY.md 8(b) "Threading").
+ *
+ * Reference interfaces replaced (paths relative to xionghuichen/mopo):
+ *   mopo_ens_create/set_params/set_elites  <- construct_model, mopo/models/constructor.py:7-43;
+ *                                             BNN.finalize/load_params, mopo/models/bnn.py:166-281;
+ *                                             BNN._end_train (_model_inds), bnn.py:337-340
+ *   mopo_ens_predict                       <- BNN.predict(inputs, factored=True), bnn.py:508-546
+ *                                             (math: BNN._compile_outputs, bnn.py:631-675)
+ *   mopo_env_step                          <- FakeEnv.step, mopo/models/fake_env.py:37-131
+ *                                             + StaticFns.termination_fn, mopo/static/<env>.py
+ *   mopo_pool_*                            <- SimpleReplayPool / FlexibleReplayPool,
+ *                                             softlearning/replay_pools/flexible_replay_pool.py:39-161
+ *   mopo_rollout                           <- MOPO._rollout_model, mopo/algorithms/mopo.py:723-765
+ */
+#ifndef MOPO_B200_H
+#define MOPO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MOPO_OK          0
+#define MOPO_EINVAL     -1   /* bad argument (reference: AssertionError / ValueError) */
+#define MOPO_ESTATE     -2   /* call order (e.g. params/elites not set; reference: RuntimeError) */
+#define MOPO_ECUDA      -3   /* CUDA runtime error */
+#define MOPO_EUNSUPPORTED -4 /* shape outside what the sm_100a kernels are built for */
+
+/* termination_fn kinds (mopo/static/<env>.py) */
+enum {
+  MOPO_TERM_NEVER    = 0,  /* halfcheetah*.py, point2d*.py : all False */
+  MOPO_TERM_HOPPER   = 1,  /* hopper.py:9-18 (incl. the abs-of-bool quirk at :12) */
+  MOPO_TERM_WALKER2D = 2,  /* walker2d.py:9-17 */
+  MOPO_TERM_ANT      = 3,  /* ant.py:9-16, antangle.py */
+  MOPO_TERM_HUMANOID = 4   /* humanoid.py:10-14 */
+};
+
+/* penalty kinds (fake_env.py:97-115) */
+enum {
+  MOPO_PEN_NONE         = 0,  /* penalty_coeff == 0 */
+  MOPO_PEN_LEARNED_VAR  = 1,  /* max_e ||std_e||_2 over all D1 dims (fake_env.py:110) */
+  MOPO_PEN_DISAGREEMENT = 2   /* max_e ||mean_e[1:] - mean_bar[1:]||_2 (fake_env.py:99-108) */
+};
+
+/* arithmetic of the ensemble contraction */
+enum {
+  MOPO_PREC_FP32 = 0,  /* fp32 FFMA path: the rtol-1e-3 parity path */
+  MOPO_PREC_BF16 = 1   /* tcgen05 kind::f16 (bf16 operands, fp32 accumulation in TMEM) */
+};
+
+typedef struct mopo_ens  mopo_ens;
+typedef struct mopo_pool mopo_pool;
+
+typedef struct {
+  int32_t obs_dim, act_dim, rew_dim;   /* D1 = obs_dim + rew_dim ; in = obs_dim + act_dim */
+  int32_t hidden_dim;                  /* 200 */
+  int32_t n_hidden;                    /* 4 */
+  int32_t num_networks;                /* 7 */
+  int32_t num_elites;                  /* 5 */
+  int32_t separate_mean_var;           /* bnn.py:657-667 (1) vs :646-655 (0) */
+  int32_t device;                      /* CUDA device ordinal */
+} mopo_ens_cfg;
+
+const char* mopo_last_error(void);
+int mopo_version(void);
+
+/* ---- ensemble (construct_model / BNN) ------------------------------------------------ */
+int mopo_ens_create(const mopo_ens_cfg* cfg, mopo_ens** out);
+int mopo_ens_destroy(mopo_ens* h);
+
+/* Parameters in the reference's own layout (fc.py:145-154): weights[l] = [E,in_l,out_l] row-major
+ * fp32, biases[l] = [E,1,out_l]; l = 0..n_hidden (last = mean head, or the 2*D1-wide combined head
+ * when separate_mean_var == 0); var_w/var_b = the separate log-variance head (NULL in combined mode).
+ * mu/sigma [1,in]; max_logvar/min_logvar [1,D1].  Pointers are HOST pointers when on_device == 0,
+ * device pointers otherwise.  Builds the fp32 and bf16 (UMMA-ready) device images. */
+int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const float* const* biases,
+                        const float* var_w, const float* var_b,
+                        const float* mu, const float* sigma,
+                        const float* max_logvar, const float* min_logvar,
+                        int on_device, void* stream);
+
+/* Elite set = BNN._model_inds (host int32[n], each in [0,E)). */
+int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n);
+
+/* BNN.predict(x, factored=True): x [B,in] device fp32 -> mean [E,B,D1], var [E,B,D1] device fp32. */
+int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var,
+                     int precision, void* stream);
+
+/* ---- FakeEnv.step --------------------------------------------------------------------- */
+typedef struct {
+  const float* obs;        /* [B,obs_dim] device */
+  const float* act;        /* [B,act_dim] device */
+  int64_t B;
+  int32_t term_kind, penalty_kind;
+  float   penalty_coeff;
+  int32_t deterministic;   /* fake_env.py:69-70,84-86 */
+  int32_t precision;
+  /* randomness: either supplied (parity runs) or Philox4x32-10 keyed by (seed, step, origin row) */
+  const float*   noise;       /* [B,D1] device: N(0,1) draw of the chosen elite for each row, or NULL */
+  const int32_t* model_inds;  /* [B] device: chosen net per row (values in the elite set), or NULL */
+  uint64_t seed;
+  uint64_t step_id;           /* Philox stream id of this step */
+  const int32_t* origin;      /* [B] device: row id fed to Philox (NULL = 0..B-1) */
+  /* outputs (device) */
+  float*   next_obs;       /* [B,obs_dim] */
+  float*   rewards;        /* [B,1] penalised */
+  uint8_t* terminals;      /* [B,1] 0/1 */
+  float*   penalty;        /* [B,1] or NULL */
+  float*   unpenalized;    /* [B,1] or NULL */
+  float*   model_means;    /* [B,D1] or NULL (info['mean'] minus the terminal column) */
+  float*   model_stds;     /* [B,D1] or NULL */
+  float*   log_prob;       /* [B] or NULL (fake_env.py:20-35) */
+  float*   dev;            /* [B] or NULL */
+  int32_t* model_inds_out; /* [B] or NULL: the net actually used per row */
+} mopo_step_args;
+
+int mopo_env_step(mopo_ens* h, const mopo_step_args* a, void* stream);
+
+/* StaticFns.termination_fn (mopo/static/<env>.py): next_obs [B,obs_dim] device fp32 -> out [B,1] uint8. */
+int mopo_termination_fn(int32_t term_kind, const float* next_obs, int64_t B, int32_t obs_dim,
+                        uint8_t* out, void* stream);
+
+/* ---- model_pool ring buffer ------------------------------------------------------------ */
+enum { MOPO_F_ACTIONS = 0, MOPO_F_REWARDS = 1, MOPO_F_TERMINALS = 2, MOPO_F_OBS = 3, MOPO_F_NEXT_OBS = 4 };
+
+int mopo_pool_create(int32_t obs_dim, int32_t act_dim, int64_t max_size, int32_t device, mopo_pool** out);
+int mopo_pool_destroy(mopo_pool* p);
+int64_t mopo_pool_size(const mopo_pool* p);
+int64_t mopo_pool_pointer(const mopo_pool* p);
+int64_t mopo_pool_max_size(const mopo_pool* p);
+/* Device pointer of a field array ([max_size, width]; fp32 except terminals = uint8). */
+void* mopo_pool_field(const mopo_pool* p, int32_t field);
+/* add_samples (flexible_replay_pool.py:57-83): device arrays of n rows, modular index, last write wins. */
+int mopo_pool_add(mopo_pool* p, const float* obs, const float* act, const float* next_obs,
+                  const float* rew, const uint8_t* term, int64_t n, void* stream);
+/* batch_by_indices (:121-135): idx device int64[n]; outputs device arrays of n rows. */
+int mopo_pool_gather(const mopo_pool* p, const int64_t* idx, int64_t n, float* obs, float* act,
+                     float* next_obs, float* rew, uint8_t* term, void* stream);
+/* random_batch (:85-92) with Philox indices in [0,size). */
+int mopo_pool_sample(const mopo_pool* p, int64_t n, uint64_t seed, uint64_t offset, int64_t* idx_out,
+                     float* obs, float* act, float* next_obs, float* rew, uint8_t* term, void* stream);
+
+/* ---- MOPO._rollout_model ------------------------------------------------------------------ */
+typedef struct {
+  const float* start_obs;        /* [B,obs_dim] device */
+  int64_t B;
+  int32_t rollout_length;        /* h */
+  const float* const* actions;   /* host array of h device pointers, each [>=n_i, act_dim] (row j = j-th
+                                    surviving row of step i, as act = policy(obs) at mopo.py:734) */
+  int32_t term_kind, penalty_kind;
+  float   penalty_coeff;
+  int32_t deterministic, precision;
+  const float* const*   noise;      /* optional host array of h device ptrs [n_i,D1], or NULL */
+  const int32_t* const* model_inds; /* optional host array of h device ptrs [n_i], or NULL */
+  uint64_t seed;
+  uint64_t rollout_id;           /* Philox stream: (rollout_id, step) */
+  int64_t  origin_base;          /* global row id of start_obs[0] (batch sharding) */
+  int64_t* steps_added;          /* host int64[h] out (len(obs) per step, mopo.py:748) */
+} mopo_rollout_args;
+
+/* Runs h fused steps device-resident (no host round trip between steps), appending every step's
+ * rows to the pool in the reference's order, then synchronises once to read the counts back. */
+int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

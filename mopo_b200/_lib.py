@@ -1,0 +1,113 @@
+"""ctypes binding of libmopo_b200.so (the C ABI in include/mopo_b200.h).
+
+There is NO CPU fallback: if the CUDA library is missing or fails to load, importing this module
+raises.  torch is used only for device memory, streams and torch.distributed.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libmopo_b200.so')
+
+OK, EINVAL, ESTATE, ECUDA, EUNSUPPORTED = 0, -1, -2, -3, -4
+TERM_NEVER, TERM_HOPPER, TERM_WALKER2D, TERM_ANT, TERM_HUMANOID = range(5)
+PEN_NONE, PEN_LEARNED_VAR, PEN_DISAGREEMENT = range(3)
+PREC_FP32, PREC_BF16 = 0, 1
+F_ACTIONS, F_REWARDS, F_TERMINALS, F_OBS, F_NEXT_OBS = range(5)
+
+c_f32p = C.c_void_p  # device/host float*, passed as raw addresses
+
+
+class EnsCfg(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ('obs_dim', 'act_dim', 'rew_dim', 'hidden_dim', 'n_hidden',
+                                          'num_networks', 'num_elites', 'separate_mean_var', 'device')]
+
+
+class StepArgs(C.Structure):
+    _fields_ = [('obs', C.c_void_p), ('act', C.c_void_p), ('B', C.c_int64),
+                ('term_kind', C.c_int32), ('penalty_kind', C.c_int32), ('penalty_coeff', C.c_float),
+                ('deterministic', C.c_int32), ('precision', C.c_int32),
+                ('noise', C.c_void_p), ('model_inds', C.c_void_p), ('seed', C.c_uint64), ('step_id', C.c_uint64),
+                ('origin', C.c_void_p),
+                ('next_obs', C.c_void_p), ('rewards', C.c_void_p), ('terminals', C.c_void_p),
+                ('penalty', C.c_void_p), ('unpenalized', C.c_void_p), ('model_means', C.c_void_p),
+                ('model_stds', C.c_void_p), ('log_prob', C.c_void_p), ('dev', C.c_void_p),
+                ('model_inds_out', C.c_void_p)]
+
+
+class RolloutArgs(C.Structure):
+    _fields_ = [('start_obs', C.c_void_p), ('B', C.c_int64), ('rollout_length', C.c_int32),
+                ('actions', C.POINTER(C.c_void_p)),
+                ('term_kind', C.c_int32), ('penalty_kind', C.c_int32), ('penalty_coeff', C.c_float),
+                ('deterministic', C.c_int32), ('precision', C.c_int32),
+                ('noise', C.POINTER(C.c_void_p)), ('model_inds', C.POINTER(C.c_void_p)),
+                ('seed', C.c_uint64), ('rollout_id', C.c_uint64), ('origin_base', C.c_int64),
+                ('steps_added', C.POINTER(C.c_int64))]
+
+
+# every symbol include/mopo_b200.h declares: (restype, argtypes)
+SYMBOLS = {
+    'mopo_last_error': (C.c_char_p, []),
+    'mopo_version': (C.c_int, []),
+    'mopo_ens_create': (C.c_int, [C.POINTER(EnsCfg), C.POINTER(C.c_void_p)]),
+    'mopo_ens_destroy': (C.c_int, [C.c_void_p]),
+    'mopo_ens_set_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_ens_set_elites': (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32]),
+    'mopo_ens_predict': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_env_step': (C.c_int, [C.c_void_p, C.POINTER(StepArgs), C.c_void_p]),
+    'mopo_termination_fn': (C.c_int, [C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    'mopo_pool_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
+    'mopo_pool_destroy': (C.c_int, [C.c_void_p]),
+    'mopo_pool_size': (C.c_int64, [C.c_void_p]),
+    'mopo_pool_pointer': (C.c_int64, [C.c_void_p]),
+    'mopo_pool_max_size': (C.c_int64, [C.c_void_p]),
+    'mopo_pool_field': (C.c_void_p, [C.c_void_p, C.c_int32]),
+    'mopo_pool_add': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    'mopo_pool_gather': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'mopo_pool_sample': (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the CUDA library; raises (never falls back) when it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError('mopo_b200: %s is missing -- build it with `python -m mopo_b200.build` '
+                          '(or __graft_entry__.build()); there is no CPU fallback' % LIB_PATH)
+    lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the ABI is incomplete
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+_EXC = {EINVAL: ValueError, ESTATE: RuntimeError, ECUDA: RuntimeError, EUNSUPPORTED: NotImplementedError}
+
+
+def check(rc):
+    """Re-raise a C status as the exception type the reference would raise."""
+    if rc != OK:
+        msg = load().mopo_last_error()
+        raise _EXC.get(rc, RuntimeError)((msg or b'').decode() or 'mopo_b200 error %d' % rc)
+
+
+def ptr(t):
+    """Device (or host) address of a torch tensor / numpy array, None -> NULL."""
+    if t is None:
+        return None
+    if hasattr(t, 'data_ptr'):
+        return t.data_ptr()
+    return t.ctypes.data
+
+
+def stream_ptr(device):
+    import torch
+    return torch.cuda.current_stream(device).cuda_stream

@@ -1,0 +1,149 @@
+"""The slice of the MOPO algorithm class that is the hot path (reference mopo/algorithms/mopo.py):
+_set_rollout_length (:675-687), _reallocate_model_pool (:689-711), _rollout_model (:723-765).
+
+`ModelRollout` carries exactly the attributes those methods read on `self` in the reference
+(_rollout_schedule, _epoch, _rollout_batch_size, _epoch_length, _model_train_freq,
+_model_retain_epochs, _pool / sampler, fake_env, _model_pool, _rollout_random, _model_type), so a
+maintainer can mix it into MOPO or call it standalone.  Two ways to supply actions:
+  * `actions=[a_0 .. a_{h-1}]` (device tensors [>=n_i, act]) or a device policy -> ONE C call
+    (mopo_rollout): h fused steps, compaction and pool writes with no host round trip;
+  * `get_action_meta(obs, hidden)` host callback as in the reference (mopo.py:734): per-step loop.
+"""
+import ctypes as C
+import numpy as np
+import torch
+
+from .. import _lib
+from ..replay_pools import SimpleReplayPool
+
+
+class ModelRollout:
+    def __init__(self, fake_env, env_pool, rollout_batch_size=100000, rollout_schedule=(20, 100, 1, 1),
+                 epoch_length=1000, model_train_freq=250, model_retain_epochs=20, deterministic=False,
+                 rollout_random=False, model_type='mlp', get_action_meta=None, seed=0):
+        self.fake_env = fake_env
+        self._pool = env_pool                       # env (offline data) pool; `sampler.random_batch` delegates to it
+        self.sampler = env_pool                     # simple_sampler.py:103-108
+        self._rollout_batch_size = int(rollout_batch_size)
+        self._rollout_schedule = list(rollout_schedule)
+        self._epoch_length = epoch_length
+        self._model_train_freq = model_train_freq
+        self._model_retain_epochs = model_retain_epochs
+        self._deterministic = deterministic
+        self._rollout_random = rollout_random
+        self._model_type = model_type
+        self._epoch = 0
+        self._rollout_length = 1
+        self._n_train_repeat = 1
+        self._rollout_count = 0
+        self.seed = int(seed)
+        if get_action_meta is not None:
+            self.get_action_meta = get_action_meta
+
+    def make_init_hidden(self, n):
+        return None
+
+    # ---- mopo.py:675-687 -----------------------------------------------------------------------
+    def _set_rollout_length(self):
+        min_epoch, max_epoch, min_length, max_length = self._rollout_schedule
+        if self._epoch <= min_epoch:
+            y = min_length
+        else:
+            dx = (self._epoch - min_epoch) / (max_epoch - min_epoch)
+            dx = min(dx, 1)
+            y = dx * (max_length - min_length) + min_length
+        self._rollout_length = int(y)
+        print('[ Model Length ] Epoch: {} (min: {}, max: {}) | Length: {} (min: {} , max: {})'.format(
+            self._epoch, min_epoch, max_epoch, self._rollout_length, min_length, max_length))
+
+    # ---- mopo.py:689-711 -----------------------------------------------------------------------
+    def _reallocate_model_pool(self):
+        obs_space = self._pool._observation_space
+        act_space = self._pool._action_space
+        rollouts_per_epoch = self._rollout_batch_size * self._epoch_length / self._model_train_freq
+        model_steps_per_epoch = int(self._rollout_length * rollouts_per_epoch)
+        new_pool_size = self._model_retain_epochs * model_steps_per_epoch
+        if not hasattr(self, '_model_pool'):
+            print('[ MOPO ] Initializing new model pool with size {:.2e}'.format(new_pool_size))
+            self._model_pool = SimpleReplayPool(obs_space, act_space, new_pool_size, device=self.fake_env.model.device.index)
+        elif self._model_pool._max_size != new_pool_size:
+            print('[ MOPO ] Updating model pool | {:.2e} --> {:.2e}'.format(self._model_pool._max_size, new_pool_size))
+            samples = self._model_pool.return_all_samples(as_numpy=False)
+            new_pool = SimpleReplayPool(obs_space, act_space, new_pool_size, device=self.fake_env.model.device.index)
+            new_pool.add_samples(samples)
+            assert self._model_pool.size == new_pool.size
+            self._model_pool = new_pool
+
+    # ---- mopo.py:723-765 -----------------------------------------------------------------------
+    def _rollout_model(self, rollout_batch_size, start_obs=None, actions=None, noise=None, model_inds=None,
+                       precision=None, origin_base=0, quiet=False, **kwargs):
+        if not quiet:
+            print('[ Model Rollout ] Starting | Epoch: {} | Rollout length: {} | Batch size: {} | Type: {}'.format(
+                self._epoch, self._rollout_length, rollout_batch_size, self._model_type))
+        deterministic = kwargs.get('deterministic', self._deterministic)
+        if start_obs is None:
+            batch = self.sampler.random_batch(rollout_batch_size)           # mopo.py:727
+            start_obs = batch['observations']                               # mopo.py:728
+        if self._model_type == 'identity':
+            raise NotImplementedError("identity model bypass (mopo.py:740-744) has no device work")
+        if actions is not None:
+            steps_added = self._rollout_fused(start_obs, actions, noise, model_inds, deterministic, precision, origin_base)
+        else:
+            steps_added = self._rollout_callback(start_obs, deterministic, precision)
+        mean_rollout_length = sum(steps_added) / rollout_batch_size
+        rollout_stats = {'mean_rollout_length': mean_rollout_length}
+        if not quiet:
+            print('[ Model Rollout ] Added: {:.1e} | Model pool: {:.1e} (max {:.1e}) | Length: {} | Train rep: {}'.format(
+                sum(steps_added), self._model_pool.size, self._model_pool._max_size, mean_rollout_length, self._n_train_repeat))
+        self._last_steps_added = steps_added
+        return rollout_stats
+
+    def _rollout_fused(self, start_obs, actions, noise, model_inds, deterministic, precision, origin_base):
+        env, model = self.fake_env, self.fake_env.model
+        dev = model.device
+        h = self._rollout_length
+        obs = torch.as_tensor(start_obs).to(device=dev, dtype=torch.float32).contiguous()
+        B = obs.shape[0]
+        keep = [obs]
+
+        def ptr_array(seq, dtype):
+            if seq is None:
+                return None
+            ts = [torch.as_tensor(s).to(device=dev, dtype=dtype).contiguous() for s in seq]
+            assert len(ts) >= h
+            keep.extend(ts)
+            return (C.c_void_p * h)(*[t.data_ptr() for t in ts[:h]])
+
+        steps = (C.c_int64 * max(h, 1))()
+        a = _lib.RolloutArgs(start_obs=obs.data_ptr(), B=B, rollout_length=h, actions=ptr_array(actions, torch.float32),
+                             term_kind=env.config.term_kind, penalty_kind=env.penalty_kind,
+                             penalty_coeff=float(env.penalty_coeff), deterministic=int(bool(deterministic)),
+                             precision=model.precision if precision is None else precision,
+                             noise=ptr_array(noise, torch.float32), model_inds=ptr_array(model_inds, torch.int32),
+                             seed=self.seed, rollout_id=self._rollout_count, origin_base=origin_base, steps_added=steps)
+        self._rollout_count += 1
+        model._ensure_handle()
+        _lib.check(_lib.load().mopo_rollout(model._handle, self._model_pool._handle, C.byref(a), _lib.stream_ptr(dev)))
+        out = [int(steps[i]) for i in range(h)]
+        while out and out[-1] == 0:          # the reference breaks out of the loop when nothing survives (mopo.py:754-756)
+            out.pop()
+        return out
+
+    def _rollout_callback(self, obs, deterministic, precision):
+        """Literal per-step loop with a host policy callback (mopo.py:730-758)."""
+        steps_added = []
+        for i in range(self._rollout_length):
+            hidden = self.make_init_hidden(1)
+            act, hidden = self.get_action_meta(obs, hidden)
+            if self._rollout_random:
+                act = np.random.uniform(low=-1, high=1, size=act.shape)
+            next_obs, rew, term, info = self.fake_env.step(obs, act, deterministic=deterministic, precision=precision,
+                                                           diagnostics=False)
+            steps_added.append(len(obs))
+            self._model_pool.add_samples({'observations': obs, 'actions': act, 'next_observations': next_obs,
+                                          'rewards': rew, 'terminals': term})
+            nonterm_mask = ~term.squeeze(-1)
+            if nonterm_mask.sum() == 0:
+                break
+            obs = next_obs[nonterm_mask]
+        return steps_added

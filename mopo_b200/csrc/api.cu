@@ -1,0 +1,414 @@
+// C ABI of libmopo_b200.so (see include/mopo_b200.h for the reference interfaces replaced).
+#include "internal.cuh"
+#include "philox.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+static thread_local char g_err[512] = "";
+
+void mopo_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+#define MOPO_API extern "C" __attribute__((visibility("default")))
+
+MOPO_API const char* mopo_last_error(void) { return g_err; }
+MOPO_API int mopo_version(void) { return 100; }
+
+#define REQUIRE(cond, code, ...)        \
+  do {                                  \
+    if (!(cond)) {                      \
+      mopo_set_error(__VA_ARGS__);      \
+      return code;                      \
+    }                                   \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------
+// ensemble
+// ------------------------------------------------------------------------------------------
+MOPO_API int mopo_ens_create(const mopo_ens_cfg* cfg, mopo_ens** out) {
+  REQUIRE(cfg && out, MOPO_EINVAL, "mopo_ens_create: null argument");
+  REQUIRE(cfg->obs_dim > 0 && cfg->act_dim > 0 && cfg->rew_dim >= 0 && cfg->hidden_dim > 0, MOPO_EINVAL,
+          "mopo_ens_create: bad dims obs=%d act=%d rew=%d hidden=%d", cfg->obs_dim, cfg->act_dim, cfg->rew_dim, cfg->hidden_dim);
+  REQUIRE(cfg->n_hidden >= 1 && cfg->n_hidden < MOPO_MAX_LAYERS - 1, MOPO_EINVAL, "mopo_ens_create: n_hidden=%d unsupported", cfg->n_hidden);
+  REQUIRE(cfg->num_networks >= 1 && cfg->num_networks <= MOPO_MAX_E, MOPO_EINVAL, "mopo_ens_create: num_networks=%d (max %d)", cfg->num_networks, MOPO_MAX_E);
+  REQUIRE(cfg->num_elites >= 1 && cfg->num_elites <= cfg->num_networks, MOPO_EINVAL, "mopo_ens_create: num_elites=%d", cfg->num_elites);
+  REQUIRE(cfg->obs_dim + cfg->rew_dim <= MOPO_MAX_D1, MOPO_EINVAL, "mopo_ens_create: obs_dim+rew_dim > %d", MOPO_MAX_D1);
+  int ndev = 0;
+  CUDA_TRY(cudaGetDeviceCount(&ndev));
+  REQUIRE(cfg->device >= 0 && cfg->device < ndev, MOPO_EINVAL, "mopo_ens_create: device %d of %d", cfg->device, ndev);
+  CUDA_TRY(cudaSetDevice(cfg->device));
+  mopo_ens* h = new mopo_ens();
+  h->cfg = *cfg;
+  h->E = cfg->num_networks; h->in = cfg->obs_dim + cfg->act_dim; h->D1 = cfg->obs_dim + cfg->rew_dim;
+  h->H = cfg->hidden_dim; h->L = cfg->n_hidden; h->HO = 2 * h->D1;
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, cfg->device));
+  h->sm_count = prop.multiProcessorCount;
+  for (int l = 0; l <= h->L; ++l) {
+    int K = l == 0 ? h->in : h->H, N = l == h->L ? h->HO : h->H;
+    CUDA_TRY(cudaMalloc(&h->W[l], sizeof(float) * h->E * K * N));
+    CUDA_TRY(cudaMalloc(&h->b[l], sizeof(float) * h->E * N));
+  }
+  CUDA_TRY(cudaMalloc(&h->mu, sizeof(float) * h->in));
+  CUDA_TRY(cudaMalloc(&h->sigma, sizeof(float) * h->in));
+  CUDA_TRY(cudaMalloc(&h->max_lv, sizeof(float) * h->D1));
+  CUDA_TRY(cudaMalloc(&h->min_lv, sizeof(float) * h->D1));
+  CUDA_TRY(cudaMalloc(&h->elites, sizeof(int32_t) * h->E));
+  *out = h;
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_destroy(mopo_ens* h) {
+  if (!h) return MOPO_OK;
+  cudaSetDevice(h->cfg.device);
+  for (int l = 0; l < MOPO_MAX_LAYERS; ++l) { if (h->W[l]) cudaFree(h->W[l]); if (h->b[l]) cudaFree(h->b[l]); }
+  cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
+  if (h->tc_img) cudaFree(h->tc_img);
+  DevBuf* bufs[] = {&h->xn, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
+                    &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts};
+  for (DevBuf* b : bufs) b->release();
+  delete h;
+  return MOPO_OK;
+}
+
+// dst[e, k, col0 + n] = src[e, k, n]   (fuse the mean head and the separate logvar head side by side)
+__global__ void place_cols_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int n_src, int n_dst, int col0) {
+  int64_t tot = (int64_t)rows * n_src;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / n_src; int c = (int)(i % n_src);
+    dst[r * n_dst + col0 + c] = src[i];
+  }
+}
+
+static int upload(float* dst, const float* src, size_t n, int on_device, cudaStream_t st) {
+  CUDA_TRY(cudaMemcpyAsync(dst, src, n * sizeof(float), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const float* const* biases,
+                                   const float* var_w, const float* var_b, const float* mu, const float* sigma,
+                                   const float* max_logvar, const float* min_logvar, int on_device, void* stream) {
+  REQUIRE(h && weights && biases && mu && sigma && max_logvar && min_logvar, MOPO_EINVAL, "mopo_ens_set_params: null argument");
+  REQUIRE(!h->cfg.separate_mean_var || (var_w && var_b), MOPO_EINVAL, "mopo_ens_set_params: separate_mean_var needs var_w/var_b");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const int E = h->E, H = h->H, D1 = h->D1;
+  for (int l = 0; l < h->L; ++l) {
+    REQUIRE(weights[l] && biases[l], MOPO_EINVAL, "mopo_ens_set_params: layer %d null", l);
+    int K = l == 0 ? h->in : H;
+    TRY(upload(h->W[l], weights[l], (size_t)E * K * H, on_device, st));
+    TRY(upload(h->b[l], biases[l], (size_t)E * H, on_device, st));
+  }
+  REQUIRE(weights[h->L] && biases[h->L], MOPO_EINVAL, "mopo_ens_set_params: head null");
+  if (!h->cfg.separate_mean_var) {                       // bnn.py:185: last layer already 2*D1 wide
+    TRY(upload(h->W[h->L], weights[h->L], (size_t)E * H * h->HO, on_device, st));
+    TRY(upload(h->b[h->L], biases[h->L], (size_t)E * h->HO, on_device, st));
+  } else {                                               // bnn.py:657-667: both heads read the last hidden activation
+    TRY(h->misc.reserve(sizeof(float) * ((size_t)E * H * D1 + (size_t)E * D1)));
+    float* tw = h->misc.as<float>();
+    float* tb = tw + (size_t)E * H * D1;
+    const float* srcw[2] = {weights[h->L], var_w};
+    const float* srcb[2] = {biases[h->L], var_b};
+    for (int s = 0; s < 2; ++s) {
+      TRY(upload(tw, srcw[s], (size_t)E * H * D1, on_device, st));
+      TRY(upload(tb, srcb[s], (size_t)E * D1, on_device, st));
+      place_cols_kernel<<<256, 256, 0, st>>>(tw, h->W[h->L], E * H, D1, h->HO, s * D1);
+      place_cols_kernel<<<8, 256, 0, st>>>(tb, h->b[h->L], E, D1, h->HO, s * D1);
+      CUDA_TRY(cudaGetLastError());
+      if (!on_device) CUDA_TRY(cudaStreamSynchronize(st));   // host staging may be reused by the caller
+    }
+  }
+  TRY(upload(h->mu, mu, h->in, on_device, st));
+  TRY(upload(h->sigma, sigma, h->in, on_device, st));
+  TRY(upload(h->max_lv, max_logvar, D1, on_device, st));
+  TRY(upload(h->min_lv, min_logvar, D1, on_device, st));
+  if (tc_supported(h)) TRY(tc_build_images(h, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  h->params_set = true;
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n) {
+  REQUIRE(h && elites, MOPO_EINVAL, "mopo_ens_set_elites: null argument");
+  REQUIRE(n >= 1 && n <= h->E, MOPO_EINVAL, "mopo_ens_set_elites: n=%d outside [1,%d]", n, h->E);
+  for (int i = 0; i < n; ++i) REQUIRE(elites[i] >= 0 && elites[i] < h->E, MOPO_EINVAL, "mopo_ens_set_elites: index %d out of range", elites[i]);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  CUDA_TRY(cudaMemcpy(h->elites, elites, sizeof(int32_t) * n, cudaMemcpyHostToDevice));
+  h->n_elites = n;
+  h->elites_set = true;
+  return MOPO_OK;
+}
+
+static int forward(mopo_ens* h, int precision, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
+                   int64_t ldb, cudaStream_t st) {
+  if (precision == MOPO_PREC_FP32) return fp32_forward(h, xn, n_max, d_n, mean, lv, ldb, st);
+  if (precision == MOPO_PREC_BF16) {
+    REQUIRE(tc_supported(h), MOPO_EUNSUPPORTED, "bf16 tcgen05 path supports hidden_dim=200, n_hidden=4, in<=32, 2*D1<=48, E<=7 only");
+    return tc_forward(h, xn, n_max, d_n, mean, lv, ldb, st);
+  }
+  mopo_set_error("unknown precision %d", precision);
+  return MOPO_EINVAL;
+}
+
+MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, int precision, void* stream) {
+  REQUIRE(h && (B == 0 || (x && mean && var)), MOPO_EINVAL, "mopo_ens_predict: null argument");
+  REQUIRE(B >= 0 && B < (1ll << 31), MOPO_EINVAL, "mopo_ens_predict: B=%lld", (long long)B);
+  REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_predict: parameters not set");
+  if (B == 0) return MOPO_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  TRY(h->xn.reserve(sizeof(float) * B * h->in));
+  // prep with act_dim folded: x is already concat(obs, act)
+  TRY(launch_prep(x, x, h->mu, h->sigma, h->xn.as<float>(), B, nullptr, h->in, 0, st));
+  TRY(h->lv.reserve(sizeof(float) * h->E * B * h->D1));
+  TRY(forward(h, precision, h->xn.as<float>(), B, nullptr, mean, h->lv.as<float>(), B, st));
+  TRY(launch_exp(h->lv.as<float>(), var, (int64_t)h->E * B * h->D1, st));
+  return MOPO_OK;
+}
+
+static int check_step_common(const mopo_ens* h, int term_kind, int penalty_kind, int deterministic, const char* who) {
+  REQUIRE(h->params_set, MOPO_ESTATE, "%s: parameters not set", who);
+  REQUIRE(term_kind >= MOPO_TERM_NEVER && term_kind <= MOPO_TERM_HUMANOID, MOPO_EINVAL, "%s: term_kind=%d", who, term_kind);
+  REQUIRE(penalty_kind >= MOPO_PEN_NONE && penalty_kind <= MOPO_PEN_DISAGREEMENT, MOPO_EINVAL, "%s: penalty_kind=%d", who, penalty_kind);
+  REQUIRE(term_kind == MOPO_TERM_NEVER || term_kind == MOPO_TERM_HUMANOID || h->cfg.obs_dim >= 2, MOPO_EINVAL, "%s: termination needs obs_dim >= 2", who);
+  (void)deterministic;
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_env_step(mopo_ens* h, const mopo_step_args* a, void* stream) {
+  REQUIRE(h && a, MOPO_EINVAL, "mopo_env_step: null argument");
+  REQUIRE(a->B >= 0 && a->B < (1ll << 31), MOPO_EINVAL, "mopo_env_step: B=%lld", (long long)a->B);
+  TRY(check_step_common(h, a->term_kind, a->penalty_kind, a->deterministic, "mopo_env_step"));
+  REQUIRE(a->deterministic || a->model_inds || h->elites_set, MOPO_ESTATE, "mopo_env_step: elites not set (BNN._model_inds exists only after train, bnn.py:337-340)");
+  if (a->B == 0) return MOPO_OK;
+  REQUIRE(a->obs && a->act && a->next_obs && a->rewards && a->terminals, MOPO_EINVAL, "mopo_env_step: null obs/act/outputs");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const int64_t B = a->B;
+  TRY(h->xn.reserve(sizeof(float) * B * h->in));
+  TRY(h->mean.reserve(sizeof(float) * h->E * B * h->D1));
+  TRY(h->lv.reserve(sizeof(float) * h->E * B * h->D1));
+  TRY(launch_prep(a->obs, a->act, h->mu, h->sigma, h->xn.as<float>(), B, nullptr, h->cfg.obs_dim, h->cfg.act_dim, st));
+  TRY(forward(h, a->precision, h->xn.as<float>(), B, nullptr, h->mean.as<float>(), h->lv.as<float>(), B, st));
+  TailArgs t;
+  memset(&t, 0, sizeof(t));
+  t.mean = h->mean.as<float>(); t.lv = h->lv.as<float>(); t.ldb = B;
+  t.obs = a->obs; t.act = a->act; t.n_max = B; t.d_n = nullptr;
+  t.E = h->E; t.D1 = h->D1; t.obs_dim = h->cfg.obs_dim; t.act_dim = h->cfg.act_dim;
+  t.term_kind = a->term_kind; t.penalty_kind = a->penalty_kind; t.coeff = a->penalty_coeff; t.deterministic = a->deterministic;
+  t.noise = a->noise; t.model_inds = a->model_inds; t.elites = h->elites; t.n_elites = h->n_elites;
+  t.seed = a->seed; t.step_id = a->step_id; t.origin = a->origin; t.origin_base = 0;
+  t.next_obs = a->next_obs; t.rewards = a->rewards; t.terminals = a->terminals;
+  t.penalty = a->penalty; t.unpenalized = a->unpenalized; t.model_means = a->model_means; t.model_stds = a->model_stds;
+  t.log_prob = a->log_prob; t.dev = a->dev; t.model_inds_out = a->model_inds_out;
+  TRY(launch_tail(t, st));
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_termination_fn(int32_t term_kind, const float* next_obs, int64_t B, int32_t obs_dim, uint8_t* out, void* stream) {
+  REQUIRE(term_kind >= MOPO_TERM_NEVER && term_kind <= MOPO_TERM_HUMANOID, MOPO_EINVAL, "mopo_termination_fn: term_kind=%d", term_kind);
+  REQUIRE(B >= 0 && obs_dim >= 1 && (B == 0 || (next_obs && out)), MOPO_EINVAL, "mopo_termination_fn: bad argument");
+  REQUIRE(term_kind == MOPO_TERM_NEVER || term_kind == MOPO_TERM_HUMANOID || obs_dim >= 2, MOPO_EINVAL, "mopo_termination_fn: needs obs_dim >= 2");
+  return launch_term_only(term_kind, next_obs, B, obs_dim, out, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------
+// pool
+// ------------------------------------------------------------------------------------------
+MOPO_API int mopo_pool_create(int32_t obs_dim, int32_t act_dim, int64_t max_size, int32_t device, mopo_pool** out) {
+  REQUIRE(out && obs_dim > 0 && act_dim > 0 && max_size > 0, MOPO_EINVAL, "mopo_pool_create: bad argument");
+  CUDA_TRY(cudaSetDevice(device));
+  mopo_pool* p = new mopo_pool();
+  p->obs_dim = obs_dim; p->act_dim = act_dim; p->device = device; p->max_size = max_size; p->size = 0; p->pointer = 0;
+  CUDA_TRY(cudaMalloc(&p->actions, sizeof(float) * max_size * act_dim));
+  CUDA_TRY(cudaMalloc(&p->rewards, sizeof(float) * max_size));
+  CUDA_TRY(cudaMalloc(&p->terminals, max_size));
+  CUDA_TRY(cudaMalloc(&p->obs, sizeof(float) * max_size * obs_dim));
+  CUDA_TRY(cudaMalloc(&p->next_obs, sizeof(float) * max_size * obs_dim));
+  // flexible_replay_pool.py:39-43: fields are zero-initialised
+  CUDA_TRY(cudaMemset(p->actions, 0, sizeof(float) * max_size * act_dim));
+  CUDA_TRY(cudaMemset(p->rewards, 0, sizeof(float) * max_size));
+  CUDA_TRY(cudaMemset(p->terminals, 0, max_size));
+  CUDA_TRY(cudaMemset(p->obs, 0, sizeof(float) * max_size * obs_dim));
+  CUDA_TRY(cudaMemset(p->next_obs, 0, sizeof(float) * max_size * obs_dim));
+  *out = p;
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_pool_destroy(mopo_pool* p) {
+  if (!p) return MOPO_OK;
+  cudaSetDevice(p->device);
+  cudaFree(p->actions); cudaFree(p->rewards); cudaFree(p->terminals); cudaFree(p->obs); cudaFree(p->next_obs);
+  delete p;
+  return MOPO_OK;
+}
+MOPO_API int64_t mopo_pool_size(const mopo_pool* p) { return p ? p->size : -1; }
+MOPO_API int64_t mopo_pool_pointer(const mopo_pool* p) { return p ? p->pointer : -1; }
+MOPO_API int64_t mopo_pool_max_size(const mopo_pool* p) { return p ? p->max_size : -1; }
+MOPO_API void* mopo_pool_field(const mopo_pool* p, int32_t f) {
+  if (!p) return nullptr;
+  switch (f) {
+    case MOPO_F_ACTIONS: return p->actions;
+    case MOPO_F_REWARDS: return p->rewards;
+    case MOPO_F_TERMINALS: return p->terminals;
+    case MOPO_F_OBS: return p->obs;
+    case MOPO_F_NEXT_OBS: return p->next_obs;
+  }
+  return nullptr;
+}
+
+// rows [skip, n) of src -> ring rows (base + j) % max ; flattened so stores are coalesced per field
+template <class T>
+__global__ void ring_scatter_kernel(const T* __restrict__ src, T* __restrict__ dst, int64_t n, int64_t skip, int width,
+                                    int64_t base, int64_t max_size) {
+  int64_t tot = (n - skip) * width;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t j = skip + i / width; int c = (int)(i % width);
+    dst[((base + j) % max_size) * width + c] = src[j * width + c];
+  }
+}
+template <class T>
+__global__ void gather_rows_kernel(const T* __restrict__ src, const int64_t* __restrict__ idx, T* __restrict__ dst, int64_t n, int width) {
+  int64_t tot = n * width;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t j = i / width; int c = (int)(i % width);
+    dst[i] = src[idx[j] * width + c];
+  }
+}
+__global__ void philox_index_kernel(int64_t* idx, int64_t n, uint64_t seed, uint64_t offset, int64_t size) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    uint64_t c = offset + (uint64_t)i;
+    Philox4 r = philox4x32_10((uint32_t)c, (uint32_t)(c >> 32), 0u, MOPO_STREAM_POOL, (uint32_t)seed, (uint32_t)(seed >> 32));
+    uint64_t u = ((uint64_t)r.x << 32) | r.y;
+    idx[i] = (int64_t)__umul64hi(u, (uint64_t)size);     // floor(u * size / 2^64): np.random.randint(0, size)
+  }
+}
+
+static int grid_for(int64_t tot) { int64_t g = (tot + 255) / 256; if (g < 1) g = 1; if (g > 148 * 16) g = 148 * 16; return (int)g; }
+
+MOPO_API int mopo_pool_add(mopo_pool* p, const float* obs, const float* act, const float* next_obs,
+                             const float* rew, const uint8_t* term, int64_t n, void* stream) {
+  REQUIRE(p && n >= 0, MOPO_EINVAL, "mopo_pool_add: bad argument");
+  if (n == 0) return MOPO_OK;
+  REQUIRE(obs && act && next_obs && rew && term, MOPO_EINVAL, "mopo_pool_add: null field");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(p->device));
+  const int64_t skip = n > p->max_size ? n - p->max_size : 0;   // duplicates: the last write wins
+  ring_scatter_kernel<<<grid_for((n - skip) * p->act_dim), 256, 0, st>>>(act, p->actions, n, skip, p->act_dim, p->pointer, p->max_size);
+  ring_scatter_kernel<<<grid_for(n - skip), 256, 0, st>>>(rew, p->rewards, n, skip, 1, p->pointer, p->max_size);
+  ring_scatter_kernel<<<grid_for(n - skip), 256, 0, st>>>(term, p->terminals, n, skip, 1, p->pointer, p->max_size);
+  ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(obs, p->obs, n, skip, p->obs_dim, p->pointer, p->max_size);
+  ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(next_obs, p->next_obs, n, skip, p->obs_dim, p->pointer, p->max_size);
+  CUDA_TRY(cudaGetLastError());
+  p->pointer = (p->pointer + n) % p->max_size;                 // flexible_replay_pool.py:45-48
+  p->size = p->size + n < p->max_size ? p->size + n : p->max_size;
+  return MOPO_OK;
+}
+
+static int pool_gather_impl(const mopo_pool* p, const int64_t* idx, int64_t n, float* obs, float* act, float* next_obs,
+                            float* rew, uint8_t* term, cudaStream_t st) {
+  if (act) gather_rows_kernel<<<grid_for(n * p->act_dim), 256, 0, st>>>(p->actions, idx, act, n, p->act_dim);
+  if (rew) gather_rows_kernel<<<grid_for(n), 256, 0, st>>>(p->rewards, idx, rew, n, 1);
+  if (term) gather_rows_kernel<<<grid_for(n), 256, 0, st>>>(p->terminals, idx, term, n, 1);
+  if (obs) gather_rows_kernel<<<grid_for(n * p->obs_dim), 256, 0, st>>>(p->obs, idx, obs, n, p->obs_dim);
+  if (next_obs) gather_rows_kernel<<<grid_for(n * p->obs_dim), 256, 0, st>>>(p->next_obs, idx, next_obs, n, p->obs_dim);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_pool_gather(const mopo_pool* p, const int64_t* idx, int64_t n, float* obs, float* act,
+                                float* next_obs, float* rew, uint8_t* term, void* stream) {
+  REQUIRE(p && n >= 0 && (n == 0 || idx), MOPO_EINVAL, "mopo_pool_gather: bad argument");
+  if (n == 0) return MOPO_OK;
+  CUDA_TRY(cudaSetDevice(p->device));
+  return pool_gather_impl(p, idx, n, obs, act, next_obs, rew, term, (cudaStream_t)stream);
+}
+
+MOPO_API int mopo_pool_sample(const mopo_pool* p, int64_t n, uint64_t seed, uint64_t offset, int64_t* idx_out,
+                                float* obs, float* act, float* next_obs, float* rew, uint8_t* term, void* stream) {
+  REQUIRE(p && n >= 0 && (n == 0 || idx_out), MOPO_EINVAL, "mopo_pool_sample: bad argument");
+  REQUIRE(p->size > 0 || n == 0, MOPO_ESTATE, "mopo_pool_sample: pool is empty");
+  if (n == 0) return MOPO_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(p->device));
+  philox_index_kernel<<<grid_for(n), 256, 0, st>>>(idx_out, n, seed, offset, p->size);
+  CUDA_TRY(cudaGetLastError());
+  return pool_gather_impl(p, idx_out, n, obs, act, next_obs, rew, term, st);
+}
+
+// ------------------------------------------------------------------------------------------
+// rollout
+// ------------------------------------------------------------------------------------------
+__global__ void rollout_init_kernel(int* counts, int64_t* pool_off, int n0, int h) {
+  if (threadIdx.x == 0) { counts[0] = n0; for (int i = 1; i <= h; ++i) counts[i] = 0; *pool_off = 0; }
+}
+
+MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream) {
+  REQUIRE(h && pool && a, MOPO_EINVAL, "mopo_rollout: null argument");
+  REQUIRE(a->B >= 0 && a->B < (1ll << 31) && a->rollout_length >= 0 && a->rollout_length <= 1024, MOPO_EINVAL, "mopo_rollout: B=%lld h=%d", (long long)a->B, a->rollout_length);
+  REQUIRE(pool->obs_dim == h->cfg.obs_dim && pool->act_dim == h->cfg.act_dim && pool->device == h->cfg.device, MOPO_EINVAL, "mopo_rollout: pool/ensemble mismatch");
+  TRY(check_step_common(h, a->term_kind, a->penalty_kind, a->deterministic, "mopo_rollout"));
+  REQUIRE(a->deterministic || a->model_inds || h->elites_set, MOPO_ESTATE, "mopo_rollout: elites not set");
+  const int H = a->rollout_length;
+  const int64_t B = a->B;
+  if (a->steps_added) for (int i = 0; i < H; ++i) a->steps_added[i] = 0;
+  if (B == 0 || H == 0) return MOPO_OK;
+  REQUIRE(a->start_obs && a->actions && a->steps_added, MOPO_EINVAL, "mopo_rollout: null start_obs/actions/steps_added");
+  for (int i = 0; i < H; ++i) REQUIRE(a->actions[i], MOPO_EINVAL, "mopo_rollout: actions[%d] null", i);
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  const int od = h->cfg.obs_dim, ad = h->cfg.act_dim;
+  const int nblk = (int)((B + tail_rows_per_block() - 1) / tail_rows_per_block());
+  TRY(h->xn.reserve(sizeof(float) * B * h->in));
+  TRY(h->mean.reserve(sizeof(float) * h->E * B * h->D1));
+  TRY(h->lv.reserve(sizeof(float) * h->E * B * h->D1));
+  TRY(h->blk_counts.reserve(sizeof(int) * nblk));
+  // ro_obs[0/1]: dense obs of the current step / next_obs of the current step ; ro_origin likewise
+  for (int k = 0; k < 2; ++k) { TRY(h->ro_obs[k].reserve(sizeof(float) * B * od)); TRY(h->ro_origin[k].reserve(sizeof(int32_t) * B)); }
+  TRY(h->misc.reserve(sizeof(float) * B * od + B));                       // dense next_obs + terminals of the step
+  TRY(h->ro_counts.reserve(sizeof(int) * (H + 1) + sizeof(int64_t) * 2));
+  int64_t* d_pool_off = h->ro_counts.as<int64_t>();                          // [0] = rows appended so far
+  int* d_counts = reinterpret_cast<int*>(d_pool_off + 2);
+  float* nobs_dense = h->misc.as<float>();
+  uint8_t* term_dense = reinterpret_cast<uint8_t*>(nobs_dense + B * od);
+  rollout_init_kernel<<<1, 32, 0, st>>>(d_counts, d_pool_off, (int)B, H);
+  const float* obs_cur = a->start_obs;
+  const int32_t* origin_cur = nullptr;
+  for (int i = 0; i < H; ++i) {
+    const int* d_n = d_counts + i;
+    TRY(launch_prep(obs_cur, a->actions[i], h->mu, h->sigma, h->xn.as<float>(), B, d_n, od, ad, st));
+    TRY(forward(h, a->precision, h->xn.as<float>(), B, d_n, h->mean.as<float>(), h->lv.as<float>(), B, st));
+    TailArgs t;
+    memset(&t, 0, sizeof(t));
+    t.mean = h->mean.as<float>(); t.lv = h->lv.as<float>(); t.ldb = B;
+    t.obs = obs_cur; t.act = a->actions[i]; t.n_max = B; t.d_n = d_n;
+    t.E = h->E; t.D1 = h->D1; t.obs_dim = od; t.act_dim = ad;
+    t.term_kind = a->term_kind; t.penalty_kind = a->penalty_kind; t.coeff = a->penalty_coeff; t.deterministic = a->deterministic;
+    t.noise = a->noise ? a->noise[i] : nullptr; t.model_inds = a->model_inds ? a->model_inds[i] : nullptr;
+    t.elites = h->elites; t.n_elites = h->n_elites;
+    t.seed = a->seed; t.step_id = (a->rollout_id << 16) ^ (uint64_t)i; t.origin = origin_cur; t.origin_base = a->origin_base;
+    t.next_obs = nobs_dense; t.rewards = nullptr; t.terminals = term_dense;
+    t.p_act = pool->actions; t.p_rew = pool->rewards; t.p_obs = pool->obs; t.p_nobs = pool->next_obs; t.p_term = pool->terminals;
+    t.pool_max = pool->max_size; t.pool_base = pool->pointer; t.d_pool_off = d_pool_off;
+    t.blk_counts = h->blk_counts.as<int>();
+    TRY(launch_tail(t, st));
+    float* obs_next = h->ro_obs[i & 1].as<float>();
+    int32_t* origin_next = h->ro_origin[i & 1].as<int32_t>();
+    TRY(launch_compact(nobs_dense, term_dense, origin_cur, a->origin_base, B, d_n, h->blk_counts.as<int>(), od,
+                       obs_next, origin_next, d_counts + i + 1, d_pool_off, st));
+    obs_cur = obs_next; origin_cur = origin_next;
+  }
+  std::vector<int> counts(H + 1);
+  CUDA_TRY(cudaMemcpyAsync(counts.data(), d_counts, sizeof(int) * (H + 1), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  int64_t total = 0;
+  for (int i = 0; i < H; ++i) { a->steps_added[i] = counts[i]; total += counts[i]; }
+  pool->pointer = (pool->pointer + total) % pool->max_size;      // == h successive add_samples calls
+  pool->size = pool->size + total < pool->max_size ? pool->size + total : pool->max_size;
+  return MOPO_OK;
+}

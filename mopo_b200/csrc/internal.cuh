@@ -1,0 +1,114 @@
+// Internal declarations shared by the translation units of libmopo_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/mopo_b200.h"
+
+#define MOPO_MAX_LAYERS 8
+#define MOPO_MAX_D1 64
+#define MOPO_MAX_E 16
+
+void mopo_set_error(const char* fmt, ...);
+
+#define CUDA_TRY(expr)                                                                  \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess) {                                                            \
+      mopo_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return MOPO_ECUDA;                                                                \
+    }                                                                                   \
+  } while (0)
+
+#define TRY(expr)              \
+  do {                         \
+    int _r = (expr);           \
+    if (_r != MOPO_OK) return _r; \
+  } while (0)
+
+// Device buffer that only grows.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return MOPO_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 4;
+    CUDA_TRY(cudaMalloc(&p, want));
+    cap = want;
+    return MOPO_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct mopo_ens {
+  mopo_ens_cfg cfg;
+  int E, in, D1, H, L, HO;   // HO = 2*D1: width of the fused [mean | raw logvar] head
+  bool params_set = false, elites_set = false;
+  int sm_count = 148;
+
+  // fp32 images (reference layout): hidden layers l = 0..L-1, fused head at index L.
+  float* W[MOPO_MAX_LAYERS] = {};   // [E, K_l, N_l]
+  float* b[MOPO_MAX_LAYERS] = {};   // [E, N_l]
+  float *mu = nullptr, *sigma = nullptr, *max_lv = nullptr, *min_lv = nullptr;
+  int32_t* elites = nullptr;        // device [num_elites]
+  int n_elites = 0;
+
+  // bf16 UMMA-ready images for the tcgen05 path (built by tc_build_images).
+  void* tc_img = nullptr;
+  size_t tc_img_bytes = 0;
+
+  // scratch
+  DevBuf xn, actA, actB, mean, lv, blk_counts, misc;
+  DevBuf ro_obs[2], ro_origin[2], ro_counts;
+};
+
+struct mopo_pool {
+  int obs_dim, act_dim, device;
+  int64_t max_size, size, pointer;
+  float *actions, *rewards, *obs, *next_obs;
+  uint8_t* terminals;
+};
+
+// ---- fp32 FFMA forward (ens_fp32.cu) --------------------------------------------------------
+// xn [n_max,in] -> mean [E,ldb,D1], lv [E,ldb,D1]; rows >= *d_n (if d_n) are skipped.
+int fp32_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
+                 int64_t ldb, cudaStream_t st);
+
+// ---- tcgen05 bf16 forward (ens_tc.cu) ---------------------------------------------------------
+int tc_supported(const mopo_ens* h);
+int tc_build_images(mopo_ens* h, cudaStream_t st);
+int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
+               int64_t ldb, cudaStream_t st);
+
+// ---- step tail / pool / compaction (tail.cu) ---------------------------------------------------
+struct TailArgs {
+  const float *mean, *lv;      // [E,ldb,D1]
+  int64_t ldb;
+  const float *obs, *act;      // [n,obs] [n,act]
+  int64_t n_max; const int* d_n;
+  int E, D1, obs_dim, act_dim;
+  int term_kind, penalty_kind; float coeff; int deterministic;
+  const float* noise; const int32_t* model_inds; const int32_t* elites; int n_elites;
+  uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
+  float *next_obs, *rewards; uint8_t* terminals;
+  float *penalty, *unpenalized, *model_means, *model_stds, *log_prob, *dev; int32_t* model_inds_out;
+  // optional pool append: row j -> (pool_base + *d_pool_off + j) % pool_max
+  float *p_act, *p_rew, *p_obs, *p_nobs; uint8_t* p_term; int64_t pool_max, pool_base; const int64_t* d_pool_off;
+  // optional compaction bookkeeping
+  int* blk_counts;             // [ceil(n_max/TAIL_ROWS)] survivors per block
+};
+int launch_prep(const float* obs, const float* act, const float* mu, const float* sigma, float* xn,
+                int64_t n_max, const int* d_n, int obs_dim, int act_dim, cudaStream_t st);
+int launch_tail(const TailArgs& a, cudaStream_t st);
+int tail_rows_per_block();
+// survivors of step i -> dense obs/origin for step i+1; writes d_n_next and advances d_pool_off by n.
+int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* origin_in, int64_t origin_base,
+                   int64_t n_max, const int* d_n, const int* blk_counts, int obs_dim,
+                   float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, cudaStream_t st);
+int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, uint8_t* out, cudaStream_t st);
+int launch_exp(const float* lv, float* var, int64_t n, cudaStream_t st);

@@ -1,0 +1,269 @@
+// FakeEnv.step tail (everything after model.predict), pool ring-buffer kernels and the
+// order-preserving compaction between rollout steps.
+//
+// Reference: mopo/models/fake_env.py:63-131 (mean += obs, std, sample, elite gather, log-prob,
+// termination, penalty), mopo/static/<env>.py (termination_fn), flexible_replay_pool.py:45-83
+// (ring index), mopo/algorithms/mopo.py:753-758 (obs = next_obs[nonterm_mask]).
+#include "internal.cuh"
+#include "philox.cuh"
+
+namespace {
+
+constexpr int TAIL_ROWS = 128;
+
+__device__ __forceinline__ bool term_fn(int kind, const float* s /* s[0]=rew, s[1..]=next_obs */, int obs_dim) {
+  // Comparisons in double: the reference compares (float64) samples with Python float literals.
+  const float* o = s + 1;
+  switch (kind) {
+    case MOPO_TERM_HOPPER: {   // hopper.py:9-18; :12 is abs(bool) -> upper bound only
+      bool fin = true, lt = true;
+      for (int d = 0; d < obs_dim; ++d) fin = fin && isfinite(o[d]);
+      for (int d = 1; d < obs_dim; ++d) lt = lt && ((double)o[d] < 100.0);
+      bool nd = fin && lt && ((double)o[0] > 0.7) && (fabs((double)o[1]) < 0.2);
+      return !nd;
+    }
+    case MOPO_TERM_WALKER2D: { // walker2d.py:9-17
+      double hgt = o[0], ang = o[1];
+      bool nd = (hgt > 0.8) && (hgt < 2.0) && (ang > -1.0) && (ang < 1.0);
+      return !nd;
+    }
+    case MOPO_TERM_ANT: {      // ant.py:9-16
+      bool fin = true;
+      for (int d = 0; d < obs_dim; ++d) fin = fin && isfinite(o[d]);
+      double x = o[0];
+      return !(fin && (x >= 0.2) && (x <= 1.0));
+    }
+    case MOPO_TERM_HUMANOID: { // humanoid.py:10-14
+      double z = o[0];
+      return (z < 1.0) || (z > 2.0);
+    }
+    default: return false;     // halfcheetah.py:9-11
+  }
+}
+
+__global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
+  const int64_t n = a.d_n ? min((int64_t)*a.d_n, a.n_max) : a.n_max;
+  const int64_t j = (int64_t)blockIdx.x * TAIL_ROWS + threadIdx.x;
+  const bool valid = j < n;
+  const int E = a.E, D1 = a.D1;
+  bool alive = false;
+  if (valid) {
+    const uint32_t orow = a.origin ? (uint32_t)a.origin[j] : (uint32_t)(a.origin_base + j);
+    const float* ob = a.obs + j * a.obs_dim;
+    float smp[MOPO_MAX_D1];
+    int m = 0;
+    if (!a.deterministic) {
+      m = a.model_inds ? a.model_inds[j]
+                       : a.elites[philox_elite(orow, (uint32_t)a.step_id, a.seed, (uint32_t)a.n_elites)];
+      const float* mm = a.mean + ((int64_t)m * a.ldb + j) * D1;
+      const float* ll = a.lv + ((int64_t)m * a.ldb + j) * D1;
+      float z[4];
+      for (int d = 0; d < D1; ++d) {
+        float mu = mm[d] + (d ? ob[d - 1] : 0.0f);          // fake_env.py:66
+        float sd = sqrtf(expf(ll[d]));                        // bnn.py:675 + fake_env.py:67
+        float zz;
+        if (a.noise) zz = a.noise[j * D1 + d];
+        else { if ((d & 3) == 0) philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(d >> 2), a.seed, z); zz = z[d & 3]; }
+        smp[d] = fmaf(zz, sd, mu);                            // fake_env.py:72,79
+        if (a.model_means) a.model_means[j * D1 + d] = mu;
+        if (a.model_stds) a.model_stds[j * D1 + d] = sd;
+      }
+    } else {                                                  // fake_env.py:84-86: mean over ALL nets
+      for (int d = 0; d < D1; ++d) {
+        float sm = 0.f, ss = 0.f, o = d ? ob[d - 1] : 0.0f;
+        for (int e = 0; e < E; ++e) {
+          sm += a.mean[((int64_t)e * a.ldb + j) * D1 + d] + o;
+          ss += sqrtf(expf(a.lv[((int64_t)e * a.ldb + j) * D1 + d]));
+        }
+        smp[d] = sm / (float)E;
+        if (a.model_means) a.model_means[j * D1 + d] = smp[d];
+        if (a.model_stds) a.model_stds[j * D1 + d] = ss / (float)E;
+      }
+      m = -1;
+    }
+    // penalty (fake_env.py:97-115)
+    float pen = 0.f;
+    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
+      for (int e = 0; e < E; ++e) {
+        const float* ll = a.lv + ((int64_t)e * a.ldb + j) * D1;
+        float s2 = 0.f;
+        for (int d = 0; d < D1; ++d) { float sd = sqrtf(expf(ll[d])); s2 = fmaf(sd, sd, s2); }
+        pen = fmaxf(pen, s2);
+      }
+      pen = sqrtf(pen);
+    } else if (a.penalty_kind == MOPO_PEN_DISAGREEMENT) {
+      float d2[MOPO_MAX_E];
+      for (int e = 0; e < E; ++e) d2[e] = 0.f;
+      for (int d = 1; d < D1; ++d) {
+        float o = ob[d - 1], mbar = 0.f;
+        for (int e = 0; e < E; ++e) mbar += a.mean[((int64_t)e * a.ldb + j) * D1 + d] + o;
+        mbar /= (float)E;
+        for (int e = 0; e < E; ++e) {
+          float df = (a.mean[((int64_t)e * a.ldb + j) * D1 + d] + o) - mbar;
+          d2[e] = fmaf(df, df, d2[e]);
+        }
+      }
+      for (int e = 0; e < E; ++e) pen = fmaxf(pen, d2[e]);
+      pen = sqrtf(pen);
+    }
+    // diagnostics (fake_env.py:20-35), only on request
+    if (a.log_prob || a.dev) {
+      float prob = 0.f;
+      for (int e = 0; e < E; ++e) {
+        float slog = 0.f, sq = 0.f;
+        for (int d = 0; d < D1; ++d) {
+          float mu = a.mean[((int64_t)e * a.ldb + j) * D1 + d] + (d ? ob[d - 1] : 0.0f);
+          float l = a.lv[((int64_t)e * a.ldb + j) * D1 + d];
+          float df = smp[d] - mu;
+          slog += l; sq += df * df * expf(-l);
+        }
+        prob += expf(-0.5f * ((float)D1 * 1.8378770664093453f + slog + sq));
+      }
+      if (a.log_prob) a.log_prob[j] = logf(prob);
+      if (a.dev) {
+        float acc = 0.f;
+        for (int d = 0; d < D1; ++d) {
+          float s1 = 0.f, s2 = 0.f;
+          for (int e = 0; e < E; ++e) { float v = a.mean[((int64_t)e * a.ldb + j) * D1 + d]; s1 += v; }
+          s1 /= (float)E;
+          for (int e = 0; e < E; ++e) { float v = a.mean[((int64_t)e * a.ldb + j) * D1 + d] - s1; s2 += v * v; }
+          acc += sqrtf(s2 / (float)E);
+        }
+        a.dev[j] = acc / (float)D1;
+      }
+    }
+    const bool term = term_fn(a.term_kind, smp, a.obs_dim);   // fake_env.py:91
+    alive = !term;
+    const float unpen = smp[0];
+    const float rew = (a.penalty_kind == MOPO_PEN_NONE) ? unpen : unpen - a.coeff * pen;   // fake_env.py:115
+    if (a.next_obs) for (int d = 0; d < a.obs_dim; ++d) a.next_obs[j * a.obs_dim + d] = smp[d + 1];
+    if (a.rewards) a.rewards[j] = rew;
+    if (a.terminals) a.terminals[j] = term ? 1 : 0;
+    if (a.penalty) a.penalty[j] = pen;
+    if (a.unpenalized) a.unpenalized[j] = unpen;
+    if (a.model_inds_out) a.model_inds_out[j] = m;
+    if (a.p_obs && (n - j) <= a.pool_max) {                   // flexible_replay_pool.py:57-83, last write wins
+      const int64_t off = a.d_pool_off ? *a.d_pool_off : 0;
+      const int64_t r = (a.pool_base + off + j) % a.pool_max;
+      for (int d = 0; d < a.obs_dim; ++d) { a.p_obs[r * a.obs_dim + d] = ob[d]; a.p_nobs[r * a.obs_dim + d] = smp[d + 1]; }
+      const float* ac = a.act + j * a.act_dim;
+      for (int d = 0; d < a.act_dim; ++d) a.p_act[r * a.act_dim + d] = ac[d];
+      a.p_rew[r] = rew;
+      a.p_term[r] = term ? 1 : 0;
+    }
+  }
+  if (a.blk_counts) {
+    int c = __syncthreads_count(alive);
+    if (threadIdx.x == 0) a.blk_counts[blockIdx.x] = c;
+  }
+}
+
+__global__ void prep_kernel(const float* __restrict__ obs, const float* __restrict__ act,
+                            const float* __restrict__ mu, const float* __restrict__ sigma, float* __restrict__ xn,
+                            int64_t n_max, const int* __restrict__ d_n, int obs_dim, int act_dim) {
+  const int64_t n = d_n ? min((int64_t)*d_n, n_max) : n_max;
+  const int in = obs_dim + act_dim;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n * in; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t j = i / in; int c = (int)(i % in);
+    float v = c < obs_dim ? obs[j * obs_dim + c] : act[j * act_dim + (c - obs_dim)];
+    xn[i] = (v - mu[c]) / sigma[c];                           // mopo/models/utils.py:96
+  }
+}
+
+// mopo.py:753-758: obs = next_obs[~term], order preserved.  Same row->block map as the tail.
+__global__ void __launch_bounds__(TAIL_ROWS)
+compact_kernel(const float* __restrict__ next_obs, const uint8_t* __restrict__ term,
+               const int32_t* __restrict__ origin_in, int64_t origin_base, int64_t n_max, const int* __restrict__ d_n,
+               const int* __restrict__ blk_counts, int obs_dim, float* __restrict__ obs_out,
+               int32_t* __restrict__ origin_out, int* __restrict__ d_n_next, int64_t* __restrict__ d_pool_off) {
+  const int64_t n = min((int64_t)*d_n, n_max);
+  __shared__ int s_part[TAIL_ROWS / 32];
+  __shared__ int s_base;
+  int part = 0;
+  for (int b = threadIdx.x; b < (int)blockIdx.x; b += TAIL_ROWS) part += blk_counts[b];
+  for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (lane == 0) s_part[warp] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) { int s = 0; for (int w = 0; w < TAIL_ROWS / 32; ++w) s += s_part[w]; s_base = s; }
+  __syncthreads();
+  const int base = s_base;
+  const int64_t j = (int64_t)blockIdx.x * TAIL_ROWS + threadIdx.x;
+  const bool alive = (j < n) && (term[j] == 0);
+  const unsigned bal = __ballot_sync(0xffffffffu, alive);
+  __syncthreads();
+  if (lane == 0) s_part[warp] = __popc(bal);
+  __syncthreads();
+  int woff = 0;
+  for (int w = 0; w < warp; ++w) woff += s_part[w];
+  if (alive) {
+    const int64_t dst = base + woff + __popc(bal & ((1u << lane) - 1u));
+    for (int d = 0; d < obs_dim; ++d) obs_out[dst * obs_dim + d] = next_obs[j * obs_dim + d];
+    origin_out[dst] = origin_in ? origin_in[j] : (int32_t)(origin_base + j);
+  }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+    int tot = base;
+    for (int w = 0; w < TAIL_ROWS / 32; ++w) tot += s_part[w];
+    *d_n_next = tot;
+    if (d_pool_off) *d_pool_off += n;
+  }
+}
+
+__global__ void term_only_kernel(int kind, const float* __restrict__ next_obs, int64_t n, int obs_dim, uint8_t* __restrict__ out) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x)
+    out[j] = term_fn(kind, next_obs + j * obs_dim - 1, obs_dim) ? 1 : 0;     // term_fn skips the reward slot
+}
+
+__global__ void exp_kernel(const float* __restrict__ lv, float* __restrict__ var, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    var[i] = expf(lv[i]);
+}
+
+}  // namespace
+
+int tail_rows_per_block() { return TAIL_ROWS; }
+
+int launch_prep(const float* obs, const float* act, const float* mu, const float* sigma, float* xn,
+                int64_t n_max, const int* d_n, int obs_dim, int act_dim, cudaStream_t st) {
+  if (n_max == 0) return MOPO_OK;
+  int64_t tot = n_max * (obs_dim + act_dim);
+  int64_t g64 = (tot + 255) / 256; int grid = (int)(g64 > 148 * 16 ? 148 * 16 : g64);
+  prep_kernel<<<grid, 256, 0, st>>>(obs, act, mu, sigma, xn, n_max, d_n, obs_dim, act_dim);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int launch_tail(const TailArgs& a, cudaStream_t st) {
+  if (a.n_max == 0) return MOPO_OK;
+  int grid = (int)((a.n_max + TAIL_ROWS - 1) / TAIL_ROWS);
+  step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* origin_in, int64_t origin_base,
+                   int64_t n_max, const int* d_n, const int* blk_counts, int obs_dim,
+                   float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, cudaStream_t st) {
+  if (n_max == 0) return MOPO_OK;
+  int grid = (int)((n_max + TAIL_ROWS - 1) / TAIL_ROWS);
+  compact_kernel<<<grid, TAIL_ROWS, 0, st>>>(next_obs, term, origin_in, origin_base, n_max, d_n, blk_counts, obs_dim,
+                                             obs_out, origin_out, d_n_next, d_pool_off);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, uint8_t* out, cudaStream_t st) {
+  if (n == 0) return MOPO_OK;
+  int64_t g64 = (n + 255) / 256; int grid = (int)(g64 > 148 * 16 ? 148 * 16 : g64);
+  term_only_kernel<<<grid, 256, 0, st>>>(kind, next_obs, n, obs_dim, out);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int launch_exp(const float* lv, float* var, int64_t n, cudaStream_t st) {
+  if (n == 0) return MOPO_OK;
+  int64_t g64 = (n + 255) / 256; int grid = (int)(g64 > 148 * 16 ? 148 * 16 : g64);
+  exp_kernel<<<grid, 256, 0, st>>>(lv, var, n);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}

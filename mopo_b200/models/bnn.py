@@ -1,0 +1,309 @@
+"""BNN: the probabilistic ensemble behind construct_model (reference mopo/models/bnn.py).
+
+Host-side mirror of the reference class for the hot path: layer stack (add/finalize), scaler,
+max/min-logvar, elite state (_model_inds / random_inds, bnn.py:337-344), predict (bnn.py:508-546)
+and the .mat weight I/O (bnn.py:276-281, 559-592).  All arithmetic is the CUDA library's
+(mopo_ens_predict / mopo_env_step / mopo_rollout); there is no TF session and no CPU path.
+`train` (bnn.py:369-503) is a "next" row and raises NotImplementedError.
+"""
+import ctypes as C
+import os
+import numpy as np
+import torch
+
+from .. import _lib
+from .fc import FC
+
+
+class TensorStandardScaler:
+    """mopo/models/utils.py:45-128 (mu=0, sigma=1 until fit; sigma < 1e-12 -> 1)."""
+
+    def __init__(self, x_dim):
+        self.fitted = False
+        self.mu = np.zeros((1, x_dim), np.float32)
+        self.sigma = np.ones((1, x_dim), np.float32)
+        self.cached_mu, self.cached_sigma = np.zeros([0, x_dim]), np.ones([1, x_dim])
+        self._on_change = None
+
+    def fit(self, data):
+        data = data.detach().cpu().numpy() if torch.is_tensor(data) else np.asarray(data)
+        mu = np.mean(data, axis=0, keepdims=True)
+        sigma = np.std(data, axis=0, keepdims=True)
+        sigma[sigma < 1e-12] = 1.0
+        self.load(mu, sigma)
+        self.fitted = True
+
+    def load(self, mu, sigma):
+        self.mu = np.asarray(mu, np.float32).reshape(1, -1)
+        self.sigma = np.asarray(sigma, np.float32).reshape(1, -1)
+        self.cache()
+        if self._on_change:
+            self._on_change()
+
+    def transform(self, data):
+        return (data - self.mu) / self.sigma
+
+    def inverse_transform(self, data):
+        return self.sigma * data + self.mu
+
+    def get_vars(self):
+        return [self.mu, self.sigma]
+
+    def cache(self):
+        self.cached_mu, self.cached_sigma = self.mu.copy(), self.sigma.copy()
+
+    def load_cache(self):
+        self.load(self.cached_mu, self.cached_sigma)
+
+
+class BNN:
+    def __init__(self, params):
+        self.name = params.get('name', 'model')                        # bnn.py:42
+        self.model_dir = params.get('model_dir', None)
+        self.layers, self.var_layers = [], []
+        self.finalized = False
+        self.scaler = None
+        self.max_logvar = self.min_logvar = None
+        self.num_nets = params.get('num_networks', 1)
+        self.num_elites = params['num_elites']
+        self.separate_mean_var = params.get('separate_mean_var', False)
+        self.deterministic = params.get('deterministic', False)
+        self.model_loaded = False
+        self.device = torch.device('cuda', params.get('device', torch.cuda.current_device() if torch.cuda.is_available() else 0))
+        self.precision = params.get('precision', _lib.PREC_FP32)
+        self.seed = int(params.get('seed', 0))
+        self._handle = None
+        self._rng_calls = 0
+        if self.num_nets == 1:
+            print("Created a neural network with variance predictions.")
+        else:
+            print("Created an ensemble of {} neural networks with variance predictions | Elites: {}".format(
+                self.num_nets, self.num_elites))
+
+    # ---- structure (bnn.py:100-165) ------------------------------------------------------
+    @property
+    def is_probabilistic(self): return True
+
+    @property
+    def is_tf_model(self): return False
+
+    def add(self, layer, var_layer=False):
+        if self.finalized:
+            raise RuntimeError("Cannot modify network structure after finalizing.")
+        tgt = self.var_layers if var_layer else self.layers
+        if len(tgt) == 0 and layer.get_input_dim() is None:
+            raise ValueError("Must set input dimension for the first layer.")
+        layer = layer.copy()
+        layer.set_ensemble_size(self.num_nets)
+        if len(tgt) > 0 and not var_layer:
+            layer.set_input_dim(tgt[-1].get_output_dim())
+        tgt.append(layer)
+
+    def pop(self):
+        if len(self.layers) == 0:
+            raise RuntimeError("Network is empty.")
+        if self.finalized:
+            raise RuntimeError("Cannot modify network structure after finalizing.")
+        self.layers.pop()
+
+    def __repr__(self):
+        return 'BNN(name=%r, nets=%d, layers=%r, var_layers=%r)' % (self.name, self.num_nets, self.layers, self.var_layers)
+
+    def finalize(self, optimizer=None, optimizer_args=None, *args, **kwargs):
+        """bnn.py:166-274 minus the TF training graph: fix the head, construct variables with the
+        reference init law, create the device ensemble, load `{model_dir}/{name}.mat` if requested."""
+        if len(self.layers) == 0 or (self.separate_mean_var and len(self.var_layers) == 0):
+            raise RuntimeError("Cannot finalize an empty network.")
+        if self.finalized:
+            raise RuntimeError("Can only finalize a network once.")
+        hidden = self.layers[:-1]
+        if not hidden or any(l.activation != 'swish' for l in hidden) or len({l.output_dim for l in hidden}) != 1:
+            raise NotImplementedError("mopo_b200 builds the construct_model 'mlp' architecture only "
+                                      "(equal-width swish hidden layers + linear head)")
+        if not self.separate_mean_var:                                  # bnn.py:183-189
+            self.layers[-1].set_output_dim(2 * self.layers[-1].get_output_dim())
+            self.end_act_name = self.layers[-1].get_activation(as_func=False)
+            self.layers[-1].unset_activation()
+            d1 = self.layers[-1].get_output_dim() // 2
+        else:
+            d1 = self.var_layers[-1].get_output_dim()
+            if len(self.var_layers) != 1 or self.var_layers[0].get_input_dim() != hidden[-1].output_dim:
+                raise NotImplementedError("separate_mean_var expects one linear var head on the last hidden activation")
+        self.in_dim = self.layers[0].get_input_dim()
+        self.out_dim = d1
+        self.hidden_dim = hidden[0].output_dim
+        rng = np.random.RandomState(self.seed)
+        self.scaler = TensorStandardScaler(self.in_dim)
+        self.max_logvar = np.ones([1, d1], np.float32) / 2.                # bnn.py:196-199
+        self.min_logvar = -np.ones([1, d1], np.float32) * 10.
+        for layer in self.layers + self.var_layers:
+            layer.construct_vars(rng)
+        self._obs_dim = kwargs.get('obs_dim')          # set by construct_model; needed to split in_dim
+        self.finalized = True
+        if self.model_loaded:
+            self.load_params()
+        else:
+            self._sync_device()
+        self.scaler._on_change = self._sync_device
+
+    # ---- device handle --------------------------------------------------------------------
+    def _ensure_handle(self):
+        if self._handle is not None:
+            return
+        lib = _lib.load()
+        obs_dim = self._obs_dim if self._obs_dim is not None else self.out_dim - 1
+        cfg = _lib.EnsCfg(obs_dim=obs_dim, act_dim=self.in_dim - obs_dim, rew_dim=self.out_dim - obs_dim,
+                          hidden_dim=self.hidden_dim, n_hidden=len(self.layers) - 1, num_networks=self.num_nets,
+                          num_elites=self.num_elites, separate_mean_var=int(self.separate_mean_var),
+                          device=self.device.index or 0)
+        h = C.c_void_p()
+        _lib.check(lib.mopo_ens_create(C.byref(cfg), C.byref(h)))
+        self._handle = h
+
+    def _sync_device(self):
+        """Push host parameters (reference layout) to the device images."""
+        if not self.finalized:
+            return
+        self._ensure_handle()
+        lib = _lib.load()
+        keep = []
+
+        def arr(a):
+            a = np.ascontiguousarray(a, np.float32); keep.append(a); return a.ctypes.data
+
+        n = len(self.layers)
+        W = (C.c_void_p * n)(*[arr(l.weights) for l in self.layers])
+        b = (C.c_void_p * n)(*[arr(l.biases) for l in self.layers])
+        vw = arr(self.var_layers[0].weights) if self.separate_mean_var else None
+        vb = arr(self.var_layers[0].biases) if self.separate_mean_var else None
+        _lib.check(lib.mopo_ens_set_params(self._handle, W, b, vw, vb, arr(self.scaler.mu), arr(self.scaler.sigma),
+                                           arr(self.max_logvar), arr(self.min_logvar), 0, _lib.stream_ptr(self.device)))
+        if getattr(self, '_model_inds', None) is not None:
+            self._push_elites()
+
+    def _push_elites(self):
+        inds = np.ascontiguousarray(self._model_inds_list, np.int32)
+        _lib.check(_lib.load().mopo_ens_set_elites(self._handle, inds.ctypes.data_as(C.POINTER(C.c_int32)), len(inds)))
+
+    def set_params(self, weights, biases, var_weights=None, var_biases=None, mu=None, sigma=None,
+                   max_logvar=None, min_logvar=None):
+        """Install parameters in the reference layout (what TF `var.load` does at bnn.py:276-281)."""
+        for l, w, b in zip(self.layers, weights, biases):
+            assert w.shape == (self.num_nets, l.input_dim, l.output_dim), (w.shape, l)
+            l.weights = np.array(w, np.float32); l.biases = np.array(b, np.float32).reshape(self.num_nets, 1, -1)
+        if self.separate_mean_var:
+            self.var_layers[0].weights = np.array(var_weights, np.float32)
+            self.var_layers[0].biases = np.array(var_biases, np.float32).reshape(self.num_nets, 1, -1)
+        if max_logvar is not None: self.max_logvar = np.array(max_logvar, np.float32).reshape(1, -1)
+        if min_logvar is not None: self.min_logvar = np.array(min_logvar, np.float32).reshape(1, -1)
+        if mu is not None:
+            self.scaler._on_change = None
+            self.scaler.load(mu, sigma)
+            self.scaler._on_change = self._sync_device
+        self._sync_device()
+
+    # ---- elites (bnn.py:337-344) ----------------------------------------------------------
+    @property
+    def _model_inds(self):
+        if not hasattr(self, '_model_inds_list'):
+            raise AttributeError("'BNN' object has no attribute '_model_inds' (set by _end_train, bnn.py:337-340)")
+        return self._model_inds_list
+
+    @_model_inds.setter
+    def _model_inds(self, inds):
+        self._model_inds_list = [int(i) for i in inds]
+        if self._handle is not None:
+            self._push_elites()
+
+    def _end_train(self, holdout_losses):
+        sorted_inds = np.argsort(holdout_losses)
+        self._model_inds = sorted_inds[:self.num_elites].tolist()
+        print('Using {} / {} models: {}'.format(self.num_elites, self.num_nets, self._model_inds))
+
+    def random_inds(self, batch_size):
+        inds = np.random.choice(self._model_inds, size=batch_size)
+        return inds
+
+    def reset(self):
+        rng = np.random.RandomState(self.seed + 1 + self._rng_calls); self._rng_calls += 1
+        for layer in self.layers + self.var_layers:
+            layer.construct_vars(rng)
+        self._sync_device()
+
+    # ---- predict (bnn.py:508-546) -----------------------------------------------------------
+    def predict(self, inputs, factored=False, *args, **kwargs):
+        is_np = not torch.is_tensor(inputs)
+        x = torch.as_tensor(inputs)
+        if x.dim() != 2:
+            raise NotImplementedError("3-D (per-net) inputs are the training path (bnn.py:541-545); not on the rollout hot path")
+        if x.shape[1] != self.in_dim:
+            raise ValueError("Invalid input dimension.")                   # fc.py:103
+        x = x.to(device=self.device, dtype=torch.float32).contiguous()
+        B = x.shape[0]
+        mean = torch.empty((self.num_nets, B, self.out_dim), dtype=torch.float32, device=self.device)
+        var = torch.empty_like(mean)
+        self._ensure_handle()
+        _lib.check(_lib.load().mopo_ens_predict(self._handle, x.data_ptr(), B, mean.data_ptr(), var.data_ptr(),
+                                               kwargs.get('precision', self.precision), _lib.stream_ptr(self.device)))
+        if not factored:                                                   # bnn.py:261-263
+            m = mean.mean(0)
+            mean, var = m, var.mean(0) + (mean - m).square().mean(0)
+        if is_np:
+            return mean.cpu().numpy(), var.cpu().numpy()
+        return mean, var
+
+    def train(self, *args, **kwargs):
+        raise NotImplementedError("BNN.train (bnn.py:369-503) is outside the rollout hot path (SURVEY.md 8(f) f3); "
+                                  "load reference-trained weights with load_dir / set_params and set _model_inds")
+
+    # ---- .mat weight I/O (bnn.py:276-281, 559-592) --------------------------------------------
+    def _all_vars(self):
+        """nonoptvars + optvars order (bnn.py:224-225): [mu, sigma] + per layer [W, b] (+ var layers) + [max_lv, min_lv]."""
+        v = [self.scaler.mu, self.scaler.sigma]
+        for l in self.layers + self.var_layers:
+            v += [l.weights, l.biases]
+        return v + [self.max_logvar, self.min_logvar]
+
+    def save(self, savedir, timestep):
+        from scipy.io import savemat
+        if not self.finalized:
+            raise RuntimeError()
+        model_dir = self.model_dir if savedir is None else savedir
+        if not self.separate_mean_var:
+            with open(os.path.join(model_dir, '{}_{}.nns'.format(self.name, timestep)), "w+") as f:
+                for layer in self.layers[:-1]:
+                    f.write("%s\n" % repr(layer))
+                last = self.layers[-1].copy()
+                last.set_activation(self.end_act_name)
+                last.set_output_dim(last.get_output_dim() // 2)
+                f.write("%s\n" % repr(last))
+        else:
+            with open(os.path.join(model_dir, '{}_{}.nns'.format(self.name, timestep)), "w+") as f:
+                for layer in self.layers:
+                    f.write("%s\n" % repr(layer))
+            with open(os.path.join(model_dir, '{}_{}_var.nns'.format(self.name, timestep)), "w+") as f:
+                for layer in self.var_layers:
+                    f.write("%s\n" % repr(layer))
+        savemat(os.path.join(model_dir, '{}_{}.mat'.format(self.name, timestep)),
+                {str(i): v for i, v in enumerate(self._all_vars())})
+
+    def load_params(self, path=None):
+        from scipy.io import loadmat
+        d = loadmat(path or os.path.join(self.model_dir, "%s.mat" % self.name))
+        n_l = len(self.layers)
+        vals = [np.asarray(d[str(i)], np.float32) for i in range(2 + 2 * (n_l + len(self.var_layers)) + 2)]
+        mu, sigma = vals[0], vals[1]
+        Ws = vals[2:2 + 2 * n_l:2]; bs = vals[3:3 + 2 * n_l:2]
+        k = 2 + 2 * n_l
+        vw = vb = None
+        if self.separate_mean_var:
+            vw, vb = vals[k], vals[k + 1]; k += 2
+        self.set_params(Ws, bs, vw, vb, mu, sigma, vals[k], vals[k + 1])
+
+    def __del__(self):
+        try:
+            if self._handle is not None:
+                _lib.load().mopo_ens_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass
