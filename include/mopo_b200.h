@@ -70,6 +70,8 @@ typedef struct {
 
 const char* mopo_last_error(void);
 int mopo_version(void);
+/* number of kernels this library has launched in this process (bench.py reports the delta) */
+int64_t mopo_launch_count(void);
 
 /* ---- ensemble (construct_model / BNN) ------------------------------------------------ */
 int mopo_ens_create(const mopo_ens_cfg* cfg, mopo_ens** out);
@@ -91,6 +93,12 @@ int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n);
 
 /* BNN.predict(x, factored=True): x [B,in] device fp32 -> mean [E,B,D1], var [E,B,D1] device fp32. */
 int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var,
+                     int precision, void* stream);
+
+/* The contraction alone (BNN._compile_outputs(ret_log_var=True), bnn.py:631-673) on ALREADY SCALED inputs
+ * xn = (x - mu) / sigma [B,in]: -> mean [E,B,D1], clamped logvar [E,B,D1].  This is the kernel the roofline
+ * is quoted on (bench.py times it alone). */
+int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar,
                      int precision, void* stream);
 
 /* ---- FakeEnv.step --------------------------------------------------------------------- */

@@ -49,12 +49,14 @@ class RolloutArgs(C.Structure):
 SYMBOLS = {
     'mopo_last_error': (C.c_char_p, []),
     'mopo_version': (C.c_int, []),
+    'mopo_launch_count': (C.c_int64, []),
     'mopo_ens_create': (C.c_int, [C.POINTER(EnsCfg), C.POINTER(C.c_void_p)]),
     'mopo_ens_destroy': (C.c_int, [C.c_void_p]),
     'mopo_ens_set_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_set_elites': (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32]),
     'mopo_ens_predict': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_ens_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_env_step': (C.c_int, [C.c_void_p, C.POINTER(StepArgs), C.c_void_p]),
     'mopo_termination_fn': (C.c_int, [C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     'mopo_pool_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),

@@ -16,6 +16,11 @@ void mopo_set_error(const char* fmt, ...) {
 
 #define MOPO_API extern "C" __attribute__((visibility("default")))
 
+#include <atomic>
+static std::atomic<long long> g_launches{0};
+void mopo_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+MOPO_API int64_t mopo_launch_count(void) { return g_launches.load(); }
+
 MOPO_API const char* mopo_last_error(void) { return g_err; }
 MOPO_API int mopo_version(void) { return 100; }
 
@@ -117,8 +122,8 @@ MOPO_API int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const
     for (int s = 0; s < 2; ++s) {
       TRY(upload(tw, srcw[s], (size_t)E * H * D1, on_device, st));
       TRY(upload(tb, srcb[s], (size_t)E * D1, on_device, st));
-      place_cols_kernel<<<256, 256, 0, st>>>(tw, h->W[h->L], E * H, D1, h->HO, s * D1);
-      place_cols_kernel<<<8, 256, 0, st>>>(tb, h->b[h->L], E, D1, h->HO, s * D1);
+      MOPO_COUNT_LAUNCH, place_cols_kernel<<<256, 256, 0, st>>>(tw, h->W[h->L], E * H, D1, h->HO, s * D1);
+      MOPO_COUNT_LAUNCH, place_cols_kernel<<<8, 256, 0, st>>>(tb, h->b[h->L], E, D1, h->HO, s * D1);
       CUDA_TRY(cudaGetLastError());
       if (!on_device) CUDA_TRY(cudaStreamSynchronize(st));   // host staging may be reused by the caller
     }
@@ -153,6 +158,15 @@ static int forward(mopo_ens* h, int precision, const float* xn, int64_t n_max, c
   }
   mopo_set_error("unknown precision %d", precision);
   return MOPO_EINVAL;
+}
+
+MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar, int precision, void* stream) {
+  REQUIRE(h && (B == 0 || (xn && mean && logvar)), MOPO_EINVAL, "mopo_ens_forward: null argument");
+  REQUIRE(B >= 0 && B < (1ll << 31), MOPO_EINVAL, "mopo_ens_forward: B=%lld", (long long)B);
+  REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_forward: parameters not set");
+  if (B == 0) return MOPO_OK;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  return forward(h, precision, xn, B, nullptr, mean, logvar, B, (cudaStream_t)stream);
 }
 
 MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, int precision, void* stream) {
@@ -299,11 +313,11 @@ MOPO_API int mopo_pool_add(mopo_pool* p, const float* obs, const float* act, con
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaSetDevice(p->device));
   const int64_t skip = n > p->max_size ? n - p->max_size : 0;   // duplicates: the last write wins
-  ring_scatter_kernel<<<grid_for((n - skip) * p->act_dim), 256, 0, st>>>(act, p->actions, n, skip, p->act_dim, p->pointer, p->max_size);
-  ring_scatter_kernel<<<grid_for(n - skip), 256, 0, st>>>(rew, p->rewards, n, skip, 1, p->pointer, p->max_size);
-  ring_scatter_kernel<<<grid_for(n - skip), 256, 0, st>>>(term, p->terminals, n, skip, 1, p->pointer, p->max_size);
-  ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(obs, p->obs, n, skip, p->obs_dim, p->pointer, p->max_size);
-  ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(next_obs, p->next_obs, n, skip, p->obs_dim, p->pointer, p->max_size);
+  MOPO_COUNT_LAUNCH, ring_scatter_kernel<<<grid_for((n - skip) * p->act_dim), 256, 0, st>>>(act, p->actions, n, skip, p->act_dim, p->pointer, p->max_size);
+  MOPO_COUNT_LAUNCH, ring_scatter_kernel<<<grid_for(n - skip), 256, 0, st>>>(rew, p->rewards, n, skip, 1, p->pointer, p->max_size);
+  MOPO_COUNT_LAUNCH, ring_scatter_kernel<<<grid_for(n - skip), 256, 0, st>>>(term, p->terminals, n, skip, 1, p->pointer, p->max_size);
+  MOPO_COUNT_LAUNCH, ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(obs, p->obs, n, skip, p->obs_dim, p->pointer, p->max_size);
+  MOPO_COUNT_LAUNCH, ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(next_obs, p->next_obs, n, skip, p->obs_dim, p->pointer, p->max_size);
   CUDA_TRY(cudaGetLastError());
   p->pointer = (p->pointer + n) % p->max_size;                 // flexible_replay_pool.py:45-48
   p->size = p->size + n < p->max_size ? p->size + n : p->max_size;
@@ -312,11 +326,11 @@ MOPO_API int mopo_pool_add(mopo_pool* p, const float* obs, const float* act, con
 
 static int pool_gather_impl(const mopo_pool* p, const int64_t* idx, int64_t n, float* obs, float* act, float* next_obs,
                             float* rew, uint8_t* term, cudaStream_t st) {
-  if (act) gather_rows_kernel<<<grid_for(n * p->act_dim), 256, 0, st>>>(p->actions, idx, act, n, p->act_dim);
-  if (rew) gather_rows_kernel<<<grid_for(n), 256, 0, st>>>(p->rewards, idx, rew, n, 1);
-  if (term) gather_rows_kernel<<<grid_for(n), 256, 0, st>>>(p->terminals, idx, term, n, 1);
-  if (obs) gather_rows_kernel<<<grid_for(n * p->obs_dim), 256, 0, st>>>(p->obs, idx, obs, n, p->obs_dim);
-  if (next_obs) gather_rows_kernel<<<grid_for(n * p->obs_dim), 256, 0, st>>>(p->next_obs, idx, next_obs, n, p->obs_dim);
+  if (act) MOPO_COUNT_LAUNCH, gather_rows_kernel<<<grid_for(n * p->act_dim), 256, 0, st>>>(p->actions, idx, act, n, p->act_dim);
+  if (rew) MOPO_COUNT_LAUNCH, gather_rows_kernel<<<grid_for(n), 256, 0, st>>>(p->rewards, idx, rew, n, 1);
+  if (term) MOPO_COUNT_LAUNCH, gather_rows_kernel<<<grid_for(n), 256, 0, st>>>(p->terminals, idx, term, n, 1);
+  if (obs) MOPO_COUNT_LAUNCH, gather_rows_kernel<<<grid_for(n * p->obs_dim), 256, 0, st>>>(p->obs, idx, obs, n, p->obs_dim);
+  if (next_obs) MOPO_COUNT_LAUNCH, gather_rows_kernel<<<grid_for(n * p->obs_dim), 256, 0, st>>>(p->next_obs, idx, next_obs, n, p->obs_dim);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -336,7 +350,7 @@ MOPO_API int mopo_pool_sample(const mopo_pool* p, int64_t n, uint64_t seed, uint
   if (n == 0) return MOPO_OK;
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaSetDevice(p->device));
-  philox_index_kernel<<<grid_for(n), 256, 0, st>>>(idx_out, n, seed, offset, p->size);
+  MOPO_COUNT_LAUNCH, philox_index_kernel<<<grid_for(n), 256, 0, st>>>(idx_out, n, seed, offset, p->size);
   CUDA_TRY(cudaGetLastError());
   return pool_gather_impl(p, idx_out, n, obs, act, next_obs, rew, term, st);
 }
@@ -376,7 +390,7 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   int* d_counts = reinterpret_cast<int*>(d_pool_off + 2);
   float* nobs_dense = h->misc.as<float>();
   uint8_t* term_dense = reinterpret_cast<uint8_t*>(nobs_dense + B * od);
-  rollout_init_kernel<<<1, 32, 0, st>>>(d_counts, d_pool_off, (int)B, H);
+  MOPO_COUNT_LAUNCH, rollout_init_kernel<<<1, 32, 0, st>>>(d_counts, d_pool_off, (int)B, H);
   const float* obs_cur = a->start_obs;
   const int32_t* origin_cur = nullptr;
   for (int i = 0; i < H; ++i) {

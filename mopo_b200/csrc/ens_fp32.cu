@@ -108,12 +108,12 @@ int fp32_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, fl
   for (int l = 0; l < h->L; ++l) {
     dim3 grid((H + BN - 1) / BN, (unsigned)((n_max + BM - 1) / BM), E);
     float* out = bufs[l & 1];
-    ens_layer_fp32<0><<<grid, blk, 0, st>>>(A, strideA, lda, h->W[l], h->b[l], out, strideAct, nullptr, nullptr, 0,
+    MOPO_COUNT_LAUNCH, ens_layer_fp32<0><<<grid, blk, 0, st>>>(A, strideA, lda, h->W[l], h->b[l], out, strideAct, nullptr, nullptr, 0,
                                             nullptr, nullptr, (int)n_max, d_n, H, K, 0);
     A = out; strideA = strideAct; lda = H; K = H;
   }
   dim3 grid((h->HO + BN - 1) / BN, (unsigned)((n_max + BM - 1) / BM), E);
-  ens_layer_fp32<1><<<grid, blk, 0, st>>>(A, strideA, lda, h->W[h->L], h->b[h->L], nullptr, 0, mean, lv, ldb,
+  MOPO_COUNT_LAUNCH, ens_layer_fp32<1><<<grid, blk, 0, st>>>(A, strideA, lda, h->W[h->L], h->b[h->L], nullptr, 0, mean, lv, ldb,
                                           h->max_lv, h->min_lv, (int)n_max, d_n, h->HO, K, h->D1);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;

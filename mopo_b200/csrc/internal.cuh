@@ -12,6 +12,8 @@
 #define MOPO_MAX_E 16
 
 void mopo_set_error(const char* fmt, ...);
+void mopo_count_launch();
+#define MOPO_COUNT_LAUNCH mopo_count_launch()
 
 #define CUDA_TRY(expr)                                                                  \
   do {                                                                                  \

@@ -228,7 +228,7 @@ int launch_prep(const float* obs, const float* act, const float* mu, const float
   if (n_max == 0) return MOPO_OK;
   int64_t tot = n_max * (obs_dim + act_dim);
   int64_t g64 = (tot + 255) / 256; int grid = (int)(g64 > 148 * 16 ? 148 * 16 : g64);
-  prep_kernel<<<grid, 256, 0, st>>>(obs, act, mu, sigma, xn, n_max, d_n, obs_dim, act_dim);
+  MOPO_COUNT_LAUNCH, prep_kernel<<<grid, 256, 0, st>>>(obs, act, mu, sigma, xn, n_max, d_n, obs_dim, act_dim);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -236,7 +236,7 @@ int launch_prep(const float* obs, const float* act, const float* mu, const float
 int launch_tail(const TailArgs& a, cudaStream_t st) {
   if (a.n_max == 0) return MOPO_OK;
   int grid = (int)((a.n_max + TAIL_ROWS - 1) / TAIL_ROWS);
-  step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
+  MOPO_COUNT_LAUNCH, step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -246,7 +246,7 @@ int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* or
                    float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, cudaStream_t st) {
   if (n_max == 0) return MOPO_OK;
   int grid = (int)((n_max + TAIL_ROWS - 1) / TAIL_ROWS);
-  compact_kernel<<<grid, TAIL_ROWS, 0, st>>>(next_obs, term, origin_in, origin_base, n_max, d_n, blk_counts, obs_dim,
+  MOPO_COUNT_LAUNCH, compact_kernel<<<grid, TAIL_ROWS, 0, st>>>(next_obs, term, origin_in, origin_base, n_max, d_n, blk_counts, obs_dim,
                                              obs_out, origin_out, d_n_next, d_pool_off);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
@@ -255,7 +255,7 @@ int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* or
 int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, uint8_t* out, cudaStream_t st) {
   if (n == 0) return MOPO_OK;
   int64_t g64 = (n + 255) / 256; int grid = (int)(g64 > 148 * 16 ? 148 * 16 : g64);
-  term_only_kernel<<<grid, 256, 0, st>>>(kind, next_obs, n, obs_dim, out);
+  MOPO_COUNT_LAUNCH, term_only_kernel<<<grid, 256, 0, st>>>(kind, next_obs, n, obs_dim, out);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -263,7 +263,7 @@ int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, ui
 int launch_exp(const float* lv, float* var, int64_t n, cudaStream_t st) {
   if (n == 0) return MOPO_OK;
   int64_t g64 = (n + 255) / 256; int grid = (int)(g64 > 148 * 16 ? 148 * 16 : g64);
-  exp_kernel<<<grid, 256, 0, st>>>(lv, var, n);
+  MOPO_COUNT_LAUNCH, exp_kernel<<<grid, 256, 0, st>>>(lv, var, n);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }

@@ -88,7 +88,7 @@ def forward(params, inputs, dtype=np.float32, ret_log_var=False):
     hidden_last = None
     for l in range(n_layers):
         if cur.ndim == 2:
-            raw = np.einsum('ij,ajk->aik', cur, c(W[l])) + c(b[l])   # fc.py:99
+            raw = np.matmul(cur[None], c(W[l])) + c(b[l])              # fc.py:99 einsum('ij,ajk->aik') == broadcast matmul (BLAS)
         else:
             raw = np.matmul(cur, c(W[l])) + c(b[l])                  # fc.py:101
         if l < n_layers - 1:
