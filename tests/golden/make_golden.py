@@ -90,7 +90,9 @@ def termination_case(static, domain, obs_dim, seed):
     if domain in ('ant', 'antangle'):
         nobs[-32:, 0] = 0.6
     obs = np.zeros_like(nobs); act = np.zeros((B, 1), np.float32)
-    term = static[domain].termination_fn(obs, act, nobs)
+    # In the reference pipeline next_obs is float64 (samples = f32 mean + f64 noise * f32 std, fake_env.py:72), so the
+    # thresholds are compared in double: feed the f32-representable values as float64.
+    term = static[domain].termination_fn(obs, act, nobs.astype(np.float64))
     return dict(domain=domain, next_obs=nobs, term=np.asarray(term))
 
 

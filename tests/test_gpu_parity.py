@@ -100,7 +100,7 @@ def test_step_matches_reference_golden(path):
     np.testing.assert_allclose(info['log_prob'][fin], g['info_log_prob'][fin], rtol=5e-3, atol=5e-3)
     # termination: bit-exact on identical next_obs ...
     t_same = static[domain].termination_fn(obs, act, g['next_obs'].astype(np.float32))
-    t_ref32 = OracleStatic(domain).termination_fn(obs, act, g['next_obs'].astype(np.float32))
+    t_ref32 = OracleStatic(domain).termination_fn(obs, act, g['next_obs'].astype(np.float32).astype(np.float64))
     assert np.array_equal(t_same, t_ref32)
     # ... and end to end (fixtures have no row within rounding distance of a threshold)
     assert np.array_equal(term, g['term'])

@@ -36,7 +36,7 @@ def test_step_matches_reference(path):
 @pytest.mark.parametrize('path', golden_files('term_'))
 def test_termination_matches_reference(path):
     g = np.load(path)
-    nobs = g['next_obs']
+    nobs = g['next_obs'].astype(np.float64)      # the pipeline dtype (see make_golden.termination_case)
     fns = StaticFns(str(g['domain']))
     term = fns.termination_fn(np.zeros_like(nobs), np.zeros((len(nobs), 1), np.float32), nobs)
     assert term.dtype == bool and term.shape == (len(nobs), 1)
