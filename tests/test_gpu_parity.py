@@ -150,8 +150,11 @@ def test_pool_matches_reference_golden():
     idx = np.array([0, 5, 36, 5])
     b = pool.batch_by_indices(idx)
     assert np.array_equal(b['rewards'], g['final_rewards'][idx])
-    with pytest.raises(ValueError):
-        pool.batch_by_indices(np.array([10 ** 6 * 37 + 38]))
+    part = SimpleReplayPool(int(g['obs_dim']), int(g['act_dim']), 37)
+    part.add_samples({k: g['chunk0_%s' % k] for k in part.fields})          # 10 rows of 37
+    with pytest.raises(ValueError):                                        # flexible_replay_pool.py:122-125
+        part.batch_by_indices(np.array([3, 37 + 12]))
+    assert part.batch_by_indices(np.array([37 + 2]))['rewards'].shape == (1, 1)
     d = pool.random_batch_device(1000, seed=3)
     ii = d['indices'].cpu().numpy()
     assert ii.min() >= 0 and ii.max() < pool.size and len(np.unique(ii)) > 20
@@ -194,6 +197,10 @@ def test_rollout_matches_oracle(domain, B, h, max_size):
         p['max_logvar'][:] = -9.0
         p['weights'][-1] = p['weights'][-1] * 0.02
         p['biases'][-1] = p['biases'][-1] * 0.0
+        # spread heights / angles across the termination thresholds so a fraction dies at every step
+        r0 = np.random.RandomState(77)
+        obs[:, 0] = r0.uniform(0.6, 1.5, B).astype(np.float32)
+        obs[:, 1] = r0.uniform(-0.25, 0.25, B).astype(np.float32)
     od, ad = SHAPES[domain]
     rng = np.random.RandomState(5)
     acts = [np.tanh(rng.standard_normal((B, ad))).astype(np.float32) for _ in range(h)]
