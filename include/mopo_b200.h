@@ -177,6 +177,12 @@ typedef struct {
  * rows to the pool in the reference's order, then synchronises once to read the counts back. */
 int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream);
 
+/* ---- debug ---------------------------------------------------------------------------------- */
+/* tcgen05 known-answer probe: D[M,N] = A[M,K] * B[N,K]^T (bf16 bit patterns in, fp32 out; device pointers),
+ * cta_group 1|2, A operand from shared memory (0) or tensor memory (1).  Used by tests/test_gpu_umma.py. */
+int mopo_debug_umma_probe(int cta_group, int a_in_tmem, const uint16_t* A, const uint16_t* B, float* D,
+                          int M, int N, int K, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
