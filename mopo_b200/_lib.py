@@ -70,6 +70,9 @@ SYMBOLS = {
     'mopo_pool_sample': (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mopo_debug_umma_probe': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    'mopo_debug_tc_trace': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'mopo_debug_pipe_bench': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_debug_mma_rate': (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
 }
 

@@ -169,6 +169,16 @@ MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* me
   return forward(h, precision, xn, B, nullptr, mean, logvar, B, (cudaStream_t)stream);
 }
 
+MOPO_API int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar,
+                                 unsigned long long* trace, void* stream) {
+  REQUIRE(h && xn && mean && logvar && trace && B > 0, MOPO_EINVAL, "mopo_debug_tc_trace: bad argument");
+  CUDA_TRY(cudaMemsetAsync(trace, 0, sizeof(unsigned long long) * 4 * 2048, (cudaStream_t)stream));
+  h->tc_trace = trace;
+  int rc = mopo_ens_forward(h, xn, B, mean, logvar, MOPO_PREC_BF16, stream);
+  h->tc_trace = nullptr;
+  return rc;
+}
+
 MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, int precision, void* stream) {
   REQUIRE(h && (B == 0 || (x && mean && var)), MOPO_EINVAL, "mopo_ens_predict: null argument");
   REQUIRE(B >= 0 && B < (1ll << 31), MOPO_EINVAL, "mopo_ens_predict: B=%lld", (long long)B);

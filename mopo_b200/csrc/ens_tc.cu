@@ -113,6 +113,7 @@ struct TcArgs {
   const int* d_n;
   int E;
   TcShape s;
+  unsigned long long* trace;   // debug timeline (mopo_debug_tc_trace) or nullptr
 };
 
 struct Bars {
@@ -145,7 +146,18 @@ __device__ __forceinline__ void swish_pack16(const uint32_t (&v)[16], uint32_t (
 // TMEM column (inside a region) of K-chunk c of the in-place A operand
 __device__ __forceinline__ int a_col(int c) { return c < 7 ? 8 * c : NH1 + 8 * (c - 7); }
 
+constexpr int TRACE_CAP = 2048;   // events per role
+// timeline probe: role r (0 issuer, 1 epilogue WG0, 2 epilogue WG1, 3 loader) of pair 0 / leader CTA appends (tag, clock)
+#define TR(role, tag)                                                                                   \
+  do {                                                                                                  \
+    if (TRACE && a.trace && pair == 0 && rank == 0 && lane == 0 && tr_n < TRACE_CAP)                    \
+      a.trace[(role) * TRACE_CAP + tr_n++] = ((unsigned long long)(tag) << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull); \
+  } while (0)
+
+template <bool TRACE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_kernel(TcArgs a) {
+  int tr_n = 0;
+  (void)tr_n;
   extern __shared__ __align__(128) uint8_t smem[];
   const TcShape s = a.s;
   uint8_t* sW0 = smem;
@@ -155,10 +167,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   float* sLv = reinterpret_cast<float*>(sX + 2 * s.x_bytes());     // max_lv[D1], min_lv[D1]
   Bars* bars = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(sLv) + 2 * MOPO_MAX_D1 * sizeof(float));
 
-  const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
+  const int tid = threadIdx.x, lane = tid % 32;
+  const int warp = __shfl_sync(0xffffffffu, tid / 32, 0);    // warp-uniform for the compiler (uniform registers)
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x / 2, n_pairs = gridDim.x / 2;
-  const int n = a.d_n ? min(*a.d_n, a.n_max) : a.n_max;
+  const int n = __shfl_sync(0xffffffffu, a.d_n ? min(*a.d_n, a.n_max) : a.n_max, 0);
   const int n_tiles = (n + 255) / 256;
 
   // pair -> (net, slot among the pairs of that net)
@@ -190,7 +203,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   if (tid == 0) mbar_wait(&bars->w_full, 0);
   __syncthreads();
   cluster_sync_all();                                // both CTAs' weights and barriers are ready
-  const uint32_t tbase = bars->tmem_base;
+  const uint32_t tbase = __shfl_sync(0xffffffffu, bars->tmem_base, 0);
 
   if (warp == 9) {
     // ===== input loader: fp32 [rows, in] -> bf16 K-panels, + two constant-1 columns for the bias rows =====
@@ -198,6 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       const int sbuf = it & 1;
       if (it >= 2) mbar_wait(&bars->x_free[sbuf], ((it >> 1) - 1) & 1);
       const int tile = slot + it * cnt;
+      TR(3, 70);
       uint8_t* dst = sX + sbuf * s.x_bytes();
       for (int rr = lane; rr < 128; rr += 32) {
         const int row = tile * 256 + (int)rank * 128 + rr;
@@ -218,17 +232,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&bars->x_full[sbuf], 0);
+      TR(3, 71);
     }
   } else if (warp == 8) {
     // ===== MMA issuer: one thread of the leader CTA drives both SMs' tensor cores =====
-    if (rank == 0 && lane == 0) {
+    if (rank == 0) {                                  // all 32 lanes run the loop; elect_one() issues
       const uint32_t id1 = idesc_bf16(256, NH1), id2 = idesc_bf16(256, NH2), idh = idesc_bf16(256, s.NHEAD);
       uint32_t g = 0;                                 // global layer counter -> accumulator region
       uint32_t grp_par = 0;
       for (int it = 0; it < my_tiles; ++it) {
         const int sbuf = it & 1;
+        TR(0, 1);
         mbar_wait_cluster(&bars->x_full[sbuf], (it >> 1) & 1);
         tc_fence_after();
+        TR(0, 2);
         // ---- L0 (SS) ----
         {
           const uint32_t dcol = tbase + (g & 1) * REGION_COLS;
@@ -237,11 +254,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
             for (int ks = 0; ks < s.K0 / 16; ++ks) {
               const uint64_t ad = smem_desc(xa + ks * 2 * X_PANEL, X_PANEL, 128);
               const uint64_t bd = smem_desc(smem_u32(sW0) + ks * 2 * W_PANEL + (half ? ROWS1 * 16 : 0), W_PANEL, 128);
-              mma_ss<2>(dcol + (half ? NH1 : 0), ad, bd, half ? id2 : id1, ks > 0);
+              if (elect_one()) mma_ss<2>(dcol + (half ? NH1 : 0), ad, bd, half ? id2 : id1, ks > 0);
             }
-            mma_commit<2>(&bars->d_full[half]);
+            if (elect_one()) mma_commit<2>(&bars->d_full[half]);
+            TR(0, 30 + half);
           }
-          mma_commit<2>(&bars->x_free[sbuf]);
+          if (elect_one()) mma_commit<2>(&bars->x_free[sbuf]);
           ++g;
         }
         // ---- L1..L3 and head (TS): A = in-place bf16 activations in the previous region ----
@@ -257,11 +275,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
                 const int gi = ks == 0 ? 0 : ks == 4 ? 1 : ks == 7 ? 2 : 3;
                 mbar_wait_cluster(&bars->grp[gi], grp_par);
                 tc_fence_after();
+                TR(0, 100 + l * 10 + gi);
               }
               const uint64_t bd = smem_desc(smem_u32(wl) + ks * 2 * panel + ((!head && half) ? ROWS1 * 16 : 0), panel, 128);
-              mma_ts<2>(dcol + (half ? NH1 : 0), acol + a_col(ks), bd, head ? idh : (half ? id2 : id1), ks > 0);
+              if (elect_one()) mma_ts<2>(dcol + (half ? NH1 : 0), acol + a_col(ks), bd, head ? idh : (half ? id2 : id1), ks > 0);
             }
-            mma_commit<2>(head ? &bars->d_head : &bars->d_full[half]);
+            if (elect_one()) mma_commit<2>(head ? &bars->d_head : &bars->d_full[half]);
+            TR(0, 30 + l * 2 + half);
           }
           grp_par ^= 1;
           ++g;
@@ -279,9 +299,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
     for (int it = 0; it < my_tiles; ++it) {
       const int tile = slot + it * cnt;
       for (int l = 0; l < 4; ++l) {
+        TR(1 + wg, 40 + l);
         mbar_wait(&bars->d_full[wg], dpar);
         dpar ^= 1;
         tc_fence_after();
+        TR(1 + wg, 50 + l);
         const uint32_t reg = tbase + lane_off + (g & 1) * REGION_COLS;
         for (int c = c_lo; c < c_hi; ++c) {
           uint32_t v[16], p[8];
@@ -299,12 +321,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
           }
         }
         ++g;
+        TR(1 + wg, 60 + l);
       }
       if (wg == 0) {
         // ---- head epilogue: mean = cols [0,D1), logvar = clamp(cols [D1,2*D1))  (bnn.py:654-655 / 669-670) ----
+        TR(1, 44);
         mbar_wait(&bars->d_head, hpar);
         hpar ^= 1;
         tc_fence_after();
+        TR(1, 54);
         const uint32_t reg = tbase + lane_off + (g & 1) * REGION_COLS;
         const int row = tile * 256 + (int)rank * 128 + rr;
         float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1;
@@ -330,6 +355,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
           }
         }
         tc_fence_before();
+        TR(1, 64);
       }
       ++g;
     }
@@ -378,10 +404,16 @@ int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, floa
   a.img = reinterpret_cast<const uint8_t*>(h->tc_img);
   a.xn = xn; a.max_lv = h->max_lv; a.min_lv = h->min_lv; a.mean = mean; a.lv = lv; a.ldb = ldb;
   a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E; a.s = make_shape(h->in, h->D1);
+  a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
   const size_t smem = tc_smem_bytes(a.s);
-  CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   const int n_pairs = h->sm_count / 2;
-  MOPO_COUNT_LAUNCH, ens_tc_kernel<<<2 * n_pairs, NTHREADS, smem, st>>>(a);
+  if (a.trace) {
+    CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    MOPO_COUNT_LAUNCH, ens_tc_kernel<true><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
+  } else {
+    CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    MOPO_COUNT_LAUNCH, ens_tc_kernel<false><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
+  }
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }

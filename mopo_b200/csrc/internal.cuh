@@ -63,6 +63,7 @@ struct mopo_ens {
   // bf16 UMMA-ready images for the tcgen05 path (built by tc_build_images).
   void* tc_img = nullptr;
   size_t tc_img_bytes = 0;
+  void* tc_trace = nullptr;         // device uint64[4][2048] timeline buffer while mopo_debug_tc_trace runs
 
   // scratch
   DevBuf xn, actA, actB, mean, lv, blk_counts, misc;

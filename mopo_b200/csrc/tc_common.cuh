@@ -70,6 +70,16 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// One lane of a fully converged warp (elect.sync).  Issuing tcgen05.mma / commit under this predicate, from
+// warp-uniform control flow, lets the compiler keep the descriptors in uniform registers; issuing from a
+// `lane == 0` branch instead makes it wrap every UTCHMMA in an ELECT/BRA.U.ANY waterfall loop (~100 cycles each,
+// measured with mopo_debug_mma_rate).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- tcgen05: TMEM allocation ----------------------------------------------------------------------
 template <int CG> __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
   if (CG == 1) asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols) : "memory");

@@ -1,0 +1,60 @@
+#!/usr/bin/env python
+"""Decode the tcgen05 forward timeline (mopo_debug_tc_trace) and run the pipe-rate microbenchmarks.
+usage (on a GPU box): python tools/tc_timeline.py [B] > gpurun_out/timeline.txt"""
+import os
+import sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
+from mopo_b200 import _lib
+from mopo_b200.models.constructor import construct_model
+from oracle import ensemble as ens
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 50000
+lib = _lib.load()
+dev = torch.device('cuda', 0)
+st = torch.cuda.current_stream(dev)
+
+names = {0: 'tanh.f32', 1: 'tanh.bf16x2', 2: 'ex2.f32', 3: 'tanh.f16x2', 4: 'fma.bf16x2', 5: 'fma.f32'}
+for kind in range(6):
+    nb, iters = 148, 2000
+    cyc = torch.zeros(nb + 1, dtype=torch.int64, device=dev)
+    for _ in range(2):
+        _lib.check(lib.mopo_debug_pipe_bench(kind, iters, cyc.data_ptr(), nb, st.cuda_stream))
+    torch.cuda.synchronize()
+    c = cyc[:nb].cpu().numpy().astype(np.float64)
+    per_clk = 512 * 8 * iters / np.median(c)
+    print('pipe bench %-12s: %.2f instr-results/clk/SM (x2 elements if packed)' % (names[kind], per_clk))
+
+obs_dim, act_dim = 17, 6
+so, sys.stdout = sys.stdout, open(os.devnull, 'w')
+p = ens.init_params(obs_dim, act_dim, seed=0, separate_mean_var=True)
+model = construct_model(obs_dim=obs_dim, act_dim=act_dim, separate_mean_var=True, name='prof', device=0, precision=_lib.PREC_BF16)
+model.set_params(p['weights'], p['biases'], p['var_weights'], p['var_biases'], p['mu'], p['sigma'], p['max_logvar'], p['min_logvar'])
+sys.stdout = so
+xn = torch.randn(B, obs_dim + act_dim, device=dev)
+mean = torch.empty(7, B, obs_dim + 1, device=dev)
+lv = torch.empty_like(mean)
+trace = torch.zeros(4 * 2048, dtype=torch.int64, device=dev)
+for _ in range(2):
+    _lib.check(lib.mopo_debug_tc_trace(model._handle, xn.data_ptr(), B, mean.data_ptr(), lv.data_ptr(), trace.data_ptr(), st.cuda_stream))
+torch.cuda.synchronize()
+t = trace.cpu().numpy().astype(np.uint64).reshape(4, 2048)
+ev = []
+for role in range(4):
+    for v in t[role]:
+        if v == 0:
+            break
+        ev.append((int(v & np.uint64(0xFFFFFFFFFFFF)), role, int(v >> np.uint64(48))))
+ev.sort()
+if ev:
+    t0 = ev[0][0]
+    print('events: %d, span %d cycles' % (len(ev), ev[-1][0] - t0))
+    role_names = ['MMA ', 'WG0 ', 'WG1 ', 'LOAD']
+    last = {}
+    lim = int(os.environ.get('TL_MAX', '400'))
+    for c, role, tag in ev[:lim]:
+        d = c - last.get(role, c)
+        last[role] = c
+        print('%9d  %s%s tag %3d  (+%d)' % (c - t0, '    ' * role * 3, role_names[role], tag, d))
