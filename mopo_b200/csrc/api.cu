@@ -74,7 +74,7 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   for (int l = 0; l < MOPO_MAX_LAYERS; ++l) { if (h->W[l]) cudaFree(h->W[l]); if (h->b[l]) cudaFree(h->b[l]); }
   cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
   if (h->tc_img) cudaFree(h->tc_img);
-  DevBuf* bufs[] = {&h->xn, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
+  DevBuf* bufs[] = {&h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
                     &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts};
   for (DevBuf* b : bufs) b->release();
   delete h;

@@ -1,26 +1,34 @@
 // tcgen05 ensemble forward (MOPO_PREC_BF16): BNN._compile_outputs (reference mopo/models/bnn.py:631-675,
 // fc.py:96-106) for all 7 nets on the 5th-gen tensor cores.
 //
-// Design ("net-stationary"): a CTA PAIR (cluster of 2, tcgen05 cta_group::2, M = 256 rows per MMA) owns ONE
-// net.  Its bf16 weights (4 hidden layers + fused [mean|logvar] head, 286 KB) stay resident in the pair's
-// shared memory for the whole launch -- each CTA holds the N-half of every layer that cta_group::2 expects
-// from it (143 KB) -- and row tiles of 256 scaled inputs stream through:
+// Design ("net-stationary pairs, two row tiles in flight"):
+//   * A CTA PAIR (cluster of 2, tcgen05 cta_group::2, M = 256 rows per MMA) holds ONE net's bf16 weights
+//     (4 hidden layers + fused [mean|logvar] head) resident in its shared memory; each CTA keeps the N-half of
+//     every layer that cta_group::2 expects from it.  (net, 256-row tile) units are range-partitioned over the
+//     74 pairs; a pair reloads weights only when its range crosses into the next net.
+//   * TWO row tiles X and Y are in flight per pair, one layer apart in phase: while the 8 epilogue warps turn
+//     tile X's accumulator into the next layer's A operand (swish), the tensor pipe computes tile Y's layer,
+//     and vice versa.  The epilogue is MUFU-bound (one tanh.approx per activation, 16/clk/SM, measured), the MMA
+//     of a layer is ~15 % shorter, so in steady state the special-function unit never waits.
+//   * Tensor memory (512 columns) cannot hold two TS-form tiles (2 x (208 acc + 104 packed A) = 624), so the
+//     tiles differ: X chains its activations through TENSOR MEMORY (TS-form MMA, A = packed bf16x2 columns),
+//     Y chains them through SHARED MEMORY (SS-form MMA, K-panel bf16).  Column map (per CTA, 128 lanes):
+//         [  0,104) X.A   packed activations of X (K = 208)
+//         [104,216) X.D1  accumulator, output features   0..111
+//         [216,312) X.D2  accumulator, output features 112..199 + 8 padding columns  [304,312)
+//         [304,400) Y.D2  8 padding columns [304,312) + output features 112..199
+//         [400,512) Y.D1  accumulator, output features   0..111
+//     The N = 208 hidden width (200 features + 8 zero-weight padding rows) is issued as N = 112 + N = 96; the
+//     padding columns of X.D2 and Y.D2 are the SAME eight columns: both tiles write zeros there and nobody reads
+//     them, which is what makes 208 + 104 + 208 - 8 = 512 fit.  The weight image therefore orders a layer's
+//     output rows as [f0..111 | pad | f112..199 | pad]: Y's second half starts at the first pad, X's 8 rows later.
+//   * bias is folded into the GEMM through two constant-1 K columns (bias split hi + lo bf16), the 1/2 of
+//     swish(x) = xh + xh * tanh(xh), xh = x/2, is folded into the weights.
 //
-//   L0 : D0 = x0 (smem, K-panel bf16)        * W0^T     SS-form MMA
-//   L1..L3 : D = A_l (TMEM, packed bf16x2)   * W_l^T    TS-form MMA, A never leaves tensor memory
-//   head   : [mean | raw logvar] = A_4 * Wh^T           TS-form MMA
-//
-// Accumulators live in TMEM (two 208-column regions, ping-pong by layer).  The epilogue warps read a region
-// with tcgen05.ld, apply bias (folded into the GEMM through two constant-1 K columns, bias split hi+lo),
-// swish  h = xh + xh*tanh(xh), xh = x/2 (the 1/2 is folded into the weights), and write the next layer's
-// A operand IN PLACE over the accumulator columns they have just consumed (tcgen05.st).  Each layer's MMA is
-// issued as two N-halves (112 + 96 columns) with separate commits, so epilogue warpgroup 1 converts the
-// first half while the tensor pipe is still producing the second, and the next layer's K-steps start as
-// soon as the 16-column groups they need have been written (mbarriers grp[0..3]).
-//
-// Warp roles (320 threads): warps 0-3 epilogue of N-half 1 (+ head), warps 4-7 epilogue of N-half 2,
-// warp 8 lane 0 of the leader CTA issues every MMA of the pair, warp 9 loads weights (cp.async.bulk) and
-// the input tiles (fp32 -> bf16 K-panels, double buffered).
+// Warp roles (320 threads): warps 0-3 epilogue of output features 0..111 (+ mean head), warps 4-7 epilogue of
+// features 112..199 (+ logvar head), warp 8 of the leader CTA issues every MMA of the pair (elect.sync, warp-
+// uniform control flow -> descriptors stay in uniform registers), warp 9 loads weights and input tiles with
+// bulk async copies (the inputs arrive pre-tiled in bf16 K-panels from panelize_kernel).
 #include "internal.cuh"
 #include "tc_common.cuh"
 
@@ -28,24 +36,25 @@ namespace {
 
 using namespace tc;
 
-constexpr int HP = 208;          // hidden width padded to a multiple of 16 (200 features + 2 bias-one columns)
 constexpr int H = 200;
-constexpr int NH1 = 112, NH2 = 96;                 // N-halves of a hidden layer (each a legal cta_group::2 N)
-constexpr int ROWS1 = NH1 / 2, ROWS2 = NH2 / 2;    // B rows this CTA provides for each half (56, 48)
-constexpr int WROWS = ROWS1 + ROWS2;               // 104 weight rows per CTA per hidden layer
-constexpr int KPANELS = HP / 8;                    // 26 K-panels
-constexpr int W_PANEL = WROWS * 16;                // 1664 B
-constexpr int W_LAYER = KPANELS * W_PANEL;         // 43264 B
-constexpr int X_PANEL = 128 * 16;                  // 2048 B
+constexpr int KH = 208;                     // hidden K: 200 features + 2 bias-one columns + 6 zeros
+constexpr int KPANELS = KH / 8;             // 26
+constexpr int NH1 = 112, NH2 = 96;          // the two MMAs of a hidden layer
+constexpr int WROWS = 112;                  // weight rows per CTA per hidden layer: 56 (half 1) + 56 (half 2 window)
+constexpr int W_PANEL = WROWS * 16;         // 1792 B
+constexpr int W_LAYER = KPANELS * W_PANEL;  // 46592 B
+constexpr int A_PANEL = 128 * 16;           // 2048 B: one K-panel of a 128-row A tile
+constexpr int AY_BYTES = KPANELS * A_PANEL; // 53248 B
 constexpr int NTHREADS = 320;
-constexpr int REGION_COLS = 256;                   // TMEM columns between the two accumulator regions
+// tensor-memory column map
+constexpr int C_XA = 0, C_XD1 = 104, C_XD2 = 216, C_YD2 = 304, C_YD1 = 400;
 
 struct TcShape {
   int in, D1, HO, K0, NHEAD;     // K0 = roundup(in + 2, 16), NHEAD = roundup(2*D1, 16)
   __host__ __device__ int w0_bytes() const { return (K0 / 8) * W_PANEL; }
   __host__ __device__ int head_bytes() const { return KPANELS * (NHEAD / 2) * 16; }
   __host__ __device__ int img_bytes() const { return w0_bytes() + 3 * W_LAYER + head_bytes(); }
-  __host__ __device__ int x_bytes() const { return (K0 / 8) * X_PANEL; }
+  __host__ __device__ int x_bytes() const { return (K0 / 8) * A_PANEL; }      // one 128-row input block
 };
 
 __host__ __device__ inline TcShape make_shape(int in, int D1) {
@@ -58,6 +67,10 @@ __host__ __device__ inline TcShape make_shape(int in, int D1) {
 
 // ---------------------------------------------------------------------------------------------
 // weight image: [net e][cta rank r] -> W0 | W1 | W2 | W3 | head, each in K-panel layout
+//   element (row j, k) of a block at byte (k/8) * (rows*16) + j*16 + (k%8)*2
+// hidden-layer block of CTA r, local row j:
+//   j <  56 : output feature 56 r + j
+//   j >= 56 : virtual row g = 112 + 48 r + (j - 56) of [f0..111 | pad 112..119 | f112..199 at 120..207 | pad 208..215]
 // ---------------------------------------------------------------------------------------------
 struct ImgSrc {
   const float* W[5];
@@ -85,12 +98,16 @@ __global__ void build_image_kernel(ImgSrc src, __nv_bfloat16* __restrict__ img, 
     const int k = kc * 8 + kk;
     const int Kin = layer == 0 ? s.in : H;
     const int Nout = layer == 4 ? s.HO : H;
-    int n;
+    int n;                                        // output feature of this row, or -1 for a padding row
     if (layer == 4) n = r * (s.NHEAD / 2) + j;
-    else n = j < ROWS1 ? r * ROWS1 + j : NH1 + r * ROWS2 + (j - ROWS1);
+    else if (j < 56) n = 56 * r + j;
+    else {
+      const int g = 112 + 48 * r + (j - 56);
+      n = (g >= 120 && g < 208) ? g - 8 : -1;
+    }
     const float scale = layer == 4 ? 1.0f : 0.5f; // hidden layers produce xh = x/2 for the tanh form of swish
     float v = 0.f;
-    if (n < Nout) {
+    if (n >= 0 && n < Nout) {
       if (k < Kin) v = scale * src.W[layer][((int64_t)e * Kin + k) * Nout + n];
       else if (k < Kin + 2) v = bias_part(scale * src.b[layer][(int64_t)e * Nout + n], k - Kin);
     }
@@ -99,11 +116,40 @@ __global__ void build_image_kernel(ImgSrc src, __nv_bfloat16* __restrict__ img, 
 }
 
 // ---------------------------------------------------------------------------------------------
+// input tiles: fp32 rows [n, in] -> bf16 K-panel blocks of 128 rows: xt[block][kc][r][8], with the two
+// constant-1 bias columns at k = in, in+1; rows >= n are zero.  One thread per (row, kc) 16-byte slot.
+// ---------------------------------------------------------------------------------------------
+__global__ void panelize_kernel(const float* __restrict__ xn, uint4* __restrict__ xt, int n_max, const int* __restrict__ d_n,
+                                int in, int K0) {
+  const int n = d_n ? min(*d_n, n_max) : n_max;
+  const int kcs = K0 / 8;
+  const int64_t slots = (int64_t)((n + 255) / 256) * 256 * kcs;     // whole 256-row tiles (both CTAs' blocks)
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i % 128);
+    const int kc = (int)((i / 128) % kcs);
+    const int64_t blk = i / (128 * kcs);
+    const int64_t row = blk * 128 + r;
+    uint32_t p[4] = {0, 0, 0, 0};
+    if (row < n) {
+      const float* src = xn + row * in;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k0 = kc * 8 + 2 * j, k1 = k0 + 1;
+        const float v0 = k0 < in ? src[k0] : (k0 < in + 2 ? 1.f : 0.f);
+        const float v1 = k1 < in ? src[k1] : (k1 < in + 2 ? 1.f : 0.f);
+        p[j] = pack_bf16x2(v0, v1);
+      }
+    }
+    xt[i] = make_uint4(p[0], p[1], p[2], p[3]);     // i == (blk * kcs + kc) * 128 + r
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // forward kernel
 // ---------------------------------------------------------------------------------------------
 struct TcArgs {
-  const uint8_t* img;      // weight images
-  const float* xn;         // [n, in] scaled inputs
+  const uint8_t* img;      // weight images [E][2][img_bytes]
+  const uint8_t* xt;       // input tiles (panelize_kernel)
   const float* max_lv;     // [D1]
   const float* min_lv;     // [D1]
   float* mean;             // [E, ldb, D1]
@@ -117,12 +163,12 @@ struct TcArgs {
 };
 
 struct Bars {
-  uint64_t w_full;
-  uint64_t x_full[2];      // leader: both CTAs' input tiles are in smem          (count 2)
-  uint64_t x_free[2];      // each CTA: L0 MMAs that read buffer s have retired    (count 1, commit)
-  uint64_t grp[4];         // leader: 16-col groups of the next A operand written  (count 8 = 4 warps x 2 CTAs)
-  uint64_t d_full[2];      // each CTA: N-half h of the current layer is in TMEM   (count 1, commit)
-  uint64_t d_head;         // each CTA: head accumulator is in TMEM               (count 1, commit)
+  uint64_t w_full;         // weights of the current net are in smem (tx)
+  uint64_t x_ld[2];        // this CTA's input slot t has landed (tx)
+  uint64_t x_full[2];      // leader: both CTAs' input slot t are in smem                  (count 2)
+  uint64_t x_free[2];      // each CTA: the L0 MMAs that read slot t have retired           (commit)
+  uint64_t d_full[2];      // each CTA: the accumulator of tile t's current stage is ready  (commit)
+  uint64_t a_ready[2];     // leader: tile t's epilogue stage is done (A operand written / D consumed) (count 16)
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -132,22 +178,99 @@ __device__ __forceinline__ float tanh_fast(float x) {
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x))); }
+// softplus(x) = max(x,0) + log(1 + exp(-|x|)); ex2/lg2-based: absolute error < 1e-6 over the clamp's range
+__device__ __forceinline__ float softplus_fast(float x) { return fmaxf(x, 0.0f) + __logf(1.0f + __expf(-fabsf(x))); }
 
-// 16 accumulator columns (xh, fp32) -> 8 packed bf16x2 of swish(x) = xh + xh * tanh(xh)
-__device__ __forceinline__ void swish_pack16(const uint32_t (&v)[16], uint32_t (&p)[8]) {
+// swish of two accumulator columns (xh = x/2 already) -> packed bf16x2
+__device__ __forceinline__ uint32_t swish2(uint32_t a, uint32_t b) {
+  const float x = __uint_as_float(a), y = __uint_as_float(b);
+  return pack_bf16x2(fmaf(x, tanh_fast(x), x), fmaf(y, tanh_fast(y), y));
+}
+
+template <int N> __device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&v)[32]) {
+  if constexpr (N == 32) tmem_ld32(taddr, v);
+  else if constexpr (N == 16) tmem_ld16(taddr, reinterpret_cast<uint32_t (&)[16]>(v));
+  else tmem_ld8(taddr, reinterpret_cast<uint32_t (&)[8]>(v));
+}
+
+// N accumulator columns (output features feat..feat+N-1 of this thread's row) -> swish -> next layer's A operand:
+// tile X: packed columns C_XA + feat/2 of tensor memory; tile Y: K-panels feat/8.. of the smem A tile (this row's 16 B)
+template <bool IS_X, int N>
+__device__ __forceinline__ void swish_store(const uint32_t (&v)[32], int feat, uint32_t tlane, uint8_t* ay_row) {
+  uint32_t p[N / 2];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
-    p[j] = pack_bf16x2(fmaf(a, tanh_fast(a), a), fmaf(b, tanh_fast(b), b));
+  for (int j = 0; j < N / 2; ++j) p[j] = swish2(v[2 * j], v[2 * j + 1]);
+  if constexpr (IS_X) {
+    if constexpr (N == 32) tmem_st16(tlane + C_XA + feat / 2, reinterpret_cast<const uint32_t (&)[16]>(p));
+    else if constexpr (N == 16) tmem_st8(tlane + C_XA + feat / 2, reinterpret_cast<const uint32_t (&)[8]>(p));
+    else tmem_st4(tlane + C_XA + feat / 2, reinterpret_cast<const uint32_t (&)[4]>(p));
+  } else {
+#pragma unroll
+    for (int q = 0; q < N / 8; ++q)
+      st_shared_v4(ay_row + (feat / 8 + q) * A_PANEL, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
   }
 }
 
-// TMEM column (inside a region) of K-chunk c of the in-place A operand
-__device__ __forceinline__ int a_col(int c) { return c < 7 ? 8 * c : NH1 + 8 * (c - 7); }
+// one hidden-layer epilogue of one warp: its 32 rows x (112 or 88) accumulator columns, software pipelined
+// (the tcgen05.ld of the next chunk is in flight while the current chunk goes through the MUFU)
+template <bool IS_X, int WG>
+__device__ __forceinline__ void epi_hidden(uint32_t tlane, uint8_t* ay_row) {
+  constexpr int src = WG == 0 ? (IS_X ? C_XD1 : C_YD1) : (IS_X ? C_XD2 : C_YD2 + 8);
+  constexpr int f0 = WG == 0 ? 0 : 112;
+  uint32_t va[32], vb[32];
+  tmem_ld_n<32>(tlane + src, va);
+  tmem_ld_wait();
+  tmem_ld_n<32>(tlane + src + 32, vb);
+  swish_store<IS_X, 32>(va, f0, tlane, ay_row);
+  tmem_ld_wait();
+  if constexpr (WG == 0) {
+    tmem_ld_n<32>(tlane + src + 64, va);
+    swish_store<IS_X, 32>(vb, f0 + 32, tlane, ay_row);
+    tmem_ld_wait();
+    tmem_ld_n<16>(tlane + src + 96, vb);
+    swish_store<IS_X, 32>(va, f0 + 64, tlane, ay_row);
+    tmem_ld_wait();
+    swish_store<IS_X, 16>(vb, f0 + 96, tlane, ay_row);
+  } else {
+    tmem_ld_n<16>(tlane + src + 64, va);
+    swish_store<IS_X, 32>(vb, f0 + 32, tlane, ay_row);
+    tmem_ld_wait();
+    tmem_ld_n<8>(tlane + src + 80, vb);
+    swish_store<IS_X, 16>(va, f0 + 64, tlane, ay_row);
+    tmem_ld_wait();
+    swish_store<IS_X, 8>(vb, f0 + 80, tlane, ay_row);
+  }
+  if constexpr (IS_X) tmem_st_wait();
+  else fence_proxy_async_smem();
+}
+
+// head epilogue: mean = cols [0,D1) (warpgroup 0), logvar = clamp(cols [D1,2*D1)) (warpgroup 1)  (bnn.py:654-655 / 669-670)
+template <int WG>
+__device__ __forceinline__ void epi_head(uint32_t tdst, const TcShape& s, const float* sLv, float* mrow, float* lrow, bool valid) {
+  const int c_lo = WG == 0 ? 0 : s.D1 / 16, c_hi = WG == 0 ? (s.D1 + 15) / 16 : (s.HO + 15) / 16;
+  for (int c = c_lo; c < c_hi; ++c) {
+    uint32_t v[16];
+    tmem_ld16(tdst + 16 * c, v);
+    tmem_ld_wait();
+    if (valid) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int col = 16 * c + j;
+        const float x = __uint_as_float(v[j]);
+        if (WG == 0) { if (col < s.D1) mrow[col] = x; }
+        else if (col >= s.D1 && col < s.HO) {
+          const int d = col - s.D1;
+          const float mx = sLv[d], mn = sLv[MOPO_MAX_D1 + d];
+          float lg = mx - softplus_fast(mx - x);
+          lrow[d] = mn + softplus_fast(lg - mn);
+        }
+      }
+    }
+  }
+}
 
 constexpr int TRACE_CAP = 2048;   // events per role
-// timeline probe: role r (0 issuer, 1 epilogue WG0, 2 epilogue WG1, 3 loader) of pair 0 / leader CTA appends (tag, clock)
+// timeline probe: role r (0 issuer, 1 epilogue WG0 warp 0, 2 epilogue WG1 warp 4, 3 loader) of pair 0 / leader CTA
 #define TR(role, tag)                                                                                   \
   do {                                                                                                  \
     if (TRACE && a.trace && pair == 0 && rank == 0 && lane == 0 && tr_n < TRACE_CAP)                    \
@@ -163,7 +286,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   uint8_t* sW0 = smem;
   uint8_t* sW = sW0 + s.w0_bytes();                 // 3 hidden layers
   uint8_t* sWh = sW + 3 * W_LAYER;
-  uint8_t* sX = sWh + s.head_bytes();               // 2 input buffers
+  uint8_t* sAY = sWh + s.head_bytes();              // tile Y's activations (K-panel bf16)
+  uint8_t* sX = sAY + AY_BYTES;                     // input slots of tiles X, Y
   float* sLv = reinterpret_cast<float*>(sX + 2 * s.x_bytes());     // max_lv[D1], min_lv[D1]
   Bars* bars = reinterpret_cast<Bars*>(reinterpret_cast<uint8_t*>(sLv) + 2 * MOPO_MAX_D1 * sizeof(float));
 
@@ -172,20 +296,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x / 2, n_pairs = gridDim.x / 2;
   const int n = __shfl_sync(0xffffffffu, a.d_n ? min(*a.d_n, a.n_max) : a.n_max, 0);
-  const int n_tiles = (n + 255) / 256;
-
-  // pair -> (net, slot among the pairs of that net)
-  const int base = n_pairs / a.E, rem = n_pairs % a.E;
-  int e, slot, cnt;
-  if (pair < rem * (base + 1)) { e = pair / (base + 1); slot = pair % (base + 1); cnt = base + 1; }
-  else { const int q = pair - rem * (base + 1); e = rem + q / base; slot = q % base; cnt = base; }
-  const int my_tiles = slot < n_tiles ? (n_tiles - slot + cnt - 1) / cnt : 0;
+  const int nT = (n + 255) / 256;                            // 256-row tiles
+  const int64_t U = (int64_t)a.E * nT;                       // (net, tile) units, net-major
+  const int u0 = (int)(U * pair / n_pairs), u1 = (int)(U * (pair + 1) / n_pairs);
 
   if (tid == 0) {
     mbar_init(&bars->w_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&bars->x_full[i], 2); mbar_init(&bars->x_free[i], 1); mbar_init(&bars->d_full[i], 1); }
-    for (int i = 0; i < 4; ++i) mbar_init(&bars->grp[i], 8);
-    mbar_init(&bars->d_head, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->x_ld[i], 1); mbar_init(&bars->x_full[i], 2); mbar_init(&bars->x_free[i], 1);
+      mbar_init(&bars->d_full[i], 1); mbar_init(&bars->a_ready[i], 16);
+    }
     fence_barrier_init();
   }
   for (int i = tid; i < s.D1; i += NTHREADS) { sLv[i] = a.max_lv[i]; sLv[MOPO_MAX_D1 + i] = a.min_lv[i]; }
@@ -193,171 +313,157 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (warp == 9 && lane == 0) {                      // resident weights: one bulk copy per layer block
-    const uint8_t* src = a.img + ((size_t)e * 2 + rank) * s.img_bytes();
-    mbar_expect_tx(&bars->w_full, (uint32_t)s.img_bytes());
-    uint32_t off = 0;
-    const uint32_t sizes[5] = {(uint32_t)s.w0_bytes(), W_LAYER, W_LAYER, W_LAYER, (uint32_t)s.head_bytes()};
-    for (int i = 0; i < 5; ++i) { bulk_g2s(smem + off, src + off, sizes[i], &bars->w_full); off += sizes[i]; }
-  }
-  if (tid == 0) mbar_wait(&bars->w_full, 0);
-  __syncthreads();
-  cluster_sync_all();                                // both CTAs' weights and barriers are ready
   const uint32_t tbase = __shfl_sync(0xffffffffu, bars->tmem_base, 0);
+  if (warp < 4) {
+    // constant K columns 200..207 of both tiles' A operands: [1, 1, 0, 0, 0, 0, 0, 0] (the bias rows); written once
+    const uint32_t ones[4] = {0x3F803F80u, 0u, 0u, 0u};
+    tmem_st4(tbase + ((uint32_t)(warp * 32) << 16) + C_XA + 100, ones);
+    tmem_st_wait();
+    st_shared_v4(sAY + 25 * A_PANEL + tid * 16, 0x3F803F80u, 0u, 0u, 0u);
+    fence_proxy_async_smem();
+    tc_fence_before();
+  }
+  __syncthreads();
 
-  if (warp == 9) {
-    // ===== input loader: fp32 [rows, in] -> bf16 K-panels, + two constant-1 columns for the bias rows =====
-    for (int it = 0; it < my_tiles; ++it) {
-      const int sbuf = it & 1;
-      if (it >= 2) mbar_wait(&bars->x_free[sbuf], ((it >> 1) - 1) & 1);
-      const int tile = slot + it * cnt;
-      TR(3, 70);
-      uint8_t* dst = sX + sbuf * s.x_bytes();
-      for (int rr = lane; rr < 128; rr += 32) {
-        const int row = tile * 256 + (int)rank * 128 + rr;
-        const bool ok = row < n;
-        const float* src = a.xn + (size_t)row * s.in;
-        for (int kc = 0; kc < s.K0 / 8; ++kc) {
-          uint32_t p[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int k0 = kc * 8 + 2 * j, k1 = k0 + 1;
-            const float v0 = !ok ? 0.f : (k0 < s.in ? src[k0] : (k0 < s.in + 2 ? 1.f : 0.f));
-            const float v1 = !ok ? 0.f : (k1 < s.in ? src[k1] : (k1 < s.in + 2 ? 1.f : 0.f));
-            p[j] = pack_bf16x2(v0, v1);
+  // phase bookkeeping that survives net switches
+  uint32_t n_stage[2] = {0, 0};      // issuer: stages issued / epilogue: stages consumed, per tile slot
+  uint32_t n_x[2] = {0, 0};          // issuer / loader: input-slot uses
+  uint32_t seg = 0;
+
+  for (int u = u0; u < u1; ++seg) {
+    const int e = u / nT;
+    const int t_lo = u - e * nT;
+    const int u_end = min(u1, (e + 1) * nT);
+    const int cnt = u_end - u;                      // tiles of net e handled by this pair
+    const int n_super = (cnt + 1) / 2;
+    u = u_end;
+
+    // ---- weights of net e -> smem (all MMAs of the previous net have retired: the epilogue saw their commits) ----
+    cluster_sync_all();
+    if (warp == 9 && lane == 0) {
+      const uint8_t* src = a.img + ((size_t)e * 2 + rank) * s.img_bytes();
+      mbar_expect_tx(&bars->w_full, (uint32_t)s.img_bytes());
+      uint32_t off = 0;
+      const uint32_t sizes[5] = {(uint32_t)s.w0_bytes(), W_LAYER, W_LAYER, W_LAYER, (uint32_t)s.head_bytes()};
+      for (int i = 0; i < 5; ++i) { bulk_g2s(smem + off, src + off, sizes[i], &bars->w_full); off += sizes[i]; }
+    }
+    mbar_wait(&bars->w_full, seg & 1);
+    cluster_sync_all();                              // both CTAs' weights are in place before any MMA reads them
+
+    if (warp == 9) {
+      // ===== input loader: one bulk copy per 128-row block (bf16 K-panels from panelize_kernel) =====
+      if (lane == 0) {
+        for (int k = 0; k < n_super; ++k) {
+          for (int t = 0; t < 2; ++t) {
+            if (2 * k + t >= cnt) continue;
+            if (n_x[t] > 0) mbar_wait(&bars->x_free[t], (n_x[t] - 1) & 1);
+            TR(3, 70 + t);
+            const int64_t blk = 2 * (int64_t)(t_lo + 2 * k + t) + rank;
+            mbar_expect_tx(&bars->x_ld[t], (uint32_t)s.x_bytes());
+            bulk_g2s(sX + t * s.x_bytes(), a.xt + blk * s.x_bytes(), (uint32_t)s.x_bytes(), &bars->x_ld[t]);
+            mbar_wait(&bars->x_ld[t], n_x[t] & 1);
+            mbar_arrive_cluster(&bars->x_full[t], 0);
+            TR(3, 72 + t);
+            ++n_x[t];
           }
-          *reinterpret_cast<uint4*>(dst + kc * X_PANEL + rr * 16) = make_uint4(p[0], p[1], p[2], p[3]);
         }
       }
-      fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(&bars->x_full[sbuf], 0);
-      TR(3, 71);
-    }
-  } else if (warp == 8) {
-    // ===== MMA issuer: one thread of the leader CTA drives both SMs' tensor cores =====
-    if (rank == 0) {                                  // all 32 lanes run the loop; elect_one() issues
-      const uint32_t id1 = idesc_bf16(256, NH1), id2 = idesc_bf16(256, NH2), idh = idesc_bf16(256, s.NHEAD);
-      uint32_t g = 0;                                 // global layer counter -> accumulator region
-      uint32_t grp_par = 0;
-      for (int it = 0; it < my_tiles; ++it) {
-        const int sbuf = it & 1;
-        TR(0, 1);
-        mbar_wait_cluster(&bars->x_full[sbuf], (it >> 1) & 1);
-        tc_fence_after();
-        TR(0, 2);
-        // ---- L0 (SS) ----
-        {
-          const uint32_t dcol = tbase + (g & 1) * REGION_COLS;
-          const uint32_t xa = smem_u32(sX + sbuf * s.x_bytes());
-          for (int half = 0; half < 2; ++half) {
-            for (int ks = 0; ks < s.K0 / 16; ++ks) {
-              const uint64_t ad = smem_desc(xa + ks * 2 * X_PANEL, X_PANEL, 128);
-              const uint64_t bd = smem_desc(smem_u32(sW0) + ks * 2 * W_PANEL + (half ? ROWS1 * 16 : 0), W_PANEL, 128);
-              if (elect_one()) mma_ss<2>(dcol + (half ? NH1 : 0), ad, bd, half ? id2 : id1, ks > 0);
-            }
-            if (elect_one()) mma_commit<2>(&bars->d_full[half]);
-            TR(0, 30 + half);
-          }
-          if (elect_one()) mma_commit<2>(&bars->x_free[sbuf]);
-          ++g;
-        }
-        // ---- L1..L3 and head (TS): A = in-place bf16 activations in the previous region ----
-        for (int l = 1; l <= 4; ++l) {
-          const uint32_t acol = tbase + ((g - 1) & 1) * REGION_COLS;
-          const uint32_t dcol = tbase + (g & 1) * REGION_COLS;
-          const bool head = l == 4;
-          const uint8_t* wl = head ? sWh : sW + (l - 1) * W_LAYER;
-          const int panel = head ? (s.NHEAD / 2) * 16 : W_PANEL;
-          for (int half = 0; half < (head ? 1 : 2); ++half) {
-            for (int ks = 0; ks < KPANELS / 2; ++ks) {
-              if (half == 0 && (ks == 0 || ks == 4 || ks == 7 || ks == 10)) {
-                const int gi = ks == 0 ? 0 : ks == 4 ? 1 : ks == 7 ? 2 : 3;
-                mbar_wait_cluster(&bars->grp[gi], grp_par);
-                tc_fence_after();
-                TR(0, 100 + l * 10 + gi);
+    } else if (warp == 8) {
+      // ===== MMA issuer (leader CTA): all lanes run the loop, one elected lane issues =====
+      if (rank == 0) {
+        const uint32_t id1 = idesc_bf16(256, NH1), id2 = idesc_bf16(256, NH2), idh = idesc_bf16(256, s.NHEAD);
+        const uint32_t w0a = smem_u32(sW0), wa = smem_u32(sW), wha = smem_u32(sWh), aya = smem_u32(sAY), xa = smem_u32(sX);
+        const uint32_t hpanel = (uint32_t)(s.NHEAD / 2) * 16;
+        for (int k = 0; k < n_super; ++k) {
+          for (int j = 0; j < 5; ++j) {
+            for (int t = 0; t < 2; ++t) {
+              if (2 * k + t >= cnt) continue;
+              if (j == 0) { mbar_wait_cluster(&bars->x_full[t], n_x[t] & 1); ++n_x[t]; }
+              if (n_stage[t] > 0) mbar_wait_cluster(&bars->a_ready[t], (n_stage[t] - 1) & 1);
+              tc_fence_after();
+              TR(0, 10 * j + t);
+              const uint32_t d1 = tbase + (t == 0 ? C_XD1 : C_YD1), d2 = tbase + (t == 0 ? C_XD2 : C_YD2);
+              const uint32_t h2off = 56 * 16 + (t == 0 ? 8 * 16 : 0);       // half-2 window: X starts 8 rows later
+              if (elect_one()) {
+                if (j == 0) {
+                  for (int ks = 0; ks < s.K0 / 16; ++ks) {
+                    const uint64_t ad = smem_desc(xa + t * s.x_bytes() + ks * 2 * A_PANEL, A_PANEL, 128);
+                    const uint32_t b = w0a + ks * 2 * W_PANEL;
+                    mma_ss<2>(d1, ad, smem_desc(b, W_PANEL, 128), id1, ks > 0);
+                    mma_ss<2>(d2, ad, smem_desc(b + h2off, W_PANEL, 128), id2, ks > 0);
+                  }
+                  mma_commit<2>(&bars->x_free[t]);
+                } else if (j < 4) {
+                  const uint32_t wl = wa + (j - 1) * W_LAYER;
+                  if (t == 0) {
+#pragma unroll
+                    for (int ks = 0; ks < KPANELS / 2; ++ks) {
+                      const uint32_t b = wl + ks * 2 * W_PANEL;
+                      mma_ts<2>(d1, tbase + C_XA + 8 * ks, smem_desc(b, W_PANEL, 128), id1, ks > 0);
+                      mma_ts<2>(d2, tbase + C_XA + 8 * ks, smem_desc(b + h2off, W_PANEL, 128), id2, ks > 0);
+                    }
+                  } else {
+#pragma unroll
+                    for (int ks = 0; ks < KPANELS / 2; ++ks) {
+                      const uint32_t b = wl + ks * 2 * W_PANEL;
+                      const uint64_t ad = smem_desc(aya + ks * 2 * A_PANEL, A_PANEL, 128);
+                      mma_ss<2>(d1, ad, smem_desc(b, W_PANEL, 128), id1, ks > 0);
+                      mma_ss<2>(d2, ad, smem_desc(b + h2off, W_PANEL, 128), id2, ks > 0);
+                    }
+                  }
+                } else {
+                  if (t == 0) {
+#pragma unroll
+                    for (int ks = 0; ks < KPANELS / 2; ++ks)
+                      mma_ts<2>(d1, tbase + C_XA + 8 * ks, smem_desc(wha + ks * 2 * hpanel, hpanel, 128), idh, ks > 0);
+                  } else {
+#pragma unroll
+                    for (int ks = 0; ks < KPANELS / 2; ++ks)
+                      mma_ss<2>(d1, smem_desc(aya + ks * 2 * A_PANEL, A_PANEL, 128), smem_desc(wha + ks * 2 * hpanel, hpanel, 128), idh, ks > 0);
+                  }
+                }
+                mma_commit<2>(&bars->d_full[t]);
               }
-              const uint64_t bd = smem_desc(smem_u32(wl) + ks * 2 * panel + ((!head && half) ? ROWS1 * 16 : 0), panel, 128);
-              if (elect_one()) mma_ts<2>(dcol + (half ? NH1 : 0), acol + a_col(ks), bd, head ? idh : (half ? id2 : id1), ks > 0);
+              __syncwarp();
+              ++n_stage[t];
             }
-            if (elect_one()) mma_commit<2>(head ? &bars->d_head : &bars->d_full[half]);
-            TR(0, 30 + l * 2 + half);
           }
-          grp_par ^= 1;
-          ++g;
         }
       }
-    }
-    __syncwarp();
-  } else {
-    // ===== epilogue warpgroups: warps 0-3 -> N-half 1 (+ head), warps 4-7 -> N-half 2 =====
-    const int wg = warp / 4;                          // 0 or 1
-    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-    const int rr = (warp & 3) * 32 + lane;            // row inside this CTA's 128-row slice
-    uint32_t g = 0, dpar = 0, hpar = 0;
-    const int c_lo = wg == 0 ? 0 : 7, c_hi = wg == 0 ? 7 : 13;
-    for (int it = 0; it < my_tiles; ++it) {
-      const int tile = slot + it * cnt;
-      for (int l = 0; l < 4; ++l) {
-        TR(1 + wg, 40 + l);
-        mbar_wait(&bars->d_full[wg], dpar);
-        dpar ^= 1;
-        tc_fence_after();
-        TR(1 + wg, 50 + l);
-        const uint32_t reg = tbase + lane_off + (g & 1) * REGION_COLS;
-        for (int c = c_lo; c < c_hi; ++c) {
-          uint32_t v[16], p[8];
-          tmem_ld16(reg + 16 * c, v);
-          tmem_ld_wait();
-          swish_pack16(v, p);
-          if (c == 12) p[4] = 0x3F803F80u;            // columns 200/201 := 1.0 -> next layer's bias rows (hi + lo)
-          tmem_st8(reg + a_col(c), p);
-          const bool last = (c == 3 || c == 6 || c == 9 || c == 12);
-          if (last) {
-            tmem_st_wait();
+    } else {
+      // ===== epilogue warps: 0-3 -> features 0..111 / mean head, 4-7 -> features 112..199 / logvar head =====
+      const int wg = warp >> 2, q = warp & 3;
+      const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+      const int rr = q * 32 + lane;                     // row inside this CTA's 128-row block
+      uint8_t* ay_row = sAY + rr * 16;
+      for (int k = 0; k < n_super; ++k) {
+        for (int j = 0; j < 5; ++j) {
+          for (int t = 0; t < 2; ++t) {
+            if (2 * k + t >= cnt) continue;
+            if (q == 0) TR(1 + wg, 100 + 10 * j + t);
+            mbar_wait(&bars->d_full[t], n_stage[t] & 1);
+            ++n_stage[t];
+            tc_fence_after();
+            if (q == 0) TR(1 + wg, 200 + 10 * j + t);
+            if (j < 4) {
+              if (t == 0) { if (wg == 0) epi_hidden<true, 0>(tlane, ay_row); else epi_hidden<true, 1>(tlane, ay_row); }
+              else        { if (wg == 0) epi_hidden<false, 0>(tlane, ay_row); else epi_hidden<false, 1>(tlane, ay_row); }
+            } else {
+              const int64_t row = 256 * (int64_t)(t_lo + 2 * k + t) + (int64_t)rank * 128 + rr;
+              float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1;
+              float* lrow = a.lv + ((size_t)e * a.ldb + row) * s.D1;
+              const uint32_t tdst = tlane + (t == 0 ? C_XD1 : C_YD1);
+              if (wg == 0) epi_head<0>(tdst, s, sLv, mrow, lrow, row < n);
+              else epi_head<1>(tdst, s, sLv, mrow, lrow, row < n);
+            }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(&bars->grp[c == 3 ? 0 : c == 6 ? 1 : c == 9 ? 2 : 3], 0);
+            if (lane == 0) mbar_arrive_cluster(&bars->a_ready[t], 0);
+            if (q == 0) TR(1 + wg, 300 + 10 * j + t);
           }
         }
-        ++g;
-        TR(1 + wg, 60 + l);
       }
-      if (wg == 0) {
-        // ---- head epilogue: mean = cols [0,D1), logvar = clamp(cols [D1,2*D1))  (bnn.py:654-655 / 669-670) ----
-        TR(1, 44);
-        mbar_wait(&bars->d_head, hpar);
-        hpar ^= 1;
-        tc_fence_after();
-        TR(1, 54);
-        const uint32_t reg = tbase + lane_off + (g & 1) * REGION_COLS;
-        const int row = tile * 256 + (int)rank * 128 + rr;
-        float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1;
-        float* lrow = a.lv + ((size_t)e * a.ldb + row) * s.D1;
-        for (int c = 0; c < s.NHEAD / 16; ++c) {
-          uint32_t v[16];
-          tmem_ld16(reg + 16 * c, v);
-          tmem_ld_wait();
-          if (row < n) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int col = 16 * c + j;
-              const float x = __uint_as_float(v[j]);
-              if (col < s.D1) mrow[col] = x;
-              else if (col < s.HO) {
-                const int d = col - s.D1;
-                const float mx = sLv[d], mn = sLv[MOPO_MAX_D1 + d];
-                float lg = mx - softplus_f(mx - x);
-                lg = mn + softplus_f(lg - mn);
-                lrow[d] = lg;
-              }
-            }
-          }
-        }
-        tc_fence_before();
-        TR(1, 64);
-      }
-      ++g;
     }
   }
   __syncwarp();
@@ -368,14 +474,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
 }
 
 size_t tc_smem_bytes(const TcShape& s) {
-  return (size_t)s.img_bytes() + 2 * s.x_bytes() + 2 * MOPO_MAX_D1 * sizeof(float) + sizeof(Bars) + 128;
+  return (size_t)s.img_bytes() + AY_BYTES + 2 * s.x_bytes() + 2 * MOPO_MAX_D1 * sizeof(float) + sizeof(Bars) + 128;
 }
 
 }  // namespace
 
 int tc_supported(const mopo_ens* h) {
   if (h->H != H || h->L != 4) return 0;
-  if (h->in + 2 > 64 || h->HO > 96) return 0;
+  if (h->in + 2 > 64 || h->HO > 112) return 0;
   if (h->E > h->sm_count / 2) return 0;
   return tc_smem_bytes(make_shape(h->in, h->D1)) <= 227 * 1024;
 }
@@ -401,9 +507,20 @@ int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, floa
   if (n_max == 0) return MOPO_OK;
   if (!h->tc_img) { mopo_set_error("tc_forward: weight images not built"); return MOPO_ESTATE; }
   TcArgs a;
+  a.s = make_shape(h->in, h->D1);
+  // inputs -> bf16 K-panel tiles (whole 256-row tiles, zero padded)
+  const int64_t tiles = (n_max + 255) / 256;
+  TRY(h->xtiles.reserve((size_t)tiles * 2 * a.s.x_bytes()));
+  {
+    const int64_t slots = tiles * 256 * (a.s.K0 / 8);
+    const int grid = (int)((slots + 255) / 256 > 148 * 8 ? 148 * 8 : (slots + 255) / 256);
+    MOPO_COUNT_LAUNCH, panelize_kernel<<<grid, 256, 0, st>>>(xn, h->xtiles.as<uint4>(), (int)n_max, d_n, h->in, a.s.K0);
+    CUDA_TRY(cudaGetLastError());
+  }
   a.img = reinterpret_cast<const uint8_t*>(h->tc_img);
-  a.xn = xn; a.max_lv = h->max_lv; a.min_lv = h->min_lv; a.mean = mean; a.lv = lv; a.ldb = ldb;
-  a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E; a.s = make_shape(h->in, h->D1);
+  a.xt = h->xtiles.as<uint8_t>();
+  a.max_lv = h->max_lv; a.min_lv = h->min_lv; a.mean = mean; a.lv = lv; a.ldb = ldb;
+  a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E;
   a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
   const size_t smem = tc_smem_bytes(a.s);
   const int n_pairs = h->sm_count / 2;

@@ -66,7 +66,7 @@ struct mopo_ens {
   void* tc_trace = nullptr;         // device uint64[4][2048] timeline buffer while mopo_debug_tc_trace runs
 
   // scratch
-  DevBuf xn, actA, actB, mean, lv, blk_counts, misc;
+  DevBuf xn, xtiles, actA, actB, mean, lv, blk_counts, misc;
   DevBuf ro_obs[2], ro_origin[2], ro_counts;
 };
 
