@@ -362,7 +362,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
             mbar_expect_tx(&bars->x_ld[t], (uint32_t)s.x_bytes());
             bulk_g2s(sX + t * s.x_bytes(), a.xt + blk * s.x_bytes(), (uint32_t)s.x_bytes(), &bars->x_ld[t]);
             mbar_wait(&bars->x_ld[t], n_x[t] & 1);
-            mbar_arrive_cluster(&bars->x_full[t], 0);
+            mbar_arrive_remote(&bars->x_full[t], 0);
             TR(3, 72 + t);
             ++n_x[t];
           }
@@ -459,7 +459,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(&bars->a_ready[t], 0);
+            if (lane == 0) mbar_arrive_remote(&bars->a_ready[t], 0);
             if (q == 0) TR(1 + wg, 300 + 10 * j + t);
           }
         }
