@@ -74,7 +74,7 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   for (int l = 0; l < MOPO_MAX_LAYERS; ++l) { if (h->W[l]) cudaFree(h->W[l]); if (h->b[l]) cudaFree(h->b[l]); }
   cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
   if (h->tc_img) cudaFree(h->tc_img);
-  DevBuf* bufs[] = {&h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
+  DevBuf* bufs[] = {&h->sel, &h->selm, &h->selv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
                     &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts};
   for (DevBuf* b : bufs) b->release();
   delete h;
@@ -195,6 +195,49 @@ MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mea
   return MOPO_OK;
 }
 
+// One ensemble pass of a FakeEnv.step: scaler + forward.  On the tensor-core path a stochastic step with the
+// learned-variance (or no) penalty and no mixture diagnostics takes the fused head: only the chosen net's mean /
+// variance row and the per-net variance sums leave the SM.  Fills the TailArgs inputs accordingly.
+static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_kind, int deterministic,
+                        const float* obs, const float* act, int64_t B, const int* d_n, const int32_t* model_inds,
+                        uint64_t seed, uint64_t step_id, const int32_t* origin, int64_t origin_base,
+                        TailArgs* t, cudaStream_t st) {
+  const int E = h->E, D1 = h->D1;
+  if (precision == MOPO_PREC_BF16) {
+    REQUIRE(tc_supported(h), MOPO_EUNSUPPORTED, "bf16 tcgen05 path supports hidden_dim=200, n_hidden=4 and shapes whose weights fit one CTA pair (in+2<=32, 2*D1<=48 at E<=74)");
+    const bool fused = !deterministic && !want_diag && penalty_kind != MOPO_PEN_DISAGREEMENT;
+    TcPrep q = {};
+    q.obs = obs; q.act = act; q.n_max = B; q.d_n = d_n; q.model_inds = model_inds;
+    q.seed = seed; q.step_id = step_id; q.origin = origin; q.origin_base = origin_base;
+    TcOut o = {};
+    if (fused) {
+      TRY(h->sel.reserve(sizeof(int32_t) * B));
+      TRY(h->selm.reserve(sizeof(float) * B * D1));
+      TRY(h->selv.reserve(sizeof(float) * B * D1));
+      TRY(h->pen2.reserve(sizeof(float) * 2 * E * B));
+      q.sel = h->sel.as<int32_t>();
+      o.sel = q.sel; o.selm = h->selm.as<float>(); o.selv = h->selv.as<float>(); o.pen2 = h->pen2.as<float>(); o.ldb = B;
+      t->sel = o.sel; t->selm = o.selm; t->selv = o.selv; t->pen2 = o.pen2;
+    } else {
+      TRY(h->mean.reserve(sizeof(float) * E * B * D1));
+      TRY(h->lv.reserve(sizeof(float) * E * B * D1));
+      o.mean = h->mean.as<float>(); o.lv = h->lv.as<float>(); o.ldb = B;
+      t->mean = o.mean; t->lv = o.lv;
+    }
+    t->ldb = B;
+    TRY(tc_tiles_from_step(h, q, st));
+    return tc_launch(h, B, d_n, o, st);
+  }
+  REQUIRE(precision == MOPO_PREC_FP32, MOPO_EINVAL, "unknown precision %d", precision);
+  TRY(h->xn.reserve(sizeof(float) * B * h->in));
+  TRY(h->mean.reserve(sizeof(float) * E * B * D1));
+  TRY(h->lv.reserve(sizeof(float) * E * B * D1));
+  TRY(launch_prep(obs, act, h->mu, h->sigma, h->xn.as<float>(), B, d_n, h->cfg.obs_dim, h->cfg.act_dim, st));
+  TRY(fp32_forward(h, h->xn.as<float>(), B, d_n, h->mean.as<float>(), h->lv.as<float>(), B, st));
+  t->mean = h->mean.as<float>(); t->lv = h->lv.as<float>(); t->ldb = B;
+  return MOPO_OK;
+}
+
 static int check_step_common(const mopo_ens* h, int term_kind, int penalty_kind, int deterministic, const char* who) {
   REQUIRE(h->params_set, MOPO_ESTATE, "%s: parameters not set", who);
   REQUIRE(term_kind >= MOPO_TERM_NEVER && term_kind <= MOPO_TERM_HUMANOID, MOPO_EINVAL, "%s: term_kind=%d", who, term_kind);
@@ -214,14 +257,10 @@ MOPO_API int mopo_env_step(mopo_ens* h, const mopo_step_args* a, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   const int64_t B = a->B;
-  TRY(h->xn.reserve(sizeof(float) * B * h->in));
-  TRY(h->mean.reserve(sizeof(float) * h->E * B * h->D1));
-  TRY(h->lv.reserve(sizeof(float) * h->E * B * h->D1));
-  TRY(launch_prep(a->obs, a->act, h->mu, h->sigma, h->xn.as<float>(), B, nullptr, h->cfg.obs_dim, h->cfg.act_dim, st));
-  TRY(forward(h, a->precision, h->xn.as<float>(), B, nullptr, h->mean.as<float>(), h->lv.as<float>(), B, st));
   TailArgs t;
   memset(&t, 0, sizeof(t));
-  t.mean = h->mean.as<float>(); t.lv = h->lv.as<float>(); t.ldb = B;
+  TRY(step_forward(h, a->precision, a->log_prob || a->dev, a->penalty_kind, a->deterministic, a->obs, a->act, B, nullptr,
+                   a->model_inds, a->seed, a->step_id, a->origin, 0, &t, st));
   t.obs = a->obs; t.act = a->act; t.n_max = B; t.d_n = nullptr;
   t.E = h->E; t.D1 = h->D1; t.obs_dim = h->cfg.obs_dim; t.act_dim = h->cfg.act_dim;
   t.term_kind = a->term_kind; t.penalty_kind = a->penalty_kind; t.coeff = a->penalty_coeff; t.deterministic = a->deterministic;
@@ -388,9 +427,6 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   const int od = h->cfg.obs_dim, ad = h->cfg.act_dim;
   const int nblk = (int)((B + tail_rows_per_block() - 1) / tail_rows_per_block());
-  TRY(h->xn.reserve(sizeof(float) * B * h->in));
-  TRY(h->mean.reserve(sizeof(float) * h->E * B * h->D1));
-  TRY(h->lv.reserve(sizeof(float) * h->E * B * h->D1));
   TRY(h->blk_counts.reserve(sizeof(int) * nblk));
   // ro_obs[0/1]: dense obs of the current step / next_obs of the current step ; ro_origin likewise
   for (int k = 0; k < 2; ++k) { TRY(h->ro_obs[k].reserve(sizeof(float) * B * od)); TRY(h->ro_origin[k].reserve(sizeof(int32_t) * B)); }
@@ -405,17 +441,17 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   const int32_t* origin_cur = nullptr;
   for (int i = 0; i < H; ++i) {
     const int* d_n = d_counts + i;
-    TRY(launch_prep(obs_cur, a->actions[i], h->mu, h->sigma, h->xn.as<float>(), B, d_n, od, ad, st));
-    TRY(forward(h, a->precision, h->xn.as<float>(), B, d_n, h->mean.as<float>(), h->lv.as<float>(), B, st));
     TailArgs t;
     memset(&t, 0, sizeof(t));
-    t.mean = h->mean.as<float>(); t.lv = h->lv.as<float>(); t.ldb = B;
+    const uint64_t step_id = (a->rollout_id << 16) ^ (uint64_t)i;
+    TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, a->actions[i], B, d_n,
+                     a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st));
     t.obs = obs_cur; t.act = a->actions[i]; t.n_max = B; t.d_n = d_n;
     t.E = h->E; t.D1 = h->D1; t.obs_dim = od; t.act_dim = ad;
     t.term_kind = a->term_kind; t.penalty_kind = a->penalty_kind; t.coeff = a->penalty_coeff; t.deterministic = a->deterministic;
     t.noise = a->noise ? a->noise[i] : nullptr; t.model_inds = a->model_inds ? a->model_inds[i] : nullptr;
     t.elites = h->elites; t.n_elites = h->n_elites;
-    t.seed = a->seed; t.step_id = (a->rollout_id << 16) ^ (uint64_t)i; t.origin = origin_cur; t.origin_base = a->origin_base;
+    t.seed = a->seed; t.step_id = step_id; t.origin = origin_cur; t.origin_base = a->origin_base;
     t.next_obs = nobs_dense; t.rewards = nullptr; t.terminals = term_dense;
     t.p_act = pool->actions; t.p_rew = pool->rewards; t.p_obs = pool->obs; t.p_nobs = pool->next_obs; t.p_term = pool->terminals;
     t.pool_max = pool->max_size; t.pool_base = pool->pointer; t.d_pool_off = d_pool_off;

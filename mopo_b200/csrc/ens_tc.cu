@@ -31,6 +31,7 @@
 // bulk async copies (the inputs arrive pre-tiled in bf16 K-panels from panelize_kernel).
 #include "internal.cuh"
 #include "tc_common.cuh"
+#include "philox.cuh"
 
 namespace {
 
@@ -99,7 +100,12 @@ __global__ void build_image_kernel(ImgSrc src, __nv_bfloat16* __restrict__ img, 
     const int Kin = layer == 0 ? s.in : H;
     const int Nout = layer == 4 ? s.HO : H;
     int n;                                        // output feature of this row, or -1 for a padding row
-    if (layer == 4) n = r * (s.NHEAD / 2) + j;
+    if (layer == 4) {
+      // head rows of CTA r = epilogue warpgroup r's block: [mean(d) x P | raw logvar(d) x P], d = r*dh + i, P = NHEAD/4
+      const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
+      const int part = j / P, ii = j % P, d = r * dh + ii;
+      n = d < (r ? s.D1 : dh) ? part * s.D1 + d : -1;
+    }
     else if (j < 56) n = 56 * r + j;
     else {
       const int g = 112 + 48 * r + (j - 56);
@@ -115,6 +121,8 @@ __global__ void build_image_kernel(ImgSrc src, __nv_bfloat16* __restrict__ img, 
   }
 }
 
+// Head column order (see build_image_kernel): warpgroup w of the epilogue owns output dims d = w*dh + i, i < P,
+// dh = ceil(D1/2), P = NHEAD/4: its accumulator block is columns [w*NHEAD/2, (w+1)*NHEAD/2) = [mean x P | raw x P].
 // ---------------------------------------------------------------------------------------------
 // input tiles: fp32 rows [n, in] -> bf16 K-panel blocks of 128 rows: xt[block][kc][r][8], with the two
 // constant-1 bias columns at k = in, in+1; rows >= n are zero.  One thread per (row, kc) 16-byte slot.
@@ -144,6 +152,49 @@ __global__ void panelize_kernel(const float* __restrict__ xn, uint4* __restrict_
   }
 }
 
+// FakeEnv.step front end for the tensor-core path: concat(obs, act) (fake_env.py:46), scaler (models/utils.py:96),
+// bf16 K-panel tiling, and the per-row elite pick (bnn.py:342-344: supplied indices, or Philox over the elite list)
+// in one pass.  sel == nullptr skips the pick (deterministic / full-output steps).
+struct PrepArgs {
+  const float *obs, *act, *mu, *sigma;
+  uint4* xt;
+  int n_max; const int* d_n;
+  int obs_dim, act_dim, K0;
+  int32_t* sel; const int32_t* model_inds; const int32_t* elites; int n_elites;
+  uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
+};
+
+__global__ void prep_tiles_kernel(PrepArgs a) {
+  const int n = a.d_n ? min(*a.d_n, a.n_max) : a.n_max;
+  const int in = a.obs_dim + a.act_dim, kcs = a.K0 / 8;
+  const int64_t slots = (int64_t)((n + 255) / 256) * 256 * kcs;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += (int64_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i % 128);
+    const int kc = (int)((i / 128) % kcs);
+    const int64_t row = (i / (128 * kcs)) * 128 + r;
+    uint32_t p[4] = {0, 0, 0, 0};
+    if (row < n) {
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = kc * 8 + j;
+        if (k < in) {
+          const float x = k < a.obs_dim ? a.obs[row * a.obs_dim + k] : a.act[row * a.act_dim + (k - a.obs_dim)];
+          v[j] = (x - a.mu[k]) / a.sigma[k];
+        } else v[j] = k < in + 2 ? 1.f : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) p[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+      if (kc == 0 && a.sel) {
+        const uint32_t orow = a.origin ? (uint32_t)a.origin[row] : (uint32_t)(a.origin_base + row);
+        a.sel[row] = a.model_inds ? a.model_inds[row]
+                                  : a.elites[philox_elite(orow, (uint32_t)a.step_id, a.seed, (uint32_t)a.n_elites)];
+      }
+    }
+    a.xt[i] = make_uint4(p[0], p[1], p[2], p[3]);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // forward kernel
 // ---------------------------------------------------------------------------------------------
@@ -152,9 +203,15 @@ struct TcArgs {
   const uint8_t* xt;       // input tiles (panelize_kernel)
   const float* max_lv;     // [D1]
   const float* min_lv;     // [D1]
+  // FULL output (sel == nullptr): everything BNN.predict returns
   float* mean;             // [E, ldb, D1]
   float* lv;               // [E, ldb, D1]
   int64_t ldb;
+  // FUSED output (sel != nullptr): what FakeEnv.step keeps of the [E,B,D1] arrays (fake_env.py:78-81,110)
+  const int32_t* sel;      // [n] net chosen for each row (the elite pick)
+  float* selm;             // [n, D1] mean of the chosen net
+  float* selv;             // [n, D1] variance of the chosen net
+  float* pen2;             // [2, E, ldb] sum_d var_d over each warpgroup's half of the output dims
   int n_max;
   const int* d_n;
   int E;
@@ -244,29 +301,52 @@ __device__ __forceinline__ void epi_hidden(uint32_t tlane, uint8_t* ay_row) {
   else fence_proxy_async_smem();
 }
 
-// head epilogue: mean = cols [0,D1) (warpgroup 0), logvar = clamp(cols [D1,2*D1)) (warpgroup 1)  (bnn.py:654-655 / 669-670)
-template <int WG>
-__device__ __forceinline__ void epi_head(uint32_t tdst, const TcShape& s, const float* sLv, float* mrow, float* lrow, bool valid) {
-  const int c_lo = WG == 0 ? 0 : s.D1 / 16, c_hi = WG == 0 ? (s.D1 + 15) / 16 : (s.HO + 15) / 16;
-  for (int c = c_lo; c < c_hi; ++c) {
-    uint32_t v[16];
-    tmem_ld16(tdst + 16 * c, v);
+// head epilogue.  Soft clamp + exp of bnn.py:654-655/669-670,675 in closed form:
+//   lv1 = max - softplus(max - raw), lv = min + softplus(lv1 - min), var = exp(lv)
+//   =>  var = e^min + e^lv1 = e^min + 1 / (e^-max + e^-raw)                  (exp(softplus(y)) = 1 + e^y)
+// two MUFU ops per output dim instead of five.  sC[0][w*P+i] = e^min_d, sC[1][w*P+i] = e^-max_d for the dims of
+// warpgroup w (padding dims: 0 and +inf, so they contribute var = 0).
+// FUSED: pen2[w][e][row] = sum of var over this warpgroup's dims; rows whose chosen net is e also store mean / var.
+// FULL : mean[e][row][d], lv[e][row][d] = log(var).
+template <bool FUSED>
+__device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s, const float* sC, const TcArgs& a,
+                                         int e, int64_t row, bool valid) {
+  const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
+  const int d0 = wg * dh, nd = wg ? s.D1 - dh : dh;
+  const float* cmin = sC + wg * P;
+  const float* cnmax = sC + MOPO_MAX_D1 + wg * P;
+  bool mine = false;
+  if (FUSED) mine = valid && a.sel[row] == e;
+  float pen = 0.f;
+  for (int c = 0; c < P / 4; ++c) {
+    uint32_t mv[4], rv[4];
+    tmem_ld4(tblk + 4 * c, mv);
+    tmem_ld4(tblk + P + 4 * c, rv);
     tmem_ld_wait();
-    if (valid) {
+    float var[4];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int col = 16 * c + j;
-        const float x = __uint_as_float(v[j]);
-        if (WG == 0) { if (col < s.D1) mrow[col] = x; }
-        else if (col >= s.D1 && col < s.HO) {
-          const int d = col - s.D1;
-          const float mx = sLv[d], mn = sLv[MOPO_MAX_D1 + d];
-          float lg = mx - softplus_fast(mx - x);
-          lrow[d] = mn + softplus_fast(lg - mn);
-        }
+    for (int i = 0; i < 4; ++i) {
+      var[i] = cmin[4 * c + i] + __fdividef(1.0f, cnmax[4 * c + i] + __expf(-__uint_as_float(rv[i])));
+      pen += var[i];
+    }
+    if (FUSED) {
+      if (mine) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (4 * c + i < nd) {
+            a.selm[row * s.D1 + d0 + 4 * c + i] = __uint_as_float(mv[i]);
+            a.selv[row * s.D1 + d0 + 4 * c + i] = var[i];
+          }
       }
+    } else if (valid) {
+      float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1 + d0;
+      float* lrow = a.lv + ((size_t)e * a.ldb + row) * s.D1 + d0;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (4 * c + i < nd) { mrow[4 * c + i] = __uint_as_float(mv[i]); lrow[4 * c + i] = __logf(var[i]); }
     }
   }
+  if (FUSED && valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
 }
 
 constexpr int TRACE_CAP = 2048;   // events per role
@@ -308,7 +388,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
     }
     fence_barrier_init();
   }
-  for (int i = tid; i < s.D1; i += NTHREADS) { sLv[i] = a.max_lv[i]; sLv[MOPO_MAX_D1 + i] = a.min_lv[i]; }
+  for (int i = tid; i < 2 * (s.NHEAD / 4); i += NTHREADS) {          // head constants per warpgroup block (see epi_head)
+    const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
+    const int w = i / P, d = w * dh + i % P;
+    const bool ok = d < (w ? s.D1 : dh);
+    sLv[i] = ok ? expf(a.min_lv[d]) : 0.0f;
+    sLv[MOPO_MAX_D1 + i] = ok ? expf(-a.max_lv[d]) : __int_as_float(0x7f800000);
+  }
   if (warp == 8) { tmem_alloc<2>(&bars->tmem_base, 512); tmem_relinquish<2>(); }
   tc_fence_before();
   __syncthreads();
@@ -451,11 +537,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
               else        { if (wg == 0) epi_hidden<false, 0>(tlane, ay_row); else epi_hidden<false, 1>(tlane, ay_row); }
             } else {
               const int64_t row = 256 * (int64_t)(t_lo + 2 * k + t) + (int64_t)rank * 128 + rr;
-              float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1;
-              float* lrow = a.lv + ((size_t)e * a.ldb + row) * s.D1;
-              const uint32_t tdst = tlane + (t == 0 ? C_XD1 : C_YD1);
-              if (wg == 0) epi_head<0>(tdst, s, sLv, mrow, lrow, row < n);
-              else epi_head<1>(tdst, s, sLv, mrow, lrow, row < n);
+              const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1) + wg * (s.NHEAD / 2);
+              if (a.sel) epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n);
+              else epi_head<false>(tblk, wg, s, sLv, a, e, row, row < n);
             }
             tc_fence_before();
             __syncwarp();
@@ -502,24 +586,47 @@ int tc_build_images(mopo_ens* h, cudaStream_t st) {
   return MOPO_OK;
 }
 
-int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
-               int64_t ldb, cudaStream_t st) {
+static int tc_reserve_tiles(mopo_ens* h, int64_t n_max, const TcShape& s, int* grid) {
+  const int64_t tiles = (n_max + 255) / 256;
+  TRY(h->xtiles.reserve((size_t)tiles * 2 * s.x_bytes()));
+  const int64_t blocks = (tiles * 256 * (s.K0 / 8) + 255) / 256;
+  *grid = (int)(blocks > 148 * 8 ? 148 * 8 : blocks);
+  return MOPO_OK;
+}
+
+int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st) {
+  const TcShape s = make_shape(h->in, h->D1);
+  int grid;
+  TRY(tc_reserve_tiles(h, n_max, s, &grid));
+  MOPO_COUNT_LAUNCH, panelize_kernel<<<grid, 256, 0, st>>>(xn, h->xtiles.as<uint4>(), (int)n_max, d_n, h->in, s.K0);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st) {
+  const TcShape s = make_shape(h->in, h->D1);
+  int grid;
+  TRY(tc_reserve_tiles(h, q.n_max, s, &grid));
+  PrepArgs a;
+  a.obs = q.obs; a.act = q.act; a.mu = h->mu; a.sigma = h->sigma; a.xt = h->xtiles.as<uint4>();
+  a.n_max = (int)q.n_max; a.d_n = q.d_n; a.obs_dim = h->cfg.obs_dim; a.act_dim = h->cfg.act_dim; a.K0 = s.K0;
+  a.sel = q.sel; a.model_inds = q.model_inds; a.elites = h->elites; a.n_elites = h->n_elites;
+  a.seed = q.seed; a.step_id = q.step_id; a.origin = q.origin; a.origin_base = q.origin_base;
+  MOPO_COUNT_LAUNCH, prep_tiles_kernel<<<grid, 256, 0, st>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaStream_t st) {
   if (n_max == 0) return MOPO_OK;
-  if (!h->tc_img) { mopo_set_error("tc_forward: weight images not built"); return MOPO_ESTATE; }
+  if (!h->tc_img) { mopo_set_error("tc_launch: weight images not built"); return MOPO_ESTATE; }
   TcArgs a;
   a.s = make_shape(h->in, h->D1);
-  // inputs -> bf16 K-panel tiles (whole 256-row tiles, zero padded)
-  const int64_t tiles = (n_max + 255) / 256;
-  TRY(h->xtiles.reserve((size_t)tiles * 2 * a.s.x_bytes()));
-  {
-    const int64_t slots = tiles * 256 * (a.s.K0 / 8);
-    const int grid = (int)((slots + 255) / 256 > 148 * 8 ? 148 * 8 : (slots + 255) / 256);
-    MOPO_COUNT_LAUNCH, panelize_kernel<<<grid, 256, 0, st>>>(xn, h->xtiles.as<uint4>(), (int)n_max, d_n, h->in, a.s.K0);
-    CUDA_TRY(cudaGetLastError());
-  }
   a.img = reinterpret_cast<const uint8_t*>(h->tc_img);
   a.xt = h->xtiles.as<uint8_t>();
-  a.max_lv = h->max_lv; a.min_lv = h->min_lv; a.mean = mean; a.lv = lv; a.ldb = ldb;
+  a.max_lv = h->max_lv; a.min_lv = h->min_lv;
+  a.mean = o.mean; a.lv = o.lv; a.ldb = o.ldb;
+  a.sel = o.sel; a.selm = o.selm; a.selv = o.selv; a.pen2 = o.pen2;
   a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E;
   a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
   const size_t smem = tc_smem_bytes(a.s);
@@ -533,4 +640,13 @@ int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, floa
   }
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
+}
+
+int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
+               int64_t ldb, cudaStream_t st) {
+  if (n_max == 0) return MOPO_OK;
+  TRY(tc_tiles_from_xn(h, xn, n_max, d_n, st));
+  TcOut o = {};
+  o.mean = mean; o.lv = lv; o.ldb = ldb;
+  return tc_launch(h, n_max, d_n, o, st);
 }

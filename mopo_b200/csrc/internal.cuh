@@ -67,6 +67,7 @@ struct mopo_ens {
 
   // scratch
   DevBuf xn, xtiles, actA, actB, mean, lv, blk_counts, misc;
+  DevBuf sel, selm, selv, pen2;    // fused-head step outputs
   DevBuf ro_obs[2], ro_origin[2], ro_counts;
 };
 
@@ -87,6 +88,19 @@ int tc_supported(const mopo_ens* h);
 int tc_build_images(mopo_ens* h, cudaStream_t st);
 int tc_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
                int64_t ldb, cudaStream_t st);
+// Pieces of the tensor-core step: input tiling (+ scaler + elite pick) into h->xtiles, then the forward kernel with
+// either the full [E,B,D1] outputs or the fused-head outputs (chosen net's mean/var + per-net variance sums).
+struct TcPrep {
+  const float *obs, *act; int64_t n_max; const int* d_n;
+  int32_t* sel; const int32_t* model_inds; uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
+};
+struct TcOut {
+  float *mean, *lv; int64_t ldb;                                   // full
+  const int32_t* sel; float *selm, *selv, *pen2;                   // fused (sel != nullptr); pen2 = [2, E, ldb]
+};
+int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st);
+int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st);
+int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaStream_t st);
 
 // ---- step tail / pool / compaction (tail.cu) ---------------------------------------------------
 struct TailArgs {
@@ -100,6 +114,8 @@ struct TailArgs {
   uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
   float *next_obs, *rewards; uint8_t* terminals;
   float *penalty, *unpenalized, *model_means, *model_stds, *log_prob, *dev; int32_t* model_inds_out;
+  // fused-head inputs (instead of mean / lv): chosen net, its mean / variance rows, per-net variance sums [2,E,ldb]
+  const int32_t* sel; const float *selm, *selv, *pen2;
   // optional pool append: row j -> (pool_base + *d_pool_off + j) % pool_max
   float *p_act, *p_rew, *p_obs, *p_nobs; uint8_t* p_term; int64_t pool_max, pool_base; const int64_t* d_pool_off;
   // optional compaction bookkeeping

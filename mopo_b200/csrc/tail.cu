@@ -52,7 +52,30 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
     const float* ob = a.obs + j * a.obs_dim;
     float smp[MOPO_MAX_D1];
     int m = 0;
-    if (!a.deterministic) {
+    float pen = 0.f;
+    if (a.sel) {
+      // fused-head step (stochastic, learned-variance or no penalty): the forward kernel kept only the chosen net's
+      // mean / variance row and each net's variance sum (fake_env.py:78-81,110)
+      m = a.sel[j];
+      const float* mm = a.selm + j * D1;
+      const float* vv = a.selv + j * D1;
+      float z[4];
+      for (int d = 0; d < D1; ++d) {
+        const float mu = mm[d] + (d ? ob[d - 1] : 0.0f);          // fake_env.py:66
+        const float sd = sqrtf(vv[d]);                             // fake_env.py:67
+        float zz;
+        if (a.noise) zz = a.noise[j * D1 + d];
+        else { if ((d & 3) == 0) philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(d >> 2), a.seed, z); zz = z[d & 3]; }
+        smp[d] = fmaf(zz, sd, mu);                                 // fake_env.py:72,79
+        if (a.model_means) a.model_means[j * D1 + d] = mu;
+        if (a.model_stds) a.model_stds[j * D1 + d] = sd;
+      }
+      if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
+        for (int e = 0; e < E; ++e)
+          pen = fmaxf(pen, a.pen2[(int64_t)e * a.ldb + j] + a.pen2[((int64_t)E + e) * a.ldb + j]);
+        pen = sqrtf(pen);                                          // max_e ||std_e||_2
+      }
+    } else if (!a.deterministic) {
       m = a.model_inds ? a.model_inds[j]
                        : a.elites[philox_elite(orow, (uint32_t)a.step_id, a.seed, (uint32_t)a.n_elites)];
       const float* mm = a.mean + ((int64_t)m * a.ldb + j) * D1;
@@ -82,8 +105,8 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
       m = -1;
     }
     // penalty (fake_env.py:97-115)
-    float pen = 0.f;
-    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
+    if (a.sel) {
+    } else if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
       for (int e = 0; e < E; ++e) {
         const float* ll = a.lv + ((int64_t)e * a.ldb + j) * D1;
         float s2 = 0.f;

@@ -1,0 +1,169 @@
+"""GPU parity tests of the tcgen05 (bf16 operands, fp32 accumulation) path against the oracle.
+
+BASELINE.json asks for rtol 1e-3 on the fp32 path and says "bf16 path reported separately": the bars here are
+the bf16 ones.  Activations are rounded to bf16 (rel 2^-9) at every layer, so errors are bounded relative to the
+SCALE of the outputs (normalised max error), not per element; integer / index results stay bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ensemble as ens
+from oracle.fake_env import FakeEnv as OracleEnv
+from oracle.static_fns import StaticFns as OracleStatic
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = {'halfcheetah': (17, 6), 'hopper': (11, 3), 'walker2d': (17, 6), 'ant': (27, 8)}
+BF16_NORM_ERR = 2e-2        # max |got - ref| / max |ref| per output array
+BF16_VAR_RTOL = 6e-2        # variances: exp() of a logvar carrying ~1e-2 absolute error
+
+
+@pytest.fixture(scope='module', autouse=True)
+def _built():
+    import __graft_entry__ as ge
+    ge.build()
+
+
+def make_model(p, precision):
+    from mopo_b200.models.constructor import construct_model
+    m = construct_model(obs_dim=p['obs_dim'], act_dim=p['act_dim'], hidden_dim=p['hidden_dim'],
+                        num_networks=p['num_networks'], separate_mean_var=p['separate_mean_var'], name='t', device=0,
+                        precision=precision)
+    m.set_params(p['weights'], p['biases'], p.get('var_weights'), p.get('var_biases'), p['mu'], p['sigma'],
+                 p['max_logvar'], p['min_logvar'])
+    m._model_inds = [0, 1, 2, 3, 4]
+    return m
+
+
+def norm_err(got, ref):
+    return float(np.abs(np.asarray(got, np.float64) - ref).max() / max(np.abs(ref).max(), 1e-12))
+
+
+@pytest.mark.parametrize('domain,B,sep', [('halfcheetah', 300, True), ('hopper', 1000, True), ('halfcheetah', 777, False),
+                                          ('walker2d', 5000, True), ('hopper', 1, True), ('hopper', 256, True)])
+def test_predict_bf16_matches_oracle(domain, B, sep):
+    """BNN.predict(factored=True) on the tensor-core path: ragged row counts (partial tiles, a single row, several
+    tiles per CTA pair), both head modes."""
+    from mopo_b200 import _lib
+    p, obs, act = ens.synthetic_case(domain, B, seed=11, separate_mean_var=sep)
+    x = np.concatenate([obs, act], -1)
+    m = make_model(p, _lib.PREC_BF16)
+    mean, var = m.predict(x, factored=True)
+    m64, v64 = ens.forward(p, x, np.float64)
+    assert mean.shape == m64.shape
+    assert np.isfinite(mean).all() and np.isfinite(var).all()
+    assert norm_err(mean, m64) < BF16_NORM_ERR
+    np.testing.assert_allclose(var, v64, rtol=BF16_VAR_RTOL)
+
+
+def test_bf16_unsupported_shape_raises():
+    """No silent fallback: a shape whose weights do not fit one CTA pair's shared memory raises (use PREC_FP32)."""
+    from mopo_b200 import _lib
+    p, obs, act = ens.synthetic_case('ant', 8, seed=1)
+    m = make_model(p, _lib.PREC_BF16)
+    with pytest.raises(NotImplementedError):
+        m.predict(np.concatenate([obs, act], -1), factored=True)
+
+
+def test_predict_bf16_close_to_fp32_path():
+    """Same weights through both device paths: the difference is bf16 rounding only."""
+    from mopo_b200 import _lib
+    p, obs, act = ens.synthetic_case('halfcheetah', 2048, seed=5)
+    x = np.concatenate([obs, act], -1)
+    a_mean, a_var = make_model(p, _lib.PREC_BF16).predict(x, factored=True)
+    b_mean, b_var = make_model(p, _lib.PREC_FP32).predict(x, factored=True)
+    assert norm_err(a_mean, b_mean.astype(np.float64)) < BF16_NORM_ERR
+    np.testing.assert_allclose(a_var, b_var, rtol=BF16_VAR_RTOL)
+
+
+@pytest.mark.parametrize('domain,B', [('halfcheetah', 1000), ('hopper', 513), ('walker2d', 300)])
+@pytest.mark.parametrize('diagnostics', [False, True])
+def test_step_bf16_matches_oracle(domain, B, diagnostics):
+    """FakeEnv.step on the tensor-core path with injected noise / elite indices: elite gather bit-exact; samples,
+    penalised reward and penalty within the bf16 bar.  diagnostics=False takes the fused-head path (only the elite
+    row and the per-net variance norms leave the SM), diagnostics=True the full [E,B,D1] path."""
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    import mopo_b200.static as static
+    od, ad = SHAPES[domain]
+    p, obs, act = ens.synthetic_case(domain, B, seed=9)
+    rng = np.random.RandomState(3)
+    noise = rng.standard_normal((7, B, od + 1))
+    inds = rng.choice(5, size=B)
+    o_env = OracleEnv(ens.OracleModel(p), OracleStatic(domain), penalty_coeff=1.0, penalty_learned_var=True)
+    r_nobs, r_rew, r_term, r_info = o_env.step(obs, act, noise=noise, model_inds=inds)
+    env = FakeEnv(make_model(p, _lib.PREC_BF16), static[domain], penalty_coeff=1.0, penalty_learned_var=True)
+    nobs, rew, term, info = env.step(obs, act, noise=noise, model_inds=inds, diagnostics=diagnostics)
+    assert (info['model_inds'] == inds).all()
+    assert norm_err(nobs, r_nobs) < BF16_NORM_ERR
+    assert norm_err(rew, r_rew) < BF16_NORM_ERR
+    np.testing.assert_allclose(info['penalty'], r_info['penalty'], rtol=BF16_VAR_RTOL)
+    # termination is a threshold test on next_obs: rows may flip only where the oracle's value sits within the bf16 error
+    flips = np.flatnonzero(term.ravel() != r_term.ravel())
+    if domain == 'halfcheetah':
+        assert flips.size == 0
+    else:
+        tol = BF16_NORM_ERR * np.abs(r_nobs).max()
+        thr = {'hopper': [(0, 0.7), (1, 0.2), (1, -0.2)], 'walker2d': [(0, 0.8), (0, 2.0), (1, -1.0), (1, 1.0)]}[domain]
+        for j in flips:
+            near = any(abs(r_nobs[j, c] - v) < tol for c, v in thr) or (np.abs(np.abs(r_nobs[j, 1:]) - 100) < tol).any()
+            assert near, (j, r_nobs[j, :2])
+
+
+def test_step_bf16_fused_equals_full_path():
+    """The fused-head step and the full-output step share the GEMMs: results must agree to fp32 rounding of the
+    variance algebra (var = e^min + 1/(e^-max + e^-raw) vs the soft-clamp chain)."""
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    import mopo_b200.static as static
+    p, obs, act = ens.synthetic_case('hopper', 2000, seed=2)
+    rng = np.random.RandomState(8)
+    noise = rng.standard_normal((2000, 12)).astype(np.float32)
+    inds = rng.choice(5, size=2000)
+    env = FakeEnv(make_model(p, _lib.PREC_BF16), static['hopper'], penalty_coeff=1.0, penalty_learned_var=True)
+    a = env.step(obs, act, noise=noise, model_inds=inds, diagnostics=False)
+    b = env.step(obs, act, noise=noise, model_inds=inds, diagnostics=True)
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(a[1], b[1], rtol=1e-4, atol=1e-5)
+    assert (a[2] == b[2]).all()
+    np.testing.assert_allclose(a[3]['penalty'], b[3]['penalty'], rtol=1e-4)
+
+
+def test_rollout_bf16_pool_indexing_exact():
+    """h-step device rollout on the tensor-core path (HalfCheetah: nothing terminates): steps_added, pointer, size
+    and row placement are exact; the ring wraps (max_size < B*h)."""
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    import mopo_b200.static as static
+    B, h, od, ad, max_size = 1500, 3, 17, 6, 4000
+    p, obs, _ = ens.synthetic_case('halfcheetah', B, seed=4)
+    rng = np.random.RandomState(6)
+    acts = [np.tanh(rng.standard_normal((B, ad))).astype(np.float32) for _ in range(h)]
+    env = FakeEnv(make_model(p, _lib.PREC_BF16), static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=1)
+    ro = ModelRollout(env, SimpleReplayPool(od, ad, 10), rollout_batch_size=B, rollout_schedule=(0, 1, h, h), seed=1)
+    ro._set_rollout_length()
+    ro._model_pool = SimpleReplayPool(od, ad, max_size)
+    ro._rollout_model(B, start_obs=obs, actions=acts, quiet=True)
+    assert ro._last_steps_added == [B] * h
+    pool = ro._model_pool
+    assert pool._pointer == (B * h) % max_size and pool.size == max_size
+    got = {k: v.cpu().numpy() for k, v in pool.fields.items()}
+    # row r of step i landed at (i*B + r) % max_size; the last write wins
+    for i in range(h):
+        for r in (0, 1, B // 2, B - 1):
+            idx = (i * B + r) % max_size
+            if (i * B + r) + max_size < B * h:
+                continue                                    # overwritten later
+            np.testing.assert_array_equal(got['actions'][idx], acts[i][r])
+            if i == 0:
+                np.testing.assert_array_equal(got['observations'][idx], obs[r])
+    # step i+1 observations == step i next_observations (mopo.py:750-758) where both survive in the ring
+    i = h - 2
+    rows = np.arange(B)
+    a_idx, b_idx = (i * B + rows) % max_size, ((i + 1) * B + rows) % max_size
+    keep = (i * B + rows) + max_size >= B * h
+    np.testing.assert_array_equal(got['next_observations'][a_idx[keep]], got['observations'][b_idx[keep]])
+    assert np.isfinite(got['rewards']).all() and not got['terminals'].any()
