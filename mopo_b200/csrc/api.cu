@@ -74,7 +74,7 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   for (int l = 0; l < MOPO_MAX_LAYERS; ++l) { if (h->W[l]) cudaFree(h->W[l]); if (h->b[l]) cudaFree(h->b[l]); }
   cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
   if (h->tc_img) cudaFree(h->tc_img);
-  DevBuf* bufs[] = {&h->sel, &h->selm, &h->selv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
+  DevBuf* bufs[] = {&h->sel, &h->selmv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
                     &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts};
   for (DevBuf* b : bufs) b->release();
   delete h;
@@ -169,12 +169,31 @@ MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* me
   return forward(h, precision, xn, B, nullptr, mean, logvar, B, (cudaStream_t)stream);
 }
 
+__global__ void fill_mod_kernel(int32_t* p, int64_t n, int m) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = (int32_t)(i % m);
+}
+
 MOPO_API int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar,
                                  unsigned long long* trace, void* stream) {
-  REQUIRE(h && xn && mean && logvar && trace && B > 0, MOPO_EINVAL, "mopo_debug_tc_trace: bad argument");
-  CUDA_TRY(cudaMemsetAsync(trace, 0, sizeof(unsigned long long) * 4 * 2048, (cudaStream_t)stream));
+  REQUIRE(h && xn && trace && B > 0, MOPO_EINVAL, "mopo_debug_tc_trace: bad argument");
+  REQUIRE(h->params_set && tc_supported(h), MOPO_ESTATE, "mopo_debug_tc_trace: tensor-core path unavailable");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemsetAsync(trace, 0, sizeof(unsigned long long) * 4 * 2048, st));
   h->tc_trace = trace;
-  int rc = mopo_ens_forward(h, xn, B, mean, logvar, MOPO_PREC_BF16, stream);
+  int rc;
+  if (mean && logvar) {
+    rc = mopo_ens_forward(h, xn, B, mean, logvar, MOPO_PREC_BF16, stream);
+  } else {                                       // fused-head mode: row i "chooses" net i % 5
+    rc = h->sel.reserve(sizeof(int32_t) * B);
+    if (!rc) rc = h->selmv.reserve(sizeof(float2) * B * h->D1);
+    if (!rc) rc = h->pen2.reserve(sizeof(float) * 2 * h->E * B);
+    if (!rc) { fill_mod_kernel<<<148, 256, 0, st>>>(h->sel.as<int32_t>(), B, 5); rc = tc_tiles_from_xn(h, xn, B, nullptr, st); }
+    if (!rc) {
+      TcOut o = {};
+      o.sel = h->sel.as<int32_t>(); o.selmv = h->selmv.as<float2>(); o.pen2 = h->pen2.as<float>(); o.ldb = B;
+      rc = tc_launch(h, B, nullptr, o, st);
+    }
+  }
   h->tc_trace = nullptr;
   return rc;
 }
@@ -212,12 +231,11 @@ static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_
     TcOut o = {};
     if (fused) {
       TRY(h->sel.reserve(sizeof(int32_t) * B));
-      TRY(h->selm.reserve(sizeof(float) * B * D1));
-      TRY(h->selv.reserve(sizeof(float) * B * D1));
+      TRY(h->selmv.reserve(sizeof(float2) * B * D1));
       TRY(h->pen2.reserve(sizeof(float) * 2 * E * B));
       q.sel = h->sel.as<int32_t>();
-      o.sel = q.sel; o.selm = h->selm.as<float>(); o.selv = h->selv.as<float>(); o.pen2 = h->pen2.as<float>(); o.ldb = B;
-      t->sel = o.sel; t->selm = o.selm; t->selv = o.selv; t->pen2 = o.pen2;
+      o.sel = q.sel; o.selmv = h->selmv.as<float2>(); o.pen2 = h->pen2.as<float>(); o.ldb = B;
+      t->sel = o.sel; t->selmv = o.selmv; t->pen2 = o.pen2;
     } else {
       TRY(h->mean.reserve(sizeof(float) * E * B * D1));
       TRY(h->lv.reserve(sizeof(float) * E * B * D1));

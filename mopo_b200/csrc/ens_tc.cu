@@ -209,8 +209,7 @@ struct TcArgs {
   int64_t ldb;
   // FUSED output (sel != nullptr): what FakeEnv.step keeps of the [E,B,D1] arrays (fake_env.py:78-81,110)
   const int32_t* sel;      // [n] net chosen for each row (the elite pick)
-  float* selm;             // [n, D1] mean of the chosen net
-  float* selv;             // [n, D1] variance of the chosen net
+  float2* selmv;           // [D1, ldb] (mean, variance) of the chosen net, dimension-major so that stores coalesce
   float* pen2;             // [2, E, ldb] sum_d var_d over each warpgroup's half of the output dims
   int n_max;
   const int* d_n;
@@ -306,17 +305,16 @@ __device__ __forceinline__ void epi_hidden(uint32_t tlane, uint8_t* ay_row) {
 //   =>  var = e^min + e^lv1 = e^min + 1 / (e^-max + e^-raw)                  (exp(softplus(y)) = 1 + e^y)
 // two MUFU ops per output dim instead of five.  sC[0][w*P+i] = e^min_d, sC[1][w*P+i] = e^-max_d for the dims of
 // warpgroup w (padding dims: 0 and +inf, so they contribute var = 0).
-// FUSED: pen2[w][e][row] = sum of var over this warpgroup's dims; rows whose chosen net is e also store mean / var.
+// FUSED: pen2[w][e][row] = sum of var over this warpgroup's dims; rows whose chosen net is e (`mine`, prefetched by the
+//        caller) also store (mean, var) to selmv[d][row].
 // FULL : mean[e][row][d], lv[e][row][d] = log(var).
 template <bool FUSED>
 __device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s, const float* sC, const TcArgs& a,
-                                         int e, int64_t row, bool valid) {
+                                         int e, int64_t row, bool valid, bool mine) {
   const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
   const int d0 = wg * dh, nd = wg ? s.D1 - dh : dh;
   const float* cmin = sC + wg * P;
   const float* cnmax = sC + MOPO_MAX_D1 + wg * P;
-  bool mine = false;
-  if (FUSED) mine = valid && a.sel[row] == e;
   float pen = 0.f;
   for (int c = 0; c < P / 4; ++c) {
     uint32_t mv[4], rv[4];
@@ -333,10 +331,7 @@ __device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s
       if (mine) {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          if (4 * c + i < nd) {
-            a.selm[row * s.D1 + d0 + 4 * c + i] = __uint_as_float(mv[i]);
-            a.selv[row * s.D1 + d0 + 4 * c + i] = var[i];
-          }
+          if (4 * c + i < nd) a.selmv[(int64_t)(d0 + 4 * c + i) * a.ldb + row] = make_float2(__uint_as_float(mv[i]), var[i]);
       }
     } else if (valid) {
       float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1 + d0;
@@ -412,8 +407,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   __syncthreads();
 
   // phase bookkeeping that survives net switches
-  uint32_t n_stage[2] = {0, 0};      // issuer: stages issued / epilogue: stages consumed, per tile slot
-  uint32_t n_x[2] = {0, 0};          // issuer / loader: input-slot uses
+  // (use counts packed 16 bits per tile slot: a per-slot array indexed by t would live in local memory)
+  uint32_t n_stage = 0;              // issuer: stages issued / epilogue: stages consumed
+  uint32_t n_x = 0;                  // issuer / loader: input-slot uses
+#define CNT(v, t) (((v) >> (16 * (t))) & 0xFFFFu)
+#define INC(v, t) ((v) += 1u << (16 * (t)))
   uint32_t seg = 0;
 
   for (int u = u0; u < u1; ++seg) {
@@ -442,15 +440,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
         for (int k = 0; k < n_super; ++k) {
           for (int t = 0; t < 2; ++t) {
             if (2 * k + t >= cnt) continue;
-            if (n_x[t] > 0) mbar_wait(&bars->x_free[t], (n_x[t] - 1) & 1);
+            if (CNT(n_x, t) > 0) mbar_wait(&bars->x_free[t], (CNT(n_x, t) - 1) & 1);
             TR(3, 70 + t);
             const int64_t blk = 2 * (int64_t)(t_lo + 2 * k + t) + rank;
             mbar_expect_tx(&bars->x_ld[t], (uint32_t)s.x_bytes());
             bulk_g2s(sX + t * s.x_bytes(), a.xt + blk * s.x_bytes(), (uint32_t)s.x_bytes(), &bars->x_ld[t]);
-            mbar_wait(&bars->x_ld[t], n_x[t] & 1);
+            mbar_wait(&bars->x_ld[t], CNT(n_x, t) & 1);
             mbar_arrive_remote(&bars->x_full[t], 0);
             TR(3, 72 + t);
-            ++n_x[t];
+            INC(n_x, t);
           }
         }
       }
@@ -465,8 +463,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
           for (int j = 0; j < 5; ++j) {
             for (int t = 0; t < 2; ++t) {
               if (2 * k + t >= cnt) continue;
-              if (j == 0) { mbar_wait_cluster(&bars->x_full[t], n_x[t] & 1); ++n_x[t]; }
-              if (n_stage[t] > 0) mbar_wait_cluster(&bars->a_ready[t], (n_stage[t] - 1) & 1);
+              if (j == 0) { mbar_wait_cluster(&bars->x_full[t], CNT(n_x, t) & 1); INC(n_x, t); }
+              if (CNT(n_stage, t) > 0) mbar_wait_cluster(&bars->a_ready[t], (CNT(n_stage, t) - 1) & 1);
               tc_fence_after();
               TR(0, 10 * j + t);
               const uint32_t d1 = tbase + (t == 0 ? C_XD1 : C_YD1), d2 = tbase + (t == 0 ? C_XD2 : C_YD2);
@@ -512,7 +510,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
                 mma_commit<2>(&bars->d_full[t]);
               }
               __syncwarp();
-              ++n_stage[t];
+              INC(n_stage, t);
             }
           }
         }
@@ -524,12 +522,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       const int rr = q * 32 + lane;                     // row inside this CTA's 128-row block
       uint8_t* ay_row = sAY + rr * 16;
       for (int k = 0; k < n_super; ++k) {
+        bool mine0 = false, mine1 = false;             // fused head: is net e the one this row keeps?  (prefetched)
+        if (a.sel) {
+          const int64_t row0 = 256 * (int64_t)(t_lo + 2 * k) + (int64_t)rank * 128 + rr;
+          if (row0 < n) mine0 = a.sel[row0] == e;
+          if (2 * k + 1 < cnt && row0 + 256 < n) mine1 = a.sel[row0 + 256] == e;
+        }
         for (int j = 0; j < 5; ++j) {
           for (int t = 0; t < 2; ++t) {
             if (2 * k + t >= cnt) continue;
             if (q == 0) TR(1 + wg, 100 + 10 * j + t);
-            mbar_wait(&bars->d_full[t], n_stage[t] & 1);
-            ++n_stage[t];
+            mbar_wait(&bars->d_full[t], CNT(n_stage, t) & 1);
+            INC(n_stage, t);
             tc_fence_after();
             if (q == 0) TR(1 + wg, 200 + 10 * j + t);
             if (j < 4) {
@@ -538,8 +542,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
             } else {
               const int64_t row = 256 * (int64_t)(t_lo + 2 * k + t) + (int64_t)rank * 128 + rr;
               const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1) + wg * (s.NHEAD / 2);
-              if (a.sel) epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n);
-              else epi_head<false>(tblk, wg, s, sLv, a, e, row, row < n);
+              if (a.sel) epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n, t == 0 ? mine0 : mine1);
+              else epi_head<false>(tblk, wg, s, sLv, a, e, row, row < n, false);
             }
             tc_fence_before();
             __syncwarp();
@@ -626,7 +630,7 @@ int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaSt
   a.xt = h->xtiles.as<uint8_t>();
   a.max_lv = h->max_lv; a.min_lv = h->min_lv;
   a.mean = o.mean; a.lv = o.lv; a.ldb = o.ldb;
-  a.sel = o.sel; a.selm = o.selm; a.selv = o.selv; a.pen2 = o.pen2;
+  a.sel = o.sel; a.selmv = o.selmv; a.pen2 = o.pen2;
   a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E;
   a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
   const size_t smem = tc_smem_bytes(a.s);

@@ -67,7 +67,7 @@ struct mopo_ens {
 
   // scratch
   DevBuf xn, xtiles, actA, actB, mean, lv, blk_counts, misc;
-  DevBuf sel, selm, selv, pen2;    // fused-head step outputs
+  DevBuf sel, selmv, pen2;         // fused-head step outputs
   DevBuf ro_obs[2], ro_origin[2], ro_counts;
 };
 
@@ -96,7 +96,7 @@ struct TcPrep {
 };
 struct TcOut {
   float *mean, *lv; int64_t ldb;                                   // full
-  const int32_t* sel; float *selm, *selv, *pen2;                   // fused (sel != nullptr); pen2 = [2, E, ldb]
+  const int32_t* sel; float2* selmv; float* pen2;                  // fused (sel != nullptr): selmv [D1, ldb], pen2 [2, E, ldb]
 };
 int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st);
 int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st);
@@ -114,8 +114,8 @@ struct TailArgs {
   uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
   float *next_obs, *rewards; uint8_t* terminals;
   float *penalty, *unpenalized, *model_means, *model_stds, *log_prob, *dev; int32_t* model_inds_out;
-  // fused-head inputs (instead of mean / lv): chosen net, its mean / variance rows, per-net variance sums [2,E,ldb]
-  const int32_t* sel; const float *selm, *selv, *pen2;
+  // fused-head inputs (instead of mean / lv): chosen net, its (mean, variance) [D1,ldb], per-net variance sums [2,E,ldb]
+  const int32_t* sel; const float2* selmv; const float* pen2;
   // optional pool append: row j -> (pool_base + *d_pool_off + j) % pool_max
   float *p_act, *p_rew, *p_obs, *p_nobs; uint8_t* p_term; int64_t pool_max, pool_base; const int64_t* d_pool_off;
   // optional compaction bookkeeping

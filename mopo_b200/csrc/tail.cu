@@ -57,12 +57,11 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
       // fused-head step (stochastic, learned-variance or no penalty): the forward kernel kept only the chosen net's
       // mean / variance row and each net's variance sum (fake_env.py:78-81,110)
       m = a.sel[j];
-      const float* mm = a.selm + j * D1;
-      const float* vv = a.selv + j * D1;
       float z[4];
       for (int d = 0; d < D1; ++d) {
-        const float mu = mm[d] + (d ? ob[d - 1] : 0.0f);          // fake_env.py:66
-        const float sd = sqrtf(vv[d]);                             // fake_env.py:67
+        const float2 mv = a.selmv[(int64_t)d * a.ldb + j];         // coalesced over the rows of the block
+        const float mu = mv.x + (d ? ob[d - 1] : 0.0f);            // fake_env.py:66
+        const float sd = sqrtf(mv.y);                              // fake_env.py:67
         float zz;
         if (a.noise) zz = a.noise[j * D1 + d];
         else { if ((d & 3) == 0) philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(d >> 2), a.seed, z); zz = z[d & 3]; }

@@ -37,8 +37,10 @@ xn = torch.randn(B, obs_dim + act_dim, device=dev)
 mean = torch.empty(7, B, obs_dim + 1, device=dev)
 lv = torch.empty_like(mean)
 trace = torch.zeros(4 * 2048, dtype=torch.int64, device=dev)
+fused = os.environ.get('TL_FUSED', '0') == '1'
+print('mode:', 'fused head' if fused else 'full outputs')
 for _ in range(2):
-    _lib.check(lib.mopo_debug_tc_trace(model._handle, xn.data_ptr(), B, mean.data_ptr(), lv.data_ptr(), trace.data_ptr(), st.cuda_stream))
+    _lib.check(lib.mopo_debug_tc_trace(model._handle, xn.data_ptr(), B, None if fused else mean.data_ptr(), None if fused else lv.data_ptr(), trace.data_ptr(), st.cuda_stream))
 torch.cuda.synchronize()
 t = trace.cpu().numpy().astype(np.uint64).reshape(4, 2048)
 ev = []
