@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 static thread_local char g_err[512] = "";
 
@@ -169,8 +170,8 @@ MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* me
   return forward(h, precision, xn, B, nullptr, mean, logvar, B, (cudaStream_t)stream);
 }
 
-__global__ void fill_mod_kernel(int32_t* p, int64_t n, int m) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = (int32_t)(i % m);
+__global__ void fill_mod_kernel(int32_t* p, int64_t n, int m) {   // m > 0: i % m ; m <= 0: the constant -m
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = m > 0 ? (int32_t)(i % m) : -m;
 }
 
 MOPO_API int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar,
@@ -187,7 +188,7 @@ MOPO_API int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float*
     rc = h->sel.reserve(sizeof(int32_t) * B);
     if (!rc) rc = h->selmv.reserve(sizeof(float2) * B * h->D1);
     if (!rc) rc = h->pen2.reserve(sizeof(float) * 2 * h->E * B);
-    if (!rc) { fill_mod_kernel<<<148, 256, 0, st>>>(h->sel.as<int32_t>(), B, 5); rc = tc_tiles_from_xn(h, xn, B, nullptr, st); }
+    if (!rc) { const char* md = getenv("MOPO_TRACE_SELMOD"); fill_mod_kernel<<<148, 256, 0, st>>>(h->sel.as<int32_t>(), B, md ? atoi(md) : 5); rc = tc_tiles_from_xn(h, xn, B, nullptr, st); }
     if (!rc) {
       TcOut o = {};
       o.sel = h->sel.as<int32_t>(); o.selmv = h->selmv.as<float2>(); o.pen2 = h->pen2.as<float>(); o.ldb = B;

@@ -344,6 +344,44 @@ __device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s
   if (FUSED && valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
 }
 
+// Fused head with the column count known at compile time (P = 4 * P4 columns per part): all tensor-memory loads are
+// issued before the first wait and the ex2 / rcp chains of the 4 * P4 dims overlap, instead of one 4-dim group at a time.
+template <int P4>
+__device__ __forceinline__ void epi_head_fused(uint32_t tblk, int wg, const TcShape& s, const float* sC, const TcArgs& a,
+                                               int e, int64_t row, bool valid, bool mine, uint64_t* done_bar, int lane) {
+  constexpr int P = 4 * P4;
+  const int dh = (s.D1 + 1) / 2;
+  const int d0 = wg * dh, nd = wg ? s.D1 - dh : dh;
+  const float* cmin = sC + wg * P;
+  const float* cnmax = sC + MOPO_MAX_D1 + wg * P;
+  uint32_t mv[P4][4], rv[P4][4];
+#pragma unroll
+  for (int c = 0; c < P4; ++c) { tmem_ld4(tblk + 4 * c, mv[c]); tmem_ld4(tblk + P + 4 * c, rv[c]); }
+  tmem_ld_wait();
+  // the accumulator is in registers: hand the columns back to the MMA warp NOW, before the global stores below
+  // (an arrive after them would carry release semantics over the stores and wait for their acknowledgement)
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive_remote(done_bar, 0);
+  float var[P4][4], pen = 0.f;
+#pragma unroll
+  for (int c = 0; c < P4; ++c)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      var[c][i] = cmin[4 * c + i] + __fdividef(1.0f, cnmax[4 * c + i] + __expf(-__uint_as_float(rv[c][i])));
+      pen += var[c][i];
+    }
+  if (valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
+  if (mine) {
+    float2* dst = a.selmv + (int64_t)d0 * a.ldb + row;
+#pragma unroll
+    for (int c = 0; c < P4; ++c)
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (4 * c + i < nd) dst[(int64_t)(4 * c + i) * a.ldb] = make_float2(__uint_as_float(mv[c][i]), var[c][i]);
+  }
+}
+
 constexpr int TRACE_CAP = 2048;   // events per role
 // timeline probe: role r (0 issuer, 1 epilogue WG0 warp 0, 2 epilogue WG1 warp 4, 3 loader) of pair 0 / leader CTA
 #define TR(role, tag)                                                                                   \
@@ -535,6 +573,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
             mbar_wait(&bars->d_full[t], CNT(n_stage, t) & 1);
             INC(n_stage, t);
             tc_fence_after();
+            bool arrived = false;
             if (q == 0) TR(1 + wg, 200 + 10 * j + t);
             if (j < 4) {
               if (t == 0) { if (wg == 0) epi_hidden<true, 0>(tlane, ay_row); else epi_hidden<true, 1>(tlane, ay_row); }
@@ -542,12 +581,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
             } else {
               const int64_t row = 256 * (int64_t)(t_lo + 2 * k + t) + (int64_t)rank * 128 + rr;
               const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1) + wg * (s.NHEAD / 2);
-              if (a.sel) epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n, t == 0 ? mine0 : mine1);
+              if (a.sel) {
+                const bool mine = t == 0 ? mine0 : mine1;
+                if (s.NHEAD == 48) { epi_head_fused<3>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane); arrived = true; }        // obs 17 (+1)
+                else if (s.NHEAD == 32) { epi_head_fused<2>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane); arrived = true; }   // obs 11 (+1)
+                else epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n, mine);
+              }
               else epi_head<false>(tblk, wg, s, sLv, a, e, row, row < n, false);
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_remote(&bars->a_ready[t], 0);
+            if (!arrived) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_remote(&bars->a_ready[t], 0);
+            }
             if (q == 0) TR(1 + wg, 300 + 10 * j + t);
           }
         }
