@@ -164,34 +164,59 @@ struct PrepArgs {
   uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
 };
 
-__global__ void prep_tiles_kernel(PrepArgs a) {
+// one CTA per 128-row block; rows go through shared memory so that global reads and the 16-byte tile writes coalesce
+__global__ void __launch_bounds__(128) prep_tiles_kernel(PrepArgs a) {
+  extern __shared__ float sIn[];                    // [128, in] scaled inputs
   const int n = a.d_n ? min(*a.d_n, a.n_max) : a.n_max;
-  const int in = a.obs_dim + a.act_dim, kcs = a.K0 / 8;
-  const int64_t slots = (int64_t)((n + 255) / 256) * 256 * kcs;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < slots; i += (int64_t)gridDim.x * blockDim.x) {
-    const int r = (int)(i % 128);
-    const int kc = (int)((i / 128) % kcs);
-    const int64_t row = (i / (128 * kcs)) * 128 + r;
-    uint32_t p[4] = {0, 0, 0, 0};
-    if (row < n) {
-      float v[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int k = kc * 8 + j;
-        if (k < in) {
-          const float x = k < a.obs_dim ? a.obs[row * a.obs_dim + k] : a.act[row * a.act_dim + (k - a.obs_dim)];
-          v[j] = (x - a.mu[k]) / a.sigma[k];
-        } else v[j] = k < in + 2 ? 1.f : 0.f;
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) p[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-      if (kc == 0 && a.sel) {
-        const uint32_t orow = a.origin ? (uint32_t)a.origin[row] : (uint32_t)(a.origin_base + row);
-        a.sel[row] = a.model_inds ? a.model_inds[row]
-                                  : a.elites[philox_elite(orow, (uint32_t)a.step_id, a.seed, (uint32_t)a.n_elites)];
-      }
+  const int od = a.obs_dim, ad = a.act_dim, in = od + ad, kcs = a.K0 / 8;
+  const int n_blocks = ((n + 255) / 256) * 2;
+  const int tid = threadIdx.x;
+  float* sMu = sIn + 128 * in;            // [in]
+  float* sSg = sMu + in;                  // [in]
+  for (int i = tid; i < in; i += 128) { sMu[i] = a.mu[i]; sSg[i] = a.sigma[i]; }
+  for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+    const int64_t j0 = (int64_t)blk * 128;
+    const int rows = (int)max((int64_t)0, min((int64_t)128, n - j0));
+    __syncthreads();
+    // raw rows -> smem (flat contiguous spans, loads batched in flight); the scaler is applied on the way out
+    float* sObs = sIn;                      // [128, od]
+    float* sAct = sIn + 128 * od;           // [128, ad]
+    {
+      const float* go = a.obs + j0 * od;
+      const float* ga = a.act + j0 * ad;
+#pragma unroll 8
+      for (int i = tid; i < rows * od; i += 128) sObs[i] = go[i];
+#pragma unroll 4
+      for (int i = tid; i < rows * ad; i += 128) sAct[i] = ga[i];
     }
-    a.xt[i] = make_uint4(p[0], p[1], p[2], p[3]);
+    __syncthreads();
+    const bool ok = tid < rows;
+    for (int kc = 0; kc < kcs; ++kc) {
+      uint32_t p[4] = {0, 0, 0, 0};
+      if (ok) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int k0 = kc * 8 + 2 * q, k1 = k0 + 1;
+          float v[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int k = u ? k1 : k0;
+            if (k < in) {
+              const float x = k < od ? sObs[tid * od + k] : sAct[tid * ad + (k - od)];
+              v[u] = (x - sMu[k]) / sSg[k];                                          // models/utils.py:96
+            } else v[u] = k < in + 2 ? 1.f : 0.f;
+          }
+          p[q] = pack_bf16x2(v[0], v[1]);
+        }
+      }
+      a.xt[((int64_t)blk * kcs + kc) * 128 + tid] = make_uint4(p[0], p[1], p[2], p[3]);
+    }
+    if (ok && a.sel) {
+      const int64_t row = j0 + tid;
+      const uint32_t orow = a.origin ? (uint32_t)a.origin[row] : (uint32_t)(a.origin_base + row);
+      a.sel[row] = a.model_inds ? a.model_inds[row]
+                                : a.elites[philox_elite(orow, (uint32_t)a.step_id, a.seed, (uint32_t)a.n_elites)];
+    }
   }
 }
 
@@ -662,7 +687,9 @@ int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st) {
   a.n_max = (int)q.n_max; a.d_n = q.d_n; a.obs_dim = h->cfg.obs_dim; a.act_dim = h->cfg.act_dim; a.K0 = s.K0;
   a.sel = q.sel; a.model_inds = q.model_inds; a.elites = h->elites; a.n_elites = h->n_elites;
   a.seed = q.seed; a.step_id = q.step_id; a.origin = q.origin; a.origin_base = q.origin_base;
-  MOPO_COUNT_LAUNCH, prep_tiles_kernel<<<grid, 256, 0, st>>>(a);
+  const int64_t blocks = ((q.n_max + 255) / 256) * 2;
+  (void)grid;
+  MOPO_COUNT_LAUNCH, prep_tiles_kernel<<<(int)(blocks > 148 * 16 ? 148 * 16 : blocks), 128, sizeof(float) * (128 + 2) * h->in, st>>>(a);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }

@@ -53,28 +53,7 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
     float smp[MOPO_MAX_D1];
     int m = 0;
     float pen = 0.f;
-    if (a.sel) {
-      // fused-head step (stochastic, learned-variance or no penalty): the forward kernel kept only the chosen net's
-      // mean / variance row and each net's variance sum (fake_env.py:78-81,110)
-      m = a.sel[j];
-      float z[4];
-      for (int d = 0; d < D1; ++d) {
-        const float2 mv = a.selmv[(int64_t)d * a.ldb + j];         // coalesced over the rows of the block
-        const float mu = mv.x + (d ? ob[d - 1] : 0.0f);            // fake_env.py:66
-        const float sd = sqrtf(mv.y);                              // fake_env.py:67
-        float zz;
-        if (a.noise) zz = a.noise[j * D1 + d];
-        else { if ((d & 3) == 0) philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(d >> 2), a.seed, z); zz = z[d & 3]; }
-        smp[d] = fmaf(zz, sd, mu);                                 // fake_env.py:72,79
-        if (a.model_means) a.model_means[j * D1 + d] = mu;
-        if (a.model_stds) a.model_stds[j * D1 + d] = sd;
-      }
-      if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
-        for (int e = 0; e < E; ++e)
-          pen = fmaxf(pen, a.pen2[(int64_t)e * a.ldb + j] + a.pen2[((int64_t)E + e) * a.ldb + j]);
-        pen = sqrtf(pen);                                          // max_e ||std_e||_2
-      }
-    } else if (!a.deterministic) {
+    if (!a.deterministic) {
       m = a.model_inds ? a.model_inds[j]
                        : a.elites[philox_elite(orow, (uint32_t)a.step_id, a.seed, (uint32_t)a.n_elites)];
       const float* mm = a.mean + ((int64_t)m * a.ldb + j) * D1;
@@ -104,8 +83,7 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
       m = -1;
     }
     // penalty (fake_env.py:97-115)
-    if (a.sel) {
-    } else if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
+    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
       for (int e = 0; e < E; ++e) {
         const float* ll = a.lv + ((int64_t)e * a.ldb + j) * D1;
         float s2 = 0.f;
@@ -177,6 +155,118 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
   if (a.blk_counts) {
     int c = __syncthreads_count(alive);
     if (threadIdx.x == 0) a.blk_counts[blockIdx.x] = c;
+  }
+}
+
+// Fused-head step tail (stochastic step, learned-variance or no penalty; tensor-core path): the forward kernel kept
+// only the chosen net's (mean, variance) per output dim [D1, ldb] and each net's variance sums [2, E, ldb]
+// (fake_env.py:78-81,110).  One thread per row for the arithmetic; the row-major obs / act / next_obs / pool traffic
+// goes through shared memory so that every global access of the block is a contiguous span.
+__global__ void __launch_bounds__(TAIL_ROWS) step_tail_fused_kernel(TailArgs a) {
+  extern __shared__ float sm[];
+  const int od = a.obs_dim, ad = a.act_dim, D1 = a.D1, E = a.E;
+  float* sObs = sm;                       // [TAIL_ROWS, od]
+  float* sNobs = sObs + TAIL_ROWS * od;   // [TAIL_ROWS, od]
+  float* sAct = sNobs + TAIL_ROWS * od;   // [TAIL_ROWS, ad]
+  const int64_t n = a.d_n ? min((int64_t)*a.d_n, a.n_max) : a.n_max;
+  const int64_t j0 = (int64_t)blockIdx.x * TAIL_ROWS;
+  const int rows = (int)max((int64_t)0, min((int64_t)TAIL_ROWS, n - j0));
+  const int tid = threadIdx.x;
+  // the block's rows are one contiguous span of each row-major array: flat, unrolled copies (loads batched in flight)
+  {
+    const float* go = a.obs + j0 * od;
+    const float* ga = a.act + j0 * ad;
+#pragma unroll 8
+    for (int i = tid; i < rows * od; i += TAIL_ROWS) sObs[i] = go[i];
+#pragma unroll 4
+    for (int i = tid; i < rows * ad; i += TAIL_ROWS) sAct[i] = ga[i];
+  }
+  __syncthreads();
+  const int64_t j = j0 + tid;
+  bool alive = false;
+  if (tid < rows) {
+    const uint32_t orow = a.origin ? (uint32_t)a.origin[j] : (uint32_t)(a.origin_base + j);
+    const float* ob = sObs + tid * od;
+    float* nob = sNobs + tid * od;
+    float unpen = 0.f, z[4];
+    float pen = 0.f;
+    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {                  // max_e ||std_e||_2  (fake_env.py:110)
+#pragma unroll 8
+      for (int e = 0; e < E; ++e)
+        pen = fmaxf(pen, a.pen2[(int64_t)e * a.ldb + j] + a.pen2[((int64_t)E + e) * a.ldb + j]);
+      pen = sqrtf(pen);
+    }
+    for (int g = 0; g < D1; g += 4) {                              // 4 output dims per Philox block
+      float2 mv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) mv[u] = g + u < D1 ? a.selmv[(int64_t)(g + u) * a.ldb + j] : make_float2(0.f, 0.f);
+      if (a.noise) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) z[u] = g + u < D1 ? a.noise[j * D1 + g + u] : 0.f;
+      } else philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(g >> 2), a.seed, z);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int d = g + u;
+        if (d < D1) {
+          const float mu = mv[u].x + (d ? ob[d - 1] : 0.0f);       // fake_env.py:66
+          const float sd = sqrtf(mv[u].y);                         // fake_env.py:67
+          const float smp = fmaf(z[u], sd, mu);                    // fake_env.py:72,79
+          if (d == 0) unpen = smp; else nob[d - 1] = smp;          // fake_env.py:90
+          if (a.model_means) a.model_means[j * D1 + d] = mu;
+          if (a.model_stds) a.model_stds[j * D1 + d] = sd;
+        }
+      }
+    }
+    const bool term = term_fn(a.term_kind, nob - 1, od);           // fake_env.py:91 (term_fn skips the reward slot)
+    alive = !term;
+    const float rew = (a.penalty_kind == MOPO_PEN_NONE) ? unpen : unpen - a.coeff * pen;   // fake_env.py:115
+    if (a.rewards) a.rewards[j] = rew;
+    if (a.terminals) a.terminals[j] = term ? 1 : 0;
+    if (a.penalty) a.penalty[j] = pen;
+    if (a.unpenalized) a.unpenalized[j] = unpen;
+    if (a.model_inds_out) a.model_inds_out[j] = a.sel[j];
+    if (a.p_obs && (n - j) <= a.pool_max) {                        // flexible_replay_pool.py:57-83, last write wins
+      const int64_t off = a.d_pool_off ? *a.d_pool_off : 0;
+      const int64_t r = (a.pool_base + off + j) % a.pool_max;
+      a.p_rew[r] = rew;
+      a.p_term[r] = term ? 1 : 0;
+    }
+  }
+  __syncthreads();
+  if (a.next_obs) {
+    float* gn = a.next_obs + j0 * od;
+#pragma unroll 8
+    for (int i = tid; i < rows * od; i += TAIL_ROWS) gn[i] = sNobs[i];
+  }
+  if (a.p_obs) {
+    const int64_t off = a.d_pool_off ? *a.d_pool_off : 0;
+    const int64_t pr0 = (a.pool_base + off + j0) % a.pool_max;
+    if (n - j0 <= a.pool_max && pr0 + rows <= a.pool_max) {        // common case: no wrap, nothing skipped -> flat copies
+      float* po = a.p_obs + pr0 * od;
+      float* pn = a.p_nobs + pr0 * od;
+      float* pa = a.p_act + pr0 * ad;
+#pragma unroll 8
+      for (int i = tid; i < rows * od; i += TAIL_ROWS) { po[i] = sObs[i]; pn[i] = sNobs[i]; }
+#pragma unroll 4
+      for (int i = tid; i < rows * ad; i += TAIL_ROWS) pa[i] = sAct[i];
+    } else {
+    for (int i = tid; i < rows * od; i += TAIL_ROWS) {
+      const int r = i / od, c = i - r * od;
+      if ((n - (j0 + r)) <= a.pool_max) {
+        const int64_t pr = (a.pool_base + off + j0 + r) % a.pool_max;
+        a.p_obs[pr * od + c] = sObs[i];
+        a.p_nobs[pr * od + c] = sNobs[i];
+      }
+    }
+    for (int i = tid; i < rows * ad; i += TAIL_ROWS) {
+      const int r = i / ad, c = i - r * ad;
+      if ((n - (j0 + r)) <= a.pool_max) a.p_act[((a.pool_base + off + j0 + r) % a.pool_max) * ad + c] = sAct[i];
+    }
+    }
+  }
+  if (a.blk_counts) {
+    int c = __syncthreads_count(alive);
+    if (tid == 0) a.blk_counts[blockIdx.x] = c;
   }
 }
 
@@ -258,7 +348,12 @@ int launch_prep(const float* obs, const float* act, const float* mu, const float
 int launch_tail(const TailArgs& a, cudaStream_t st) {
   if (a.n_max == 0) return MOPO_OK;
   int grid = (int)((a.n_max + TAIL_ROWS - 1) / TAIL_ROWS);
-  MOPO_COUNT_LAUNCH, step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
+  if (a.sel) {
+    const size_t smem = sizeof(float) * TAIL_ROWS * (2 * a.obs_dim + a.act_dim);
+    MOPO_COUNT_LAUNCH, step_tail_fused_kernel<<<grid, TAIL_ROWS, smem, st>>>(a);
+  } else {
+    MOPO_COUNT_LAUNCH, step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
+  }
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }

@@ -167,3 +167,25 @@ def test_rollout_bf16_pool_indexing_exact():
     keep = (i * B + rows) + max_size >= B * h
     np.testing.assert_array_equal(got['next_observations'][a_idx[keep]], got['observations'][b_idx[keep]])
     assert np.isfinite(got['rewards']).all() and not got['terminals'].any()
+
+
+@pytest.mark.parametrize('precision_name', ['bf16', 'fp32'])
+def test_device_rng_matches_oracle_philox(precision_name):
+    """Philox mode (no injected randomness): the per-row elite pick equals oracle/philox.py bit for bit, and the normal
+    draw recovered from (next_obs - mean) / std matches the oracle's Box-Muller normals."""
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    import mopo_b200.static as static
+    from oracle import philox
+    B, seed = 3000, 0x1234567
+    p, obs, act = ens.synthetic_case('halfcheetah', B, seed=12)
+    prec = {'bf16': _lib.PREC_BF16, 'fp32': _lib.PREC_FP32}[precision_name]
+    env = FakeEnv(make_model(p, prec), static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=seed)
+    for step in range(2):
+        nobs, rew, term, info = env.step(obs, act, diagnostics=False)
+        want_e = np.array([0, 1, 2, 3, 4])[philox.elite_index(np.arange(B), step, seed, 5)]
+        assert (info['model_inds'] == want_e).all()
+        mu, sd = info['mean'], info['std']                     # [rew, terminal, obs...] layout (fake_env.py:94-95)
+        z = (nobs - mu[:, 2:]) / sd[:, 2:]
+        want_z = philox.normals(np.arange(B), step, seed, 18)[:, 1:]
+        np.testing.assert_allclose(z, want_z, atol=2e-3)

@@ -110,3 +110,24 @@ def test_rollout_invariants():
         nxt = pool.fields['next_observations'][:steps[0]]
         keep = ~pool.fields['terminals'][:steps[0], 0]
         assert np.array_equal(pool.fields['observations'][steps[0]:steps[0] + steps[1]], nxt[keep])
+
+
+def test_philox_known_answers():
+    """Philox4x32-10 known-answer vectors (Random123 kat_vectors): pins oracle/philox.py, which pins the device RNG."""
+    from oracle import philox
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff, 0xffffffff), (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        got = philox.philox4x32_10(*[np.array([c], np.uint32) for c in ctr], key[0], key[1])
+        assert tuple(int(g[0]) for g in got) == want
+
+
+def test_philox_streams_statistics():
+    from oracle import philox
+    rows = np.arange(200000)
+    z = philox.normals(rows, 3, 12345, 18)
+    assert abs(z.mean()) < 5e-3 and abs(z.std() - 1) < 5e-3
+    e = philox.elite_index(rows, 3, 12345, 5)
+    assert e.min() == 0 and e.max() == 4
+    assert np.abs(np.bincount(e, minlength=5) / len(rows) - 0.2).max() < 5e-3
