@@ -240,7 +240,17 @@ def run_ours(args):
         ro._rollout_model(B, start_obs=d_obs, actions=d_acts, origin_base=rank * B, quiet=True)
         return sum(ro._last_steps_added)
 
-    ms, trans, launches, clocks = timed(rollout_resident, args.steps, args.warmup, sample_clocks=True)
+    import ctypes as C
+    kt_ms, kt_n = C.c_double(0), C.c_int64(0)
+    use_kt = prec == _lib.PREC_BF16
+    for _ in range(args.warmup):
+        rollout_resident()
+    if use_kt:
+        _lib.check(lib.mopo_kernel_timing(model._handle, 1))       # CUDA events around every forward launch of the timed rollouts
+    ms, trans, launches, clocks = timed(rollout_resident, args.steps, 0, sample_clocks=True)
+    if use_kt:
+        _lib.check(lib.mopo_kernel_time(model._handle, C.byref(kt_ms), C.byref(kt_n)))
+        _lib.check(lib.mopo_kernel_timing(model._handle, 0))
     ms_max = mdist.max_over_ranks(ms, device=dev)
     tot = torch.tensor([float(trans)], dtype=torch.float64, device=dev)
     if world > 1:
@@ -266,24 +276,38 @@ def run_ours(args):
         torch.distributed.all_reduce(tot_e)
     e2e_value = float(tot_e.item()) / (ms_e_max * 1e-3)
 
-    # roofline: the ensemble-forward kernel alone on B rows, CUDA events on the launching stream
-    xn = torch.randn(B, obs_dim + act_dim, device=dev)
-    mean = torch.empty(E, B, obs_dim + 1, device=dev)
-    lv = torch.empty_like(mean)
-
-    def fwd():
-        _lib.check(lib.mopo_ens_forward(model._handle, xn.data_ptr(), B, mean.data_ptr(), lv.data_ptr(), prec, stream.cuda_stream))
-        return B
-    ms_f, _, fwd_launches, _ = timed(fwd, max(args.steps, 10), 3)
-    ms_f /= max(args.steps, 10)
+    # roofline of the dominant kernel (the tcgen05 ensemble forward): algorithmic FLOPs of the rows one launch processes
+    # / its average launch duration, measured with CUDA events around every launch INSIDE the timed rollouts above
     burst, sustained, hbm, src = peaks()
-    fl = flop_per_transition(obs_dim, act_dim) * B
-    achieved = fl / (ms_f * 1e-3) / 1e12
-    roofline = {'bound': 'tensor', 'achieved': achieved, 'peak': burst, 'unit': 'TFLOP/s', 'frac': achieved / burst,
-                'traffic': None, 'kernel': 'ensemble forward (%s), %d rows/launch, %d launch(es)' % (args.precision, B, fwd_launches // max(args.steps, 10)),
-                'kernel_ms': ms_f, 'peak_source': '%s bf16 burst (kernel timed alone); sustained %.1f' % (src, sustained),
-                'frac_of_rollout_time': (ms_f * h) / (ms / args.steps) if args.workload == 'halfcheetah' else None,
-                'rollout_frac_of_sustained': value / world * flop_per_transition(obs_dim, act_dim) / 1e12 / sustained}
+    fpt = flop_per_transition(obs_dim, act_dim)
+    if use_kt and kt_n.value > 0:
+        ms_f = kt_ms.value / kt_n.value
+        rows_per_launch = trans / kt_n.value
+        where = 'timed inside the rollout (%d launches, CUDA events on the launching stream)' % kt_n.value
+    else:                                               # fp32 path: one launch per layer -> time the whole forward call alone
+        xn = torch.randn(B, obs_dim + act_dim, device=dev)
+        mean = torch.empty(E, B, obs_dim + 1, device=dev)
+        lv = torch.empty_like(mean)
+
+        def fwd():
+            _lib.check(lib.mopo_ens_forward(model._handle, xn.data_ptr(), B, mean.data_ptr(), lv.data_ptr(), prec, stream.cuda_stream))
+            return B
+        ms_f, _, _, _ = timed(fwd, max(args.steps, 10), 3)
+        ms_f /= max(args.steps, 10)
+        rows_per_launch = B
+        where = 'forward call timed alone'
+    achieved = fpt * rows_per_launch / (ms_f * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, 'profiles', 'roofline_traffic.json')
+    if os.path.exists(tpath) and use_kt:
+        traffic = json.load(open(tpath)).get('dram_bytes_per_launch')
+    roofline = {'bound': 'tensor', 'achieved': achieved, 'peak': sustained, 'unit': 'TFLOP/s', 'frac': achieved / sustained,
+                'traffic': traffic,
+                'kernel': 'ens_tc_kernel (tcgen05 ensemble forward + fused head, %s), %d rows/launch; %s' % (args.precision, rows_per_launch, where),
+                'kernel_ms': ms_f, 'flop_per_transition': fpt,
+                'peak_source': '%s bf16 sustained (kernel timed inside a long step); burst %.1f -> frac %.3f' % (src, burst, achieved / burst),
+                'kernel_share_of_step': (ms_f * (kt_n.value if use_kt and kt_n.value else h * args.steps)) / ms,
+                'rollout_frac_of_sustained': value / world * fpt / 1e12 / sustained}
 
     if rank != 0:
         return

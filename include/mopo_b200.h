@@ -177,6 +177,14 @@ typedef struct {
  * rows to the pool in the reference's order, then synchronises once to read the counts back. */
 int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream);
 
+/* ---- measurement ------------------------------------------------------------------------------- */
+/* CUDA-event timing of the ensemble-forward kernel (the dominant kernel of a step) as it runs inside
+ * mopo_env_step / mopo_rollout: events are recorded on the launching stream around each launch.
+ * mopo_kernel_timing(h, 1) starts and clears collection, mopo_kernel_time returns the summed milliseconds and the
+ * number of launches since then (synchronising on the events) and clears. bench.py's roofline uses it. */
+int mopo_kernel_timing(mopo_ens* h, int enable);
+int mopo_kernel_time(mopo_ens* h, double* ms_total, int64_t* launches);
+
 /* ---- debug ---------------------------------------------------------------------------------- */
 /* tcgen05 known-answer probe: D[M,N] = A[M,K] * B[N,K]^T (bf16 bit patterns in, fp32 out; device pointers),
  * cta_group 1|2, A operand from shared memory (0) or tensor memory (1).  Used by tests/test_gpu_umma.py. */

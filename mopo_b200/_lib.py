@@ -73,6 +73,8 @@ SYMBOLS = {
     'mopo_debug_tc_trace': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mopo_debug_pipe_bench': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_debug_mma_rate': (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    'mopo_kernel_timing': (C.c_int, [C.c_void_p, C.c_int]),
+    'mopo_kernel_time': (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
 }
 

@@ -75,6 +75,7 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   for (int l = 0; l < MOPO_MAX_LAYERS; ++l) { if (h->W[l]) cudaFree(h->W[l]); if (h->b[l]) cudaFree(h->b[l]); }
   cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
   if (h->tc_img) cudaFree(h->tc_img);
+  for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
   DevBuf* bufs[] = {&h->sel, &h->selmv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
                     &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts};
   for (DevBuf* b : bufs) b->release();
@@ -168,6 +169,29 @@ MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* me
   if (B == 0) return MOPO_OK;
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   return forward(h, precision, xn, B, nullptr, mean, logvar, B, (cudaStream_t)stream);
+}
+
+// Per-launch device timing of the ensemble-forward kernel as it runs inside steps / rollouts: CUDA events recorded
+// on the launching stream right around each launch.  enable != 0 starts (and clears) collection; the query
+// synchronises the events, returns the summed milliseconds and the number of launches, and clears.
+MOPO_API int mopo_kernel_timing(mopo_ens* h, int enable) {
+  REQUIRE(h, MOPO_EINVAL, "mopo_kernel_timing: null handle");
+  h->timing = enable != 0;
+  h->ev_used = 0;
+  return MOPO_OK;
+}
+MOPO_API int mopo_kernel_time(mopo_ens* h, double* ms_total, int64_t* launches) {
+  REQUIRE(h && ms_total && launches, MOPO_EINVAL, "mopo_kernel_time: null argument");
+  double tot = 0;
+  for (size_t i = 0; i + 1 < h->ev_used; i += 2) {
+    CUDA_TRY(cudaEventSynchronize(h->ev[i + 1]));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+    tot += ms;
+  }
+  *ms_total = tot; *launches = (int64_t)(h->ev_used / 2);
+  h->ev_used = 0;
+  return MOPO_OK;
 }
 
 __global__ void fill_mod_kernel(int32_t* p, int64_t n, int m) {   // m > 0: i % m ; m <= 0: the constant -m

@@ -708,6 +708,14 @@ int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaSt
   a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
   const size_t smem = tc_smem_bytes(a.s);
   const int n_pairs = h->sm_count / 2;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  if (h->timing) {
+    if (h->ev_used + 2 > h->ev.size()) {
+      for (int i = 0; i < 2; ++i) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); h->ev.push_back(e); }
+    }
+    ev0 = h->ev[h->ev_used]; ev1 = h->ev[h->ev_used + 1]; h->ev_used += 2;
+    CUDA_TRY(cudaEventRecord(ev0, st));
+  }
   if (a.trace) {
     CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     MOPO_COUNT_LAUNCH, ens_tc_kernel<true><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
@@ -715,6 +723,7 @@ int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaSt
     CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     MOPO_COUNT_LAUNCH, ens_tc_kernel<false><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
   }
+  if (ev1) CUDA_TRY(cudaEventRecord(ev1, st));
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }

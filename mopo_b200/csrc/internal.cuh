@@ -63,6 +63,10 @@ struct mopo_ens {
   // bf16 UMMA-ready images for the tcgen05 path (built by tc_build_images).
   void* tc_img = nullptr;
   size_t tc_img_bytes = 0;
+  // per-launch CUDA-event timing of the forward kernel (mopo_kernel_timing): events on the launching stream
+  bool timing = false;
+  std::vector<cudaEvent_t> ev;      // start/stop pairs of the launches since the last query
+  size_t ev_used = 0;
   void* tc_trace = nullptr;         // device uint64[4][2048] timeline buffer while mopo_debug_tc_trace runs
 
   // scratch
