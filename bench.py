@@ -159,6 +159,8 @@ def run_reference(args):
 # our arm
 # --------------------------------------------------------------------------------------------------
 def run_ours(args):
+    if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
+        os.environ['NCCL_DEBUG'] = 'WARN'          # keep stdout to the ONE json line (NCCL prints its version banner there)
     import torch
     from mopo_b200 import _lib, dist as mdist
     import __graft_entry__ as ge
