@@ -371,9 +371,9 @@ __device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s
 
 // Fused head with the column count known at compile time (P = 4 * P4 columns per part): all tensor-memory loads are
 // issued before the first wait and the ex2 / rcp chains of the 4 * P4 dims overlap, instead of one 4-dim group at a time.
-template <int P4>
+template <int P4, class TRF>
 __device__ __forceinline__ void epi_head_fused(uint32_t tblk, int wg, const TcShape& s, const float* sC, const TcArgs& a,
-                                               int e, int64_t row, bool valid, bool mine, uint64_t* done_bar, int lane) {
+                                               int e, int64_t row, bool valid, bool mine, uint64_t* done_bar, int lane, TRF&& tr) {
   constexpr int P = 4 * P4;
   const int dh = (s.D1 + 1) / 2;
   const int d0 = wg * dh, nd = wg ? s.D1 - dh : dh;
@@ -383,11 +383,13 @@ __device__ __forceinline__ void epi_head_fused(uint32_t tblk, int wg, const TcSh
 #pragma unroll
   for (int c = 0; c < P4; ++c) { tmem_ld4(tblk + 4 * c, mv[c]); tmem_ld4(tblk + P + 4 * c, rv[c]); }
   tmem_ld_wait();
+  tr(400);
   // the accumulator is in registers: hand the columns back to the MMA warp NOW, before the global stores below
   // (an arrive after them would carry release semantics over the stores and wait for their acknowledgement)
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive_remote(done_bar, 0);
+  tr(401);
   float var[P4][4], pen = 0.f;
 #pragma unroll
   for (int c = 0; c < P4; ++c)
@@ -397,6 +399,7 @@ __device__ __forceinline__ void epi_head_fused(uint32_t tblk, int wg, const TcSh
       pen += var[c][i];
     }
   if (valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
+  tr(402);
   if (mine) {
     float2* dst = a.selmv + (int64_t)d0 * a.ldb + row;
 #pragma unroll
@@ -608,8 +611,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
               const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1) + wg * (s.NHEAD / 2);
               if (a.sel) {
                 const bool mine = t == 0 ? mine0 : mine1;
-                if (s.NHEAD == 48) { epi_head_fused<3>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane); arrived = true; }        // obs 17 (+1)
-                else if (s.NHEAD == 32) { epi_head_fused<2>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane); arrived = true; }   // obs 11 (+1)
+                auto tr = [&](int tag) { if (q == 0) TR(1 + wg, tag); };
+                if (s.NHEAD == 48) { epi_head_fused<3>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane, tr); arrived = true; }        // obs 17 (+1)
+                else if (s.NHEAD == 32) { epi_head_fused<2>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane, tr); arrived = true; }   // obs 11 (+1)
                 else epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n, mine);
               }
               else epi_head<false>(tblk, wg, s, sLv, a, e, row, row < n, false);
