@@ -192,7 +192,7 @@ int mopo_debug_umma_probe(int cta_group, int a_in_tmem, const uint16_t* A, const
                           int M, int N, int K, void* stream);
 
 /* Timeline probe of the tcgen05 forward: runs mopo_ens_forward(bf16) once with per-role clock64 stamps of CTA
- * pair 0; trace = device uint64[4*2048] (role-major: 0 MMA issuer, 1/2 epilogue warpgroups, 3 input loader),
+ * pair 0; trace = device uint64[5*2048] (role-major: 0 MMA issuer, 1/2 hidden-epilogue warpgroups, 3 input loader, 4 head warps),
  * entry = tag << 48 | clock.  tools/tc_timeline.py decodes it. */
 int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar,
                         unsigned long long* trace, void* stream);

@@ -29,7 +29,7 @@ def needs_build():
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
-    flags = [f for f in NVCC_FLAGS if not f.startswith('--use_fast_math')]
+    flags = [f for f in NVCC_FLAGS if not f.startswith('--use_fast_math')] + os.environ.get('MOPO_NVCC_EXTRA', '').split()
     objs = []
     procs = []
     os.makedirs(os.path.join(HERE, 'build'), exist_ok=True)

@@ -203,7 +203,7 @@ MOPO_API int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float*
   REQUIRE(h && xn && trace && B > 0, MOPO_EINVAL, "mopo_debug_tc_trace: bad argument");
   REQUIRE(h->params_set && tc_supported(h), MOPO_ESTATE, "mopo_debug_tc_trace: tensor-core path unavailable");
   cudaStream_t st = (cudaStream_t)stream;
-  CUDA_TRY(cudaMemsetAsync(trace, 0, sizeof(unsigned long long) * 4 * 2048, st));
+  CUDA_TRY(cudaMemsetAsync(trace, 0, sizeof(unsigned long long) * 5 * 2048, st));
   h->tc_trace = trace;
   int rc;
   if (mean && logvar) {

@@ -25,10 +25,12 @@
 //   * bias is folded into the GEMM through two constant-1 K columns (bias split hi + lo bf16), the 1/2 of
 //     swish(x) = xh + xh * tanh(xh), xh = x/2, is folded into the weights.
 //
-// Warp roles (320 threads): warps 0-3 epilogue of output features 0..111 (+ mean head), warps 4-7 epilogue of
-// features 112..199 (+ logvar head), warp 8 of the leader CTA issues every MMA of the pair (elect.sync, warp-
-// uniform control flow -> descriptors stay in uniform registers), warp 9 loads weights and input tiles with
-// bulk async copies (the inputs arrive pre-tiled in bf16 K-panels from panelize_kernel).
+// Warp roles (448 threads): warps 0-3 hidden-layer epilogue of output features 0..111, warps 4-7 of features
+// 112..199, warp 8 of the leader CTA issues every MMA of the pair (elect.sync, warp-uniform control flow ->
+// descriptors stay in uniform registers), warp 9 loads weights and input tiles with bulk async copies (the inputs
+// arrive pre-tiled in bf16 K-panels from prep_tiles_kernel), warps 10-13 own the head stage (soft clamp, variance,
+// penalty partials, elite gather, global stores): the 8 hidden-epilogue warps, whose MUFU time is the kernel's
+// critical resource, go straight from a tile's last hidden layer to the next tile's first.
 #include "internal.cuh"
 #include "tc_common.cuh"
 #include "philox.cuh"
@@ -46,7 +48,7 @@ constexpr int W_PANEL = WROWS * 16;         // 1792 B
 constexpr int W_LAYER = KPANELS * W_PANEL;  // 46592 B
 constexpr int A_PANEL = 128 * 16;           // 2048 B: one K-panel of a 128-row A tile
 constexpr int AY_BYTES = KPANELS * A_PANEL; // 53248 B
-constexpr int NTHREADS = 320;
+constexpr int NTHREADS = 448;                // 8 hidden-epilogue warps, MMA issuer, loader, 4 head warps
 // tensor-memory column map
 constexpr int C_XA = 0, C_XD1 = 104, C_XD2 = 216, C_YD2 = 304, C_YD1 = 400;
 
@@ -249,7 +251,9 @@ struct Bars {
   uint64_t x_full[2];      // leader: both CTAs' input slot t are in smem                  (count 2)
   uint64_t x_free[2];      // each CTA: the L0 MMAs that read slot t have retired           (commit)
   uint64_t d_full[2];      // each CTA: the accumulator of tile t's current stage is ready  (commit)
-  uint64_t a_ready[2];     // leader: tile t's epilogue stage is done (A operand written / D consumed) (count 16)
+  uint64_t a_ready[2];     // leader: tile t's hidden epilogue stage is done (A operand written / D consumed) (count 16)
+  uint64_t h_full[2];      // each CTA: tile t's head accumulator is ready                  (commit)
+  uint64_t h_done[2];      // leader: the head warps have read tile t's head accumulator    (count 8)
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -369,49 +373,77 @@ __device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s
   if (FUSED && valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
 }
 
-// Fused head with the column count known at compile time (P = 4 * P4 columns per part): all tensor-memory loads are
-// issued before the first wait and the ex2 / rcp chains of the 4 * P4 dims overlap, instead of one 4-dim group at a time.
-template <int P4, class TRF>
-__device__ __forceinline__ void epi_head_fused(uint32_t tblk, int wg, const TcShape& s, const float* sC, const TcArgs& a,
-                                               int e, int64_t row, bool valid, bool mine, uint64_t* done_bar, int lane, TRF&& tr) {
-  constexpr int P = 4 * P4;
-  const int dh = (s.D1 + 1) / 2;
-  const int d0 = wg * dh, nd = wg ? s.D1 - dh : dh;
-  const float* cmin = sC + wg * P;
-  const float* cnmax = sC + MOPO_MAX_D1 + wg * P;
-  uint32_t mv[P4][4], rv[P4][4];
+// FMA-pipe exp2 and reciprocal for the head warps.  The MUFU is the forward kernel's saturated resource (one tanh per
+// hidden activation): head arithmetic that queues behind it holds a tile's head accumulator columns for thousands of
+// cycles, so the head uses the (idle) FMA / ALU pipes instead.
+//   2^y, |y| <= 60: y = n + f, n = rint(y), 2^f by a degree-5 polynomial on [-0.5, 0.5] (rel. error 3e-6), exponent add.
+__device__ __forceinline__ float exp2_fma(float y) {
+  y = fminf(fmaxf(y, -60.0f), 60.0f);
+  const float t = y + 12582912.0f;                       // 1.5 * 2^23: the integer part lands in the low mantissa bits
+  const float f = y - (t - 12582912.0f);
+  float p = 1.33335581e-3f;
+  p = fmaf(p, f, 9.61812911e-3f);
+  p = fmaf(p, f, 5.55041087e-2f);
+  p = fmaf(p, f, 2.40226507e-1f);
+  p = fmaf(p, f, 6.93147182e-1f);
+  p = fmaf(p, f, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+//   1/d, d in [2^-60, 2^61]: magic-constant seed (12 % error) + 3 Newton steps (error^2 each: 1.4e-2, 2e-4, 4e-8)
+__device__ __forceinline__ float rcp_fma(float d) {
+  float x = __int_as_float(0x7EF311C7 - __float_as_int(d));
 #pragma unroll
-  for (int c = 0; c < P4; ++c) { tmem_ld4(tblk + 4 * c, mv[c]); tmem_ld4(tblk + P + 4 * c, rv[c]); }
+  for (int it = 0; it < 3; ++it) x = fmaf(x, fmaf(-d, x, 1.0f), x);
+  return x;
+}
+
+// Fused head of one row with the column count known at compile time: the accumulator block is
+// [w = 0: mean x P | raw x P][w = 1: mean x P | raw x P], P = NHEAD / 4 (see build_image_kernel).  All tensor-memory
+// loads are issued before the one wait, the columns are handed back to the MMA warp (h_done) before any arithmetic or
+// global store, and the ex2 / rcp chains of all dims overlap.
+template <int NHEAD, int D1C>                  // D1C: D1 known at compile time (0 = use s.D1): branch-free, fully interleaved
+__device__ __forceinline__ void head_fused(uint32_t tblk, const TcShape& s, const float* sC, const TcArgs& a,
+                                           int e, int64_t row, bool valid, bool mine, uint64_t* done_bar, int lane) {
+  constexpr int P = NHEAD / 4;
+  uint32_t v[NHEAD];
+#pragma unroll
+  for (int c = 0; c < NHEAD / 16; ++c) tmem_ld16(tblk + 16 * c, reinterpret_cast<uint32_t (&)[16]>(v[16 * c]));
   tmem_ld_wait();
-  tr(400);
-  // the accumulator is in registers: hand the columns back to the MMA warp NOW, before the global stores below
-  // (an arrive after them would carry release semantics over the stores and wait for their acknowledgement)
   tc_fence_before();
   __syncwarp();
   if (lane == 0) mbar_arrive_remote(done_bar, 0);
-  tr(401);
-  float var[P4][4], pen = 0.f;
+  const int D1 = D1C ? D1C : s.D1;
+  const int dh = (D1 + 1) / 2;
+  float var[2][P], pen[2] = {0.f, 0.f};
+  // padding dims have cmin = 0 and a huge (finite) cnmax: their variance is ~0, no predicate needed
 #pragma unroll
-  for (int c = 0; c < P4; ++c)
+  for (int w = 0; w < 2; ++w)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      var[c][i] = cmin[4 * c + i] + __fdividef(1.0f, cnmax[4 * c + i] + __expf(-__uint_as_float(rv[c][i])));
-      pen += var[c][i];
+    for (int i = 0; i < P; ++i) {
+      var[w][i] = sC[w * P + i] + rcp_fma(sC[MOPO_MAX_D1 + w * P + i] + exp2_fma(-1.44269504f * __uint_as_float(v[w * 2 * P + P + i])));
+      pen[w] += var[w][i];
     }
-  if (valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
-  tr(402);
+  if (valid) {
+    float* pp = a.pen2 + (size_t)e * a.ldb + row;
+    pp[0] = pen[0];
+    pp[(size_t)a.E * a.ldb] = pen[1];
+  }
   if (mine) {
-    float2* dst = a.selmv + (int64_t)d0 * a.ldb + row;
 #pragma unroll
-    for (int c = 0; c < P4; ++c)
+    for (int w = 0; w < 2; ++w) {
+      float2* dst = a.selmv + (int64_t)(w * dh) * a.ldb + row;
+      const int nd = w ? D1 - dh : dh;
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (4 * c + i < nd) dst[(int64_t)(4 * c + i) * a.ldb] = make_float2(__uint_as_float(mv[c][i]), var[c][i]);
+      for (int i = 0; i < P; ++i) {
+        if (i < nd) *dst = make_float2(__uint_as_float(v[w * 2 * P + i]), var[w][i]);
+        dst += a.ldb;
+      }
+    }
   }
 }
 
 constexpr int TRACE_CAP = 2048;   // events per role
-// timeline probe: role r (0 issuer, 1 epilogue WG0 warp 0, 2 epilogue WG1 warp 4, 3 loader) of pair 0 / leader CTA
+// timeline probe: role r (0 issuer, 1 epilogue WG0 warp 0, 2 epilogue WG1 warp 4, 3 loader, 4 head warp 12) of pair 0 / leader CTA
 #define TR(role, tag)                                                                                   \
   do {                                                                                                  \
     if (TRACE && a.trace && pair == 0 && rank == 0 && lane == 0 && tr_n < TRACE_CAP)                    \
@@ -441,11 +473,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   const int64_t U = (int64_t)a.E * nT;                       // (net, tile) units, net-major
   const int u0 = (int)(U * pair / n_pairs), u1 = (int)(U * (pair + 1) / n_pairs);
 
+#ifdef MOPO_TC_WATCHDOG
+  if (tid == 0 && blockIdx.x == 0) printf("watchdog: Bars at smem %u (w_full +0, x_ld +8, x_full +24, x_free +40, d_full +56, a_ready +72, h_full +88, h_done +104)\n", smem_u32(bars));
+#endif
   if (tid == 0) {
     mbar_init(&bars->w_full, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->x_ld[i], 1); mbar_init(&bars->x_full[i], 2); mbar_init(&bars->x_free[i], 1);
       mbar_init(&bars->d_full[i], 1); mbar_init(&bars->a_ready[i], 16);
+      mbar_init(&bars->h_full[i], 1); mbar_init(&bars->h_done[i], 8);
     }
     fence_barrier_init();
   }
@@ -454,7 +490,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
     const int w = i / P, d = w * dh + i % P;
     const bool ok = d < (w ? s.D1 : dh);
     sLv[i] = ok ? expf(a.min_lv[d]) : 0.0f;
-    sLv[MOPO_MAX_D1 + i] = ok ? expf(-a.max_lv[d]) : __int_as_float(0x7f800000);
+    sLv[MOPO_MAX_D1 + i] = ok ? fminf(expf(-a.max_lv[d]), 1e30f) : 1e30f;
   }
   if (warp == 8) { tmem_alloc<2>(&bars->tmem_base, 512); tmem_relinquish<2>(); }
   tc_fence_before();
@@ -474,8 +510,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
 
   // phase bookkeeping that survives net switches
   // (use counts packed 16 bits per tile slot: a per-slot array indexed by t would live in local memory)
-  uint32_t n_stage = 0;              // issuer: stages issued / epilogue: stages consumed
+  uint32_t n_stage = 0;              // issuer: a_ready phases consumed / hidden epilogue: d_full phases / head warps: h_full phases
   uint32_t n_x = 0;                  // issuer / loader: input-slot uses
+  uint32_t n_tile = 0;               // issuer: tiles whose head MMA has been issued
 #define CNT(v, t) (((v) >> (16 * (t))) & 0xFFFFu)
 #define INC(v, t) ((v) += 1u << (16 * (t)))
   uint32_t seg = 0;
@@ -525,12 +562,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
         const uint32_t id1 = idesc_bf16(256, NH1), id2 = idesc_bf16(256, NH2), idh = idesc_bf16(256, s.NHEAD);
         const uint32_t w0a = smem_u32(sW0), wa = smem_u32(sW), wha = smem_u32(sWh), aya = smem_u32(sAY), xa = smem_u32(sX);
         const uint32_t hpanel = (uint32_t)(s.NHEAD / 2) * 16;
+        // Issue order per super-tile k: L1..L3 of X, Y alternating, then head(X_k), L0(X_k+1), head(Y_k), L0(Y_k+1): a slot's
+        // next tile starts its first layer as soon as the head warps have drained that slot's head accumulator, without
+        // queueing behind the other slot's last hidden epilogue.  (Per slot the order is unchanged: L0..L3, head, L0' ...)
         for (int k = 0; k < n_super; ++k) {
-          for (int j = 0; j < 5; ++j) {
-            for (int t = 0; t < 2; ++t) {
-              if (2 * k + t >= cnt) continue;
-              if (j == 0) { mbar_wait_cluster(&bars->x_full[t], CNT(n_x, t) & 1); INC(n_x, t); }
-              if (CNT(n_stage, t) > 0) mbar_wait_cluster(&bars->a_ready[t], (CNT(n_stage, t) - 1) & 1);
+          for (int step = (k == 0 ? 0 : 2); step < 12; ++step) {
+            {
+              const int t = step < 8 ? (step & 1) : (step >= 10);
+              const int j = step < 2 ? 0 : step < 8 ? (step >> 1) : (step == 8 || step == 10) ? 4 : 0;
+              const int kk = (step == 9 || step == 11) ? k + 1 : k;
+              if (2 * kk + t >= cnt) continue;
+              if (j == 0) {
+                // L0 overwrites the columns the previous tile's head accumulator lives in: the head warps must have read it
+                mbar_wait_cluster(&bars->x_full[t], CNT(n_x, t) & 1, 100 * k + step); INC(n_x, t);
+                if (CNT(n_tile, t) > 0) mbar_wait_cluster(&bars->h_done[t], (CNT(n_tile, t) - 1) & 1, 100 * k + step);
+              } else {
+                mbar_wait_cluster(&bars->a_ready[t], CNT(n_stage, t) & 1, 100 * k + step); INC(n_stage, t);
+              }
               tc_fence_after();
               TR(0, 10 * j + t);
               const uint32_t d1 = tbase + (t == 0 ? C_XD1 : C_YD1), d2 = tbase + (t == 0 ? C_XD2 : C_YD2);
@@ -573,58 +621,71 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
                       mma_ss<2>(d1, smem_desc(aya + ks * 2 * A_PANEL, A_PANEL, 128), smem_desc(wha + ks * 2 * hpanel, hpanel, 128), idh, ks > 0);
                   }
                 }
-                mma_commit<2>(&bars->d_full[t]);
+                mma_commit<2>(j < 4 ? &bars->d_full[t] : &bars->h_full[t]);
               }
               __syncwarp();
-              INC(n_stage, t);
+              if (j == 4) INC(n_tile, t);
             }
           }
         }
       }
-    } else {
-      // ===== epilogue warps: 0-3 -> features 0..111 / mean head, 4-7 -> features 112..199 / logvar head =====
+    } else if (warp < 8) {
+      // ===== hidden-layer epilogue warps: 0-3 -> features 0..111, 4-7 -> features 112..199 =====
       const int wg = warp >> 2, q = warp & 3;
       const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
       const int rr = q * 32 + lane;                     // row inside this CTA's 128-row block
       uint8_t* ay_row = sAY + rr * 16;
       for (int k = 0; k < n_super; ++k) {
-        bool mine0 = false, mine1 = false;             // fused head: is net e the one this row keeps?  (prefetched)
-        if (a.sel) {
-          const int64_t row0 = 256 * (int64_t)(t_lo + 2 * k) + (int64_t)rank * 128 + rr;
-          if (row0 < n) mine0 = a.sel[row0] == e;
-          if (2 * k + 1 < cnt && row0 + 256 < n) mine1 = a.sel[row0 + 256] == e;
-        }
-        for (int j = 0; j < 5; ++j) {
+        for (int j = 0; j < 4; ++j) {
           for (int t = 0; t < 2; ++t) {
             if (2 * k + t >= cnt) continue;
             if (q == 0) TR(1 + wg, 100 + 10 * j + t);
-            mbar_wait(&bars->d_full[t], CNT(n_stage, t) & 1);
+            mbar_wait(&bars->d_full[t], CNT(n_stage, t) & 1, 100 * k + 10 * j + t);
             INC(n_stage, t);
             tc_fence_after();
-            bool arrived = false;
             if (q == 0) TR(1 + wg, 200 + 10 * j + t);
-            if (j < 4) {
-              if (t == 0) { if (wg == 0) epi_hidden<true, 0>(tlane, ay_row); else epi_hidden<true, 1>(tlane, ay_row); }
-              else        { if (wg == 0) epi_hidden<false, 0>(tlane, ay_row); else epi_hidden<false, 1>(tlane, ay_row); }
-            } else {
-              const int64_t row = 256 * (int64_t)(t_lo + 2 * k + t) + (int64_t)rank * 128 + rr;
-              const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1) + wg * (s.NHEAD / 2);
-              if (a.sel) {
-                const bool mine = t == 0 ? mine0 : mine1;
-                auto tr = [&](int tag) { if (q == 0) TR(1 + wg, tag); };
-                if (s.NHEAD == 48) { epi_head_fused<3>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane, tr); arrived = true; }        // obs 17 (+1)
-                else if (s.NHEAD == 32) { epi_head_fused<2>(tblk, wg, s, sLv, a, e, row, row < n, mine, &bars->a_ready[t], lane, tr); arrived = true; }   // obs 11 (+1)
-                else epi_head<true>(tblk, wg, s, sLv, a, e, row, row < n, mine);
-              }
-              else epi_head<false>(tblk, wg, s, sLv, a, e, row, row < n, false);
-            }
-            if (!arrived) {
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive_remote(&bars->a_ready[t], 0);
-            }
+            if (t == 0) { if (wg == 0) epi_hidden<true, 0>(tlane, ay_row); else epi_hidden<true, 1>(tlane, ay_row); }
+            else        { if (wg == 0) epi_hidden<false, 0>(tlane, ay_row); else epi_hidden<false, 1>(tlane, ay_row); }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_remote(&bars->a_ready[t], 0);
             if (q == 0) TR(1 + wg, 300 + 10 * j + t);
           }
+        }
+      }
+    } else if (warp >= 10) {
+      // ===== head warps (10-13, tensor-memory quadrant warp % 4): soft clamp, variance, penalty partials, elite gather.
+      // Off the hidden epilogue's critical path: they own a tile's head accumulator from h_full to h_done. =====
+      const int q = warp & 3;
+      const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+      const int rr = q * 32 + lane;
+      for (int k = 0; k < n_super; ++k) {
+        for (int t = 0; t < 2; ++t) {
+          if (2 * k + t >= cnt) continue;
+          const int64_t row = 256 * (int64_t)(t_lo + 2 * k + t) + (int64_t)rank * 128 + rr;
+          const bool valid = row < n;
+          bool mine = false;                           // fused head: is net e the one this row keeps?  (in flight during the wait)
+          if (a.sel && valid) mine = a.sel[row] == e;
+          if (q == 0) TR(4, 140 + t);
+          mbar_wait(&bars->h_full[t], CNT(n_stage, t) & 1, 100 * k + t);
+          INC(n_stage, t);
+          tc_fence_after();
+          if (q == 0) TR(4, 240 + t);
+          const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1);
+          bool arrived = false;
+          if (a.sel) {
+            if (s.D1 == 18) { head_fused<48, 18>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }        // obs 17 (+1)
+            else if (s.D1 == 12) { head_fused<32, 12>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }   // obs 11 (+1)
+            else if (s.NHEAD == 48) { head_fused<48, 0>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }
+            else if (s.NHEAD == 32) { head_fused<32, 0>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }
+            else { epi_head<true>(tblk, 0, s, sLv, a, e, row, valid, mine); epi_head<true>(tblk + s.NHEAD / 2, 1, s, sLv, a, e, row, valid, mine); }
+          } else { epi_head<false>(tblk, 0, s, sLv, a, e, row, valid, false); epi_head<false>(tblk + s.NHEAD / 2, 1, s, sLv, a, e, row, valid, false); }
+          if (!arrived) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_remote(&bars->h_done[t], 0);
+          }
+          if (q == 0) TR(4, 340 + t);
         }
       }
     }

@@ -9,6 +9,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace tc {
 
@@ -48,18 +49,38 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
   return ok != 0;
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {}
+// -DMOPO_TC_WATCHDOG: a wait that spins for > 2^30 cycles reports (block, warp, barrier address, parity) and traps,
+// so that a protocol bug shows up as a launch failure with a diagnosis instead of a hung GPU.
+#ifdef MOPO_TC_WATCHDOG
+#define MOPO_WATCHDOG_DECL const long long wd_t0 = clock64(); bool wd_said = false;
+#define MOPO_WATCHDOG_CHECK(bar, parity)                                                                              \
+  if (!wd_said && clock64() - wd_t0 > (1ll << 29)) {                                                                  \
+    wd_said = true;                                                                                                   \
+    printf("mbarrier watchdog: block %d warp %d lane %d bar@%u parity %u ctx %d\n", (int)blockIdx.x, (int)threadIdx.x / 32, \
+           (int)threadIdx.x % 32, smem_u32(bar) & 0xFFFFFFu, parity, ctx);                                                 \
+  }                                                                                                                   \
+  if (clock64() - wd_t0 > (1ll << 31)) __trap();
+#else
+#define MOPO_WATCHDOG_DECL
+#define MOPO_WATCHDOG_CHECK(bar, parity)
+#endif
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ctx = 0) {
+  (void)ctx;
+  MOPO_WATCHDOG_DECL
+  while (!mbar_try_wait(bar, parity)) { MOPO_WATCHDOG_CHECK(bar, parity) }
 }
 // acquire at cluster scope (pairs with mbar_arrive_cluster from the peer CTA)
-__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity, int ctx = 0) {
+  (void)ctx;
   uint32_t ok = 0;
+  MOPO_WATCHDOG_DECL
   while (!ok) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    MOPO_WATCHDOG_CHECK(bar, parity)
   }
 }
 

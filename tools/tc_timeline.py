@@ -36,15 +36,15 @@ sys.stdout = so
 xn = torch.randn(B, obs_dim + act_dim, device=dev)
 mean = torch.empty(7, B, obs_dim + 1, device=dev)
 lv = torch.empty_like(mean)
-trace = torch.zeros(4 * 2048, dtype=torch.int64, device=dev)
+trace = torch.zeros(5 * 2048, dtype=torch.int64, device=dev)
 fused = os.environ.get('TL_FUSED', '0') == '1'
 print('mode:', 'fused head' if fused else 'full outputs')
 for _ in range(2):
     _lib.check(lib.mopo_debug_tc_trace(model._handle, xn.data_ptr(), B, None if fused else mean.data_ptr(), None if fused else lv.data_ptr(), trace.data_ptr(), st.cuda_stream))
 torch.cuda.synchronize()
-t = trace.cpu().numpy().astype(np.uint64).reshape(4, 2048)
+t = trace.cpu().numpy().astype(np.uint64).reshape(5, 2048)
 ev = []
-for role in range(4):
+for role in range(5):
     for v in t[role]:
         if v == 0:
             break
@@ -53,7 +53,7 @@ ev.sort()
 if ev:
     t0 = ev[0][0]
     print('events: %d, span %d cycles' % (len(ev), ev[-1][0] - t0))
-    role_names = ['MMA ', 'WG0 ', 'WG1 ', 'LOAD']
+    role_names = ['MMA ', 'WG0 ', 'WG1 ', 'LOAD', 'HEAD']
     last = {}
     lim = int(os.environ.get('TL_MAX', '400'))
     for c, role, tag in ev[:lim]:
