@@ -171,16 +171,21 @@ typedef struct {
   uint64_t rollout_id;           /* Philox stream: (rollout_id, step) */
   int64_t  origin_base;          /* global row id of start_obs[0] (batch sharding) */
   int64_t* steps_added;          /* host int64[h] out (len(obs) per step, mopo.py:748) */
+  void* const* action_events;    /* optional host array of h cudaEvent_t (or NULL): actions[i] is valid once
+                                    action_events[i] has completed (e.g. an H2D copy on another stream); the rollout
+                                    waits for each on `stream` just before the first kernel that reads actions[i], so
+                                    uploads of later steps' actions overlap the earlier steps' compute */
 } mopo_rollout_args;
 
 /* Runs h fused steps device-resident (no host round trip between steps), appending every step's
- * rows to the pool in the reference's order, then synchronises once to read the counts back. */
+ * rows to the pool in the reference's order, then synchronises once to read the counts back
+ * (termination kinds that never terminate need no read-back: the call returns stream-ordered, without synchronising). */
 int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream);
 
 /* ---- measurement ------------------------------------------------------------------------------- */
 /* CUDA-event timing of the ensemble-forward kernel (the dominant kernel of a step) as it runs inside
  * mopo_env_step / mopo_rollout: events are recorded on the launching stream around each launch.
- * mopo_kernel_timing(h, 1) starts and clears collection, mopo_kernel_time returns the summed milliseconds and the
+ * mopo_kernel_timing(h, 1) starts and clears collection (h, 2: the step-tail kernel of mopo_rollout instead; h, 0: off), mopo_kernel_time returns the summed milliseconds and the
  * number of launches since then (synchronising on the events) and clears. bench.py's roofline uses it. */
 int mopo_kernel_timing(mopo_ens* h, int enable);
 int mopo_kernel_time(mopo_ens* h, double* ms_total, int64_t* launches);

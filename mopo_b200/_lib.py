@@ -42,7 +42,7 @@ class RolloutArgs(C.Structure):
                 ('deterministic', C.c_int32), ('precision', C.c_int32),
                 ('noise', C.POINTER(C.c_void_p)), ('model_inds', C.POINTER(C.c_void_p)),
                 ('seed', C.c_uint64), ('rollout_id', C.c_uint64), ('origin_base', C.c_int64),
-                ('steps_added', C.POINTER(C.c_int64))]
+                ('steps_added', C.POINTER(C.c_int64)), ('action_events', C.POINTER(C.c_void_p))]
 
 
 # every symbol include/mopo_b200.h declares: (restype, argtypes)

@@ -102,7 +102,7 @@ class ModelRollout:
         env, model = self.fake_env, self.fake_env.model
         dev = model.device
         h = self._rollout_length
-        obs = torch.as_tensor(start_obs).to(device=dev, dtype=torch.float32).contiguous()
+        obs = torch.as_tensor(start_obs).to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
         B = obs.shape[0]
         keep = [obs]
 
@@ -114,13 +114,40 @@ class ModelRollout:
             keep.extend(ts)
             return (C.c_void_p * h)(*[t.data_ptr() for t in ts[:h]])
 
+        # Host-resident action arrays (NumPy / CPU tensors; pinned memory makes the copies asynchronous): step 0's go up
+        # on the compute stream, the later steps' on a side stream with one event each, and the rollout waits for
+        # event i only just before the first kernel that reads actions[i] -- the uploads overlap the earlier steps.
+        act_events = None
+        if actions is not None and h > 1 and not all(torch.is_tensor(s) and s.is_cuda for s in actions[:h]):
+            cur = torch.cuda.current_stream(dev)
+            if getattr(self, '_copy_stream', None) is None:
+                self._copy_stream = torch.cuda.Stream(dev)
+            up, evs = [], []
+            for i in range(h):
+                src = torch.as_tensor(actions[i])
+                if src.is_cuda or i == 0:
+                    up.append(src.to(device=dev, dtype=torch.float32, non_blocking=True).contiguous())
+                    evs.append(None)
+                    continue
+                with torch.cuda.stream(self._copy_stream):
+                    t = src.to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
+                    e = torch.cuda.Event()
+                    e.record(self._copy_stream)
+                t.record_stream(cur)
+                up.append(t)
+                evs.append(e)
+            actions = up
+            keep.extend(evs)
+            act_events = (C.c_void_p * h)(*[e.cuda_event if e is not None else None for e in evs])
+
         steps = (C.c_int64 * max(h, 1))()
         a = _lib.RolloutArgs(start_obs=obs.data_ptr(), B=B, rollout_length=h, actions=ptr_array(actions, torch.float32),
                              term_kind=env.config.term_kind, penalty_kind=env.penalty_kind,
                              penalty_coeff=float(env.penalty_coeff), deterministic=int(bool(deterministic)),
                              precision=model.precision if precision is None else precision,
                              noise=ptr_array(noise, torch.float32), model_inds=ptr_array(model_inds, torch.int32),
-                             seed=self.seed, rollout_id=self._rollout_count, origin_base=origin_base, steps_added=steps)
+                             seed=self.seed, rollout_id=self._rollout_count, origin_base=origin_base, steps_added=steps,
+                             action_events=act_events)
         self._rollout_count += 1
         model._ensure_handle()
         _lib.check(_lib.load().mopo_rollout(model._handle, self._model_pool._handle, C.byref(a), _lib.stream_ptr(dev)))

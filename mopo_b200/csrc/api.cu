@@ -176,7 +176,8 @@ MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* me
 // synchronises the events, returns the summed milliseconds and the number of launches, and clears.
 MOPO_API int mopo_kernel_timing(mopo_ens* h, int enable) {
   REQUIRE(h, MOPO_EINVAL, "mopo_kernel_timing: null handle");
-  h->timing = enable != 0;
+  h->timing = enable == 1;            // 1: the forward kernel (tc_launch)
+  h->timing_tail = enable == 2;       // 2: the step tail inside mopo_rollout (measurement of the rest of the step)
   h->ev_used = 0;
   return MOPO_OK;
 }
@@ -245,7 +246,7 @@ MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mea
 static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_kind, int deterministic,
                         const float* obs, const float* act, int64_t B, const int* d_n, const int32_t* model_inds,
                         uint64_t seed, uint64_t step_id, const int32_t* origin, int64_t origin_base,
-                        TailArgs* t, cudaStream_t st) {
+                        TailArgs* t, cudaStream_t st, bool tiles_ready = false) {
   const int E = h->E, D1 = h->D1;
   if (precision == MOPO_PREC_BF16) {
     REQUIRE(tc_supported(h), MOPO_EUNSUPPORTED, "bf16 tcgen05 path supports hidden_dim=200, n_hidden=4 and shapes whose weights fit one CTA pair (in+2<=32, 2*D1<=48 at E<=74)");
@@ -268,7 +269,7 @@ static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_
       t->mean = o.mean; t->lv = o.lv;
     }
     t->ldb = B;
-    TRY(tc_tiles_from_step(h, q, st));
+    if (!tiles_ready) TRY(tc_tiles_from_step(h, q, st));       // else: written by the previous step's fused tail
     return tc_launch(h, B, d_n, o, st);
   }
   REQUIRE(precision == MOPO_PREC_FP32, MOPO_EINVAL, "unknown precision %d", precision);
@@ -486,13 +487,25 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   if (!static_rows) MOPO_COUNT_LAUNCH, rollout_init_kernel<<<1, 32, 0, st>>>(d_counts, d_pool_off, (int)B, H);
   const float* obs_cur = a->start_obs;
   const int32_t* origin_cur = nullptr;
+  // static rows on the fused tensor-core path: the tail of step i also tiles step i+1's inputs and picks its elites
+  const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT;
   for (int i = 0; i < H; ++i) {
     const int* d_n = static_rows ? nullptr : d_counts + i;
     TailArgs t;
     memset(&t, 0, sizeof(t));
     const uint64_t step_id = (a->rollout_id << 16) ^ (uint64_t)i;
+    // actions[i] is first read by step i's tiling pass -- or, when steps are chained, by the tail of step i-1 (below)
+    if (a->action_events && a->action_events[i] && (i == 0 || !chain))
+      CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i], 0));
     TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, a->actions[i], B, d_n,
-                     a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st));
+                     a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st,
+                     chain && i > 0));
+    if (chain && i + 1 < H) {
+      t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
+      t.K0 = (h->in + 2 + 15) / 16 * 16;
+      t.sel_next = h->sel.as<int32_t>(); t.model_inds_next = a->model_inds ? a->model_inds[i + 1] : nullptr;
+      t.step_id_next = (a->rollout_id << 16) ^ (uint64_t)(i + 1);
+    }
     t.obs = obs_cur; t.act = a->actions[i]; t.n_max = B; t.d_n = d_n;
     t.E = h->E; t.D1 = h->D1; t.obs_dim = od; t.act_dim = ad;
     t.term_kind = a->term_kind; t.penalty_kind = a->penalty_kind; t.coeff = a->penalty_coeff; t.deterministic = a->deterministic;
@@ -505,7 +518,16 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     t.pool_max = pool->max_size;
     if (static_rows) { t.pool_base = (pool->pointer + (int64_t)i * B) % pool->max_size; t.d_pool_off = nullptr; t.blk_counts = nullptr; }
     else { t.pool_base = pool->pointer; t.d_pool_off = d_pool_off; t.blk_counts = h->blk_counts.as<int>(); }
+    if (chain && i + 1 < H && a->action_events && a->action_events[i + 1])
+      CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
+    cudaEvent_t tv0 = nullptr, tv1 = nullptr;
+    if (h->timing_tail) {
+      if (h->ev_used + 2 > h->ev.size()) for (int k = 0; k < 2; ++k) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); h->ev.push_back(e); }
+      tv0 = h->ev[h->ev_used]; tv1 = h->ev[h->ev_used + 1]; h->ev_used += 2;
+      CUDA_TRY(cudaEventRecord(tv0, st));
+    }
     TRY(launch_tail(t, st));
+    if (tv1) CUDA_TRY(cudaEventRecord(tv1, st));
     if (static_rows) { obs_cur = obs_next; continue; }
     int32_t* origin_next = h->ro_origin[i & 1].as<int32_t>();
     TRY(launch_compact(nobs_dense, term_dense, origin_cur, a->origin_base, B, d_n, h->blk_counts.as<int>(), od,
@@ -513,8 +535,12 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     obs_cur = obs_next; origin_cur = origin_next;
   }
   std::vector<int> counts(H + 1, (int)B);
-  if (!static_rows) CUDA_TRY(cudaMemcpyAsync(counts.data(), d_counts, sizeof(int) * (H + 1), cudaMemcpyDeviceToHost, st));
-  CUDA_TRY(cudaStreamSynchronize(st));
+  // static rows: every count is known on the host, so the call returns without synchronising (stream-ordered like every
+  // other entry point); otherwise one D2H of the h counts + one synchronise, at the end
+  if (!static_rows) {
+    CUDA_TRY(cudaMemcpyAsync(counts.data(), d_counts, sizeof(int) * (H + 1), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+  }
   int64_t total = 0;
   for (int i = 0; i < H; ++i) { a->steps_added[i] = counts[i]; total += counts[i]; }
   pool->pointer = (pool->pointer + total) % pool->max_size;      // == h successive add_samples calls

@@ -64,7 +64,7 @@ struct mopo_ens {
   void* tc_img = nullptr;
   size_t tc_img_bytes = 0;
   // per-launch CUDA-event timing of the forward kernel (mopo_kernel_timing): events on the launching stream
-  bool timing = false;
+  bool timing = false, timing_tail = false;
   std::vector<cudaEvent_t> ev;      // start/stop pairs of the launches since the last query
   size_t ev_used = 0;
   void* tc_trace = nullptr;         // device uint64[4][2048] timeline buffer while mopo_debug_tc_trace runs
@@ -120,6 +120,9 @@ struct TailArgs {
   float *penalty, *unpenalized, *model_means, *model_stds, *log_prob, *dev; int32_t* model_inds_out;
   // fused-head inputs (instead of mean / lv): chosen net, its (mean, variance) [D1,ldb], per-net variance sums [2,E,ldb]
   const int32_t* sel; const float2* selmv; const float* pen2;
+  // optional (fused tail, static rows): also write the NEXT step's input tiles + elite picks (see step_tail_fused_kernel)
+  uint4* xt_next; const float* act_next; const float* mu; const float* sigma; int K0;
+  int32_t* sel_next; const int32_t* model_inds_next; uint64_t step_id_next;
   // optional pool append: row j -> (pool_base + *d_pool_off + j) % pool_max
   float *p_act, *p_rew, *p_obs, *p_nobs; uint8_t* p_term; int64_t pool_max, pool_base; const int64_t* d_pool_off;
   // optional compaction bookkeeping

@@ -9,7 +9,13 @@
 
 namespace {
 
-constexpr int TAIL_ROWS = 128;
+constexpr int TAIL_ROWS = 128;     // == the forward kernel's 128-row input block (the fused tail writes the next step's tiles)
+
+__device__ __forceinline__ uint32_t pack_bf16x2_rn(float a, float b) {   // lo = a, hi = b (as tc::pack_bf16x2)
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
 
 __device__ __forceinline__ bool term_fn(int kind, const float* s /* s[0]=rew, s[1..]=next_obs */, int obs_dim) {
   // Comparisons in double: the reference compares (float64) samples with Python float literals.
@@ -162,16 +168,39 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
 // only the chosen net's (mean, variance) per output dim [D1, ldb] and each net's variance sums [2, E, ldb]
 // (fake_env.py:78-81,110).  One thread per row for the arithmetic; the row-major obs / act / next_obs / pool traffic
 // goes through shared memory so that every global access of the block is a contiguous span.
+// D1C: D1 known at compile time (0 = a.D1): every load of the row is issued before the first use.
+// When a.xt_next is set (static-row rollouts) the tail is also the NEXT step's front end (fake_env.py:46 concat,
+// models/utils.py:96 scaler, bf16 K-panel input tiles, bnn.py:342-344 elite pick): this block's 128 rows are exactly
+// one input block of the forward kernel, so the next step needs no separate tiling pass.
+template <int D1C>
 __global__ void __launch_bounds__(TAIL_ROWS) step_tail_fused_kernel(TailArgs a) {
   extern __shared__ float sm[];
-  const int od = a.obs_dim, ad = a.act_dim, D1 = a.D1, E = a.E;
+  const int od = a.obs_dim, ad = a.act_dim, D1 = D1C ? D1C : a.D1, E = a.E;
+  constexpr int D1M = D1C ? D1C : MOPO_MAX_D1;
   float* sObs = sm;                       // [TAIL_ROWS, od]
   float* sNobs = sObs + TAIL_ROWS * od;   // [TAIL_ROWS, od]
   float* sAct = sNobs + TAIL_ROWS * od;   // [TAIL_ROWS, ad]
+  float* sActN = sAct + TAIL_ROWS * ad;   // [TAIL_ROWS, ad] next step's actions   (only with xt_next)
+  float* sMu = sActN + TAIL_ROWS * ad;    // [in]
+  float* sSg = sMu + od + ad;             // [in]
   const int64_t n = a.d_n ? min((int64_t)*a.d_n, a.n_max) : a.n_max;
   const int64_t j0 = (int64_t)blockIdx.x * TAIL_ROWS;
   const int rows = (int)max((int64_t)0, min((int64_t)TAIL_ROWS, n - j0));
   const int tid = threadIdx.x;
+  const int64_t j = j0 + tid;
+  const bool ok = tid < rows;
+  // this row's forward outputs: all loads in flight before anything else
+  float2 mv[D1M];
+  float p2a[MOPO_MAX_E], p2b[MOPO_MAX_E];
+  if (ok) {
+#pragma unroll
+    for (int d = 0; d < D1M; ++d) if (d < D1) mv[d] = a.selmv[(int64_t)d * a.ldb + j];
+    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
+#pragma unroll
+      for (int e = 0; e < MOPO_MAX_E; ++e)
+        if (e < E) { p2a[e] = a.pen2[(int64_t)e * a.ldb + j]; p2b[e] = a.pen2[((int64_t)E + e) * a.ldb + j]; }
+    }
+  }
   // the block's rows are one contiguous span of each row-major array: flat, unrolled copies (loads batched in flight)
   {
     const float* go = a.obs + j0 * od;
@@ -180,40 +209,45 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_fused_kernel(TailArgs a) 
     for (int i = tid; i < rows * od; i += TAIL_ROWS) sObs[i] = go[i];
 #pragma unroll 4
     for (int i = tid; i < rows * ad; i += TAIL_ROWS) sAct[i] = ga[i];
+    if (a.xt_next) {
+      const float* gn = a.act_next + j0 * ad;
+#pragma unroll 4
+      for (int i = tid; i < rows * ad; i += TAIL_ROWS) sActN[i] = gn[i];
+      for (int i = tid; i < od + ad; i += TAIL_ROWS) { sMu[i] = a.mu[i]; sSg[i] = a.sigma[i]; }
+    }
   }
   __syncthreads();
-  const int64_t j = j0 + tid;
   bool alive = false;
-  if (tid < rows) {
+  if (ok) {
     const uint32_t orow = a.origin ? (uint32_t)a.origin[j] : (uint32_t)(a.origin_base + j);
     const float* ob = sObs + tid * od;
     float* nob = sNobs + tid * od;
-    float unpen = 0.f, z[4];
+    float unpen = 0.f;
     float pen = 0.f;
     if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {                  // max_e ||std_e||_2  (fake_env.py:110)
-#pragma unroll 8
-      for (int e = 0; e < E; ++e)
-        pen = fmaxf(pen, a.pen2[(int64_t)e * a.ldb + j] + a.pen2[((int64_t)E + e) * a.ldb + j]);
+#pragma unroll
+      for (int e = 0; e < MOPO_MAX_E; ++e) if (e < E) pen = fmaxf(pen, p2a[e] + p2b[e]);
       pen = sqrtf(pen);
     }
-    for (int g = 0; g < D1; g += 4) {                              // 4 output dims per Philox block
-      float2 mv[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) mv[u] = g + u < D1 ? a.selmv[(int64_t)(g + u) * a.ldb + j] : make_float2(0.f, 0.f);
-      if (a.noise) {
+    for (int g = 0; g < D1M; g += 4) {                             // 4 output dims per Philox block
+      if (g < D1) {
+        float z[4];
+        if (a.noise) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) z[u] = g + u < D1 ? a.noise[j * D1 + g + u] : 0.f;
-      } else philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(g >> 2), a.seed, z);
+          for (int u = 0; u < 4; ++u) z[u] = g + u < D1 ? a.noise[j * D1 + g + u] : 0.f;
+        } else philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(g >> 2), a.seed, z);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int d = g + u;
-        if (d < D1) {
-          const float mu = mv[u].x + (d ? ob[d - 1] : 0.0f);       // fake_env.py:66
-          const float sd = sqrtf(mv[u].y);                         // fake_env.py:67
-          const float smp = fmaf(z[u], sd, mu);                    // fake_env.py:72,79
-          if (d == 0) unpen = smp; else nob[d - 1] = smp;          // fake_env.py:90
-          if (a.model_means) a.model_means[j * D1 + d] = mu;
-          if (a.model_stds) a.model_stds[j * D1 + d] = sd;
+        for (int u = 0; u < 4; ++u) {
+          const int d = g + u;
+          if (d < D1M && d < D1) {
+            const float mu = mv[d].x + (d ? ob[d - 1] : 0.0f);       // fake_env.py:66
+            const float sd = sqrtf(mv[d].y);                         // fake_env.py:67
+            const float smp = fmaf(z[u], sd, mu);                    // fake_env.py:72,79
+            if (d == 0) unpen = smp; else nob[d - 1] = smp;          // fake_env.py:90
+            if (a.model_means) a.model_means[j * D1 + d] = mu;
+            if (a.model_stds) a.model_stds[j * D1 + d] = sd;
+          }
         }
       }
     }
@@ -230,6 +264,35 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_fused_kernel(TailArgs a) 
       const int64_t r = (a.pool_base + off + j) % a.pool_max;
       a.p_rew[r] = rew;
       a.p_term[r] = term ? 1 : 0;
+    }
+    if (a.sel_next)                                                // next step's elite pick (bnn.py:342-344)
+      a.sel_next[j] = a.model_inds_next ? a.model_inds_next[j]
+                                        : a.elites[philox_elite(orow, (uint32_t)a.step_id_next, a.seed, (uint32_t)a.n_elites)];
+  }
+  if (a.xt_next) {
+    // next step's input block (same layout as prep_tiles_kernel): K-panel kc, row tid -> 8 bf16; rows >= n are zero
+    const int in = od + ad, kcs = a.K0 / 8;
+    const float* nob = sNobs + tid * od;
+    const float* an = sActN + tid * ad;
+    for (int kc = 0; kc < kcs; ++kc) {
+      uint32_t p[4] = {0, 0, 0, 0};
+      if (ok) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float v[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int k = kc * 8 + 2 * q + u;
+            if (k < in) v[u] = ((k < od ? nob[k] : an[k - od]) - sMu[k]) / sSg[k];   // models/utils.py:96
+            else v[u] = k < in + 2 ? 1.f : 0.f;
+          }
+          p[q] = pack_bf16x2_rn(v[0], v[1]);
+        }
+      }
+      a.xt_next[((int64_t)blockIdx.x * kcs + kc) * TAIL_ROWS + tid] = make_uint4(p[0], p[1], p[2], p[3]);
+      // the forward kernel reads whole 256-row tiles: an odd block count leaves one all-zero block to write
+      if (blockIdx.x == gridDim.x - 1 && (gridDim.x & 1))
+        a.xt_next[((int64_t)gridDim.x * kcs + kc) * TAIL_ROWS + tid] = make_uint4(0, 0, 0, 0);
     }
   }
   __syncthreads();
@@ -349,8 +412,10 @@ int launch_tail(const TailArgs& a, cudaStream_t st) {
   if (a.n_max == 0) return MOPO_OK;
   int grid = (int)((a.n_max + TAIL_ROWS - 1) / TAIL_ROWS);
   if (a.sel) {
-    const size_t smem = sizeof(float) * TAIL_ROWS * (2 * a.obs_dim + a.act_dim);
-    MOPO_COUNT_LAUNCH, step_tail_fused_kernel<<<grid, TAIL_ROWS, smem, st>>>(a);
+    const size_t smem = sizeof(float) * (TAIL_ROWS * (2 * a.obs_dim + 2 * a.act_dim) + 2 * (a.obs_dim + a.act_dim));
+    if (a.D1 == 18) MOPO_COUNT_LAUNCH, step_tail_fused_kernel<18><<<grid, TAIL_ROWS, smem, st>>>(a);        // obs 17 (+1)
+    else if (a.D1 == 12) MOPO_COUNT_LAUNCH, step_tail_fused_kernel<12><<<grid, TAIL_ROWS, smem, st>>>(a);   // obs 11 (+1)
+    else MOPO_COUNT_LAUNCH, step_tail_fused_kernel<0><<<grid, TAIL_ROWS, smem, st>>>(a);
   } else {
     MOPO_COUNT_LAUNCH, step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
   }

@@ -169,6 +169,39 @@ def test_rollout_bf16_pool_indexing_exact():
     assert np.isfinite(got['rewards']).all() and not got['terminals'].any()
 
 
+@pytest.mark.parametrize('B', [1500, 640, 100])
+def test_rollout_bf16_chained_tail_equals_stepwise(B):
+    """Static-row rollouts on the tensor-core path let the tail of step i write step i+1's input tiles and elite
+    picks (no tiling pass between steps).  With injected noise / model_inds the pool must equal, bit for bit, the
+    literal loop of FakeEnv.step calls (each of which tiles its own inputs).  B covers an odd number of 128-row
+    blocks (1500 -> 12, 640 -> 5: the zero-filled pad block) and a single partial block."""
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    import mopo_b200.static as static
+    h, od, ad = 4, 17, 6
+    p, obs, _ = ens.synthetic_case('halfcheetah', B, seed=14)
+    rng = np.random.RandomState(16)
+    acts = [np.tanh(rng.standard_normal((B, ad))).astype(np.float32) for _ in range(h)]
+    noise = [rng.standard_normal((B, od + 1)).astype(np.float32) for _ in range(h)]
+    inds = [rng.choice(5, size=B).astype(np.int32) for _ in range(h)]
+    env = FakeEnv(make_model(p, _lib.PREC_BF16), static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=1)
+    ro = ModelRollout(env, SimpleReplayPool(od, ad, 10), rollout_batch_size=B, rollout_schedule=(0, 1, h, h), seed=1)
+    ro._set_rollout_length()
+    ro._model_pool = SimpleReplayPool(od, ad, B * h)
+    ro._rollout_model(B, start_obs=obs, actions=acts, noise=noise, model_inds=inds, quiet=True)
+    got = {k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()}
+    o = obs
+    for i in range(h):
+        nobs, rew, term, info = env.step(o, acts[i], noise=noise[i], model_inds=inds[i], diagnostics=False)
+        sl = slice(i * B, (i + 1) * B)
+        np.testing.assert_array_equal(got['observations'][sl], o, err_msg='obs step %d' % i)
+        np.testing.assert_array_equal(got['next_observations'][sl], nobs.astype(np.float32), err_msg='next_obs step %d' % i)
+        np.testing.assert_array_equal(got['rewards'][sl], rew.astype(np.float32), err_msg='rew step %d' % i)
+        o = nobs.astype(np.float32)
+
+
 @pytest.mark.parametrize('precision_name', ['bf16', 'fp32'])
 def test_device_rng_matches_oracle_philox(precision_name):
     """Philox mode (no injected randomness): the per-row elite pick equals oracle/philox.py bit for bit, and the normal

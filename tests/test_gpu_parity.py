@@ -302,3 +302,36 @@ def test_callback_rollout_matches_fused():
     # different Philox step ids between the two drivers -> compare the deterministic parts only
     assert np.array_equal(pools[0]['actions'], pools[1]['actions'])
     assert np.array_equal(pools[0]['observations'][:B], pools[1]['observations'][:B])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('precision_name', ['bf16', 'fp32'])
+def test_rollout_host_actions_overlapped_upload_equals_device_actions(precision_name):
+    """Pinned host action arrays are uploaded on a side stream behind per-step events (mopo_rollout_args.action_events);
+    the pool must equal the one produced from device-resident actions, bit for bit."""
+    import torch
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    import mopo_b200.static as static
+    B, h = 3000, 4
+    p, obs, _ = ens.synthetic_case('halfcheetah', B, seed=61)
+    prec = {'bf16': _lib.PREC_BF16, 'fp32': _lib.PREC_FP32}[precision_name]
+    m = make_model(p, precision=prec)
+    rng = np.random.RandomState(3)
+    acts = [np.tanh(rng.standard_normal((B, 6))).astype(np.float32) for _ in range(h)]
+    pools = []
+    for mode in ('device', 'host'):
+        env = FakeEnv(m, static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=5)
+        ro = ModelRollout(env, SimpleReplayPool(17, 6, 10), rollout_batch_size=B, rollout_schedule=(0, 1, h, h), seed=5)
+        ro._set_rollout_length()
+        ro._model_pool = SimpleReplayPool(17, 6, B * h)
+        a = [torch.as_tensor(x).cuda() for x in acts] if mode == 'device' else [torch.as_tensor(x).pin_memory() for x in acts]
+        o = torch.as_tensor(obs).cuda() if mode == 'device' else torch.as_tensor(obs).pin_memory()
+        ro._rollout_model(B, start_obs=o, actions=a, precision=prec, quiet=True)
+        torch.cuda.synchronize()
+        assert ro._last_steps_added == [B] * h
+        pools.append({k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()})
+    for k in pools[0]:
+        assert np.array_equal(pools[0][k], pools[1][k]), k
