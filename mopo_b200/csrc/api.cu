@@ -246,7 +246,7 @@ MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mea
 static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_kind, int deterministic,
                         const float* obs, const float* act, int64_t B, const int* d_n, const int32_t* model_inds,
                         uint64_t seed, uint64_t step_id, const int32_t* origin, int64_t origin_base,
-                        TailArgs* t, cudaStream_t st, bool tiles_ready = false) {
+                        TailArgs* t, cudaStream_t st, bool tiles_ready = false, bool pdl = false) {
   const int E = h->E, D1 = h->D1;
   if (precision == MOPO_PREC_BF16) {
     REQUIRE(tc_supported(h), MOPO_EUNSUPPORTED, "bf16 tcgen05 path supports hidden_dim=200, n_hidden=4 and shapes whose weights fit one CTA pair (in+2<=32, 2*D1<=48 at E<=74)");
@@ -270,6 +270,7 @@ static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_
     }
     t->ldb = B;
     if (!tiles_ready) TRY(tc_tiles_from_step(h, q, st));       // else: written by the previous step's fused tail
+    o.pdl = pdl && tiles_ready;                                // ... behind which this launch is a programmatic dependent
     return tc_launch(h, B, d_n, o, st);
   }
   REQUIRE(precision == MOPO_PREC_FP32, MOPO_EINVAL, "unknown precision %d", precision);
@@ -489,17 +490,25 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   const int32_t* origin_cur = nullptr;
   // static rows on the fused tensor-core path: the tail of step i also tiles step i+1's inputs and picks its elites
   const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT;
+  // programmatic dependent launches between the chained kernels (not while per-kernel timing events sit between them)
+  static const bool pdl_env = getenv("MOPO_NO_PDL") == nullptr;
+  const bool pdl = chain && pdl_env && !h->timing && !h->timing_tail;
   for (int i = 0; i < H; ++i) {
     const int* d_n = static_rows ? nullptr : d_counts + i;
     TailArgs t;
     memset(&t, 0, sizeof(t));
     const uint64_t step_id = (a->rollout_id << 16) ^ (uint64_t)i;
-    // actions[i] is first read by step i's tiling pass -- or, when steps are chained, by the tail of step i-1 (below)
-    if (a->action_events && a->action_events[i] && (i == 0 || !chain))
-      CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i], 0));
+    // actions[i] is first read by step i's tiling pass -- or, when steps are chained, by the tail of step i-1, so the
+    // chained rollout waits for actions[i+1] ahead of step i's forward (which leaves forward -> tail adjacent in the
+    // stream for the programmatic dependent launch; the upload has had a whole step to arrive by then)
+    if (a->action_events) {
+      if (a->action_events[i] && (i == 0 || !chain)) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i], 0));
+      if (chain && i + 1 < H && a->action_events[i + 1]) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
+    }
     TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, a->actions[i], B, d_n,
                      a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st,
-                     chain && i > 0));
+                     chain && i > 0, pdl && !a->action_events));
+    t.pdl = chain && pdl;
     if (chain && i + 1 < H) {
       t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
       t.K0 = (h->in + 2 + 15) / 16 * 16;
@@ -518,8 +527,6 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     t.pool_max = pool->max_size;
     if (static_rows) { t.pool_base = (pool->pointer + (int64_t)i * B) % pool->max_size; t.d_pool_off = nullptr; t.blk_counts = nullptr; }
     else { t.pool_base = pool->pointer; t.d_pool_off = d_pool_off; t.blk_counts = h->blk_counts.as<int>(); }
-    if (chain && i + 1 < H && a->action_events && a->action_events[i + 1])
-      CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
     cudaEvent_t tv0 = nullptr, tv1 = nullptr;
     if (h->timing_tail) {
       if (h->ev_used + 2 > h->ev.size()) for (int k = 0; k < 2; ++k) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); h->ev.push_back(e); }

@@ -175,7 +175,7 @@ __global__ void __launch_bounds__(128) prep_tiles_kernel(PrepArgs a) {
   const int tid = threadIdx.x;
   float* sMu = sIn + 128 * in;            // [in]
   float* sSg = sMu + in;                  // [in]
-  for (int i = tid; i < in; i += 128) { sMu[i] = a.mu[i]; sSg[i] = a.sigma[i]; }
+  for (int i = tid; i < in; i += 128) { sMu[i] = a.mu[i]; sSg[i] = 1.0f / a.sigma[i]; }   // reciprocal once; the step tail tiles with the same arithmetic
   for (int blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
     const int64_t j0 = (int64_t)blk * 128;
     const int rows = (int)max((int64_t)0, min((int64_t)128, n - j0));
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(128) prep_tiles_kernel(PrepArgs a) {
             const int k = u ? k1 : k0;
             if (k < in) {
               const float x = k < od ? sObs[tid * od + k] : sAct[tid * ad + (k - od)];
-              v[u] = (x - sMu[k]) / sSg[k];                                          // models/utils.py:96
+              v[u] = (x - sMu[k]) * sSg[k];                                          // models/utils.py:96
             } else v[u] = k < in + 2 ? 1.f : 0.f;
           }
           p[q] = pack_bf16x2(v[0], v[1]);
@@ -508,6 +508,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
   }
   __syncthreads();
 
+  // PDL: the step tail that consumes this launch's outputs may be scheduled onto SMs as their CTAs exit (its input
+  // copies and Philox draws do not depend on this kernel); everything this kernel reads from or writes to global memory
+  // that the PREVIOUS grid (the previous step's tail: input tiles, elite picks, selmv / pen2 readers) touches comes after
+  // pdl_wait() in the loader and head warps, so barrier setup, TMEM allocation and the first weight load overlap it.
+  pdl_launch_dependents();
+  bool pdl_waited = false;
+
   // phase bookkeeping that survives net switches
   // (use counts packed 16 bits per tile slot: a per-slot array indexed by t would live in local memory)
   uint32_t n_stage = 0;              // issuer: a_ready phases consumed / hidden epilogue: d_full phases / head warps: h_full phases
@@ -534,6 +541,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       const uint32_t sizes[5] = {(uint32_t)s.w0_bytes(), W_LAYER, W_LAYER, W_LAYER, (uint32_t)s.head_bytes()};
       for (int i = 0; i < 5; ++i) { bulk_g2s(smem + off, src + off, sizes[i], &bars->w_full); off += sizes[i]; }
     }
+    if (warp >= 9 && !pdl_waited) { pdl_wait(); pdl_waited = true; }   // weights are in flight; inputs / outputs come next
     mbar_wait(&bars->w_full, seg & 1);
     cluster_sync_all();                              // both CTAs' weights are in place before any MMA reads them
 
@@ -690,6 +698,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       }
     }
   }
+  if (warp >= 9 && !pdl_waited) pdl_wait();           // every CTA waits before it exits (CTAs without work too)
   __syncwarp();
   tc_fence_before();
   __syncthreads();
@@ -786,7 +795,19 @@ int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaSt
     MOPO_COUNT_LAUNCH, ens_tc_kernel<true><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
   } else {
     CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    MOPO_COUNT_LAUNCH, ens_tc_kernel<false><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
+    if (o.pdl) {
+      // programmatic dependent launch behind the previous step's tail (static-row rollouts): see pdl_wait() in the kernel
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(2 * n_pairs); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      at[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      MOPO_COUNT_LAUNCH;
+      CUDA_TRY(cudaLaunchKernelEx(&cfg, ens_tc_kernel<false>, a));
+    } else {
+      MOPO_COUNT_LAUNCH, ens_tc_kernel<false><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
+    }
   }
   if (ev1) CUDA_TRY(cudaEventRecord(ev1, st));
   CUDA_TRY(cudaGetLastError());

@@ -101,6 +101,7 @@ struct TcPrep {
 struct TcOut {
   float *mean, *lv; int64_t ldb;                                   // full
   const int32_t* sel; float2* selmv; float* pen2;                  // fused (sel != nullptr): selmv [D1, ldb], pen2 [2, E, ldb]
+  bool pdl;                                                        // launch programmatically behind the previous grid (rollout chain)
 };
 int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st);
 int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st);
@@ -123,6 +124,7 @@ struct TailArgs {
   // optional (fused tail, static rows): also write the NEXT step's input tiles + elite picks (see step_tail_fused_kernel)
   uint4* xt_next; const float* act_next; const float* mu; const float* sigma; int K0;
   int32_t* sel_next; const int32_t* model_inds_next; uint64_t step_id_next;
+  bool pdl;                    // launch programmatically behind the forward kernel (rollout chain): see step_tail_fused_kernel
   // optional pool append: row j -> (pool_base + *d_pool_off + j) % pool_max
   float *p_act, *p_rew, *p_obs, *p_nobs; uint8_t* p_term; int64_t pool_max, pool_base; const int64_t* d_pool_off;
   // optional compaction bookkeeping

@@ -166,91 +166,137 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_kernel(TailArgs a) {
 
 // Fused-head step tail (stochastic step, learned-variance or no penalty; tensor-core path): the forward kernel kept
 // only the chosen net's (mean, variance) per output dim [D1, ldb] and each net's variance sums [2, E, ldb]
-// (fake_env.py:78-81,110).  One thread per row for the arithmetic; the row-major obs / act / next_obs / pool traffic
-// goes through shared memory so that every global access of the block is a contiguous span.
-// D1C: D1 known at compile time (0 = a.D1): every load of the row is issued before the first use.
+// (fake_env.py:78-81,110).
+// FOUR threads per row, in four warp-uniform groups (thread = group * 128 + row): one thread per row ran ~2900
+// dependent instructions at 10 warps per SM (ncu: 28 % issue utilisation, latency bound).  Group q draws the Philox
+// blocks g = q, q+4, .. (4 output dims each: Gaussian sample, fake_env.py:66-79), group 1 also picks the next step's
+// elite, group 3 reduces the penalty (max_e ||std_e||_2), group 0 finishes the row (termination_fn, r - lambda*u,
+// pool scalars), and group q builds K-panel q of the next step's input tile.  The row-major obs / act / next_obs /
+// pool traffic goes through shared memory so that every global access of the block is a contiguous span.
+// D1C: D1 known at compile time (0 = a.D1).
 // When a.xt_next is set (static-row rollouts) the tail is also the NEXT step's front end (fake_env.py:46 concat,
 // models/utils.py:96 scaler, bf16 K-panel input tiles, bnn.py:342-344 elite pick): this block's 128 rows are exactly
 // one input block of the forward kernel, so the next step needs no separate tiling pass.
+constexpr int TQ = 4;
+// sqrt.approx (MUFU.RSQ based, ~1 ulp): the bf16 tensor-core path's variances carry ~3 significant digits
+__device__ __forceinline__ float sqrt_fast(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// contiguous span copy, 16 bytes per thread when both ends are 16-byte aligned (n floats, NT threads)
+template <int NT>
+__device__ __forceinline__ void span_copy(float* __restrict__ dst, const float* __restrict__ src, int n, int tid) {
+  if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
+    const int n4 = n >> 2;
+    for (int i = tid; i < n4; i += NT) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i];
+    for (int i = (n4 << 2) + tid; i < n; i += NT) dst[i] = src[i];
+  } else {
+    for (int i = tid; i < n; i += NT) dst[i] = src[i];
+  }
+}
 template <int D1C>
-__global__ void __launch_bounds__(TAIL_ROWS) step_tail_fused_kernel(TailArgs a) {
-  extern __shared__ float sm[];
+__global__ void __launch_bounds__(TAIL_ROWS * TQ, 3) step_tail_fused_kernel(TailArgs a) {
+  extern __shared__ __align__(16) float sm[];
   const int od = a.obs_dim, ad = a.act_dim, D1 = D1C ? D1C : a.D1, E = a.E;
-  constexpr int D1M = D1C ? D1C : MOPO_MAX_D1;
+  constexpr int GMAX = D1C ? ((D1C + 3) / 4 + TQ - 1) / TQ : (MOPO_MAX_D1 / 4 + TQ - 1) / TQ;   // Philox blocks per group
   float* sObs = sm;                       // [TAIL_ROWS, od]
   float* sNobs = sObs + TAIL_ROWS * od;   // [TAIL_ROWS, od]
   float* sAct = sNobs + TAIL_ROWS * od;   // [TAIL_ROWS, ad]
   float* sActN = sAct + TAIL_ROWS * ad;   // [TAIL_ROWS, ad] next step's actions   (only with xt_next)
   float* sMu = sActN + TAIL_ROWS * ad;    // [in]
   float* sSg = sMu + od + ad;             // [in]
+  float* sUnpen = sSg + od + ad;          // [TAIL_ROWS] sampled reward
+  float* sPen = sUnpen + TAIL_ROWS;       // [TAIL_ROWS] penalty
   const int64_t n = a.d_n ? min((int64_t)*a.d_n, a.n_max) : a.n_max;
   const int64_t j0 = (int64_t)blockIdx.x * TAIL_ROWS;
   const int rows = (int)max((int64_t)0, min((int64_t)TAIL_ROWS, n - j0));
-  const int tid = threadIdx.x;
-  const int64_t j = j0 + tid;
-  const bool ok = tid < rows;
-  // this row's forward outputs: all loads in flight before anything else
-  float2 mv[D1M];
+  const int tid = threadIdx.x, r = tid % TAIL_ROWS, q = tid / TAIL_ROWS;
+  constexpr int NT = TAIL_ROWS * TQ;
+  const int64_t j = j0 + r;
+  const bool ok = r < rows;
+  const int nG = (D1 + 3) / 4;
+  // --- part 1: everything that does not depend on the forward kernel's outputs (under a programmatic dependent launch
+  // this runs while the forward kernel's last CTA pairs are still busy): input spans -> smem, Philox draws, elite pick
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  uint32_t orow = 0;
+  float z[GMAX][4];
+  int32_t pick = 0;
+  {
+    span_copy<NT>(sObs, a.obs + j0 * od, rows * od, tid);
+    span_copy<NT>(sAct, a.act + j0 * ad, rows * ad, tid);
+    if (a.xt_next) {
+      span_copy<NT>(sActN, a.act_next + j0 * ad, rows * ad, tid);
+      for (int i = tid; i < od + ad; i += NT) { sMu[i] = a.mu[i]; sSg[i] = 1.0f / a.sigma[i]; }   // as prep_tiles_kernel
+    }
+  }
+  if (ok) {
+    orow = a.origin ? (uint32_t)a.origin[j] : (uint32_t)(a.origin_base + j);
+#pragma unroll
+    for (int i = 0; i < GMAX; ++i) {                               // 4 output dims per Philox block
+      const int g = q + TQ * i;
+      if (g < nG) {
+        if (a.noise) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) z[i][u] = 4 * g + u < D1 ? a.noise[j * D1 + 4 * g + u] : 0.f;
+        } else philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)g, a.seed, z[i]);
+      }
+    }
+    if (q == 1 && a.sel_next)                                      // next step's elite pick (bnn.py:342-344)
+      pick = a.model_inds_next ? a.model_inds_next[j]
+                               : a.elites[philox_elite(orow, (uint32_t)a.step_id_next, a.seed, (uint32_t)a.n_elites)];
+  }
+  // --- part 2: the forward kernel's outputs
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  float2 mv[GMAX][4];
   float p2a[MOPO_MAX_E], p2b[MOPO_MAX_E];
   if (ok) {
 #pragma unroll
-    for (int d = 0; d < D1M; ++d) if (d < D1) mv[d] = a.selmv[(int64_t)d * a.ldb + j];
-    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
+    for (int i = 0; i < GMAX; ++i) {
+      const int g = q + TQ * i;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (g < nG && 4 * g + u < D1) mv[i][u] = a.selmv[(int64_t)(4 * g + u) * a.ldb + j];
+    }
+    if (q == 3 && a.penalty_kind == MOPO_PEN_LEARNED_VAR) {
 #pragma unroll
       for (int e = 0; e < MOPO_MAX_E; ++e)
         if (e < E) { p2a[e] = a.pen2[(int64_t)e * a.ldb + j]; p2b[e] = a.pen2[((int64_t)E + e) * a.ldb + j]; }
     }
   }
-  // the block's rows are one contiguous span of each row-major array: flat, unrolled copies (loads batched in flight)
-  {
-    const float* go = a.obs + j0 * od;
-    const float* ga = a.act + j0 * ad;
-#pragma unroll 8
-    for (int i = tid; i < rows * od; i += TAIL_ROWS) sObs[i] = go[i];
-#pragma unroll 4
-    for (int i = tid; i < rows * ad; i += TAIL_ROWS) sAct[i] = ga[i];
-    if (a.xt_next) {
-      const float* gn = a.act_next + j0 * ad;
-#pragma unroll 4
-      for (int i = tid; i < rows * ad; i += TAIL_ROWS) sActN[i] = gn[i];
-      for (int i = tid; i < od + ad; i += TAIL_ROWS) { sMu[i] = a.mu[i]; sSg[i] = a.sigma[i]; }
-    }
-  }
   __syncthreads();
-  bool alive = false;
   if (ok) {
-    const uint32_t orow = a.origin ? (uint32_t)a.origin[j] : (uint32_t)(a.origin_base + j);
-    const float* ob = sObs + tid * od;
-    float* nob = sNobs + tid * od;
-    float unpen = 0.f;
-    float pen = 0.f;
-    if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {                  // max_e ||std_e||_2  (fake_env.py:110)
+    const float* ob = sObs + r * od;
+    float* nob = sNobs + r * od;
 #pragma unroll
-      for (int e = 0; e < MOPO_MAX_E; ++e) if (e < E) pen = fmaxf(pen, p2a[e] + p2b[e]);
-      pen = sqrtf(pen);
-    }
-#pragma unroll
-    for (int g = 0; g < D1M; g += 4) {                             // 4 output dims per Philox block
-      if (g < D1) {
-        float z[4];
-        if (a.noise) {
-#pragma unroll
-          for (int u = 0; u < 4; ++u) z[u] = g + u < D1 ? a.noise[j * D1 + g + u] : 0.f;
-        } else philox_normal4(orow, (uint32_t)a.step_id, (uint32_t)(g >> 2), a.seed, z);
+    for (int i = 0; i < GMAX; ++i) {
+      const int g = q + TQ * i;
+      if (g < nG) {
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          const int d = g + u;
-          if (d < D1M && d < D1) {
-            const float mu = mv[d].x + (d ? ob[d - 1] : 0.0f);       // fake_env.py:66
-            const float sd = sqrtf(mv[d].y);                         // fake_env.py:67
-            const float smp = fmaf(z[u], sd, mu);                    // fake_env.py:72,79
-            if (d == 0) unpen = smp; else nob[d - 1] = smp;          // fake_env.py:90
+          const int d = 4 * g + u;
+          if (d < D1) {
+            const float mu = mv[i][u].x + (d ? ob[d - 1] : 0.0f);    // fake_env.py:66
+            const float sd = sqrt_fast(mv[i][u].y);                  // fake_env.py:67
+            const float smp = fmaf(z[i][u], sd, mu);                 // fake_env.py:72,79
+            if (d == 0) sUnpen[r] = smp; else nob[d - 1] = smp;      // fake_env.py:90
             if (a.model_means) a.model_means[j * D1 + d] = mu;
             if (a.model_stds) a.model_stds[j * D1 + d] = sd;
           }
         }
       }
     }
+    if (q == 1 && a.sel_next) a.sel_next[j] = pick;
+    if (q == 3) {
+      float pen = 0.f;
+      if (a.penalty_kind == MOPO_PEN_LEARNED_VAR) {                // max_e ||std_e||_2  (fake_env.py:110)
+#pragma unroll
+        for (int e = 0; e < MOPO_MAX_E; ++e) if (e < E) pen = fmaxf(pen, p2a[e] + p2b[e]);
+        pen = sqrt_fast(pen);
+      }
+      sPen[r] = pen;
+    }
+  }
+  __syncthreads();
+  bool alive = false;
+  if (ok && q == 0) {
+    const float* nob = sNobs + r * od;
+    const float unpen = sUnpen[r], pen = sPen[r];
     const bool term = term_fn(a.term_kind, nob - 1, od);           // fake_env.py:91 (term_fn skips the reward slot)
     alive = !term;
     const float rew = (a.penalty_kind == MOPO_PEN_NONE) ? unpen : unpen - a.coeff * pen;   // fake_env.py:115
@@ -261,70 +307,60 @@ __global__ void __launch_bounds__(TAIL_ROWS) step_tail_fused_kernel(TailArgs a) 
     if (a.model_inds_out) a.model_inds_out[j] = a.sel[j];
     if (a.p_obs && (n - j) <= a.pool_max) {                        // flexible_replay_pool.py:57-83, last write wins
       const int64_t off = a.d_pool_off ? *a.d_pool_off : 0;
-      const int64_t r = (a.pool_base + off + j) % a.pool_max;
-      a.p_rew[r] = rew;
-      a.p_term[r] = term ? 1 : 0;
+      const int64_t pr = (a.pool_base + off + j) % a.pool_max;
+      a.p_rew[pr] = rew;
+      a.p_term[pr] = term ? 1 : 0;
     }
-    if (a.sel_next)                                                // next step's elite pick (bnn.py:342-344)
-      a.sel_next[j] = a.model_inds_next ? a.model_inds_next[j]
-                                        : a.elites[philox_elite(orow, (uint32_t)a.step_id_next, a.seed, (uint32_t)a.n_elites)];
   }
   if (a.xt_next) {
-    // next step's input block (same layout as prep_tiles_kernel): K-panel kc, row tid -> 8 bf16; rows >= n are zero
+    // next step's input block (same layout as prep_tiles_kernel): K-panel kc, row r -> 8 bf16; rows >= n are zero
     const int in = od + ad, kcs = a.K0 / 8;
-    const float* nob = sNobs + tid * od;
-    const float* an = sActN + tid * ad;
-    for (int kc = 0; kc < kcs; ++kc) {
+    const float* nob = sNobs + r * od;
+    const float* an = sActN + r * ad;
+    for (int kc = q; kc < kcs; kc += TQ) {
       uint32_t p[4] = {0, 0, 0, 0};
       if (ok) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int w = 0; w < 4; ++w) {
           float v[2];
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
-            const int k = kc * 8 + 2 * q + u;
-            if (k < in) v[u] = ((k < od ? nob[k] : an[k - od]) - sMu[k]) / sSg[k];   // models/utils.py:96
+            const int k = kc * 8 + 2 * w + u;
+            if (k < in) v[u] = ((k < od ? nob[k] : an[k - od]) - sMu[k]) * sSg[k];   // models/utils.py:96
             else v[u] = k < in + 2 ? 1.f : 0.f;
           }
-          p[q] = pack_bf16x2_rn(v[0], v[1]);
+          p[w] = pack_bf16x2_rn(v[0], v[1]);
         }
       }
-      a.xt_next[((int64_t)blockIdx.x * kcs + kc) * TAIL_ROWS + tid] = make_uint4(p[0], p[1], p[2], p[3]);
+      a.xt_next[((int64_t)blockIdx.x * kcs + kc) * TAIL_ROWS + r] = make_uint4(p[0], p[1], p[2], p[3]);
       // the forward kernel reads whole 256-row tiles: an odd block count leaves one all-zero block to write
       if (blockIdx.x == gridDim.x - 1 && (gridDim.x & 1))
-        a.xt_next[((int64_t)gridDim.x * kcs + kc) * TAIL_ROWS + tid] = make_uint4(0, 0, 0, 0);
+        a.xt_next[((int64_t)gridDim.x * kcs + kc) * TAIL_ROWS + r] = make_uint4(0, 0, 0, 0);
     }
   }
-  __syncthreads();
   if (a.next_obs) {
-    float* gn = a.next_obs + j0 * od;
-#pragma unroll 8
-    for (int i = tid; i < rows * od; i += TAIL_ROWS) gn[i] = sNobs[i];
+    span_copy<NT>(a.next_obs + j0 * od, sNobs, rows * od, tid);
   }
   if (a.p_obs) {
     const int64_t off = a.d_pool_off ? *a.d_pool_off : 0;
     const int64_t pr0 = (a.pool_base + off + j0) % a.pool_max;
     if (n - j0 <= a.pool_max && pr0 + rows <= a.pool_max) {        // common case: no wrap, nothing skipped -> flat copies
-      float* po = a.p_obs + pr0 * od;
-      float* pn = a.p_nobs + pr0 * od;
-      float* pa = a.p_act + pr0 * ad;
-#pragma unroll 8
-      for (int i = tid; i < rows * od; i += TAIL_ROWS) { po[i] = sObs[i]; pn[i] = sNobs[i]; }
-#pragma unroll 4
-      for (int i = tid; i < rows * ad; i += TAIL_ROWS) pa[i] = sAct[i];
+      span_copy<NT>(a.p_obs + pr0 * od, sObs, rows * od, tid);
+      span_copy<NT>(a.p_nobs + pr0 * od, sNobs, rows * od, tid);
+      span_copy<NT>(a.p_act + pr0 * ad, sAct, rows * ad, tid);
     } else {
-    for (int i = tid; i < rows * od; i += TAIL_ROWS) {
-      const int r = i / od, c = i - r * od;
-      if ((n - (j0 + r)) <= a.pool_max) {
-        const int64_t pr = (a.pool_base + off + j0 + r) % a.pool_max;
-        a.p_obs[pr * od + c] = sObs[i];
-        a.p_nobs[pr * od + c] = sNobs[i];
+      for (int i = tid; i < rows * od; i += NT) {
+        const int rr = i / od, c = i - rr * od;
+        if ((n - (j0 + rr)) <= a.pool_max) {
+          const int64_t pr = (a.pool_base + off + j0 + rr) % a.pool_max;
+          a.p_obs[pr * od + c] = sObs[i];
+          a.p_nobs[pr * od + c] = sNobs[i];
+        }
       }
-    }
-    for (int i = tid; i < rows * ad; i += TAIL_ROWS) {
-      const int r = i / ad, c = i - r * ad;
-      if ((n - (j0 + r)) <= a.pool_max) a.p_act[((a.pool_base + off + j0 + r) % a.pool_max) * ad + c] = sAct[i];
-    }
+      for (int i = tid; i < rows * ad; i += NT) {
+        const int rr = i / ad, c = i - rr * ad;
+        if ((n - (j0 + rr)) <= a.pool_max) a.p_act[((a.pool_base + off + j0 + rr) % a.pool_max) * ad + c] = sAct[i];
+      }
     }
   }
   if (a.blk_counts) {
@@ -412,10 +448,17 @@ int launch_tail(const TailArgs& a, cudaStream_t st) {
   if (a.n_max == 0) return MOPO_OK;
   int grid = (int)((a.n_max + TAIL_ROWS - 1) / TAIL_ROWS);
   if (a.sel) {
-    const size_t smem = sizeof(float) * (TAIL_ROWS * (2 * a.obs_dim + 2 * a.act_dim) + 2 * (a.obs_dim + a.act_dim));
-    if (a.D1 == 18) MOPO_COUNT_LAUNCH, step_tail_fused_kernel<18><<<grid, TAIL_ROWS, smem, st>>>(a);        // obs 17 (+1)
-    else if (a.D1 == 12) MOPO_COUNT_LAUNCH, step_tail_fused_kernel<12><<<grid, TAIL_ROWS, smem, st>>>(a);   // obs 11 (+1)
-    else MOPO_COUNT_LAUNCH, step_tail_fused_kernel<0><<<grid, TAIL_ROWS, smem, st>>>(a);
+    const size_t smem = sizeof(float) * (TAIL_ROWS * (2 * a.obs_dim + 2 * a.act_dim + 2) + 2 * (a.obs_dim + a.act_dim));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(TAIL_ROWS * TQ); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = a.pdl ? 1 : 0;      // rollout chain: may be scheduled while the forward kernel drains
+    MOPO_COUNT_LAUNCH;
+    if (a.D1 == 18) CUDA_TRY(cudaLaunchKernelEx(&cfg, step_tail_fused_kernel<18>, a));        // obs 17 (+1)
+    else if (a.D1 == 12) CUDA_TRY(cudaLaunchKernelEx(&cfg, step_tail_fused_kernel<12>, a));   // obs 11 (+1)
+    else CUDA_TRY(cudaLaunchKernelEx(&cfg, step_tail_fused_kernel<0>, a));
   } else {
     MOPO_COUNT_LAUNCH, step_tail_kernel<<<grid, TAIL_ROWS, 0, st>>>(a);
   }
