@@ -375,6 +375,8 @@ def main():
         run_reference(args)
     else:
         run_ours(args)
+        from mopo_b200 import dist as mdist
+        mdist.shutdown()
 
 
 if __name__ == '__main__':

@@ -111,3 +111,10 @@ def max_over_ranks(value, device=None):
 def barrier():
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.barrier()
+
+
+def shutdown():
+    """Tear the process group down (quiet exit under torchrun)."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.destroy_process_group()

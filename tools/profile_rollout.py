@@ -7,6 +7,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from mopo_b200 import _lib
+if os.environ.get('MOPO_LIB'):            # A/B runs: another build of the library (same ABI)
+    _lib.LIB_PATH = os.path.abspath(os.environ['MOPO_LIB'])
 from mopo_b200.models.constructor import construct_model
 from mopo_b200.models.fake_env import FakeEnv
 from mopo_b200.replay_pools import SimpleReplayPool
