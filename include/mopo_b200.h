@@ -17,6 +17,8 @@
  *   mopo_pool_*                            <- SimpleReplayPool / FlexibleReplayPool,
  *                                             softlearning/replay_pools/flexible_replay_pool.py:39-161
  *   mopo_rollout                           <- MOPO._rollout_model, mopo/algorithms/mopo.py:723-765
+ *   mopo_policy_*                          <- the SAC actor graph (mlp_gaussian_policy + apply_squashing_func,
+ *                                             mopo.py:292-312) and MOPO.get_action_meta, mopo.py:468-485
  */
 #ifndef MOPO_B200_H
 #define MOPO_B200_H
@@ -57,6 +59,7 @@ enum {
 
 typedef struct mopo_ens  mopo_ens;
 typedef struct mopo_pool mopo_pool;
+typedef struct mopo_policy mopo_policy;
 
 typedef struct {
   int32_t obs_dim, act_dim, rew_dim;   /* D1 = obs_dim + rew_dim ; in = obs_dim + act_dim */
@@ -155,6 +158,32 @@ int mopo_pool_gather(const mopo_pool* p, const int64_t* idx, int64_t n, float* o
 int mopo_pool_sample(const mopo_pool* p, int64_t n, uint64_t seed, uint64_t offset, int64_t* idx_out,
                      float* obs, float* act, float* next_obs, float* rew, uint8_t* term, void* stream);
 
+/* ---- policy (SAC actor) inside the rollout: MOPO.get_action_meta -------------------------------------- */
+/* mlp_gaussian_policy (mopo.py:292-303) with hidden_sizes (H, H), ReLU on both hidden layers, then
+ *   mu = dense(net, act_dim), log_std = clip(dense(net, act_dim), -20, 2), pi = mu + N(0,1) * exp(log_std),
+ * squashed by apply_squashing_func (mopo.py:281-290): action = tanh(pi) (tanh(mu) when deterministic). */
+int mopo_policy_create(int32_t obs_dim, int32_t act_dim, int32_t hidden_dim, int32_t device, mopo_policy** out);
+int mopo_policy_destroy(mopo_policy* p);
+/* tf.layers.dense layout: kernel [in,out] row-major fp32, bias [out].  weights / biases = {hidden 0 [obs,H],
+ * hidden 1 [H,H], mu [H,act], log_std [H,act]}.  Host pointers when on_device == 0. */
+int mopo_policy_set_params(mopo_policy* p, const float* const* weights, const float* const* biases,
+                           int on_device, void* stream);
+typedef struct {
+  const float* obs;          /* [B,obs_dim] device */
+  int64_t B;
+  int32_t deterministic;     /* get_action_meta(deterministic=True): tanh(mu) */
+  int32_t random_uniform;    /* MOPO._rollout_random (mopo.py:738): uniform(-1,1) actions, the network is not run */
+  int32_t precision;         /* MOPO_PREC_FP32 (FFMA, the rtol-1e-3 parity path) | MOPO_PREC_BF16 (tcgen05) */
+  const float* noise;        /* [B,act_dim] device N(0,1) draw (parity runs), or NULL: Philox4x32-10 */
+  uint64_t seed, step_id;    /* Philox key / stream id of this call */
+  const int32_t* origin;     /* [B] device row ids fed to Philox, or NULL = origin_base + 0..B-1 */
+  int64_t origin_base;
+  float* actions;            /* [B,act_dim] device out */
+  float* mu_out;             /* [B,act_dim] or NULL: pre-squash mean */
+  float* std_out;            /* [B,act_dim] or NULL: exp(clipped log_std) */
+} mopo_policy_args;
+int mopo_policy_act(mopo_policy* p, const mopo_policy_args* a, void* stream);
+
 /* ---- MOPO._rollout_model ------------------------------------------------------------------ */
 typedef struct {
   const float* start_obs;        /* [B,obs_dim] device */
@@ -175,6 +204,10 @@ typedef struct {
                                     action_events[i] has completed (e.g. an H2D copy on another stream); the rollout
                                     waits for each on `stream` just before the first kernel that reads actions[i], so
                                     uploads of later steps' actions overlap the earlier steps' compute */
+  mopo_policy* policy;           /* optional: act = policy(obs) on the device at every step (mopo.py:734); then
+                                    `actions` may be NULL (or hold NULL entries) and nothing crosses PCIe in the loop */
+  int32_t rollout_random;        /* with `policy`: uniform(-1,1) actions instead (mopo.py:736-738) */
+  int32_t policy_deterministic;  /* with `policy`: tanh(mu) */
 } mopo_rollout_args;
 
 /* Runs h fused steps device-resident (no host round trip between steps), appending every step's

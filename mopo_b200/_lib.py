@@ -42,7 +42,15 @@ class RolloutArgs(C.Structure):
                 ('deterministic', C.c_int32), ('precision', C.c_int32),
                 ('noise', C.POINTER(C.c_void_p)), ('model_inds', C.POINTER(C.c_void_p)),
                 ('seed', C.c_uint64), ('rollout_id', C.c_uint64), ('origin_base', C.c_int64),
-                ('steps_added', C.POINTER(C.c_int64)), ('action_events', C.POINTER(C.c_void_p))]
+                ('steps_added', C.POINTER(C.c_int64)), ('action_events', C.POINTER(C.c_void_p)),
+                ('policy', C.c_void_p), ('rollout_random', C.c_int32), ('policy_deterministic', C.c_int32)]
+
+
+class PolicyArgs(C.Structure):
+    _fields_ = [('obs', C.c_void_p), ('B', C.c_int64), ('deterministic', C.c_int32), ('random_uniform', C.c_int32),
+                ('precision', C.c_int32), ('noise', C.c_void_p), ('seed', C.c_uint64), ('step_id', C.c_uint64),
+                ('origin', C.c_void_p), ('origin_base', C.c_int64), ('actions', C.c_void_p), ('mu_out', C.c_void_p),
+                ('std_out', C.c_void_p)]
 
 
 # every symbol include/mopo_b200.h declares: (restype, argtypes)
@@ -76,6 +84,10 @@ SYMBOLS = {
     'mopo_kernel_timing': (C.c_int, [C.c_void_p, C.c_int]),
     'mopo_kernel_time': (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
+    'mopo_policy_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    'mopo_policy_destroy': (C.c_int, [C.c_void_p]),
+    'mopo_policy_set_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_void_p]),
+    'mopo_policy_act': (C.c_int, [C.c_void_p, C.POINTER(PolicyArgs), C.c_void_p]),
 }
 
 _lib = None

@@ -20,7 +20,7 @@ from ..replay_pools import SimpleReplayPool
 class ModelRollout:
     def __init__(self, fake_env, env_pool, rollout_batch_size=100000, rollout_schedule=(20, 100, 1, 1),
                  epoch_length=1000, model_train_freq=250, model_retain_epochs=20, deterministic=False,
-                 rollout_random=False, model_type='mlp', get_action_meta=None, seed=0):
+                 rollout_random=False, model_type='mlp', get_action_meta=None, policy=None, seed=0):
         self.fake_env = fake_env
         self._pool = env_pool                       # env (offline data) pool; `sampler.random_batch` delegates to it
         self.sampler = env_pool                     # simple_sampler.py:103-108
@@ -37,8 +37,11 @@ class ModelRollout:
         self._n_train_repeat = 1
         self._rollout_count = 0
         self.seed = int(seed)
+        self._device_policy = policy                # mopo_b200.policies.GaussianPolicy: act = policy(obs) runs on the device
         if get_action_meta is not None:
             self.get_action_meta = get_action_meta
+        elif policy is not None:
+            self.get_action_meta = policy.get_action_meta
 
     def make_init_hidden(self, n):
         return None
@@ -86,7 +89,7 @@ class ModelRollout:
             start_obs = batch['observations']                               # mopo.py:728
         if self._model_type == 'identity':
             raise NotImplementedError("identity model bypass (mopo.py:740-744) has no device work")
-        if actions is not None:
+        if actions is not None or self._device_policy is not None:
             steps_added = self._rollout_fused(start_obs, actions, noise, model_inds, deterministic, precision, origin_base)
         else:
             steps_added = self._rollout_callback(start_obs, deterministic, precision)
@@ -147,7 +150,9 @@ class ModelRollout:
                              precision=model.precision if precision is None else precision,
                              noise=ptr_array(noise, torch.float32), model_inds=ptr_array(model_inds, torch.int32),
                              seed=self.seed, rollout_id=self._rollout_count, origin_base=origin_base, steps_added=steps,
-                             action_events=act_events)
+                             action_events=act_events,
+                             policy=self._device_policy._handle if (actions is None and self._device_policy is not None) else None,
+                             rollout_random=int(bool(self._rollout_random)), policy_deterministic=0)
         self._rollout_count += 1
         model._ensure_handle()
         _lib.check(_lib.load().mopo_rollout(model._handle, self._model_pool._handle, C.byref(a), _lib.stream_ptr(dev)))

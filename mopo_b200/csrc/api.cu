@@ -15,7 +15,6 @@ void mopo_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-#define MOPO_API extern "C" __attribute__((visibility("default")))
 
 #include <atomic>
 static std::atomic<long long> g_launches{0};
@@ -24,14 +23,6 @@ MOPO_API int64_t mopo_launch_count(void) { return g_launches.load(); }
 
 MOPO_API const char* mopo_last_error(void) { return g_err; }
 MOPO_API int mopo_version(void) { return 100; }
-
-#define REQUIRE(cond, code, ...)        \
-  do {                                  \
-    if (!(cond)) {                      \
-      mopo_set_error(__VA_ARGS__);      \
-      return code;                      \
-    }                                   \
-  } while (0)
 
 // ------------------------------------------------------------------------------------------
 // ensemble
@@ -77,7 +68,7 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   if (h->tc_img) cudaFree(h->tc_img);
   for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
   DevBuf* bufs[] = {&h->sel, &h->selmv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
-                    &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts};
+                    &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts, &h->ro_act};
   for (DevBuf* b : bufs) b->release();
   delete h;
   return MOPO_OK;
@@ -466,8 +457,12 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   const int64_t B = a->B;
   if (a->steps_added) for (int i = 0; i < H; ++i) a->steps_added[i] = 0;
   if (B == 0 || H == 0) return MOPO_OK;
-  REQUIRE(a->start_obs && a->actions && a->steps_added, MOPO_EINVAL, "mopo_rollout: null start_obs/actions/steps_added");
-  for (int i = 0; i < H; ++i) REQUIRE(a->actions[i], MOPO_EINVAL, "mopo_rollout: actions[%d] null", i);
+  REQUIRE(a->start_obs && (a->actions || a->policy) && a->steps_added, MOPO_EINVAL, "mopo_rollout: null start_obs/actions/steps_added");
+  for (int i = 0; i < H; ++i) REQUIRE(a->policy || a->actions[i], MOPO_EINVAL, "mopo_rollout: actions[%d] null (and no policy)", i);
+  if (a->policy) {
+    REQUIRE(a->policy->obs_dim == h->cfg.obs_dim && a->policy->act_dim == h->cfg.act_dim && a->policy->device == h->cfg.device, MOPO_EINVAL, "mopo_rollout: policy/ensemble mismatch");
+    REQUIRE(a->policy->params_set || a->rollout_random, MOPO_ESTATE, "mopo_rollout: policy parameters not set");
+  }
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   const int od = h->cfg.obs_dim, ad = h->cfg.act_dim;
@@ -489,7 +484,9 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   const float* obs_cur = a->start_obs;
   const int32_t* origin_cur = nullptr;
   // static rows on the fused tensor-core path: the tail of step i also tiles step i+1's inputs and picks its elites
-  const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT;
+  // (with a device policy, act[i+1] = policy(next_obs[i]) does not exist yet when the tail of step i runs: no chaining)
+  const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT && !a->policy;
+  if (a->policy) TRY(h->ro_act.reserve(sizeof(float) * B * ad));
   // programmatic dependent launches between the chained kernels (not while per-kernel timing events sit between them)
   static const bool pdl_env = getenv("MOPO_NO_PDL") == nullptr;
   const bool pdl = chain && pdl_env && !h->timing && !h->timing_tail;
@@ -505,7 +502,17 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
       if (a->action_events[i] && (i == 0 || !chain)) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i], 0));
       if (chain && i + 1 < H && a->action_events[i + 1]) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
     }
-    TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, a->actions[i], B, d_n,
+    const float* act_i = (a->actions && a->actions[i]) ? a->actions[i] : nullptr;
+    if (!act_i) {                                      // act = policy(obs) on the device (mopo.py:734 / :736-738)
+      PolicyRun pr = {};
+      pr.obs = obs_cur; pr.n_max = B; pr.d_n = d_n;
+      pr.deterministic = a->policy_deterministic; pr.random_uniform = a->rollout_random; pr.precision = a->precision;
+      pr.seed = a->seed; pr.step_id = step_id; pr.origin = origin_cur; pr.origin_base = a->origin_base;
+      pr.actions = h->ro_act.as<float>();
+      TRY(policy_run(a->policy, pr, st));
+      act_i = pr.actions;
+    }
+    TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, act_i, B, d_n,
                      a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st,
                      chain && i > 0, pdl && !a->action_events));
     t.pdl = chain && pdl;
@@ -515,7 +522,7 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
       t.sel_next = h->sel.as<int32_t>(); t.model_inds_next = a->model_inds ? a->model_inds[i + 1] : nullptr;
       t.step_id_next = (a->rollout_id << 16) ^ (uint64_t)(i + 1);
     }
-    t.obs = obs_cur; t.act = a->actions[i]; t.n_max = B; t.d_n = d_n;
+    t.obs = obs_cur; t.act = act_i; t.n_max = B; t.d_n = d_n;
     t.E = h->E; t.D1 = h->D1; t.obs_dim = od; t.act_dim = ad;
     t.term_kind = a->term_kind; t.penalty_kind = a->penalty_kind; t.coeff = a->penalty_coeff; t.deterministic = a->deterministic;
     t.noise = a->noise ? a->noise[i] : nullptr; t.model_inds = a->model_inds ? a->model_inds[i] : nullptr;

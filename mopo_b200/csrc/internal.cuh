@@ -24,6 +24,16 @@ void mopo_count_launch();
     }                                                                                   \
   } while (0)
 
+#define MOPO_API extern "C" __attribute__((visibility("default")))
+
+#define REQUIRE(cond, code, ...)        \
+  do {                                  \
+    if (!(cond)) {                      \
+      mopo_set_error(__VA_ARGS__);      \
+      return code;                      \
+    }                                   \
+  } while (0)
+
 #define TRY(expr)              \
   do {                         \
     int _r = (expr);           \
@@ -72,7 +82,7 @@ struct mopo_ens {
   // scratch
   DevBuf xn, xtiles, actA, actB, mean, lv, blk_counts, misc;
   DevBuf sel, selmv, pen2;         // fused-head step outputs
-  DevBuf ro_obs[2], ro_origin[2], ro_counts;
+  DevBuf ro_obs[2], ro_origin[2], ro_counts, ro_act;
 };
 
 struct mopo_pool {
@@ -140,3 +150,24 @@ int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* or
                    float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, cudaStream_t st);
 int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, uint8_t* out, cudaStream_t st);
 int launch_exp(const float* lv, float* var, int64_t n, cudaStream_t st);
+
+// ---- policy (policy.cu): the SAC actor inside the rollout (mopo.py:292-312, 468-485) --------------------------
+struct mopo_policy {
+  int obs_dim = 0, act_dim = 0, H = 0, device = 0, sm_count = 148;
+  bool params_set = false;
+  float* W[4] = {};            // fp32, tf.layers.dense layout [in,out]: hidden 0, hidden 1, mu, log_std
+  float* b[4] = {};
+  void* tc_img = nullptr;      // bf16 UMMA-ready image (policy_tc_kernel)
+  size_t tc_img_bytes = 0;
+  DevBuf h0, h1;               // fp32 path activations
+};
+struct PolicyRun {
+  const float* obs; int64_t n_max; const int* d_n;
+  int deterministic, random_uniform, precision;
+  const float* noise; uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
+  float *actions, *mu_out, *std_out;
+};
+int policy_run(mopo_policy* p, const PolicyRun& r, cudaStream_t st);
+int policy_tc_supported(const mopo_policy* p);
+int policy_tc_build_image(mopo_policy* p, cudaStream_t st);
+int policy_tc_launch(mopo_policy* p, const PolicyRun& r, cudaStream_t st);

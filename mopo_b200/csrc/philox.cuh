@@ -8,6 +8,7 @@
 #define MOPO_STREAM_ELITE 0u
 #define MOPO_STREAM_NOISE 1u
 #define MOPO_STREAM_POOL  2u
+#define MOPO_STREAM_POLICY 3u   /* the policy's action noise (mopo.py:307) / uniform actions of rollout_random (mopo.py:738) */
 
 struct Philox4 { uint32_t x, y, z, w; };
 
@@ -38,8 +39,9 @@ __host__ __device__ __forceinline__ float mopo_u01(uint32_t x) { return ((float)
 
 #ifdef __CUDACC__
 // 4 standard normals from one Philox block (two Box-Muller pairs).
-__device__ __forceinline__ void philox_normal4(uint32_t row, uint32_t step, uint32_t blk, uint64_t seed, float out[4]) {
-  Philox4 r = philox4x32_10(row, step, blk, MOPO_STREAM_NOISE, (uint32_t)seed, (uint32_t)(seed >> 32));
+__device__ __forceinline__ void philox_normal4(uint32_t row, uint32_t step, uint32_t blk, uint64_t seed, float out[4],
+                                               uint32_t stream = MOPO_STREAM_NOISE) {
+  Philox4 r = philox4x32_10(row, step, blk, stream, (uint32_t)seed, (uint32_t)(seed >> 32));
   float u0 = mopo_u01(r.x), u1 = mopo_u01(r.y), u2 = mopo_u01(r.z), u3 = mopo_u01(r.w);
   // fast intrinsics (lg2 / sin / cos MUFU forms): arguments stay in (0,1) and [0, 2*pi), where their absolute error
   // is ~1e-6 -- far below the sampling resolution of a 24-bit uniform

@@ -8,7 +8,7 @@ Box-Muller normals match to ~1e-5 (the device uses approximate lg2 / sin / cos).
 """
 import numpy as np
 
-STREAM_ELITE, STREAM_NOISE, STREAM_POOL = 0, 1, 2
+STREAM_ELITE, STREAM_NOISE, STREAM_POOL, STREAM_POLICY = 0, 1, 2, 3
 _M0, _M1, _W0, _W1 = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85
 _MASK = np.uint64(0xFFFFFFFF)
 
@@ -41,15 +41,26 @@ def elite_index(rows, step_id, seed, n_elites):
     return ((x.astype(np.uint64) * np.uint64(n_elites)) >> np.uint64(32)).astype(np.int64)
 
 
-def normals(rows, step_id, seed, d1):
+def normals(rows, step_id, seed, d1, stream=STREAM_NOISE):
     """philox_normal4 over draw blocks 0..ceil(d1/4): standard normals [len(rows), d1] (float64 arithmetic)."""
     rows = np.asarray(rows, np.uint32)
     out = np.empty((len(rows), 4 * ((d1 + 3) // 4)))
     for blk in range((d1 + 3) // 4):
-        r = philox4x32_10(rows, np.uint32(step_id & 0xFFFFFFFF), blk, STREAM_NOISE, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+        r = philox4x32_10(rows, np.uint32(step_id & 0xFFFFFFFF), blk, stream, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
         u = [u01(x).astype(np.float64) for x in r]
         r0, r1 = np.sqrt(-2.0 * np.log(u[0])), np.sqrt(-2.0 * np.log(u[2]))
         a0, a1 = 2 * np.pi * u[1], 2 * np.pi * u[3]
         out[:, 4 * blk + 0], out[:, 4 * blk + 1] = r0 * np.cos(a0), r0 * np.sin(a0)
         out[:, 4 * blk + 2], out[:, 4 * blk + 3] = r1 * np.cos(a1), r1 * np.sin(a1)
     return out[:, :d1]
+
+
+def uniforms_pm1(rows, step_id, seed, d):
+    """rollout_random actions (mopo.py:738): 2 * u01 - 1 over draw blocks of 4, stream STREAM_POLICY (float32 arithmetic)."""
+    rows = np.asarray(rows, np.uint32)
+    out = np.empty((len(rows), 4 * ((d + 3) // 4)), np.float32)
+    for blk in range((d + 3) // 4):
+        r = philox4x32_10(rows, np.uint32(step_id & 0xFFFFFFFF), blk, STREAM_POLICY, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+        for u in range(4):
+            out[:, 4 * blk + u] = np.float32(2.0) * u01(r[u]).astype(np.float32) - np.float32(1.0)
+    return out[:, :d]

@@ -44,7 +44,8 @@ def test_struct_layouts_match_header(lib):
     assert lib.StepArgs.B.offset == 16 and lib.StepArgs.noise.offset == 48
     assert lib.StepArgs.next_obs.offset == 88 and C.sizeof(lib.StepArgs) == 168
     assert lib.RolloutArgs.actions.offset == 24 and lib.RolloutArgs.noise.offset == 56
-    assert lib.RolloutArgs.action_events.offset == 104 and C.sizeof(lib.RolloutArgs) == 112
+    assert lib.RolloutArgs.action_events.offset == 104 and lib.RolloutArgs.policy.offset == 112 and C.sizeof(lib.RolloutArgs) == 128
+    assert lib.PolicyArgs.noise.offset == 32 and lib.PolicyArgs.actions.offset == 72 and C.sizeof(lib.PolicyArgs) == 96
 
 
 def test_null_handle_calls_fail_cleanly(lib):
