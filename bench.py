@@ -195,8 +195,14 @@ def run_ours(args):
         mdist.broadcast_params(model, src=0)                               # NCCL: replicate the ensemble (not timed)
         env = FakeEnv(model, static[args.workload], penalty_coeff=1.0, penalty_learned_var=True, seed=123)
         env_pool = SimpleReplayPool(obs_dim, act_dim, 16, device=local)
+        pol = None
+        if args.policy == 'device':                    # act = policy(obs) on the device every step
+            from mopo_b200.policies import GaussianPolicy
+            from oracle import policy as opol          # (random-init weights only; nothing of oracle/ is executed in the timed path)
+            pol = GaussianPolicy(obs_dim, act_dim, device=local, precision=prec, seed=123)
+            pol.set_params(*opol.init_params(obs_dim, act_dim, seed=0))
         ro = ModelRollout(env, env_pool, rollout_batch_size=B, rollout_schedule=(20, 100, h, h), epoch_length=1000,
-                          model_train_freq=1000, model_retain_epochs=5, seed=123)
+                          model_train_freq=1000, model_retain_epochs=5, seed=123, policy=pol)
         ro._set_rollout_length()
         ro._reallocate_model_pool()                                        # 5 * h * B = 1.25 M rows (d4rl/base.py:19-21)
     finally:
@@ -205,7 +211,7 @@ def run_ours(args):
         # probe the requested precision once
         d_obs = torch.as_tensor(obs, device=dev)
         d_acts = [torch.as_tensor(a, device=dev) for a in acts]
-        ro._rollout_model(B, start_obs=d_obs, actions=d_acts, origin_base=rank * B, quiet=True)
+        ro._rollout_model(B, start_obs=d_obs, actions=None if pol else d_acts, origin_base=rank * B, quiet=True)
     except NotImplementedError as e:
         if rank == 0:
             print(json.dumps({'error': 'precision %s unavailable: %s' % (args.precision, e)}))
@@ -239,7 +245,7 @@ def run_ours(args):
         return ms, trans, l1 - l0, clocks
 
     def rollout_resident():
-        ro._rollout_model(B, start_obs=d_obs, actions=d_acts, origin_base=rank * B, quiet=True)
+        ro._rollout_model(B, start_obs=d_obs, actions=None if pol else d_acts, origin_base=rank * B, quiet=True)
         return sum(ro._last_steps_added)
 
     import ctypes as C
@@ -271,14 +277,14 @@ def run_ours(args):
     # e2e: public API with pinned HOST buffers; H2D of starts + actions and D2H of the stats inside the timed region
     h_obs = torch.as_tensor(obs).pin_memory()
     h_acts = [torch.as_tensor(a).pin_memory() for a in acts]
-    h2d = h_obs.numel() * 4 + sum(a.numel() * 4 for a in h_acts)
+    h2d = h_obs.numel() * 4 + (0 if pol else sum(a.numel() * 4 for a in h_acts))
     h_rew = torch.empty(B, 1, dtype=torch.float32).pin_memory()
     d2h = h_rew.numel() * 4
 
     def rollout_e2e():
         # pinned host buffers straight into the public call: it uploads the starts + step 0's actions on the compute
         # stream and the later steps' actions on a side stream, overlapped with the earlier steps
-        ro._rollout_model(B, start_obs=h_obs, actions=h_acts, origin_base=rank * B, quiet=True)
+        ro._rollout_model(B, start_obs=h_obs, actions=None if pol else h_acts, origin_base=rank * B, quiet=True)
         pool = ro._model_pool                           # result read-back: the penalised rewards of the rollout's last step
         last = (pool._pointer - B) % pool._max_size
         if last + B <= pool._max_size:
@@ -346,7 +352,7 @@ def run_ours(args):
         'config': {'workload': '%s-shaped (obs %d, act %d) 7-net/5-elite 4x200 ensemble rollout, B=%d starts per GPU, h=%d, lambda=1.0, into a %d-row device model_pool'
                                % (args.workload, obs_dim, act_dim, B, h, ro._model_pool._max_size),
                    'rollout_batch_size': B, 'rollout_length': h, 'transitions_per_step_per_gpu': trans // args.steps,
-                   'l2': 'flushed (256 MiB write) between timed rollouts', 'parallelism': 'batch-sharded x%d, no data-path collective' % world},
+                   'actions': 'on-device policy (2x256 ReLU Gaussian actor) every step' if pol else 'precomputed tanh(N(0,1)) arrays', 'l2': 'flushed (256 MiB write) between timed rollouts', 'parallelism': 'batch-sharded x%d, no data-path collective' % world},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                 'ms_per_step': ms_e_max / args.steps},
         'gpu_launches': launches,
@@ -369,6 +375,7 @@ def main():
     ap.add_argument('--h', type=int, default=5)
     ap.add_argument('--cpu-sample', type=int, default=4000, help='starts in the bounded CPU-baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--policy', default='none', choices=['none', 'device'], help="'device': actions from the on-device SAC actor each step (row f1) instead of precomputed action arrays")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
     if args.impl == 'reference':

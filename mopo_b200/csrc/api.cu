@@ -487,9 +487,13 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   // (with a device policy, act[i+1] = policy(next_obs[i]) does not exist yet when the tail of step i runs: no chaining)
   const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT && !a->policy;
   if (a->policy) TRY(h->ro_act.reserve(sizeof(float) * B * ad));
+  const bool policy_tiles = a->policy && !a->rollout_random && a->precision == MOPO_PREC_BF16 && !a->deterministic &&
+                            a->penalty_kind != MOPO_PEN_DISAGREEMENT && tc_supported(h) && policy_tc_supported(a->policy);
   // programmatic dependent launches between the chained kernels (not while per-kernel timing events sit between them)
   static const bool pdl_env = getenv("MOPO_NO_PDL") == nullptr;
   const bool pdl = chain && pdl_env && !h->timing && !h->timing_tail;
+  // the same between policy -> forward -> tail -> policy when the policy kernel is the tiling pass of a static-row rollout
+  const bool pdl_pol = policy_tiles && static_rows && pdl_env && !h->timing && !h->timing_tail;
   for (int i = 0; i < H; ++i) {
     const int* d_n = static_rows ? nullptr : d_counts + i;
     TailArgs t;
@@ -503,19 +507,30 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
       if (chain && i + 1 < H && a->action_events[i + 1]) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
     }
     const float* act_i = (a->actions && a->actions[i]) ? a->actions[i] : nullptr;
+    bool tiles_done = false;
     if (!act_i) {                                      // act = policy(obs) on the device (mopo.py:734 / :736-738)
       PolicyRun pr = {};
       pr.obs = obs_cur; pr.n_max = B; pr.d_n = d_n;
       pr.deterministic = a->policy_deterministic; pr.random_uniform = a->rollout_random; pr.precision = a->precision;
       pr.seed = a->seed; pr.step_id = step_id; pr.origin = origin_cur; pr.origin_base = a->origin_base;
       pr.actions = h->ro_act.as<float>();
+      if (policy_tiles) {                              // the tcgen05 policy kernel is also this step's tiling pass
+        int K0;
+        TRY(tc_reserve_xtiles(h, B, &K0));
+        TRY(h->sel.reserve(sizeof(int32_t) * B));
+        pr.xt = h->xtiles.as<uint4>(); pr.ens_mu = h->mu; pr.ens_sigma = h->sigma; pr.ens_K0 = K0;
+        pr.sel = h->sel.as<int32_t>(); pr.model_inds = a->model_inds ? a->model_inds[i] : nullptr;
+        pr.elites = h->elites; pr.n_elites = h->n_elites; pr.ens_step_id = step_id;
+        pr.pdl = pdl_pol && i > 0;                     // behind the previous step's tail
+      }
       TRY(policy_run(a->policy, pr, st));
       act_i = pr.actions;
+      tiles_done = policy_tiles;
     }
     TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, act_i, B, d_n,
                      a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st,
-                     chain && i > 0, pdl && !a->action_events));
-    t.pdl = chain && pdl;
+                     (chain && i > 0) || tiles_done, (pdl && !a->action_events) || (pdl_pol && tiles_done)));
+    t.pdl = (chain && pdl) || (pdl_pol && tiles_done);
     if (chain && i + 1 < H) {
       t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
       t.K0 = (h->in + 2 + 15) / 16 * 16;

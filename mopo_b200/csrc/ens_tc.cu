@@ -743,6 +743,14 @@ static int tc_reserve_tiles(mopo_ens* h, int64_t n_max, const TcShape& s, int* g
   return MOPO_OK;
 }
 
+// for producers of the input tiles other than the kernels of this file (the policy kernel, the step tail)
+int tc_reserve_xtiles(mopo_ens* h, int64_t n_max, int* K0) {
+  const TcShape s = make_shape(h->in, h->D1);
+  int grid;
+  *K0 = s.K0;
+  return tc_reserve_tiles(h, n_max, s, &grid);
+}
+
 int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st) {
   const TcShape s = make_shape(h->in, h->D1);
   int grid;

@@ -113,6 +113,7 @@ struct TcOut {
   const int32_t* sel; float2* selmv; float* pen2;                  // fused (sel != nullptr): selmv [D1, ldb], pen2 [2, E, ldb]
   bool pdl;                                                        // launch programmatically behind the previous grid (rollout chain)
 };
+int tc_reserve_xtiles(mopo_ens* h, int64_t n_max, int* K0);
 int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st);
 int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st);
 int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaStream_t st);
@@ -166,6 +167,11 @@ struct PolicyRun {
   int deterministic, random_uniform, precision;
   const float* noise; uint64_t seed, step_id; const int32_t* origin; int64_t origin_base;
   float *actions, *mu_out, *std_out;
+  // optional (tensor-core path): also be the ensemble step's front end -- concat(obs, act), scaler, bf16 K-panel input
+  // tiles and the per-row elite pick, exactly as prep_tiles_kernel (then the step needs no tiling pass)
+  uint4* xt; const float *ens_mu, *ens_sigma; int ens_K0;
+  int32_t* sel; const int32_t* model_inds; const int32_t* elites; int n_elites; uint64_t ens_step_id;
+  bool pdl;                    // launch programmatically behind the previous step's tail (rollout chain)
 };
 int policy_run(mopo_policy* p, const PolicyRun& r, cudaStream_t st);
 int policy_tc_supported(const mopo_policy* p);

@@ -113,12 +113,17 @@ __global__ void __launch_bounds__(P_THREADS, 1) policy_tc_kernel(PArgs a) {
   uint8_t* sWh = sW1 + s.w1_bytes();
   uint8_t* sX = sWh + s.wh_bytes();
   PBars* bars = reinterpret_cast<PBars*>(sX + s.x_bytes());
+  float* sAct = reinterpret_cast<float*>(bars + 1);       // [128, 16] this tile's actions (for the ensemble tiles)
+  float* sEmu = sAct + 128 * 16;                           // [80] ensemble scaler: mu, 1 / sigma
+  float* sErs = sEmu + 80;
   const int tid = threadIdx.x, lane = tid % 32;
   const int warp = __shfl_sync(0xffffffffu, tid / 32, 0);
   const PolicyRun& r = a.r;
-  const int64_t n = r.d_n ? min((int64_t)*r.d_n, r.n_max) : r.n_max;
-  const int nT = (int)((n + 127) / 128);
 
+  // PDL (rollout chain): the forward kernel behind this one may be scheduled as CTAs exit; everything the previous grid
+  // (the previous step's tail) wrote -- obs, the row count -- is read after pdl_wait(), so barrier setup, TMEM allocation
+  // and the weight load overlap that tail.
+  pdl_launch_dependents();
   if (tid == 0) {
     mbar_init(&bars->w_full, 1); mbar_init(&bars->d_full, 1); mbar_init(&bars->a_ready, 4);
     fence_barrier_init();
@@ -134,6 +139,10 @@ __global__ void __launch_bounds__(P_THREADS, 1) policy_tc_kernel(PArgs a) {
     const uint32_t sizes[3] = {(uint32_t)s.w0_bytes(), (uint32_t)s.w1_bytes(), (uint32_t)s.wh_bytes()};
     for (int i = 0; i < 3; ++i) { bulk_g2s(smem + off, a.img + off, sizes[i], &bars->w_full); off += sizes[i]; }
   }
+  pdl_wait();                                              // (the weight copies above are already in flight)
+  const int64_t n = r.d_n ? min((int64_t)*r.d_n, r.n_max) : r.n_max;
+  const int nT = (int)((n + 127) / 128);
+  if (a.r.xt) for (int i = tid; i < s.obs + s.act; i += P_THREADS) { sEmu[i] = a.r.ens_mu[i]; sErs[i] = 1.0f / a.r.ens_sigma[i]; }
   if (warp < 4) {
     // constant K columns 256..271 of the A operand: [1, 1, 0, ...] (the bias rows); written once
     const uint32_t ones[8] = {0x3F803F80u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
@@ -226,10 +235,40 @@ __global__ void __launch_bounds__(P_THREADS, 1) policy_tc_kernel(PArgs a) {
               if (r.noise) zz = r.noise[row * ad + d];
               else { if ((d & 3) == 0) philox_normal4(orow, (uint32_t)r.step_id, (uint32_t)(d >> 2), r.seed, z, MOPO_STREAM_POLICY); zz = z[d & 3]; }
             }
-            r.actions[row * ad + d] = tanhf(fmaf(zz, sd, mu));                             // mopo.py:301, 288-289
+            const float av = tanhf(fmaf(zz, sd, mu));                                      // mopo.py:301, 288-289
+            r.actions[row * ad + d] = av;
+            sAct[rr * 16 + d] = av;
             if (r.mu_out) r.mu_out[row * ad + d] = mu;
             if (r.std_out) r.std_out[row * ad + d] = sd;
           }
+        }
+      }
+      if (r.xt) {
+        // the ensemble step's front end for this row (as prep_tiles_kernel): fake_env.py:46 concat, models/utils.py:96
+        // scaler, bf16 K-panel tile (block t, row rr), bnn.py:342-344 elite pick
+        const int in = od + ad, ekcs = r.ens_K0 / 8;
+        for (int kc = 0; kc < ekcs; ++kc) {
+          uint32_t p[4] = {0, 0, 0, 0};
+          if (ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float v[2];
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                const int k = kc * 8 + 2 * q + u;
+                if (k < in) v[u] = ((k < od ? r.obs[row * od + k] : sAct[rr * 16 + (k - od)]) - sEmu[k]) * sErs[k];
+                else v[u] = k < in + 2 ? 1.f : 0.f;
+              }
+              p[q] = pack_bf16x2(v[0], v[1]);
+            }
+          }
+          r.xt[((int64_t)t * ekcs + kc) * 128 + rr] = make_uint4(p[0], p[1], p[2], p[3]);
+          if (t == nT - 1 && (nT & 1)) r.xt[((int64_t)nT * ekcs + kc) * 128 + rr] = make_uint4(0, 0, 0, 0);   // whole 256-row tiles
+        }
+        if (ok && r.sel) {
+          const uint32_t orow = r.origin ? (uint32_t)r.origin[row] : (uint32_t)(r.origin_base + row);
+          r.sel[row] = r.model_inds ? r.model_inds[row]
+                                    : r.elites[philox_elite(orow, (uint32_t)r.ens_step_id, r.seed, (uint32_t)r.n_elites)];
         }
       }
       // (the next tile's input block + arrive hands the accumulators back to the issuer)
@@ -241,7 +280,7 @@ __global__ void __launch_bounds__(P_THREADS, 1) policy_tc_kernel(PArgs a) {
   if (warp == 4) tmem_dealloc<1>(tbase, 512);
 }
 
-size_t policy_smem_bytes(const PShape& s) { return (size_t)s.img_bytes() + s.x_bytes() + sizeof(PBars) + 128; }
+size_t policy_smem_bytes(const PShape& s) { return (size_t)s.img_bytes() + s.x_bytes() + sizeof(PBars) + sizeof(float) * (128 * 16 + 160) + 128; }
 
 }  // namespace
 
@@ -277,8 +316,14 @@ int policy_tc_launch(mopo_policy* p, const PolicyRun& r, cudaStream_t st) {
   const int64_t tiles = (r.n_max + 127) / 128;
   const int grid = (int)(tiles < p->sm_count ? tiles : p->sm_count);
   CUDA_TRY(cudaFuncSetAttribute(policy_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(P_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = r.pdl ? 1 : 0;
   MOPO_COUNT_LAUNCH;
-  policy_tc_kernel<<<grid, P_THREADS, smem, st>>>(a);
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, policy_tc_kernel, a));
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
