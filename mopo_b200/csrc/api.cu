@@ -487,6 +487,9 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   // (with a device policy, act[i+1] = policy(next_obs[i]) does not exist yet when the tail of step i runs: no chaining)
   const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT && !a->policy;
   if (a->policy) TRY(h->ro_act.reserve(sizeof(float) * B * ad));
+  // terminating envs on the fused tensor-core path with supplied actions: the compaction tiles the next step's inputs
+  const bool compact_tiles = !static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic &&
+                             a->penalty_kind != MOPO_PEN_DISAGREEMENT && !a->policy && tc_supported(h);
   const bool policy_tiles = a->policy && !a->rollout_random && a->precision == MOPO_PREC_BF16 && !a->deterministic &&
                             a->penalty_kind != MOPO_PEN_DISAGREEMENT && tc_supported(h) && policy_tc_supported(a->policy);
   // programmatic dependent launches between the chained kernels (not while per-kernel timing events sit between them)
@@ -529,7 +532,7 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     }
     TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, act_i, B, d_n,
                      a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st,
-                     (chain && i > 0) || tiles_done, (pdl && !a->action_events) || (pdl_pol && tiles_done)));
+                     (chain && i > 0) || tiles_done || (compact_tiles && i > 0), (pdl && !a->action_events) || (pdl_pol && tiles_done)));
     t.pdl = (chain && pdl) || (pdl_pol && tiles_done);
     if (chain && i + 1 < H) {
       t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
@@ -559,8 +562,18 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     if (tv1) CUDA_TRY(cudaEventRecord(tv1, st));
     if (static_rows) { obs_cur = obs_next; continue; }
     int32_t* origin_next = h->ro_origin[i & 1].as<int32_t>();
+    CompactTiles ct = {};
+    if (compact_tiles && i + 1 < H) {                  // the compaction is also step i+1's tiling pass
+      int K0;
+      TRY(tc_reserve_xtiles(h, B, &K0));
+      TRY(h->sel.reserve(sizeof(int32_t) * B));
+      ct.xt = h->xtiles.as<uint4>(); ct.act_next = a->actions[i + 1]; ct.mu = h->mu; ct.sigma = h->sigma; ct.act_dim = ad; ct.K0 = K0;
+      ct.sel = h->sel.as<int32_t>(); ct.model_inds = a->model_inds ? a->model_inds[i + 1] : nullptr;
+      ct.elites = h->elites; ct.n_elites = h->n_elites; ct.seed = a->seed; ct.step_id = (a->rollout_id << 16) ^ (uint64_t)(i + 1);
+      if (a->action_events && a->action_events[i + 1]) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
+    }
     TRY(launch_compact(nobs_dense, term_dense, origin_cur, a->origin_base, B, d_n, h->blk_counts.as<int>(), od,
-                       obs_next, origin_next, d_counts + i + 1, d_pool_off, st));
+                       obs_next, origin_next, d_counts + i + 1, d_pool_off, ct, st));
     obs_cur = obs_next; origin_cur = origin_next;
   }
   std::vector<int> counts(H + 1, (int)B);

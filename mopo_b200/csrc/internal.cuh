@@ -146,9 +146,15 @@ int launch_prep(const float* obs, const float* act, const float* mu, const float
 int launch_tail(const TailArgs& a, cudaStream_t st);
 int tail_rows_per_block();
 // survivors of step i -> dense obs/origin for step i+1; writes d_n_next and advances d_pool_off by n.
+// optional second output of the compaction: the next step's input tiles + elite picks (xt == nullptr: off)
+struct CompactTiles {
+  uint4* xt; const float* act_next; const float *mu, *sigma; int act_dim, K0;
+  int32_t* sel; const int32_t* model_inds; const int32_t* elites; int n_elites; uint64_t seed, step_id;
+};
 int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* origin_in, int64_t origin_base,
                    int64_t n_max, const int* d_n, const int* blk_counts, int obs_dim,
-                   float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, cudaStream_t st);
+                   float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, const CompactTiles& ta,
+                   cudaStream_t st);
 int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, uint8_t* out, cudaStream_t st);
 int launch_exp(const float* lv, float* var, int64_t n, cudaStream_t st);
 

@@ -382,14 +382,18 @@ __global__ void prep_kernel(const float* __restrict__ obs, const float* __restri
 }
 
 // mopo.py:753-758: obs = next_obs[~term], order preserved.  Same row->block map as the tail.
+// With `ta.xt` set it is also the next step's front end (as prep_tiles_kernel: concat with the next step's actions,
+// scaler, bf16 K-panel tiles, elite picks), so terminating envs need no separate tiling pass after the first step either.
 __global__ void __launch_bounds__(TAIL_ROWS)
 compact_kernel(const float* __restrict__ next_obs, const uint8_t* __restrict__ term,
                const int32_t* __restrict__ origin_in, int64_t origin_base, int64_t n_max, const int* __restrict__ d_n,
                const int* __restrict__ blk_counts, int obs_dim, float* __restrict__ obs_out,
-               int32_t* __restrict__ origin_out, int* __restrict__ d_n_next, int64_t* __restrict__ d_pool_off) {
+               int32_t* __restrict__ origin_out, int* __restrict__ d_n_next, int64_t* __restrict__ d_pool_off, CompactTiles ta) {
   const int64_t n = min((int64_t)*d_n, n_max);
   __shared__ int s_part[TAIL_ROWS / 32];
   __shared__ int s_base;
+  __shared__ float s_mu[MOPO_MAX_D1 + 64], s_rs[MOPO_MAX_D1 + 64];
+  if (ta.xt) for (int i = threadIdx.x; i < obs_dim + ta.act_dim; i += TAIL_ROWS) { s_mu[i] = ta.mu[i]; s_rs[i] = 1.0f / ta.sigma[i]; }
   int part = 0;
   for (int b = threadIdx.x; b < (int)blockIdx.x; b += TAIL_ROWS) part += blk_counts[b];
   for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
@@ -410,13 +414,44 @@ compact_kernel(const float* __restrict__ next_obs, const uint8_t* __restrict__ t
   if (alive) {
     const int64_t dst = base + woff + __popc(bal & ((1u << lane) - 1u));
     for (int d = 0; d < obs_dim; ++d) obs_out[dst * obs_dim + d] = next_obs[j * obs_dim + d];
-    origin_out[dst] = origin_in ? origin_in[j] : (int32_t)(origin_base + j);
+    const int32_t org = origin_in ? origin_in[j] : (int32_t)(origin_base + j);
+    origin_out[dst] = org;
+    if (ta.xt) {
+      const int od = obs_dim, ad = ta.act_dim, in = od + ad, kcs = ta.K0 / 8;
+      const float* an = ta.act_next + dst * ad;
+      for (int kc = 0; kc < kcs; ++kc) {
+        uint32_t p[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          float v[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int k = kc * 8 + 2 * w + u;
+            if (k < in) v[u] = ((k < od ? next_obs[j * od + k] : an[k - od]) - s_mu[k]) * s_rs[k];   // models/utils.py:96
+            else v[u] = k < in + 2 ? 1.f : 0.f;
+          }
+          p[w] = pack_bf16x2_rn(v[0], v[1]);
+        }
+        ta.xt[((dst / TAIL_ROWS) * kcs + kc) * TAIL_ROWS + dst % TAIL_ROWS] = make_uint4(p[0], p[1], p[2], p[3]);
+      }
+      ta.sel[dst] = ta.model_inds ? ta.model_inds[dst]
+                                  : ta.elites[philox_elite((uint32_t)org, (uint32_t)ta.step_id, ta.seed, (uint32_t)ta.n_elites)];
+    }
   }
-  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+  if (blockIdx.x == gridDim.x - 1) {
     int tot = base;
     for (int w = 0; w < TAIL_ROWS / 32; ++w) tot += s_part[w];
-    *d_n_next = tot;
-    if (d_pool_off) *d_pool_off += n;
+    if (threadIdx.x == 0) {
+      *d_n_next = tot;
+      if (d_pool_off) *d_pool_off += n;
+    }
+    if (ta.xt) {                                        // rows tot .. next multiple of 256 of the last tile: zeros
+      const int kcs = ta.K0 / 8;
+      const int64_t end = ((int64_t)tot + 255) / 256 * 256;
+      for (int64_t rdst = tot + threadIdx.x; rdst < end; rdst += TAIL_ROWS)
+        for (int kc = 0; kc < kcs; ++kc)
+          ta.xt[((rdst / TAIL_ROWS) * kcs + kc) * TAIL_ROWS + rdst % TAIL_ROWS] = make_uint4(0, 0, 0, 0);
+    }
   }
 }
 
@@ -468,11 +503,11 @@ int launch_tail(const TailArgs& a, cudaStream_t st) {
 
 int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* origin_in, int64_t origin_base,
                    int64_t n_max, const int* d_n, const int* blk_counts, int obs_dim,
-                   float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, cudaStream_t st) {
+                   float* obs_out, int32_t* origin_out, int* d_n_next, int64_t* d_pool_off, const CompactTiles& ta, cudaStream_t st) {
   if (n_max == 0) return MOPO_OK;
   int grid = (int)((n_max + TAIL_ROWS - 1) / TAIL_ROWS);
   MOPO_COUNT_LAUNCH, compact_kernel<<<grid, TAIL_ROWS, 0, st>>>(next_obs, term, origin_in, origin_base, n_max, d_n, blk_counts, obs_dim,
-                                             obs_out, origin_out, d_n_next, d_pool_off);
+                                             obs_out, origin_out, d_n_next, d_pool_off, ta);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }

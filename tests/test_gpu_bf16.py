@@ -202,6 +202,49 @@ def test_rollout_bf16_chained_tail_equals_stepwise(B):
         o = nobs.astype(np.float32)
 
 
+@pytest.mark.parametrize('domain,B', [('hopper', 1500), ('walker2d', 700)])
+def test_rollout_bf16_terminating_compaction_tiles_equal_stepwise(domain, B):
+    """Terminating envs on the tensor-core path: the order-preserving compaction also writes the next step's input
+    tiles and elite picks.  With injected noise / model_inds the pool must equal, bit for bit, the literal loop of
+    FakeEnv.step calls over the surviving rows (mopo.py:747-758)."""
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    import mopo_b200.static as static
+    h = 4
+    p, obs, _ = ens.synthetic_case(domain, B, seed=24)
+    p['max_logvar'] = np.full_like(p['max_logvar'], -5.0)          # low noise: rows drop out gradually
+    od, ad = obs.shape[1], (3 if domain == 'hopper' else 6)
+    rng = np.random.RandomState(26)
+    acts = [np.tanh(rng.standard_normal((B, ad))).astype(np.float32) for _ in range(h)]
+    noise = [rng.standard_normal((B, od + 1)).astype(np.float32) for _ in range(h)]
+    inds = [rng.choice(5, size=B).astype(np.int32) for _ in range(h)]
+    env = FakeEnv(make_model(p, _lib.PREC_BF16), static[domain], penalty_coeff=1.0, penalty_learned_var=True, seed=1)
+    ro = ModelRollout(env, SimpleReplayPool(od, ad, 10), rollout_batch_size=B, rollout_schedule=(0, 1, h, h), seed=1)
+    ro._set_rollout_length()
+    ro._model_pool = SimpleReplayPool(od, ad, B * h)
+    ro._rollout_model(B, start_obs=obs, actions=acts, noise=noise, model_inds=inds, quiet=True)
+    got = {k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()}
+    steps = ro._last_steps_added
+    o, row = obs, 0
+    for i in range(len(steps)):
+        n = len(o)
+        assert steps[i] == n, (i, steps, n)
+        nobs, rew, term, info = env.step(o, acts[i][:n], noise=noise[i][:n], model_inds=inds[i][:n], diagnostics=False)
+        sl = slice(row, row + n)
+        np.testing.assert_array_equal(got['observations'][sl], o.astype(np.float32), err_msg='obs step %d' % i)
+        np.testing.assert_array_equal(got['next_observations'][sl], nobs.astype(np.float32), err_msg='next_obs step %d' % i)
+        np.testing.assert_array_equal(got['rewards'][sl], rew.astype(np.float32))
+        np.testing.assert_array_equal(got['terminals'][sl], term)
+        row += n
+        keep = ~term.squeeze(-1)
+        if keep.sum() == 0:
+            break
+        o = nobs[keep].astype(np.float32)
+    assert row == sum(steps) and len(steps) >= 2 and steps[1] < steps[0]
+
+
 @pytest.mark.parametrize('precision_name', ['bf16', 'fp32'])
 def test_device_rng_matches_oracle_philox(precision_name):
     """Philox mode (no injected randomness): the per-row elite pick equals oracle/philox.py bit for bit, and the normal
