@@ -335,3 +335,39 @@ def test_rollout_host_actions_overlapped_upload_equals_device_actions(precision_
         pools.append({k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()})
     for k in pools[0]:
         assert np.array_equal(pools[0][k], pools[1][k]), k
+
+
+@pytest.mark.gpu
+def test_offline_pool_restore_contiguous_and_d4rl_dict(tmp_path):
+    """loader.py:102-126 / :23-29: the offline dataset lands in the device pool exactly as FlexibleReplayPool.add_samples
+    would place it (oracle pool), incl. the f64 -> f32 cast and the bool terminals; random_batch then feeds the rollout."""
+    from mopo_b200.off_policy.loader import restore_pool, restore_pool_d4rl
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from oracle.pool import SimpleReplayPool as OraclePool
+    od, ad, n = 11, 3, 1000
+    rng = np.random.RandomState(0)
+    data = np.concatenate([rng.standard_normal((n, od)), np.tanh(rng.standard_normal((n, ad))), rng.standard_normal((n, od)),
+                           rng.standard_normal((n, 1)), (rng.uniform(size=(n, 1)) < 0.1).astype(np.float64)], axis=1)
+    path = str(tmp_path / 'pool.npy')
+    np.save(path, data)
+    pool = SimpleReplayPool(od, ad, 1500)
+    restore_pool(pool, path, max_size=1500)
+    want = OraclePool(od, ad, 1500)
+    want.add_samples({'observations': data[:, :od], 'actions': data[:, od:od + ad], 'next_observations': data[:, od + ad:2 * od + ad],
+                      'rewards': data[:, -2:-1], 'terminals': data[:, -1:].astype(bool)})
+    assert pool.size == want.size == n and pool._pointer == want._pointer
+    for k, v in pool.fields.items():
+        assert np.array_equal(v.cpu().numpy(), want.fields[k]), k
+    # wrong width -> the reference's assertion (then the BEAR fallback fails on the .npy: an exception either way)
+    np.save(path, data[:, :-1])
+    with pytest.raises(Exception):
+        restore_pool(SimpleReplayPool(od, ad, 1500), path, max_size=1500)
+    # D4RL-style dict with 1-D rewards / terminals (loader.py:26-28)
+    pool2 = SimpleReplayPool(od, ad, 1500)
+    restore_pool_d4rl(pool2, 'hopper-medium-v0', dataset={'observations': data[:, :od], 'actions': data[:, od:od + ad],
+                                                       'next_observations': data[:, od + ad:2 * od + ad],
+                                                       'rewards': data[:, -2], 'terminals': data[:, -1].astype(bool)})
+    for k, v in pool2.fields.items():
+        assert np.array_equal(v.cpu().numpy(), want.fields[k]), k
+    batch = pool2.random_batch(64)
+    assert batch['observations'].shape == (64, od)
