@@ -12,6 +12,8 @@
  *                                             BNN._end_train (_model_inds), bnn.py:337-340
  *   mopo_ens_predict                       <- BNN.predict(inputs, factored=True), bnn.py:508-546
  *                                             (math: BNN._compile_outputs, bnn.py:631-675)
+ *   mopo_ens_train_*, mopo_ens_get_params  <- BNN.train's inner loop and state handling, bnn.py:369-503 (train_op / mse_loss:
+ *                                             bnn.py:242-249, 677-700; _save_state / _set_state: bnn.py:287-307)
  *   mopo_env_step                          <- FakeEnv.step, mopo/models/fake_env.py:37-131
  *                                             + StaticFns.termination_fn, mopo/static/<env>.py
  *   mopo_pool_*                            <- SimpleReplayPool / FlexibleReplayPool,
@@ -183,6 +185,31 @@ typedef struct {
   float* std_out;            /* [B,act_dim] or NULL: exp(clipped log_std) */
 } mopo_policy_args;
 int mopo_policy_act(mopo_policy* p, const mopo_policy_args* a, void* stream);
+
+/* ---- BNN.train (bnn.py:369-503): the optimiser loop on the device -------------------------- */
+/* Start a training run: allocates Adam state (tf.train.AdamOptimizer defaults beta1 .9, beta2 .999, eps 1e-8,
+ * constructor.py:40 learning_rate 1e-3) and the per-net snapshot store.  weight_decays: HOST array of n_hidden + 2
+ * rates -- hidden layers, mean head, log-variance head (constructor.py:31-36; combined head: pass the same rate twice). */
+int mopo_ens_train_begin(mopo_ens* h, float lr, const float* weight_decays);
+/* ceil(n_cols / batch_size) Adam updates (bnn.py:421-427): batch k trains net e on rows idx[e*ld_idx + k*bs .. +bs) of
+ * inputs [n_rows, obs+act] (raw; the handle's scaler is applied) / targets [n_rows, obs+rew]; all device pointers.
+ * loss_out: optional device float[ceil(n_cols/bs)], train_loss (bnn.py:242-244) of each batch before its update.
+ * Row indices are not range-checked on the device.  Enqueues only; does not synchronise. */
+int mopo_ens_train_batches(mopo_ens* h, const float* inputs, const float* targets, int64_t n_rows, const int32_t* idx,
+                           int64_t ld_idx, int64_t n_cols, int32_t batch_size, float* loss_out, void* stream);
+/* mse_loss (bnn.py:248): mse_out[e] = mean (mean_e - target)^2 over n rows; idx == NULL: every net sees rows 0..n-1
+ * (the tiled holdout set, bnn.py:397-398), else net e sees rows idx[e*ld_idx + 0..n). */
+int mopo_ens_train_mse(mopo_ens* h, const float* inputs, const float* targets, const int32_t* idx, int64_t ld_idx,
+                       int64_t n, float* mse_out, void* stream);
+/* _save_state(net) (bnn.py:287-290) / _set_state() (bnn.py:292-307; MOPO_ESTATE if a net was never saved, the
+ * reference's KeyError).  max/min_logvar are not part of the saved state, as in the reference. */
+int mopo_ens_train_snapshot(mopo_ens* h, int32_t net, void* stream);
+int mopo_ens_train_restore(mopo_ens* h, void* stream);
+/* Finish: rebuild the bf16 tensor-core images from the trained fp32 weights, free the optimiser state (synchronises). */
+int mopo_ens_train_end(mopo_ens* h, void* stream);
+/* Device parameters -> HOST arrays in the reference layout (the inverse of mopo_ens_set_params; synchronises). */
+int mopo_ens_get_params(mopo_ens* h, float* const* weights, float* const* biases, float* var_w, float* var_b,
+                        float* max_logvar, float* min_logvar, void* stream);
 
 /* ---- MOPO._rollout_model ------------------------------------------------------------------ */
 typedef struct {

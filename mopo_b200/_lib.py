@@ -65,6 +65,15 @@ SYMBOLS = {
     'mopo_ens_set_elites': (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32]),
     'mopo_ens_predict': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_ens_train_begin': (C.c_int, [C.c_void_p, C.c_float, C.POINTER(C.c_float)]),
+    'mopo_ens_train_batches': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
+                                         C.c_int32, C.c_void_p, C.c_void_p]),
+    'mopo_ens_train_mse': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),
+    'mopo_ens_train_snapshot': (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p]),
+    'mopo_ens_train_restore': (C.c_int, [C.c_void_p, C.c_void_p]),
+    'mopo_ens_train_end': (C.c_int, [C.c_void_p, C.c_void_p]),
+    'mopo_ens_get_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     'mopo_env_step': (C.c_int, [C.c_void_p, C.POINTER(StepArgs), C.c_void_p]),
     'mopo_termination_fn': (C.c_int, [C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     'mopo_pool_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),

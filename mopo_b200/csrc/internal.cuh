@@ -57,6 +57,8 @@ struct DevBuf {
   template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+struct mopo_train;   // optimiser state while BNN.train runs (train.cu)
+
 struct mopo_ens {
   mopo_ens_cfg cfg;
   int E, in, D1, H, L, HO;   // HO = 2*D1: width of the fused [mean | raw logvar] head
@@ -83,7 +85,9 @@ struct mopo_ens {
   DevBuf xn, xtiles, actA, actB, mean, lv, blk_counts, misc;
   DevBuf sel, selmv, pen2;         // fused-head step outputs
   DevBuf ro_obs[2], ro_origin[2], ro_counts, ro_act;
+  mopo_train* tr = nullptr;
 };
+void mopo_train_release(mopo_ens* h);
 
 struct mopo_pool {
   int obs_dim, act_dim, device;

@@ -1,0 +1,547 @@
+// Ensemble training on the device: BNN.train's inner loop (reference mopo/models/bnn.py:421-427) -- the Adam step on
+//   train_loss = sum_e [ mean((mean_e - t)^2 exp(-logvar_e)) + mean(logvar_e) ]                (bnn.py:242, 693-696)
+//              + sum_l weight_decay_l * sum(W_l^2) / 2                                          (bnn.py:243, fc.py:155-156)
+//              + 0.01 sum(max_logvar) - 0.01 sum(min_logvar)                                    (bnn.py:244)
+// over all W, b, max_logvar, min_logvar (bnn.py:212-224, 249), plus mse_loss (bnn.py:248) for the holdout bookkeeping
+// and the per-net snapshot / restore of _save_state / _set_state (bnn.py:287-307).
+//
+// The master weights are the fp32 images the fp32 forward reads (mopo_ens::W / b, reference layout); training updates
+// them in place and mopo_ens_train_end rebuilds the bf16 tcgen05 images from them.  Batches are small (E x 256 rows x
+// 200 wide), so the step is launch-bound: plain fp32 FFMA tiled GEMMs (forward NN, data gradient NT, weight gradient
+// TN) with the bias / swish / swish' work in their epilogues, a deterministic loss + logvar-bound gradient reduction
+// (no float atomics: a training run is reproducible bit for bit), and one Adam launch per tensor.
+#include "internal.cuh"
+#include <math.h>
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4;
+constexpr float ADAM_B1 = 0.9f, ADAM_B2 = 0.999f, ADAM_EPS = 1e-8f;
+
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x))); }
+
+// x[e,b,:] = (inputs[r,:] - mu) / sigma, tg[e,b,:] = targets[r,:] with r = idx ? idx[e*ld + col0 + b] : b
+__global__ void gather_scale_kernel(const float* __restrict__ inputs, const float* __restrict__ targets,
+                                    const int32_t* __restrict__ idx, int64_t ld_idx, int64_t col0, int n, int E, int in,
+                                    int D1, const float* __restrict__ mu, const float* __restrict__ sigma,
+                                    float* __restrict__ x, float* __restrict__ tg) {
+  const int W = in + D1;
+  const int64_t tot = (int64_t)E * n * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    int c = (int)(i % W);
+    int64_t eb = i / W;
+    int b = (int)(eb % n), e = (int)(eb / n);
+    int64_t r = idx ? (int64_t)idx[(int64_t)e * ld_idx + col0 + b] : (int64_t)b;
+    if (c < in) x[eb * in + c] = (inputs[r * in + c] - mu[c]) / sigma[c];
+    else tg[eb * D1 + (c - in)] = targets[r * D1 + (c - in)];
+  }
+}
+
+// C[e] (M x N) = opA(A[e]) (M x K) * opB(B[e]) (K x N), fp32 FFMA, 64 x 64 x 16 tiles, 4 x 4 per thread.
+//   tA: A stored [K, M] (lda = M's row length);  tB: B stored [N, K].
+//   EPI 0: C = acc                                     (weight gradient)
+//   EPI 1: z = acc + bias[e,n]; Z = z; C = z sigmoid(z) (hidden layer forward; Z kept for the backward pass)
+//   EPI 2: C = acc + bias[e,n]                          (head forward)
+//   EPI 3: C = acc * swish'(Z[e,m,n])                   (data gradient through the previous layer's activation)
+struct GemmP {
+  const float* A; int64_t sA; int lda; int tA;
+  const float* B; int64_t sB; int ldb; int tB;
+  float* C; int64_t sC; int ldc;
+  int M, N, K;
+  const float* bias; float* Zout; const float* Zin;
+};
+
+template <int EPI>
+__global__ void __launch_bounds__(256) train_gemm_kernel(GemmP p) {
+  const int e = blockIdx.z;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  const float* Ae = p.A + (int64_t)e * p.sA;
+  const float* Be = p.B + (int64_t)e * p.sB;
+  const int tid = threadIdx.x, tx = tid % 16, ty = tid / 16;
+  float acc[TM][TN] = {};
+  for (int k0 = 0; k0 < p.K; k0 += BK) {
+    if (p.tA) {            // A[k, m]: m contiguous
+      for (int i = tid; i < BM * BK; i += 256) {
+        int k = i / BM, m = i % BM;
+        float v = 0.f;
+        if (m0 + m < p.M && k0 + k < p.K) v = Ae[(int64_t)(k0 + k) * p.lda + m0 + m];
+        As[k][m] = v;
+      }
+    } else {               // A[m, k]: k contiguous
+      for (int i = tid; i < BM * BK; i += 256) {
+        int m = i / BK, k = i % BK;
+        float v = 0.f;
+        if (m0 + m < p.M && k0 + k < p.K) v = Ae[(int64_t)(m0 + m) * p.lda + k0 + k];
+        As[k][m] = v;
+      }
+    }
+    if (p.tB) {            // B[n, k]: k contiguous
+      for (int i = tid; i < BK * BN; i += 256) {
+        int n = i / BK, k = i % BK;
+        float v = 0.f;
+        if (k0 + k < p.K && n0 + n < p.N) v = Be[(int64_t)(n0 + n) * p.ldb + k0 + k];
+        Bs[k][n] = v;
+      }
+    } else {               // B[k, n]: n contiguous
+      for (int i = tid; i < BK * BN; i += 256) {
+        int k = i / BN, n = i % BN;
+        float v = 0.f;
+        if (k0 + k < p.K && n0 + n < p.N) v = Be[(int64_t)(k0 + k) * p.ldb + n0 + n];
+        Bs[k][n] = v;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      float a[TM], b[TN];
+#pragma unroll
+      for (int i = 0; i < TM; ++i) a[i] = As[k][ty * TM + i];
+#pragma unroll
+      for (int j = 0; j < TN; ++j) b[j] = Bs[k][tx * TN + j];
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    int m = m0 + ty * TM + i;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int j = 0; j < TN; ++j) {
+      int n = n0 + tx * TN + j;
+      if (n >= p.N) continue;
+      const int64_t o = (int64_t)e * p.sC + (int64_t)m * p.ldc + n;
+      float v = acc[i][j];
+      if (EPI == 1) {
+        v += p.bias[(int64_t)e * p.N + n];
+        p.Zout[o] = v;
+        v = v * sigmoid_f(v);
+      } else if (EPI == 2) {
+        v += p.bias[(int64_t)e * p.N + n];
+      } else if (EPI == 3) {
+        float z = p.Zin[o], s = sigmoid_f(z);
+        v *= s + z * s * (1.0f - s);
+      }
+      p.C[o] = v;
+    }
+  }
+}
+
+template <int EPI>
+int gemm(const GemmP& p, int E, cudaStream_t st) {
+  dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, E);
+  MOPO_COUNT_LAUNCH;
+  train_gemm_kernel<EPI><<<grid, 256, 0, st>>>(p);
+  return MOPO_OK;
+}
+
+// db[e, c] = sum_b dZ[e, b, c]
+__global__ void colsum_kernel(const float* __restrict__ dZ, float* __restrict__ db, int n, int N) {
+  const int e = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  const float* p = dZ + (int64_t)e * n * N + c;
+  float s = 0.f;
+  for (int b = 0; b < n; ++b) s += p[(int64_t)b * N];
+  db[(int64_t)e * N + c] = s;
+}
+
+// Head backward (bnn.py:669-670, 693-696): out [E,n,2 D1] = [mean | raw] -> dOut (same layout), plus per-element
+// contributions to the loss and to d max_logvar / d min_logvar in part [3][E,n,D1] (reduced by head_reduce_kernel).
+__global__ void head_grad_kernel(const float* __restrict__ out, const float* __restrict__ tg,
+                                 const float* __restrict__ max_lv, const float* __restrict__ min_lv, int E, int n, int D1,
+                                 float* __restrict__ dOut, float* __restrict__ part) {
+  const int64_t tot = (int64_t)E * n * D1;
+  const float c = 1.0f / ((float)n * (float)D1);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    int d = (int)(i % D1);
+    int64_t eb = i / D1;
+    float mean = out[eb * 2 * D1 + d], raw = out[eb * 2 * D1 + D1 + d], t = tg[i];
+    float mx = max_lv[d], mn = min_lv[d];
+    float l1 = mx - softplus_f(mx - raw);
+    float lv = mn + softplus_f(l1 - mn);
+    float inv = expf(-lv), diff = mean - t;
+    float d_lv = (1.0f - diff * diff * inv) * c;
+    float s_min = sigmoid_f(l1 - mn), s_max = sigmoid_f(mx - raw);
+    dOut[eb * 2 * D1 + d] = 2.0f * diff * inv * c;
+    dOut[eb * 2 * D1 + D1 + d] = d_lv * s_min * s_max;
+    part[i] = (diff * diff * inv + lv) * c;
+    part[tot + i] = d_lv * s_min * (1.0f - s_max);
+    part[2 * tot + i] = d_lv * (1.0f - s_min);
+  }
+}
+
+__device__ float block_sum(float v, float* sh) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float r = 0.f;
+  if (threadIdx.x < 32) {
+    r = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  }
+  __syncthreads();
+  return r;   // valid in thread 0
+}
+
+// blocks [0, D1): g_lv[d] = 0.01 + sum_{e,b} part1, g_lv[D1 + d] = -0.01 + sum part2;  blocks [D1, D1 + E): loss_e
+__global__ void __launch_bounds__(256) head_reduce_kernel(const float* __restrict__ part, int E, int n, int D1,
+                                                          float* __restrict__ g_lv, float* __restrict__ loss_e) {
+  __shared__ float sh[8];
+  const int64_t tot = (int64_t)E * n * D1;
+  if ((int)blockIdx.x < D1) {
+    const int d = blockIdx.x;
+    float a = 0.f, b = 0.f;
+    for (int64_t r = threadIdx.x; r < (int64_t)E * n; r += blockDim.x) {
+      a += part[tot + r * D1 + d];
+      b += part[2 * tot + r * D1 + d];
+    }
+    a = block_sum(a, sh);
+    b = block_sum(b, sh);
+    if (threadIdx.x == 0) { g_lv[d] = a + 0.01f; g_lv[D1 + d] = b - 0.01f; }
+  } else {
+    const int e = blockIdx.x - D1;
+    float a = 0.f;
+    for (int64_t r = threadIdx.x; r < (int64_t)n * D1; r += blockDim.x) a += part[(int64_t)e * n * D1 + r];
+    a = block_sum(a, sh);
+    if (threadIdx.x == 0) loss_e[e] = a;
+  }
+}
+
+// mse_e = mean_{b,d} (mean - t)^2   (bnn.py:698)
+__global__ void __launch_bounds__(256) mse_kernel(const float* __restrict__ out, const float* __restrict__ tg, int n, int D1,
+                                                  float* __restrict__ mse) {
+  __shared__ float sh[8];
+  const int e = blockIdx.x;
+  float a = 0.f;
+  for (int64_t r = threadIdx.x; r < (int64_t)n * D1; r += blockDim.x) {
+    int64_t b = r / D1; int d = (int)(r % D1);
+    float diff = out[((int64_t)e * n + b) * 2 * D1 + d] - tg[(int64_t)e * n * D1 + r];
+    a += diff * diff;
+  }
+  a = block_sum(a, sh);
+  if (threadIdx.x == 0) mse[e] = a / ((float)n * (float)D1);
+}
+
+// sum of squares of a tensor slice (columns [c0, c1) of rows of length ncols) -> out[slot]; one block, deterministic
+__global__ void __launch_bounds__(1024) sumsq_kernel(const float* __restrict__ w, int64_t rows, int ncols, int c0, int c1,
+                                                     float scale, float* __restrict__ out) {
+  __shared__ float sh[32];
+  const int wc = c1 - c0;
+  float a = 0.f;
+  for (int64_t i = threadIdx.x; i < rows * wc; i += blockDim.x) {
+    float v = w[(i / wc) * ncols + c0 + (i % wc)];
+    a = fmaf(v, v, a);
+  }
+  a = block_sum(a, sh);
+  if (threadIdx.x == 0) *out = a * scale;
+}
+
+// total = sum(loss_e) + sum(decay terms) + 0.01 (sum max_lv - sum min_lv)
+__global__ void loss_total_kernel(const float* __restrict__ loss_e, int E, const float* __restrict__ decay_terms, int nd,
+                                  const float* __restrict__ max_lv, const float* __restrict__ min_lv, int D1,
+                                  float* __restrict__ out) {
+  float t = 0.f;
+  for (int e = 0; e < E; ++e) t += loss_e[e];
+  for (int i = 0; i < nd; ++i) t += decay_terms[i];
+  float a = 0.f, b = 0.f;
+  for (int d = 0; d < D1; ++d) { a += max_lv[d]; b += min_lv[d]; }
+  *out = t + 0.01f * a - 0.01f * b;
+}
+
+// tf.train.AdamOptimizer._apply_dense; the weight-decay gradient decay * w is added here (columns < split use decay_a)
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                            int64_t n, float lr_t, int ncols, int split, float decay_a, float decay_b) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float w = p[i];
+    float dec = ((int)(i % ncols) < split) ? decay_a : decay_b;
+    float gi = fmaf(dec, w, g[i]);
+    float mi = ADAM_B1 * m[i] + (1.0f - ADAM_B1) * gi;
+    float vi = ADAM_B2 * v[i] + (1.0f - ADAM_B2) * gi * gi;
+    m[i] = mi; v[i] = vi;
+    p[i] = w - lr_t * mi / (sqrtf(vi) + ADAM_EPS);
+  }
+}
+
+// dst[e] = src[e] for one net of an [E, per_net] tensor
+__global__ void copy_net_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t per_net, int e) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per_net; i += (int64_t)gridDim.x * blockDim.x)
+    dst[(int64_t)e * per_net + i] = src[(int64_t)e * per_net + i];
+}
+
+// src[r, c0 + c] -> dst[r, c]  (split the fused head back into the reference's mean / var heads)
+__global__ void take_cols_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t rows, int n_src, int n_dst, int c0) {
+  const int64_t tot = rows * n_dst;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = src[(i / n_dst) * n_src + c0 + (i % n_dst)];
+}
+
+int grid1d(int64_t tot) { int64_t g = (tot + 255) / 256; return (int)(g < 1 ? 1 : g > 148 * 8 ? 148 * 8 : g); }
+
+}  // namespace
+
+struct mopo_train {
+  float lr = 1e-3f;
+  float decay[MOPO_MAX_LAYERS + 1] = {};   // hidden 0..L-1, mean head [L], var head [L+1]
+  int64_t t = 0;
+  float *gW[MOPO_MAX_LAYERS] = {}, *gb[MOPO_MAX_LAYERS] = {};
+  float *mW[MOPO_MAX_LAYERS] = {}, *vW[MOPO_MAX_LAYERS] = {}, *mb[MOPO_MAX_LAYERS] = {}, *vb[MOPO_MAX_LAYERS] = {};
+  float *sW[MOPO_MAX_LAYERS] = {}, *sb[MOPO_MAX_LAYERS] = {};   // per-net snapshots (bnn.py:287-290)
+  float *g_lv = nullptr, *m_lv = nullptr, *v_lv = nullptr;   // [2 D1]: max | min
+  bool snap[MOPO_MAX_E] = {};
+  DevBuf x, tg, Z, Hh, out, dA, dB, part, scal;
+};
+
+static size_t wsize(const mopo_ens* h, int l) { return (size_t)h->E * (l == 0 ? h->in : h->H) * (l == h->L ? h->HO : h->H); }
+static size_t bsize(const mopo_ens* h, int l) { return (size_t)h->E * (l == h->L ? h->HO : h->H); }
+
+static void train_free(mopo_train* tr) {
+  if (!tr) return;
+  for (int l = 0; l < MOPO_MAX_LAYERS; ++l) {
+    float* ps[] = {tr->gW[l], tr->gb[l], tr->mW[l], tr->vW[l], tr->mb[l], tr->vb[l], tr->sW[l], tr->sb[l]};
+    for (float* p : ps) if (p) cudaFree(p);
+  }
+  float* qs[] = {tr->g_lv, tr->m_lv, tr->v_lv};
+  for (float* p : qs) if (p) cudaFree(p);
+  DevBuf* bufs[] = {&tr->x, &tr->tg, &tr->Z, &tr->Hh, &tr->out, &tr->dA, &tr->dB, &tr->part, &tr->scal};
+  for (DevBuf* b : bufs) b->release();
+  delete tr;
+}
+
+void mopo_train_release(mopo_ens* h) { train_free(h->tr); h->tr = nullptr; }
+
+MOPO_API int mopo_ens_train_begin(mopo_ens* h, float lr, const float* weight_decays) {
+  REQUIRE(h && weight_decays, MOPO_EINVAL, "mopo_ens_train_begin: null argument");
+  REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_train_begin: parameters not set");
+  REQUIRE(lr > 0.f, MOPO_EINVAL, "mopo_ens_train_begin: lr=%g", (double)lr);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  mopo_train_release(h);
+  mopo_train* tr = new mopo_train();
+  h->tr = tr;
+  tr->lr = lr;
+  for (int l = 0; l < h->L + 2; ++l) tr->decay[l] = weight_decays[l];
+  for (int l = 0; l <= h->L; ++l) {
+    float** ws[] = {&tr->gW[l], &tr->mW[l], &tr->vW[l], &tr->sW[l]};
+    float** bs[] = {&tr->gb[l], &tr->mb[l], &tr->vb[l], &tr->sb[l]};
+    for (float** p : ws) { CUDA_TRY(cudaMalloc(p, wsize(h, l) * sizeof(float))); CUDA_TRY(cudaMemset(*p, 0, wsize(h, l) * sizeof(float))); }
+    for (float** p : bs) { CUDA_TRY(cudaMalloc(p, bsize(h, l) * sizeof(float))); CUDA_TRY(cudaMemset(*p, 0, bsize(h, l) * sizeof(float))); }
+  }
+  float** qs[] = {&tr->g_lv, &tr->m_lv, &tr->v_lv};
+  for (float** p : qs) { CUDA_TRY(cudaMalloc(p, 2 * h->D1 * sizeof(float))); CUDA_TRY(cudaMemset(*p, 0, 2 * h->D1 * sizeof(float))); }
+  return MOPO_OK;
+}
+
+// Forward of n rows per net into tr->out ([E,n,2 D1] = [mean | raw log-variance]); keeps Z / H of every hidden layer.
+static int train_forward(mopo_ens* h, const float* inputs, const float* targets, const int32_t* idx, int64_t ld_idx,
+                         int64_t col0, int n, cudaStream_t st) {
+  mopo_train* tr = h->tr;
+  const int E = h->E, H = h->H, L = h->L, HO = h->HO, D1 = h->D1, in = h->in;
+  const size_t rows = (size_t)E * n;
+  const int wide = H > HO ? H : HO;
+  TRY(tr->x.reserve(rows * in * sizeof(float)));
+  TRY(tr->tg.reserve(rows * D1 * sizeof(float)));
+  TRY(tr->Z.reserve(rows * H * L * sizeof(float)));
+  TRY(tr->Hh.reserve(rows * H * L * sizeof(float)));
+  TRY(tr->out.reserve(rows * HO * sizeof(float)));
+  TRY(tr->dA.reserve(rows * wide * sizeof(float)));
+  TRY(tr->dB.reserve(rows * wide * sizeof(float)));
+  TRY(tr->part.reserve(3 * rows * D1 * sizeof(float)));
+  TRY(tr->scal.reserve((size_t)(2 * E + L + 8) * sizeof(float)));
+  MOPO_COUNT_LAUNCH;
+  gather_scale_kernel<<<grid1d((int64_t)rows * (in + D1)), 256, 0, st>>>(inputs, targets, idx, ld_idx, col0, n, E, in, D1, h->mu,
+                                                                       h->sigma, tr->x.as<float>(), tr->tg.as<float>());
+  const int64_t sAct = (int64_t)n * H;
+  const float* A = tr->x.as<float>();
+  int64_t sA = (int64_t)n * in;
+  int K = in;
+  for (int l = 0; l < L; ++l) {
+    float* Hl = tr->Hh.as<float>() + (size_t)l * rows * H;
+    float* Zl = tr->Z.as<float>() + (size_t)l * rows * H;
+    GemmP p{A, sA, K, 0, h->W[l], (int64_t)K * H, H, 0, Hl, sAct, H, n, H, K, h->b[l], Zl, nullptr};
+    gemm<1>(p, E, st);
+    A = Hl; sA = sAct; K = H;
+  }
+  GemmP p{A, sA, K, 0, h->W[L], (int64_t)H * HO, HO, 0, tr->out.as<float>(), (int64_t)n * HO, HO, n, HO, H, h->b[L], nullptr, nullptr};
+  gemm<2>(p, E, st);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+static int adam(float* p, const float* g, float* m, float* v, size_t n, float lr_t, int ncols, int split, float da, float db,
+                cudaStream_t st) {
+  MOPO_COUNT_LAUNCH;
+  adam_kernel<<<grid1d((int64_t)n), 256, 0, st>>>(p, g, m, v, (int64_t)n, lr_t, ncols, split, da, db);
+  return MOPO_OK;
+}
+
+// One Adam update on the batch inputs[idx[e, col0 : col0 + n]] (bnn.py:423-426).
+static int train_one_batch(mopo_ens* h, const float* inputs, const float* targets, const int32_t* idx, int64_t ld_idx,
+                           int64_t col0, int n, float* loss_out, cudaStream_t st) {
+  mopo_train* tr = h->tr;
+  const int E = h->E, H = h->H, L = h->L, HO = h->HO, D1 = h->D1, in = h->in;
+  const size_t rows = (size_t)E * n;
+  TRY(train_forward(h, inputs, targets, idx, ld_idx, col0, n, st));
+  float* scal = tr->scal.as<float>();          // [0,E): loss_e, [E, E+L+2): decay terms
+  float* dOut = tr->dA.as<float>();
+  MOPO_COUNT_LAUNCH;
+  head_grad_kernel<<<grid1d((int64_t)rows * D1), 256, 0, st>>>(tr->out.as<float>(), tr->tg.as<float>(), h->max_lv, h->min_lv, E, n,
+                                                             D1, dOut, tr->part.as<float>());
+  MOPO_COUNT_LAUNCH;
+  head_reduce_kernel<<<D1 + E, 256, 0, st>>>(tr->part.as<float>(), E, n, D1, tr->g_lv, scal);
+  if (loss_out) {
+    for (int l = 0; l < L; ++l) {
+      MOPO_COUNT_LAUNCH;
+      sumsq_kernel<<<1, 1024, 0, st>>>(h->W[l], (int64_t)(wsize(h, l) / H), H, 0, H, 0.5f * tr->decay[l], scal + E + l);
+    }
+    MOPO_COUNT_LAUNCH;
+    sumsq_kernel<<<1, 1024, 0, st>>>(h->W[L], (int64_t)E * H, HO, 0, D1, 0.5f * tr->decay[L], scal + E + L);
+    MOPO_COUNT_LAUNCH;
+    sumsq_kernel<<<1, 1024, 0, st>>>(h->W[L], (int64_t)E * H, HO, D1, HO, 0.5f * tr->decay[L + 1], scal + E + L + 1);
+    MOPO_COUNT_LAUNCH;
+    loss_total_kernel<<<1, 1, 0, st>>>(scal, E, scal + E, L + 2, h->max_lv, h->min_lv, D1, loss_out);
+  }
+  // backward
+  float* dcur = dOut;                          // dZ of the layer being processed: [E, n, N_l]
+  float* dnext = tr->dB.as<float>();
+  for (int l = L; l >= 0; --l) {
+    const int N = l == L ? HO : H, K = l == 0 ? in : H;
+    const float* In = l == 0 ? tr->x.as<float>() : tr->Hh.as<float>() + (size_t)(l - 1) * rows * H;
+    // gW[l] (K x N) = In^T (K x n) * dZ (n x N)
+    GemmP pw{In, (int64_t)n * K, K, 1, dcur, (int64_t)n * N, N, 0, tr->gW[l], (int64_t)K * N, N, K, N, n, nullptr, nullptr, nullptr};
+    gemm<0>(pw, E, st);
+    MOPO_COUNT_LAUNCH;
+    colsum_kernel<<<dim3((N + 127) / 128, E), 128, 0, st>>>(dcur, tr->gb[l], n, N);
+    if (l > 0) {
+      // dZ_{l-1} (n x K) = (dZ_l (n x N) * W_l^T (N x K)) .* swish'(Z_{l-1})
+      const float* Zp = tr->Z.as<float>() + (size_t)(l - 1) * rows * H;
+      GemmP pd{dcur, (int64_t)n * N, N, 0, h->W[l], (int64_t)K * N, N, 1, dnext, (int64_t)n * K, K, n, K, N, nullptr, nullptr, Zp};
+      gemm<3>(pd, E, st);
+      float* t = dcur; dcur = dnext; dnext = t;
+    }
+  }
+  // Adam (t is the step being applied)
+  tr->t += 1;
+  const double t = (double)tr->t;
+  const float lr_t = (float)((double)tr->lr * sqrt(1.0 - pow((double)ADAM_B2, t)) / (1.0 - pow((double)ADAM_B1, t)));
+  for (int l = 0; l <= L; ++l) {
+    const int N = l == L ? HO : H;
+    const float da = tr->decay[l], db = l == L ? tr->decay[L + 1] : tr->decay[l];
+    TRY(adam(h->W[l], tr->gW[l], tr->mW[l], tr->vW[l], wsize(h, l), lr_t, N, l == L ? D1 : N, da, db, st));
+    TRY(adam(h->b[l], tr->gb[l], tr->mb[l], tr->vb[l], bsize(h, l), lr_t, N, N, 0.f, 0.f, st));
+  }
+  TRY(adam(h->max_lv, tr->g_lv, tr->m_lv, tr->v_lv, D1, lr_t, D1, D1, 0.f, 0.f, st));
+  TRY(adam(h->min_lv, tr->g_lv + D1, tr->m_lv + D1, tr->v_lv + D1, D1, lr_t, D1, D1, 0.f, 0.f, st));
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_train_batches(mopo_ens* h, const float* inputs, const float* targets, int64_t n_rows, const int32_t* idx,
+                                      int64_t ld_idx, int64_t n_cols, int32_t batch_size, float* loss_out, void* stream) {
+  REQUIRE(h && inputs && targets && idx, MOPO_EINVAL, "mopo_ens_train_batches: null argument");
+  REQUIRE(h->tr, MOPO_ESTATE, "mopo_ens_train_batches: call mopo_ens_train_begin first");
+  REQUIRE(n_rows > 0 && n_cols >= 0 && ld_idx >= n_cols && batch_size > 0, MOPO_EINVAL,
+          "mopo_ens_train_batches: n_rows=%lld n_cols=%lld ld_idx=%lld batch_size=%d", (long long)n_rows, (long long)n_cols,
+          (long long)ld_idx, batch_size);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t k = 0;
+  for (int64_t c0 = 0; c0 < n_cols; c0 += batch_size, ++k) {
+    const int n = (int)(n_cols - c0 < batch_size ? n_cols - c0 : batch_size);
+    TRY(train_one_batch(h, inputs, targets, idx, ld_idx, c0, n, loss_out ? loss_out + k : nullptr, st));
+  }
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_train_mse(mopo_ens* h, const float* inputs, const float* targets, const int32_t* idx, int64_t ld_idx,
+                                  int64_t n, float* mse_out, void* stream) {
+  REQUIRE(h && inputs && targets && mse_out, MOPO_EINVAL, "mopo_ens_train_mse: null argument");
+  REQUIRE(h->tr, MOPO_ESTATE, "mopo_ens_train_mse: call mopo_ens_train_begin first");
+  REQUIRE(n > 0 && n < (1 << 24) && (!idx || ld_idx >= n), MOPO_EINVAL, "mopo_ens_train_mse: n=%lld ld_idx=%lld", (long long)n, (long long)ld_idx);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  TRY(train_forward(h, inputs, targets, idx, ld_idx, 0, (int)n, st));
+  MOPO_COUNT_LAUNCH;
+  mse_kernel<<<h->E, 256, 0, st>>>(h->tr->out.as<float>(), h->tr->tg.as<float>(), (int)n, h->D1, mse_out);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_train_snapshot(mopo_ens* h, int32_t net, void* stream) {
+  REQUIRE(h && h->tr, MOPO_ESTATE, "mopo_ens_train_snapshot: call mopo_ens_train_begin first");
+  REQUIRE(net >= 0 && net < h->E, MOPO_EINVAL, "mopo_ens_train_snapshot: net %d outside [0,%d)", net, h->E);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int l = 0; l <= h->L; ++l) {
+    const size_t pw = wsize(h, l) / h->E, pb = bsize(h, l) / h->E;
+    CUDA_TRY(cudaMemcpyAsync(h->tr->sW[l] + net * pw, h->W[l] + net * pw, pw * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(h->tr->sb[l] + net * pb, h->b[l] + net * pb, pb * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  }
+  h->tr->snap[net] = true;
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_train_restore(mopo_ens* h, void* stream) {
+  REQUIRE(h && h->tr, MOPO_ESTATE, "mopo_ens_train_restore: call mopo_ens_train_begin first");
+  for (int e = 0; e < h->E; ++e)     // bnn.py:298: _set_state indexes self._state[net] for every net (KeyError otherwise)
+    REQUIRE(h->tr->snap[e], MOPO_ESTATE, "mopo_ens_train_restore: net %d has no saved state", e);
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int l = 0; l <= h->L; ++l) {
+    CUDA_TRY(cudaMemcpyAsync(h->W[l], h->tr->sW[l], wsize(h, l) * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(h->b[l], h->tr->sb[l], bsize(h, l) * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  }
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_train_end(mopo_ens* h, void* stream) {
+  REQUIRE(h, MOPO_EINVAL, "mopo_ens_train_end: null argument");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (tc_supported(h)) TRY(tc_build_images(h, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  mopo_train_release(h);
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_get_params(mopo_ens* h, float* const* weights, float* const* biases, float* var_w, float* var_b,
+                                   float* max_logvar, float* min_logvar, void* stream) {
+  REQUIRE(h && weights && biases && max_logvar && min_logvar, MOPO_EINVAL, "mopo_ens_get_params: null argument");
+  REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_get_params: parameters not set");
+  REQUIRE(!h->cfg.separate_mean_var || (var_w && var_b), MOPO_EINVAL, "mopo_ens_get_params: separate_mean_var needs var_w/var_b");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int E = h->E, H = h->H, L = h->L, D1 = h->D1, HO = h->HO;
+  for (int l = 0; l < L; ++l) {
+    CUDA_TRY(cudaMemcpyAsync(weights[l], h->W[l], wsize(h, l) * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(biases[l], h->b[l], bsize(h, l) * sizeof(float), cudaMemcpyDeviceToHost, st));
+  }
+  if (!h->cfg.separate_mean_var) {
+    CUDA_TRY(cudaMemcpyAsync(weights[L], h->W[L], wsize(h, L) * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(biases[L], h->b[L], bsize(h, L) * sizeof(float), cudaMemcpyDeviceToHost, st));
+  } else {
+    TRY(h->misc.reserve(sizeof(float) * ((size_t)E * H * D1 + (size_t)E * D1)));
+    float* tw = h->misc.as<float>();
+    float* tb = tw + (size_t)E * H * D1;
+    float* dstw[2] = {weights[L], var_w};
+    float* dstb[2] = {biases[L], var_b};
+    for (int s = 0; s < 2; ++s) {
+      MOPO_COUNT_LAUNCH;
+      take_cols_kernel<<<256, 256, 0, st>>>(h->W[L], tw, (int64_t)E * H, HO, D1, s * D1);
+      MOPO_COUNT_LAUNCH;
+      take_cols_kernel<<<8, 256, 0, st>>>(h->b[L], tb, (int64_t)E, HO, D1, s * D1);
+      CUDA_TRY(cudaGetLastError());
+      CUDA_TRY(cudaMemcpyAsync(dstw[s], tw, (size_t)E * H * D1 * sizeof(float), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaMemcpyAsync(dstb[s], tb, (size_t)E * D1 * sizeof(float), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaStreamSynchronize(st));
+    }
+  }
+  CUDA_TRY(cudaMemcpyAsync(max_logvar, h->max_lv, D1 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(min_logvar, h->min_lv, D1 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return MOPO_OK;
+}

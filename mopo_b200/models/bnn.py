@@ -4,7 +4,7 @@ Host-side mirror of the reference class for the hot path: layer stack (add/final
 max/min-logvar, elite state (_model_inds / random_inds, bnn.py:337-344), predict (bnn.py:508-546)
 and the .mat weight I/O (bnn.py:276-281, 559-592).  All arithmetic is the CUDA library's
 (mopo_ens_predict / mopo_env_step / mopo_rollout); there is no TF session and no CPU path.
-`train` (bnn.py:369-503) is a "next" row and raises NotImplementedError.
+`train` (bnn.py:369-503) runs the reference's loop with every Adam step on the device (csrc/train.cu).
 """
 import ctypes as C
 import os
@@ -26,9 +26,14 @@ class TensorStandardScaler:
         self._on_change = None
 
     def fit(self, data):
-        data = data.detach().cpu().numpy() if torch.is_tensor(data) else np.asarray(data)
-        mu = np.mean(data, axis=0, keepdims=True)
-        sigma = np.std(data, axis=0, keepdims=True)
+        if torch.is_tensor(data) and data.is_cuda:     # training set resident in HBM: reduce there (float64 accumulation)
+            d64 = data.double()
+            mu = d64.mean(0, keepdim=True).float().cpu().numpy()
+            sigma = d64.std(0, unbiased=False, keepdim=True).float().cpu().numpy()
+        else:
+            data = data.detach().cpu().numpy() if torch.is_tensor(data) else np.asarray(data)
+            mu = np.mean(data, axis=0, keepdims=True)
+            sigma = np.std(data, axis=0, keepdims=True)
         sigma[sigma < 1e-12] = 1.0
         self.load(mu, sigma)
         self.fitted = True
@@ -252,9 +257,150 @@ class BNN:
             return mean.cpu().numpy(), var.cpu().numpy()
         return mean, var
 
-    def train(self, *args, **kwargs):
-        raise NotImplementedError("BNN.train (bnn.py:369-503) is outside the rollout hot path (SURVEY.md 8(f) f3); "
-                                  "load reference-trained weights with load_dir / set_params and set _model_inds")
+    # ---- train (bnn.py:369-503) ---------------------------------------------------------------
+    def _start_train(self):                                                # bnn.py:331-334
+        self._snapshots = {i: (None, 1e10) for i in range(self.num_nets)}
+        self._epochs_since_update = 0
+
+    def _save_best(self, epoch, holdout_losses):                           # bnn.py:309-329
+        updated = False
+        lib, st = _lib.load(), _lib.stream_ptr(self.device)
+        for i in range(len(holdout_losses)):
+            current = holdout_losses[i]
+            _, best = self._snapshots[i]
+            improvement = (best - current) / best
+            if improvement > 0.01:
+                self._snapshots[i] = (epoch, current)
+                _lib.check(lib.mopo_ens_train_snapshot(self._handle, i, st))    # _save_state(i), bnn.py:287-290
+                updated = True
+        if updated:
+            self._epochs_since_update = 0
+        else:
+            self._epochs_since_update += 1
+        return self._epochs_since_update > self._max_epochs_since_update
+
+    def _weight_decays(self):
+        """Per-layer rates for the C trainer: hidden layers, mean head, log-variance head (fc.py:155-156)."""
+        d = [l.weight_decay or 0.0 for l in self.layers]
+        d.append((self.var_layers[0].weight_decay or 0.0) if self.separate_mean_var else d[-1])
+        return (C.c_float * len(d))(*d)
+
+    def _pull_params(self):
+        """Device parameters -> the host FC layers (so save() and later scaler pushes see the trained weights)."""
+        outs_w = [np.empty((self.num_nets, l.input_dim, l.output_dim), np.float32) for l in self.layers]
+        outs_b = [np.empty((self.num_nets, 1, l.output_dim), np.float32) for l in self.layers]
+        n = len(self.layers)
+        W = (C.c_void_p * n)(*[a.ctypes.data for a in outs_w])
+        b = (C.c_void_p * n)(*[a.ctypes.data for a in outs_b])
+        vw = vb = None
+        if self.separate_mean_var:
+            vl = self.var_layers[0]
+            vw = np.empty((self.num_nets, vl.input_dim, vl.output_dim), np.float32)
+            vb = np.empty((self.num_nets, 1, vl.output_dim), np.float32)
+        mx, mn = np.empty((1, self.out_dim), np.float32), np.empty((1, self.out_dim), np.float32)
+        _lib.check(_lib.load().mopo_ens_get_params(self._handle, W, b, _lib.ptr(vw), _lib.ptr(vb), mx.ctypes.data,
+                                                   mn.ctypes.data, _lib.stream_ptr(self.device)))
+        for l, w, bb in zip(self.layers, outs_w, outs_b):
+            l.weights, l.biases = w, bb
+        if self.separate_mean_var:
+            self.var_layers[0].weights, self.var_layers[0].biases = vw, vb
+        self.max_logvar, self.min_logvar = mx, mn
+
+    def train(self, inputs, targets, batch_size=32, max_epochs=None, max_epochs_since_update=5, hide_progress=False,
+              holdout_ratio=0.0, max_logging=1000, max_grad_updates=None, timer=None, max_t=None, idxs=None,
+              permutation=None):
+        """BNN.train (bnn.py:369-503) with the optimiser loop on the device: the data set, the bootstrap index matrix
+        and every Adam step stay in HBM; per epoch the host sees only the E holdout losses that drive _save_best.
+        `permutation` / `idxs` (optional) pin the reference's np.random draws (bnn.py:393, 403) for parity tests;
+        otherwise they come from a device generator seeded with the model's seed."""
+        import itertools, time
+        from collections import OrderedDict
+        if self.deterministic:
+            raise NotImplementedError("deterministic=True training loss (bnn.py:246-247) is not built; MOPO trains the probabilistic model")
+        self._max_epochs_since_update = max_epochs_since_update
+        self._start_train()
+        break_train = False
+        dev = self.device
+        lib, st = _lib.load(), _lib.stream_ptr(dev)
+        gen = torch.Generator(device=dev); gen.manual_seed(self.seed + 7919 * (1 + self._rng_calls)); self._rng_calls += 1
+        inputs = torch.as_tensor(inputs).to(device=dev, dtype=torch.float32)
+        targets = torch.as_tensor(targets).to(device=dev, dtype=torch.float32)
+        if inputs.dim() != 2 or inputs.shape[1] != self.in_dim or targets.shape != (inputs.shape[0], self.out_dim):
+            raise ValueError("Invalid input dimension.")
+
+        def shuffle_rows(arr):                                             # bnn.py:388-390
+            order = torch.argsort(torch.rand(arr.shape, device=dev, generator=gen), dim=-1)
+            return torch.gather(arr, 1, order.to(torch.int64)).contiguous()
+
+        # Split into training and holdout sets (bnn.py:392-398)
+        num_holdout = min(int(inputs.shape[0] * holdout_ratio), max_logging)
+        if permutation is None:
+            permutation = torch.randperm(inputs.shape[0], device=dev, generator=gen)
+        permutation = torch.as_tensor(permutation).to(device=dev, dtype=torch.int64)
+        inputs, holdout_inputs = inputs[permutation[num_holdout:]].contiguous(), inputs[permutation[:num_holdout]].contiguous()
+        targets, holdout_targets = targets[permutation[num_holdout:]].contiguous(), targets[permutation[:num_holdout]].contiguous()
+        N = inputs.shape[0]
+        print('[ BNN ] Training {} | Holdout: {}'.format(tuple(inputs.shape), (self.num_nets,) + tuple(holdout_inputs.shape)))
+        self.scaler.fit(inputs)                                            # bnn.py:401-402 (pushes mu / sigma to the device)
+
+        if idxs is None:                                                   # bnn.py:403
+            idxs = torch.randint(N, (self.num_nets, N), device=dev, generator=gen, dtype=torch.int32)
+        idxs = torch.as_tensor(idxs).to(device=dev, dtype=torch.int32).contiguous()
+        if idxs.shape[0] != self.num_nets or int(idxs.max()) >= N or int(idxs.min()) < 0:
+            raise ValueError("idxs must be [num_nets, n] row indices into the training split")
+        epoch_iter = range(max_epochs) if max_epochs is not None else itertools.count()
+
+        self._ensure_handle()
+        _lib.check(lib.mopo_ens_train_begin(self._handle, 1e-3 if not hasattr(self, '_lr') else self._lr, self._weight_decays()))
+        mse_dev = torch.empty(2 * self.num_nets, dtype=torch.float32, device=dev)
+        n_cols = idxs.shape[1]
+        t0 = time.time()
+        grad_updates = 0
+        try:
+            for epoch in epoch_iter:
+                _lib.check(lib.mopo_ens_train_batches(self._handle, inputs.data_ptr(), targets.data_ptr(), N, idxs.data_ptr(),
+                                                      n_cols, n_cols, batch_size, None, st))        # bnn.py:421-427
+                grad_updates += int(np.ceil(n_cols / batch_size))
+                idxs = shuffle_rows(idxs)                                  # bnn.py:429
+                if not hide_progress:
+                    n_log = min(max_logging, n_cols)
+                    _lib.check(lib.mopo_ens_train_mse(self._handle, inputs.data_ptr(), targets.data_ptr(), idxs.data_ptr(),
+                                                      n_cols, n_log, mse_dev.data_ptr(), st))       # bnn.py:431-447
+                    if holdout_ratio >= 1e-12 and num_holdout > 0:
+                        _lib.check(lib.mopo_ens_train_mse(self._handle, holdout_inputs.data_ptr(), holdout_targets.data_ptr(),
+                                                          None, 0, num_holdout, mse_dev[self.num_nets:].data_ptr(), st))
+                        both = mse_dev.cpu().numpy()
+                        losses, holdout_losses = both[:self.num_nets], both[self.num_nets:]
+                        break_train = self._save_best(epoch, holdout_losses)                        # bnn.py:467
+                    else:
+                        losses = mse_dev[:self.num_nets].cpu().numpy()
+                    self._last_train_losses = losses
+                t = time.time() - t0
+                if break_train or (max_grad_updates and grad_updates > max_grad_updates):
+                    break
+                if max_t and t > max_t:
+                    print('Breaking because of timeout: {}! (max: {})'.format(t, max_t))
+                    break
+            if timer: timer.stamp('bnn_train')
+            _lib.check(lib.mopo_ens_train_restore(self._handle, st))       # _set_state, bnn.py:483 (KeyError -> RuntimeError)
+            if timer: timer.stamp('bnn_set_state')
+            if num_holdout > 0:                                            # bnn.py:486-492
+                _lib.check(lib.mopo_ens_train_mse(self._handle, holdout_inputs.data_ptr(), holdout_targets.data_ptr(),
+                                                  None, 0, num_holdout, mse_dev.data_ptr(), st))
+                holdout_losses = mse_dev[:self.num_nets].cpu().numpy()
+            else:
+                holdout_losses = np.full(self.num_nets, np.nan, np.float32)   # TF evaluates a mean over zero rows: nan
+        finally:
+            _lib.check(lib.mopo_ens_train_end(self._handle, st))
+            self._pull_params()
+        self._grad_updates = grad_updates
+        if timer: timer.stamp('bnn_holdout')
+        self._end_train(holdout_losses)
+        if timer: timer.stamp('bnn_end')
+        val_loss = (np.sort(holdout_losses)[:self.num_elites]).mean()
+        model_metrics = {'val_loss': val_loss}
+        print('[ BNN ] Holdout', np.sort(holdout_losses), model_metrics)
+        return OrderedDict(model_metrics)
 
     # ---- .mat weight I/O (bnn.py:276-281, 559-592) --------------------------------------------
     def _all_vars(self):
