@@ -21,12 +21,14 @@ constexpr float ADAM_B1 = 0.9f, ADAM_B2 = 0.999f, ADAM_EPS = 1e-8f;
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
 __device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x))); }
 
-// x[e,b,:] = (inputs[r,:] - mu) / sigma, tg[e,b,:] = targets[r,:] with r = idx ? idx[e*ld + col0 + b] : b
+// x[e,b,:] = (inputs[r,:] - mu) / sigma, tg[e,b,:] = targets[r,:] with r = idx ? idx[e*ld + col0 + b] : b; col0 lives on the
+// device (tick_kernel) so that one captured graph serves every batch of an epoch
 __global__ void gather_scale_kernel(const float* __restrict__ inputs, const float* __restrict__ targets,
-                                    const int32_t* __restrict__ idx, int64_t ld_idx, int64_t col0, int n, int E, int in,
-                                    int D1, const float* __restrict__ mu, const float* __restrict__ sigma,
-                                    float* __restrict__ x, float* __restrict__ tg) {
+                                    const int32_t* __restrict__ idx, int64_t ld_idx, const int64_t* __restrict__ d_col0,
+                                    int n, int E, int in, int D1, const float* __restrict__ mu,
+                                    const float* __restrict__ sigma, float* __restrict__ x, float* __restrict__ tg) {
   const int W = in + D1;
+  const int64_t col0 = d_col0 ? *d_col0 : 0;
   const int64_t tot = (int64_t)E * n * W;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
     int c = (int)(i % W);
@@ -52,55 +54,53 @@ struct GemmP {
   const float* bias; float* Zout; const float* Zin;
 };
 
+// Four elements of a tile along the operand's contiguous dimension: one 16-byte load when the row pitch allows it.
+__device__ __forceinline__ float4 load4(const float* __restrict__ base, int64_t row, int ld, int c, int row_lim, int c_lim, bool vec) {
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (row >= row_lim) return v;
+  const float* q = base + row * ld + c;
+  if (vec && c + 3 < c_lim) return __ldg(reinterpret_cast<const float4*>(q));
+  if (c < c_lim) v.x = __ldg(q);
+  if (c + 1 < c_lim) v.y = __ldg(q + 1);
+  if (c + 2 < c_lim) v.z = __ldg(q + 2);
+  if (c + 3 < c_lim) v.w = __ldg(q + 3);
+  return v;
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(256) train_gemm_kernel(GemmP p) {
   const int e = blockIdx.z;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  __shared__ float As[BK][BM + 4];
-  __shared__ float Bs[BK][BN + 4];
+  __shared__ __align__(16) float As[BK][BM + 4];
+  __shared__ __align__(16) float Bs[BK][BN + 4];
   const float* Ae = p.A + (int64_t)e * p.sA;
   const float* Be = p.B + (int64_t)e * p.sB;
   const int tid = threadIdx.x, tx = tid % 16, ty = tid / 16;
+  const bool vA = (p.lda % 4 == 0) && (p.sA % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0);
+  const bool vB = (p.ldb % 4 == 0) && (p.sB % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0);
+  // tile element owned by this thread for the global -> shared copy (4 along the contiguous dimension)
+  const int a_r = p.tA ? tid / 16 : tid / 4, a_c = p.tA ? (tid % 16) * 4 : (tid % 4) * 4;   // tA: (k, m4)   else (m, k4)
+  const int b_r = p.tB ? tid / 4 : tid / 16, b_c = p.tB ? (tid % 4) * 4 : (tid % 16) * 4;   // tB: (n, k4)   else (k, n4)
+  auto fetchA = [&](int k0) {
+    return p.tA ? load4(Ae, k0 + a_r, p.lda, m0 + a_c, p.K, p.M, vA) : load4(Ae, m0 + a_r, p.lda, k0 + a_c, p.M, p.K, vA);
+  };
+  auto fetchB = [&](int k0) {
+    return p.tB ? load4(Be, n0 + b_r, p.ldb, k0 + b_c, p.N, p.K, vB) : load4(Be, k0 + b_r, p.ldb, n0 + b_c, p.K, p.N, vB);
+  };
   float acc[TM][TN] = {};
+  float4 ra = fetchA(0), rb = fetchB(0);
   for (int k0 = 0; k0 < p.K; k0 += BK) {
-    if (p.tA) {            // A[k, m]: m contiguous
-      for (int i = tid; i < BM * BK; i += 256) {
-        int k = i / BM, m = i % BM;
-        float v = 0.f;
-        if (m0 + m < p.M && k0 + k < p.K) v = Ae[(int64_t)(k0 + k) * p.lda + m0 + m];
-        As[k][m] = v;
-      }
-    } else {               // A[m, k]: k contiguous
-      for (int i = tid; i < BM * BK; i += 256) {
-        int m = i / BK, k = i % BK;
-        float v = 0.f;
-        if (m0 + m < p.M && k0 + k < p.K) v = Ae[(int64_t)(m0 + m) * p.lda + k0 + k];
-        As[k][m] = v;
-      }
-    }
-    if (p.tB) {            // B[n, k]: k contiguous
-      for (int i = tid; i < BK * BN; i += 256) {
-        int n = i / BK, k = i % BK;
-        float v = 0.f;
-        if (k0 + k < p.K && n0 + n < p.N) v = Be[(int64_t)(n0 + n) * p.ldb + k0 + k];
-        Bs[k][n] = v;
-      }
-    } else {               // B[k, n]: n contiguous
-      for (int i = tid; i < BK * BN; i += 256) {
-        int k = i / BN, n = i % BN;
-        float v = 0.f;
-        if (k0 + k < p.K && n0 + n < p.N) v = Be[(int64_t)(k0 + k) * p.ldb + n0 + n];
-        Bs[k][n] = v;
-      }
-    }
+    if (p.tA) *reinterpret_cast<float4*>(&As[a_r][a_c]) = ra;
+    else { As[a_c][a_r] = ra.x; As[a_c + 1][a_r] = ra.y; As[a_c + 2][a_r] = ra.z; As[a_c + 3][a_r] = ra.w; }
+    if (p.tB) { Bs[b_c][b_r] = rb.x; Bs[b_c + 1][b_r] = rb.y; Bs[b_c + 2][b_r] = rb.z; Bs[b_c + 3][b_r] = rb.w; }
+    else *reinterpret_cast<float4*>(&Bs[b_r][b_c]) = rb;
     __syncthreads();
+    if (k0 + BK < p.K) { ra = fetchA(k0 + BK); rb = fetchB(k0 + BK); }     // next tile in flight under this tile's FMAs
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
-      float a[TM], b[TN];
-#pragma unroll
-      for (int i = 0; i < TM; ++i) a[i] = As[k][ty * TM + i];
-#pragma unroll
-      for (int j = 0; j < TN; ++j) b[j] = Bs[k][tx * TN + j];
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * TM]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * TN]);
+      const float a[TM] = {a4.x, a4.y, a4.z, a4.w}, b[TN] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
       for (int i = 0; i < TM; ++i)
 #pragma unroll
@@ -141,14 +141,24 @@ int gemm(const GemmP& p, int E, cudaStream_t st) {
   return MOPO_OK;
 }
 
-// db[e, c] = sum_b dZ[e, b, c]
-__global__ void colsum_kernel(const float* __restrict__ dZ, float* __restrict__ db, int n, int N) {
-  const int e = blockIdx.y, c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= N) return;
-  const float* p = dZ + (int64_t)e * n * N + c;
+// db[e, c] = sum_b dZ[e, b, c]: 32 columns x 8 row groups per block, fixed summation order (deterministic)
+__global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ dZ, float* __restrict__ db, int n, int N) {
+  __shared__ float sh[8][33];
+  const int e = blockIdx.y, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
   float s = 0.f;
-  for (int b = 0; b < n; ++b) s += p[(int64_t)b * N];
-  db[(int64_t)e * N + c] = s;
+  if (c < N) {
+    const float* p = dZ + (int64_t)e * n * N + c;
+    for (int b = w; b < n; b += 8) s += p[(int64_t)b * N];
+  }
+  sh[w][lane] = s;
+  __syncthreads();
+  if (w == 0 && c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sh[i][lane];
+    db[(int64_t)e * N + c] = t;
+  }
 }
 
 // Head backward (bnn.py:669-670, 693-696): out [E,n,2 D1] = [mean | raw] -> dOut (same layout), plus per-element
@@ -254,12 +264,35 @@ __global__ void loss_total_kernel(const float* __restrict__ loss_e, int E, const
   *out = t + 0.01f * a - 0.01f * b;
 }
 
-// tf.train.AdamOptimizer._apply_dense; the weight-decay gradient decay * w is added here (columns < split use decay_a)
-__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-                            int64_t n, float lr_t, int ncols, int split, float decay_a, float decay_b) {
+// Per-batch bookkeeping on the device: ctr = {next batch's first column, Adam step t, this batch's first column};
+// lr_t = lr sqrt(1 - b2^t) / (1 - b1^t) for the step being applied.
+__global__ void tick_kernel(int64_t* __restrict__ ctr, float* __restrict__ lr_t, float lr, int bs) {
+  const int64_t t = ++ctr[1];
+  ctr[2] = ctr[0];
+  ctr[0] += bs;
+  *lr_t = (float)((double)lr * sqrt(1.0 - pow((double)ADAM_B2, (double)t)) / (1.0 - pow((double)ADAM_B1, (double)t)));
+}
+
+// tf.train.AdamOptimizer._apply_dense for every trainable tensor in ONE launch (blockIdx.y = tensor); the weight-decay
+// gradient decay * w is added here (columns < split use decay_a, the rest decay_b: the fused [mean | logvar] head).
+constexpr int ADAM_MAX_TENSORS = 2 * MOPO_MAX_LAYERS + 2;
+struct AdamBatch {
+  float* p[ADAM_MAX_TENSORS]; const float* g[ADAM_MAX_TENSORS]; float* m[ADAM_MAX_TENSORS]; float* v[ADAM_MAX_TENSORS];
+  int64_t n[ADAM_MAX_TENSORS]; int ncols[ADAM_MAX_TENSORS], split[ADAM_MAX_TENSORS];
+  float decay_a[ADAM_MAX_TENSORS], decay_b[ADAM_MAX_TENSORS];
+  const float* lr_t;
+};
+__global__ void __launch_bounds__(256) adam_kernel(AdamBatch a) {
+  const int t = blockIdx.y;
+  const float lr_t = *a.lr_t;
+  float* __restrict__ p = a.p[t]; const float* __restrict__ g = a.g[t];
+  float* __restrict__ m = a.m[t]; float* __restrict__ v = a.v[t];
+  const int64_t n = a.n[t];
+  const int ncols = a.ncols[t], split = a.split[t];
+  const float da = a.decay_a[t], db = a.decay_b[t];
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float w = p[i];
-    float dec = ((int)(i % ncols) < split) ? decay_a : decay_b;
+    float dec = ((int)(i % ncols) < split) ? da : db;
     float gi = fmaf(dec, w, g[i]);
     float mi = ADAM_B1 * m[i] + (1.0f - ADAM_B1) * gi;
     float vi = ADAM_B2 * v[i] + (1.0f - ADAM_B2) * gi * gi;
@@ -295,6 +328,13 @@ struct mopo_train {
   float *g_lv = nullptr, *m_lv = nullptr, *v_lv = nullptr;   // [2 D1]: max | min
   bool snap[MOPO_MAX_E] = {};
   DevBuf x, tg, Z, Hh, out, dA, dB, part, scal;
+  cudaStream_t side = nullptr;   // weight / bias gradients run here, beside the data-gradient chain
+  cudaEvent_t ev_fork[MOPO_MAX_LAYERS] = {}, ev_join = nullptr;
+  int64_t* ctr = nullptr;      // device {next col0, Adam t, current col0}
+  float* lr_t = nullptr;       // device
+  // the captured batch step (full batches on a non-default stream): valid for exactly these arguments
+  cudaGraphExec_t graph = nullptr;
+  const void *g_in = nullptr, *g_tg = nullptr, *g_idx = nullptr; int64_t g_ld = 0; int g_bs = 0; int g_nodes = 0;
 };
 
 static size_t wsize(const mopo_ens* h, int l) { return (size_t)h->E * (l == 0 ? h->in : h->H) * (l == h->L ? h->HO : h->H); }
@@ -310,6 +350,12 @@ static void train_free(mopo_train* tr) {
   for (float* p : qs) if (p) cudaFree(p);
   DevBuf* bufs[] = {&tr->x, &tr->tg, &tr->Z, &tr->Hh, &tr->out, &tr->dA, &tr->dB, &tr->part, &tr->scal};
   for (DevBuf* b : bufs) b->release();
+  if (tr->ctr) cudaFree(tr->ctr);
+  if (tr->lr_t) cudaFree(tr->lr_t);
+  if (tr->graph) cudaGraphExecDestroy(tr->graph);
+  for (cudaEvent_t e : tr->ev_fork) if (e) cudaEventDestroy(e);
+  if (tr->ev_join) cudaEventDestroy(tr->ev_join);
+  if (tr->side) cudaStreamDestroy(tr->side);
   delete tr;
 }
 
@@ -333,27 +379,43 @@ MOPO_API int mopo_ens_train_begin(mopo_ens* h, float lr, const float* weight_dec
   }
   float** qs[] = {&tr->g_lv, &tr->m_lv, &tr->v_lv};
   for (float** p : qs) { CUDA_TRY(cudaMalloc(p, 2 * h->D1 * sizeof(float))); CUDA_TRY(cudaMemset(*p, 0, 2 * h->D1 * sizeof(float))); }
+  CUDA_TRY(cudaMalloc(&tr->ctr, 4 * sizeof(int64_t)));
+  CUDA_TRY(cudaMemset(tr->ctr, 0, 4 * sizeof(int64_t)));
+  CUDA_TRY(cudaMalloc(&tr->lr_t, sizeof(float)));
+  CUDA_TRY(cudaStreamCreateWithFlags(&tr->side, cudaStreamNonBlocking));
+  for (int l = 0; l <= h->L; ++l) CUDA_TRY(cudaEventCreateWithFlags(&tr->ev_fork[l], cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&tr->ev_join, cudaEventDisableTiming));
+  return MOPO_OK;
+}
+
+// Scratch for n rows per net.  Growing a buffer moves it, which invalidates the captured graph.
+static int train_reserve(mopo_ens* h, int n) {
+  mopo_train* tr = h->tr;
+  const int E = h->E, H = h->H, L = h->L, HO = h->HO, D1 = h->D1, in = h->in;
+  const size_t rows = (size_t)E * n;
+  const int wide = H > HO ? H : HO;
+  DevBuf* bufs[] = {&tr->x, &tr->tg, &tr->Z, &tr->Hh, &tr->out, &tr->dA, &tr->dB, &tr->part, &tr->scal};
+  const size_t want[] = {rows * in, rows * D1, rows * H * L, rows * H * L, rows * HO, rows * wide, rows * wide * L, 3 * rows * D1,
+                         (size_t)(2 * E + L + 8)};
+  bool moved = false;
+  for (int i = 0; i < 9; ++i) {
+    void* before = bufs[i]->p;
+    TRY(bufs[i]->reserve(want[i] * sizeof(float)));
+    moved |= before != bufs[i]->p;
+  }
+  if (moved && tr->graph) { cudaGraphExecDestroy(tr->graph); tr->graph = nullptr; }
   return MOPO_OK;
 }
 
 // Forward of n rows per net into tr->out ([E,n,2 D1] = [mean | raw log-variance]); keeps Z / H of every hidden layer.
 static int train_forward(mopo_ens* h, const float* inputs, const float* targets, const int32_t* idx, int64_t ld_idx,
-                         int64_t col0, int n, cudaStream_t st) {
+                         const int64_t* d_col0, int n, cudaStream_t st) {
   mopo_train* tr = h->tr;
   const int E = h->E, H = h->H, L = h->L, HO = h->HO, D1 = h->D1, in = h->in;
   const size_t rows = (size_t)E * n;
-  const int wide = H > HO ? H : HO;
-  TRY(tr->x.reserve(rows * in * sizeof(float)));
-  TRY(tr->tg.reserve(rows * D1 * sizeof(float)));
-  TRY(tr->Z.reserve(rows * H * L * sizeof(float)));
-  TRY(tr->Hh.reserve(rows * H * L * sizeof(float)));
-  TRY(tr->out.reserve(rows * HO * sizeof(float)));
-  TRY(tr->dA.reserve(rows * wide * sizeof(float)));
-  TRY(tr->dB.reserve(rows * wide * sizeof(float)));
-  TRY(tr->part.reserve(3 * rows * D1 * sizeof(float)));
-  TRY(tr->scal.reserve((size_t)(2 * E + L + 8) * sizeof(float)));
+  TRY(train_reserve(h, n));
   MOPO_COUNT_LAUNCH;
-  gather_scale_kernel<<<grid1d((int64_t)rows * (in + D1)), 256, 0, st>>>(inputs, targets, idx, ld_idx, col0, n, E, in, D1, h->mu,
+  gather_scale_kernel<<<grid1d((int64_t)rows * (in + D1)), 256, 0, st>>>(inputs, targets, idx, ld_idx, d_col0, n, E, in, D1, h->mu,
                                                                        h->sigma, tr->x.as<float>(), tr->tg.as<float>());
   const int64_t sAct = (int64_t)n * H;
   const float* A = tr->x.as<float>();
@@ -372,20 +434,16 @@ static int train_forward(mopo_ens* h, const float* inputs, const float* targets,
   return MOPO_OK;
 }
 
-static int adam(float* p, const float* g, float* m, float* v, size_t n, float lr_t, int ncols, int split, float da, float db,
-                cudaStream_t st) {
-  MOPO_COUNT_LAUNCH;
-  adam_kernel<<<grid1d((int64_t)n), 256, 0, st>>>(p, g, m, v, (int64_t)n, lr_t, ncols, split, da, db);
-  return MOPO_OK;
-}
-
-// One Adam update on the batch inputs[idx[e, col0 : col0 + n]] (bnn.py:423-426).
+// One Adam update on the batch inputs[idx[e, col0 : col0 + n]] (bnn.py:423-426); col0 and the Adam step count advance on
+// the device (tick_kernel), so the same launch sequence -- or its captured graph -- serves every batch.
 static int train_one_batch(mopo_ens* h, const float* inputs, const float* targets, const int32_t* idx, int64_t ld_idx,
-                           int64_t col0, int n, float* loss_out, cudaStream_t st) {
+                           int bs, int n, float* loss_out, cudaStream_t st) {
   mopo_train* tr = h->tr;
   const int E = h->E, H = h->H, L = h->L, HO = h->HO, D1 = h->D1, in = h->in;
   const size_t rows = (size_t)E * n;
-  TRY(train_forward(h, inputs, targets, idx, ld_idx, col0, n, st));
+  MOPO_COUNT_LAUNCH;
+  tick_kernel<<<1, 1, 0, st>>>(tr->ctr, tr->lr_t, tr->lr, bs);
+  TRY(train_forward(h, inputs, targets, idx, ld_idx, tr->ctr + 2, n, st));
   float* scal = tr->scal.as<float>();          // [0,E): loss_e, [E, E+L+2): decay terms
   float* dOut = tr->dA.as<float>();
   MOPO_COUNT_LAUNCH;
@@ -405,37 +463,50 @@ static int train_one_batch(mopo_ens* h, const float* inputs, const float* target
     MOPO_COUNT_LAUNCH;
     loss_total_kernel<<<1, 1, 0, st>>>(scal, E, scal + E, L + 2, h->max_lv, h->min_lv, D1, loss_out);
   }
-  // backward
-  float* dcur = dOut;                          // dZ of the layer being processed: [E, n, N_l]
-  float* dnext = tr->dB.as<float>();
+  // backward.  dZ_l feeds three independent consumers: gW_l = In_l^T dZ_l, gb_l = colsum(dZ_l) (side stream) and the
+  // chain dZ_{l-1} = (dZ_l W_l^T) .* swish'(Z_{l-1}) (main stream); every dZ_l has its own buffer so the branches overlap.
+  const int wide = H > HO ? H : HO;
+  float* dZ[MOPO_MAX_LAYERS];
+  dZ[L] = dOut;
+  for (int l = 0; l < L; ++l) dZ[l] = tr->dB.as<float>() + (size_t)l * rows * wide;
   for (int l = L; l >= 0; --l) {
     const int N = l == L ? HO : H, K = l == 0 ? in : H;
     const float* In = l == 0 ? tr->x.as<float>() : tr->Hh.as<float>() + (size_t)(l - 1) * rows * H;
+    CUDA_TRY(cudaEventRecord(tr->ev_fork[l], st));
+    CUDA_TRY(cudaStreamWaitEvent(tr->side, tr->ev_fork[l], 0));
     // gW[l] (K x N) = In^T (K x n) * dZ (n x N)
-    GemmP pw{In, (int64_t)n * K, K, 1, dcur, (int64_t)n * N, N, 0, tr->gW[l], (int64_t)K * N, N, K, N, n, nullptr, nullptr, nullptr};
-    gemm<0>(pw, E, st);
+    GemmP pw{In, (int64_t)n * K, K, 1, dZ[l], (int64_t)n * N, N, 0, tr->gW[l], (int64_t)K * N, N, K, N, n, nullptr, nullptr, nullptr};
+    gemm<0>(pw, E, tr->side);
     MOPO_COUNT_LAUNCH;
-    colsum_kernel<<<dim3((N + 127) / 128, E), 128, 0, st>>>(dcur, tr->gb[l], n, N);
+    colsum_kernel<<<dim3((N + 31) / 32, E), 256, 0, tr->side>>>(dZ[l], tr->gb[l], n, N);
     if (l > 0) {
       // dZ_{l-1} (n x K) = (dZ_l (n x N) * W_l^T (N x K)) .* swish'(Z_{l-1})
       const float* Zp = tr->Z.as<float>() + (size_t)(l - 1) * rows * H;
-      GemmP pd{dcur, (int64_t)n * N, N, 0, h->W[l], (int64_t)K * N, N, 1, dnext, (int64_t)n * K, K, n, K, N, nullptr, nullptr, Zp};
+      GemmP pd{dZ[l], (int64_t)n * N, N, 0, h->W[l], (int64_t)K * N, N, 1, dZ[l - 1], (int64_t)n * K, K, n, K, N, nullptr, nullptr, Zp};
       gemm<3>(pd, E, st);
-      float* t = dcur; dcur = dnext; dnext = t;
     }
   }
-  // Adam (t is the step being applied)
-  tr->t += 1;
-  const double t = (double)tr->t;
-  const float lr_t = (float)((double)tr->lr * sqrt(1.0 - pow((double)ADAM_B2, t)) / (1.0 - pow((double)ADAM_B1, t)));
+  CUDA_TRY(cudaEventRecord(tr->ev_join, tr->side));
+  CUDA_TRY(cudaStreamWaitEvent(st, tr->ev_join, 0));
+  AdamBatch ab;
+  int nt = 0;
+  size_t biggest = 0;
+  auto add = [&](float* p, const float* g, float* m, float* v, size_t cnt, int ncols, int split, float da, float db) {
+    ab.p[nt] = p; ab.g[nt] = g; ab.m[nt] = m; ab.v[nt] = v; ab.n[nt] = (int64_t)cnt; ab.ncols[nt] = ncols; ab.split[nt] = split;
+    ab.decay_a[nt] = da; ab.decay_b[nt] = db; ++nt;
+    if (cnt > biggest) biggest = cnt;
+  };
   for (int l = 0; l <= L; ++l) {
     const int N = l == L ? HO : H;
-    const float da = tr->decay[l], db = l == L ? tr->decay[L + 1] : tr->decay[l];
-    TRY(adam(h->W[l], tr->gW[l], tr->mW[l], tr->vW[l], wsize(h, l), lr_t, N, l == L ? D1 : N, da, db, st));
-    TRY(adam(h->b[l], tr->gb[l], tr->mb[l], tr->vb[l], bsize(h, l), lr_t, N, N, 0.f, 0.f, st));
+    add(h->W[l], tr->gW[l], tr->mW[l], tr->vW[l], wsize(h, l), N, l == L ? D1 : N, tr->decay[l], l == L ? tr->decay[L + 1] : tr->decay[l]);
+    add(h->b[l], tr->gb[l], tr->mb[l], tr->vb[l], bsize(h, l), N, N, 0.f, 0.f);
   }
-  TRY(adam(h->max_lv, tr->g_lv, tr->m_lv, tr->v_lv, D1, lr_t, D1, D1, 0.f, 0.f, st));
-  TRY(adam(h->min_lv, tr->g_lv + D1, tr->m_lv + D1, tr->v_lv + D1, D1, lr_t, D1, D1, 0.f, 0.f, st));
+  add(h->max_lv, tr->g_lv, tr->m_lv, tr->v_lv, D1, D1, D1, 0.f, 0.f);
+  add(h->min_lv, tr->g_lv + D1, tr->m_lv + D1, tr->v_lv + D1, D1, D1, D1, 0.f, 0.f);
+  ab.lr_t = tr->lr_t;
+  int gx = (int)((biggest + 1023) / 1024); if (gx < 1) gx = 1; if (gx > 148) gx = 148;
+  MOPO_COUNT_LAUNCH;
+  adam_kernel<<<dim3(gx, nt), 256, 0, st>>>(ab);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -449,10 +520,42 @@ MOPO_API int mopo_ens_train_batches(mopo_ens* h, const float* inputs, const floa
           (long long)ld_idx, batch_size);
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemsetAsync(h->tr->ctr, 0, sizeof(int64_t), st));      // first column of this call's first batch
+  mopo_train* tr = h->tr;
+  const int64_t n_full = n_cols / batch_size;
   int64_t k = 0;
-  for (int64_t c0 = 0; c0 < n_cols; c0 += batch_size, ++k) {
+  // Launch-bound loop (35 small kernels per batch): capture one full batch once, replay it for the others.
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (st) CUDA_TRY(cudaStreamIsCapturing(st, &cap));
+  if (st && cap == cudaStreamCaptureStatusNone && !loss_out && n_full >= 4) {
+    TRY(train_reserve(h, batch_size));
+    bool fresh = false;
+    if (!(tr->graph && tr->g_in == inputs && tr->g_tg == targets && tr->g_idx == idx && tr->g_ld == ld_idx && tr->g_bs == batch_size)) {
+      if (tr->graph) { cudaGraphExecDestroy(tr->graph); tr->graph = nullptr; }
+      cudaGraph_t g = nullptr;
+      const long long before = (long long)mopo_launch_count();
+      CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      int rc = train_one_batch(h, inputs, targets, idx, ld_idx, batch_size, batch_size, nullptr, st);
+      cudaError_t ce = cudaStreamEndCapture(st, &g);
+      if (rc != MOPO_OK) { if (g) cudaGraphDestroy(g); return rc; }
+      CUDA_TRY(ce);
+      tr->g_nodes = (int)((long long)mopo_launch_count() - before);
+      cudaError_t ci = cudaGraphInstantiate(&tr->graph, g, 0);
+      cudaGraphDestroy(g);
+      CUDA_TRY(ci);
+      tr->g_in = inputs; tr->g_tg = targets; tr->g_idx = idx; tr->g_ld = ld_idx; tr->g_bs = batch_size;
+      fresh = true;                     // the launches counted during the capture stand for the first replay
+    }
+    for (; k < n_full; ++k) {
+      CUDA_TRY(cudaGraphLaunch(tr->graph, st));
+      if (!(fresh && k == 0)) for (int i = 0; i < tr->g_nodes; ++i) mopo_count_launch();
+    }
+    tr->t += n_full;
+  }
+  for (int64_t c0 = k * batch_size; c0 < n_cols; c0 += batch_size, ++k) {
     const int n = (int)(n_cols - c0 < batch_size ? n_cols - c0 : batch_size);
-    TRY(train_one_batch(h, inputs, targets, idx, ld_idx, c0, n, loss_out ? loss_out + k : nullptr, st));
+    TRY(train_one_batch(h, inputs, targets, idx, ld_idx, batch_size, n, loss_out ? loss_out + k : nullptr, st));
+    tr->t += 1;
   }
   return MOPO_OK;
 }
@@ -464,7 +567,7 @@ MOPO_API int mopo_ens_train_mse(mopo_ens* h, const float* inputs, const float* t
   REQUIRE(n > 0 && n < (1 << 24) && (!idx || ld_idx >= n), MOPO_EINVAL, "mopo_ens_train_mse: n=%lld ld_idx=%lld", (long long)n, (long long)ld_idx);
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
-  TRY(train_forward(h, inputs, targets, idx, ld_idx, 0, (int)n, st));
+  TRY(train_forward(h, inputs, targets, idx, ld_idx, nullptr, (int)n, st));
   MOPO_COUNT_LAUNCH;
   mse_kernel<<<h->E, 256, 0, st>>>(h->tr->out.as<float>(), h->tr->tg.as<float>(), (int)n, h->D1, mse_out);
   CUDA_TRY(cudaGetLastError());

@@ -350,49 +350,59 @@ class BNN:
             raise ValueError("idxs must be [num_nets, n] row indices into the training split")
         epoch_iter = range(max_epochs) if max_epochs is not None else itertools.count()
 
-        self._ensure_handle()
-        _lib.check(lib.mopo_ens_train_begin(self._handle, 1e-3 if not hasattr(self, '_lr') else self._lr, self._weight_decays()))
-        mse_dev = torch.empty(2 * self.num_nets, dtype=torch.float32, device=dev)
-        n_cols = idxs.shape[1]
-        t0 = time.time()
-        grad_updates = 0
-        try:
-            for epoch in epoch_iter:
-                _lib.check(lib.mopo_ens_train_batches(self._handle, inputs.data_ptr(), targets.data_ptr(), N, idxs.data_ptr(),
-                                                      n_cols, n_cols, batch_size, None, st))        # bnn.py:421-427
-                grad_updates += int(np.ceil(n_cols / batch_size))
-                idxs = shuffle_rows(idxs)                                  # bnn.py:429
-                if not hide_progress:
-                    n_log = min(max_logging, n_cols)
-                    _lib.check(lib.mopo_ens_train_mse(self._handle, inputs.data_ptr(), targets.data_ptr(), idxs.data_ptr(),
-                                                      n_cols, n_log, mse_dev.data_ptr(), st))       # bnn.py:431-447
-                    if holdout_ratio >= 1e-12 and num_holdout > 0:
-                        _lib.check(lib.mopo_ens_train_mse(self._handle, holdout_inputs.data_ptr(), holdout_targets.data_ptr(),
-                                                          None, 0, num_holdout, mse_dev[self.num_nets:].data_ptr(), st))
-                        both = mse_dev.cpu().numpy()
-                        losses, holdout_losses = both[:self.num_nets], both[self.num_nets:]
-                        break_train = self._save_best(epoch, holdout_losses)                        # bnn.py:467
-                    else:
-                        losses = mse_dev[:self.num_nets].cpu().numpy()
-                    self._last_train_losses = losses
-                t = time.time() - t0
-                if break_train or (max_grad_updates and grad_updates > max_grad_updates):
-                    break
-                if max_t and t > max_t:
-                    print('Breaking because of timeout: {}! (max: {})'.format(t, max_t))
-                    break
-            if timer: timer.stamp('bnn_train')
-            _lib.check(lib.mopo_ens_train_restore(self._handle, st))       # _set_state, bnn.py:483 (KeyError -> RuntimeError)
-            if timer: timer.stamp('bnn_set_state')
-            if num_holdout > 0:                                            # bnn.py:486-492
-                _lib.check(lib.mopo_ens_train_mse(self._handle, holdout_inputs.data_ptr(), holdout_targets.data_ptr(),
-                                                  None, 0, num_holdout, mse_dev.data_ptr(), st))
-                holdout_losses = mse_dev[:self.num_nets].cpu().numpy()
-            else:
-                holdout_losses = np.full(self.num_nets, np.nan, np.float32)   # TF evaluates a mean over zero rows: nan
-        finally:
-            _lib.check(lib.mopo_ens_train_end(self._handle, st))
-            self._pull_params()
+        # The optimiser loop runs on a side stream: its 35 small launches per batch are captured once into a CUDA graph
+        # and replayed (stream capture is not possible on the legacy default stream).
+        cur = torch.cuda.current_stream(dev)
+        if getattr(self, '_train_stream', None) is None:
+            self._train_stream = torch.cuda.Stream(dev)
+        self._train_stream.wait_stream(cur)
+        with torch.cuda.stream(self._train_stream):
+            st = _lib.stream_ptr(dev)
+            self._ensure_handle()
+            _lib.check(lib.mopo_ens_train_begin(self._handle, 1e-3 if not hasattr(self, '_lr') else self._lr, self._weight_decays()))
+            mse_dev = torch.empty(2 * self.num_nets, dtype=torch.float32, device=dev)
+            n_cols = idxs.shape[1]
+            t0 = time.time()
+            grad_updates = 0
+            try:
+                for epoch in epoch_iter:
+                    _lib.check(lib.mopo_ens_train_batches(self._handle, inputs.data_ptr(), targets.data_ptr(), N, idxs.data_ptr(),
+                                                          n_cols, n_cols, batch_size, None, st))        # bnn.py:421-427
+                    grad_updates += int(np.ceil(n_cols / batch_size))
+                    idxs = shuffle_rows(idxs)                                  # bnn.py:429
+                    if not hide_progress:
+                        n_log = min(max_logging, n_cols)
+                        _lib.check(lib.mopo_ens_train_mse(self._handle, inputs.data_ptr(), targets.data_ptr(), idxs.data_ptr(),
+                                                          n_cols, n_log, mse_dev.data_ptr(), st))       # bnn.py:431-447
+                        if holdout_ratio >= 1e-12 and num_holdout > 0:
+                            _lib.check(lib.mopo_ens_train_mse(self._handle, holdout_inputs.data_ptr(), holdout_targets.data_ptr(),
+                                                              None, 0, num_holdout, mse_dev[self.num_nets:].data_ptr(), st))
+                            both = mse_dev.cpu().numpy()
+                            losses, holdout_losses = both[:self.num_nets], both[self.num_nets:]
+                            break_train = self._save_best(epoch, holdout_losses)                        # bnn.py:467
+                        else:
+                            losses = mse_dev[:self.num_nets].cpu().numpy()
+                        self._last_train_losses = losses
+                    t = time.time() - t0
+                    if break_train or (max_grad_updates and grad_updates > max_grad_updates):
+                        break
+                    if max_t and t > max_t:
+                        print('Breaking because of timeout: {}! (max: {})'.format(t, max_t))
+                        break
+                if timer: timer.stamp('bnn_train')
+                _lib.check(lib.mopo_ens_train_restore(self._handle, st))       # _set_state, bnn.py:483 (KeyError -> RuntimeError)
+                if timer: timer.stamp('bnn_set_state')
+                if num_holdout > 0:                                            # bnn.py:486-492
+                    _lib.check(lib.mopo_ens_train_mse(self._handle, holdout_inputs.data_ptr(), holdout_targets.data_ptr(),
+                                                      None, 0, num_holdout, mse_dev.data_ptr(), st))
+                    holdout_losses = mse_dev[:self.num_nets].cpu().numpy()
+                else:
+                    holdout_losses = np.full(self.num_nets, np.nan, np.float32)   # TF evaluates a mean over zero rows: nan
+            finally:
+                _lib.check(lib.mopo_ens_train_end(self._handle, st))
+                self._pull_params()
+
+        cur.wait_stream(self._train_stream)
         self._grad_updates = grad_updates
         if timer: timer.stamp('bnn_holdout')
         self._end_train(holdout_losses)

@@ -292,3 +292,34 @@ def test_bnn_train_learns_and_feeds_the_rollout(tmp_path):
     # no holdout -> no saved state -> the reference's KeyError in _set_state (bnn.py:298), RuntimeError here
     with pytest.raises(RuntimeError):
         model.train(inputs[:500], targets[:500], batch_size=256, max_epochs=1, holdout_ratio=0.0)
+
+
+@pytest.mark.gpu
+def test_train_graph_replay_equals_direct_launches():
+    """On a non-default stream the full batches of an epoch replay one captured CUDA graph (column offset and Adam
+    step count live on the device); the result is bit-identical to launching every kernel directly, over two epochs
+    with a ragged last batch, and the launch count claims the same number of kernels."""
+    import torch
+    from mopo_b200 import _lib
+    p, inputs, targets, rng = _problem(17, 6, 200, 7, True, 1000, seed=21)
+    n_cols, bs = 6 * 64 + 17, 64
+    idx = rng.randint(1000, size=(7, n_cols)).astype(np.int32)
+    d_in, d_tg, d_idx = (torch.as_tensor(a).cuda() for a in (inputs, targets, idx))
+    results, counts = [], []
+    side = torch.cuda.Stream()
+    for stream in (None, side):
+        lib, h = _handle(p)
+        _lib.check(lib.mopo_ens_train_begin(h, 1e-3, _decays(p)))
+        torch.cuda.synchronize()
+        c0 = lib.mopo_launch_count()
+        for _ in range(2):
+            _lib.check(lib.mopo_ens_train_batches(h, d_in.data_ptr(), d_tg.data_ptr(), 1000, d_idx.data_ptr(), n_cols, n_cols, bs,
+                                                  None, stream.cuda_stream if stream is not None else None))
+        torch.cuda.synchronize()
+        counts.append(lib.mopo_launch_count() - c0)
+        results.append(_get_params(lib, h, p))
+        _lib.check(lib.mopo_ens_train_end(h, None))
+        lib.mopo_ens_destroy(h)
+    assert counts[0] == counts[1] and counts[0] % 14 == 0
+    for (ac, ak), (bc, bk) in zip(otr._leaves(results[0]), otr._leaves(results[1])):
+        assert np.array_equal(ac[ak], bc[bk]), ak
