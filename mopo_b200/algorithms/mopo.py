@@ -1,5 +1,5 @@
 """The slice of the MOPO algorithm class that is the hot path (reference mopo/algorithms/mopo.py):
-_set_rollout_length (:675-687), _reallocate_model_pool (:689-711), _rollout_model (:723-765).
+_set_rollout_length (:675-687), _reallocate_model_pool (:689-711), _train_model (:712-720), _rollout_model (:723-765).
 
 `ModelRollout` carries exactly the attributes those methods read on `self` in the reference
 (_rollout_schedule, _epoch, _rollout_batch_size, _epoch_length, _model_train_freq,
@@ -76,6 +76,27 @@ class ModelRollout:
             new_pool.add_samples(samples)
             assert self._model_pool.size == new_pool.size
             self._model_pool = new_pool
+
+    # ---- mopo.py:712-720 -----------------------------------------------------------------------
+    def _train_model(self, **kwargs):
+        """env pool -> (obs|act) / (rew|delta obs) -> BNN.train, all in HBM.  Under torch.distributed the optimiser loop is
+        latency-bound, so rank 0 trains and the parameters + elites are broadcast (one NCCL call)."""
+        from ..models.constructor import format_samples_for_training
+        from .. import dist as mdist
+        import torch.distributed as tdist
+        if self._model_type == 'identity':
+            print('[ MOPO ] Identity model, skipping model')
+            return {}
+        model = self.fake_env.model
+        multi = tdist.is_available() and tdist.is_initialized() and tdist.get_world_size() > 1
+        model_metrics = {}
+        if not multi or tdist.get_rank() == 0:
+            env_samples = self._pool.return_all_samples(as_numpy=False)
+            train_inputs, train_outputs = format_samples_for_training(env_samples)
+            model_metrics = model.train(train_inputs, train_outputs, **kwargs)
+        if multi:
+            mdist.broadcast_params(model, src=0)
+        return model_metrics
 
     # ---- mopo.py:723-765 -----------------------------------------------------------------------
     def _rollout_model(self, rollout_batch_size, start_obs=None, actions=None, noise=None, model_inds=None,

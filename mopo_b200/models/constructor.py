@@ -45,6 +45,9 @@ def format_samples_for_training(samples):
     """constructor.py:46-57: (obs|act) -> (rew|delta_obs)."""
     obs, act, next_obs, rew = samples['observations'], samples['actions'], samples['next_observations'], samples['rewards']
     delta_obs = next_obs - obs
+    if hasattr(obs, 'is_cuda'):                  # device pool fields stay in HBM (torch tensors)
+        import torch
+        return torch.cat((obs, act), dim=-1), torch.cat((rew, delta_obs), dim=-1)
     inputs = np.concatenate((obs, act), axis=-1)
     outputs = np.concatenate((rew, delta_obs), axis=-1)
     return inputs, outputs

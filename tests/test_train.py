@@ -323,3 +323,44 @@ def test_train_graph_replay_equals_direct_launches():
     assert counts[0] == counts[1] and counts[0] % 14 == 0
     for (ac, ak), (bc, bk) in zip(otr._leaves(results[0]), otr._leaves(results[1])):
         assert np.array_equal(ac[ak], bc[bk]), ak
+
+
+@pytest.mark.gpu
+def test_train_model_then_rollout_stays_on_device():
+    """MOPO's model phase end to end (mopo.py:528-529, 554-560): offline env pool -> _train_model (BNN.train on the pool's
+    device fields) -> elites -> _rollout_model with the on-device actor on the tensor-core path into the model pool."""
+    import torch
+    from mopo_b200 import _lib
+    import mopo_b200.static as static
+    from mopo_b200.models.constructor import construct_model
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    from mopo_b200.policies import GaussianPolicy
+    samples = _dynamics(5000, obs_dim=17, act_dim=6, seed=2)
+    samples['terminals'] = np.zeros((5000, 1), bool)
+    env_pool = SimpleReplayPool(17, 6, 5000)
+    env_pool.add_samples(samples)
+    model = construct_model(obs_dim=17, act_dim=6, hidden_dim=200, num_networks=7, num_elites=5, separate_mean_var=True,
+                            precision=_lib.PREC_BF16, seed=5)
+    env = FakeEnv(model, static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=7)
+    from oracle import policy as opol
+    pol = GaussianPolicy(17, 6, device=0, precision=_lib.PREC_BF16, seed=9)
+    pol.set_params(*opol.init_params(17, 6, seed=4))
+    ro = ModelRollout(env, env_pool, rollout_batch_size=2000, rollout_schedule=(0, 1, 3, 3), epoch_length=1000,
+                      model_train_freq=1000, model_retain_epochs=1, policy=pol, seed=3)
+    metrics = ro._train_model(batch_size=256, max_epochs=8, holdout_ratio=0.2)
+    assert np.isfinite(metrics['val_loss']) and len(model._model_inds) == 5
+    ro._set_rollout_length()
+    ro._reallocate_model_pool()
+    stats = ro._rollout_model(2000, quiet=True)
+    torch.cuda.synchronize()
+    assert stats['mean_rollout_length'] == 3.0 and ro._model_pool.size == 6000
+    f = {k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()}
+    assert np.isfinite(f['next_observations']).all() and np.isfinite(f['rewards']).all()
+    # the trained model is a model of these dynamics: one-step predictions from pool states track the generator
+    x = np.concatenate([samples['observations'][:300], samples['actions'][:300]], -1)
+    mean, _ = model.predict(x, factored=False, precision=_lib.PREC_FP32)
+    want = np.concatenate([samples['rewards'][:300], samples['next_observations'][:300] - samples['observations'][:300]], -1)
+    base = (want ** 2).mean()
+    assert ((mean - want) ** 2).mean() < 0.5 * base
