@@ -19,6 +19,8 @@
  *   mopo_pool_*                            <- SimpleReplayPool / FlexibleReplayPool,
  *                                             softlearning/replay_pools/flexible_replay_pool.py:39-161
  *   mopo_rollout                           <- MOPO._rollout_model, mopo/algorithms/mopo.py:723-765
+ *   mopo_sac_*                             <- the SAC update (actor, twin critics, alpha, Polyak targets): graph mopo.py:271-457,
+ *                                             MOPO._do_training / _training_batch, mopo.py:801-843
  *   mopo_policy_*                          <- the SAC actor graph (mlp_gaussian_policy + apply_squashing_func,
  *                                             mopo.py:292-312) and MOPO.get_action_meta, mopo.py:468-485
  */
@@ -210,6 +212,45 @@ int mopo_ens_train_end(mopo_ens* h, void* stream);
 /* Device parameters -> HOST arrays in the reference layout (the inverse of mopo_ens_set_params; synchronises). */
 int mopo_ens_get_params(mopo_ens* h, float* const* weights, float* const* biases, float* var_w, float* var_b,
                         float* max_logvar, float* min_logvar, void* stream);
+
+/* ---- the SAC update: MOPO._do_training (mopo.py:829-843) on the device ---------------------- */
+typedef struct mopo_sac mopo_sac;
+typedef struct {
+  float reward_scale, discount, tau;       /* mopo.py:60-66 defaults 1.0, 0.99, 5e-3 */
+  float policy_lr, q_lr;                   /* Adam learning rates (mopo.py:417-441), default 3e-4 */
+  float target_entropy;                    /* 'auto' = -act_dim (mopo.py:165-168) */
+  int32_t target_update_interval;          /* mopo.py:839: Polyak update every k-th update (default 1) */
+  int32_t reserved;
+} mopo_sac_hparams;
+int mopo_sac_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, int32_t device, const mopo_sac_hparams* hp, mopo_sac** out);
+int mopo_sac_destroy(mopo_sac* s);
+/* HOST arrays, tf.layers.dense layout (kernel [in,out], bias [out]): pi_W/pi_b = {hidden0, hidden1, mu, log_std} of scope
+ * main/pi; q*_W/q*_b = {hidden0, hidden1, out} of main/q1, main/q2 (input = concat(obs, act)).  Runs target_init
+ * (target critics <- main, mopo.py:451-452) and resets the four Adam states. */
+int mopo_sac_set_params(mopo_sac* s, const float* const* pi_W, const float* const* pi_b, const float* const* q1_W,
+                        const float* const* q1_b, const float* const* q2_W, const float* const* q2_b, float log_alpha, void* stream);
+/* The inverse (HOST outputs); q1t / q2t (target critics) may be NULL. */
+int mopo_sac_get_params(mopo_sac* s, float* const* pi_W, float* const* pi_b, float* const* q1_W, float* const* q1_b,
+                        float* const* q2_W, float* const* q2_b, float* const* q1t_W, float* const* q1t_b,
+                        float* const* q2t_W, float* const* q2t_b, float* log_alpha, void* stream);
+typedef struct {
+  const float *obs, *act, *rew;            /* device [n,obs_dim] [n,act_dim] [n] (rewards[..., 0]) */
+  const uint8_t* term;                     /* device [n] */
+  const float* next_obs;                   /* device [n,obs_dim] */
+  int64_t n;
+  const float* eps;                        /* optional device [2n,act_dim]: tf.random_normal of pi(s) (rows 0..n-1) and of
+                                              pi(s') (rows n..2n-1); NULL = Philox stream 4 keyed (seed, update index, row) */
+  uint64_t seed;
+  float* losses_out;                       /* optional device float[4]: q1_loss, q2_loss, policy_loss, alpha_loss */
+} mopo_sac_batch;
+/* One training step: all gradients at the pre-update variables, four Adam steps, Polyak update.  Enqueues only. */
+int mopo_sac_update(mopo_sac* s, const mopo_sac_batch* b, void* stream);
+/* n_updates x { _training_batch (mopo.py:801-821): n_env rows of env_pool then n_model rows of model_pool, indices drawn on
+ * the device; one update }.  losses_out: optional device float[n_updates][4]. */
+int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, const mopo_pool* model_pool, int32_t n_env,
+                               int32_t n_model, uint64_t seed, int32_t n_updates, float* losses_out, void* stream);
+/* Copy the actor (scope main/pi) into a rollout policy handle, device to device (rebuilds its tensor-core image). */
+int mopo_sac_export_policy(mopo_sac* s, mopo_policy* p, void* stream);
 
 /* ---- MOPO._rollout_model ------------------------------------------------------------------ */
 typedef struct {

@@ -53,6 +53,16 @@ class PolicyArgs(C.Structure):
                 ('std_out', C.c_void_p)]
 
 
+class SacHParams(C.Structure):
+    _fields_ = [('reward_scale', C.c_float), ('discount', C.c_float), ('tau', C.c_float), ('policy_lr', C.c_float),
+                ('q_lr', C.c_float), ('target_entropy', C.c_float), ('target_update_interval', C.c_int32), ('reserved', C.c_int32)]
+
+
+class SacBatch(C.Structure):
+    _fields_ = [('obs', C.c_void_p), ('act', C.c_void_p), ('rew', C.c_void_p), ('term', C.c_void_p), ('next_obs', C.c_void_p),
+                ('n', C.c_int64), ('eps', C.c_void_p), ('seed', C.c_uint64), ('losses_out', C.c_void_p)]
+
+
 # every symbol include/mopo_b200.h declares: (restype, argtypes)
 SYMBOLS = {
     'mopo_last_error': (C.c_char_p, []),
@@ -93,6 +103,14 @@ SYMBOLS = {
     'mopo_kernel_timing': (C.c_int, [C.c_void_p, C.c_int]),
     'mopo_kernel_time': (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
+    'mopo_sac_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(SacHParams), C.POINTER(C.c_void_p)]),
+    'mopo_sac_destroy': (C.c_int, [C.c_void_p]),
+    'mopo_sac_set_params': (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 6 + [C.c_float, C.c_void_p]),
+    'mopo_sac_get_params': (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 10 + [C.POINTER(C.c_float), C.c_void_p]),
+    'mopo_sac_update': (C.c_int, [C.c_void_p, C.POINTER(SacBatch), C.c_void_p]),
+    'mopo_sac_update_from_pools': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.c_int32,
+                                             C.c_void_p, C.c_void_p]),
+    'mopo_sac_export_policy': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     'mopo_policy_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     'mopo_policy_destroy': (C.c_int, [C.c_void_p]),
     'mopo_policy_set_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_void_p]),

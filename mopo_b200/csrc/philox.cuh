@@ -9,6 +9,7 @@
 #define MOPO_STREAM_NOISE 1u
 #define MOPO_STREAM_POOL  2u
 #define MOPO_STREAM_POLICY 3u   /* the policy's action noise (mopo.py:307) / uniform actions of rollout_random (mopo.py:738) */
+#define MOPO_STREAM_SAC 4u      // policy noise inside the SAC update (rows 0..n-1: pi(s), n..2n-1: pi(s'))
 
 struct Philox4 { uint32_t x, y, z, w; };
 

@@ -8,7 +8,7 @@ Box-Muller normals match to ~1e-5 (the device uses approximate lg2 / sin / cos).
 """
 import numpy as np
 
-STREAM_ELITE, STREAM_NOISE, STREAM_POOL, STREAM_POLICY = 0, 1, 2, 3
+STREAM_ELITE, STREAM_NOISE, STREAM_POOL, STREAM_POLICY, STREAM_SAC = 0, 1, 2, 3, 4     # SAC: policy noise inside the SAC update
 _M0, _M1, _W0, _W1 = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85
 _MASK = np.uint64(0xFFFFFFFF)
 
