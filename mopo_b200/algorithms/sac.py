@@ -135,9 +135,17 @@ class SACUpdate:
         if model_pool is None:                                             # real_ratio == 1.0 (mopo.py:816-819)
             n_env, n_model = n_env + n_model, 0
         losses = torch.empty((n_updates, 4), dtype=torch.float32, device=self.device) if return_losses else None
-        _lib.check(_lib.load().mopo_sac_update_from_pools(self._handle, env_pool._handle, model_pool._handle if model_pool is not None else None,
-                                                          n_env, n_model, self.seed, int(n_updates), _lib.ptr(losses),
-                                                          _lib.stream_ptr(self.device)))
+        # on a side stream: the ~45 launches of an update are captured once and replayed as a CUDA graph (stream capture is
+        # not possible on the legacy default stream)
+        cur = torch.cuda.current_stream(self.device)
+        if getattr(self, '_stream', None) is None:
+            self._stream = torch.cuda.Stream(self.device)
+        self._stream.wait_stream(cur)
+        with torch.cuda.stream(self._stream):
+            _lib.check(_lib.load().mopo_sac_update_from_pools(self._handle, env_pool._handle, model_pool._handle if model_pool is not None else None,
+                                                              n_env, n_model, self.seed, int(n_updates), _lib.ptr(losses),
+                                                              _lib.stream_ptr(self.device)))
+        cur.wait_stream(self._stream)
         self._num_train_steps += int(n_updates)
         if return_losses:
             m = losses.mean(0).cpu().numpy().tolist()

@@ -364,7 +364,7 @@ static int sac_reserve(mopo_sac* s, int n) {
 
 // One _do_training step on a batch already in device memory.
 static int sac_update_impl(mopo_sac* s, const float* obs, const float* act, const float* rew, const uint8_t* term, const float* next_obs,
-                           int n, const float* eps_in, uint64_t seed, float* losses_out, cudaStream_t st) {
+                           int n, const float* eps_in, uint64_t seed, float* losses_out, cudaStream_t st, bool ticked = false) {
   const int od = s->od, ad = s->ad, H = s->H, in_q = od + ad;
   TRY(sac_reserve(s, n));
   float *Xpi = s->Xpi.as<float>(), *H0p = s->H0p.as<float>(), *H1p = s->H1p.as<float>(), *HD = s->HD.as<float>();
@@ -372,8 +372,10 @@ static int sac_update_impl(mopo_sac* s, const float* obs, const float* act, cons
   float *T0 = s->T0.as<float>(), *T1 = s->T1.as<float>(), *To = s->To.as<float>(), *dQo = s->dQo.as<float>();
   float *dZ1q = s->dZ1q.as<float>(), *dZ0q = s->dZ0q.as<float>(), *dXa = s->dXa.as<float>(), *dHD = s->dHD.as<float>();
   float *dZ1p = s->dZ1p.as<float>(), *dZ0p = s->dZ0p.as<float>();
-  MOPO_COUNT_LAUNCH;
-  sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
+  if (!ticked) {
+    MOPO_COUNT_LAUNCH;
+    sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
+  }
   // policy on [s; s']
   CUDA_TRY(cudaMemcpyAsync(Xpi, obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
   CUDA_TRY(cudaMemcpyAsync(Xpi + (size_t)n * od, next_obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
@@ -481,12 +483,45 @@ MOPO_API int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, 
   float *bo = s->bo.as<float>(), *ba = s->ba.as<float>(), *br = s->br.as<float>(), *bno = s->bno.as<float>();
   uint8_t* bt = s->bt.as<uint8_t>();
   int64_t* bidx = s->bidx.as<int64_t>();
-  for (int k = 0; k < n_updates; ++k) {
-    const uint64_t off = (uint64_t)s->updates;
-    if (n_env) TRY(mopo_pool_sample(env_pool, n_env, seed, 2 * off, bidx, bo, ba, bno, br, bt, stream));
-    if (n_model) TRY(mopo_pool_sample(model_pool, n_model, seed, 2 * off + 1, bidx + n_env, bo + (size_t)n_env * od, ba + (size_t)n_env * ad,
-                                      bno + (size_t)n_env * od, br + n_env, bt + n_env, stream));
-    TRY(sac_update_impl(s, bo, ba, br, bt, bno, n, nullptr, seed, losses_out ? losses_out + 4 * k : nullptr, st));
+  const int interval = s->hp.target_update_interval > 0 ? s->hp.target_update_interval : 1;
+  // one iteration: tick (update index, lr_t) -> draw env rows, draw model rows (offsets 2u, 2u + 1 read on the device) -> update
+  auto iteration = [&](float* lo) -> int {
+    MOPO_COUNT_LAUNCH;
+    sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
+    if (n_env) TRY(pool_sample_dev(env_pool, n_env, seed, s->d_step, 0, bidx, bo, ba, bno, br, bt, st));
+    if (n_model) TRY(pool_sample_dev(model_pool, n_model, seed, s->d_step, 1, bidx + n_env, bo + (size_t)n_env * od, ba + (size_t)n_env * ad,
+                                     bno + (size_t)n_env * od, br + n_env, bt + n_env, st));
+    return sac_update_impl(s, bo, ba, br, bt, bno, n, nullptr, seed, lo, st, true);
+  };
+  int k = 0;
+  // ~45 small launches per update: capture the iteration once per call and replay it (needs a capturable stream, no
+  // per-update host-side variation: Polyak every update, no loss read-back)
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (st) CUDA_TRY(cudaStreamIsCapturing(st, &cap));
+  if (st && cap == cudaStreamCaptureStatusNone && !losses_out && interval == 1 && n_updates >= 8) {
+    TRY(sac_reserve(s, n));
+    cudaGraph_t g = nullptr;
+    cudaGraphExec_t ge = nullptr;
+    const long long before = (long long)mopo_launch_count();
+    CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    int rc = iteration(nullptr);
+    cudaError_t ce = cudaStreamEndCapture(st, &g);
+    s->updates -= 1;                                  // the capture enqueued nothing
+    if (rc != MOPO_OK) { if (g) cudaGraphDestroy(g); return rc; }
+    CUDA_TRY(ce);
+    const int nodes = (int)((long long)mopo_launch_count() - before);
+    cudaError_t ci = cudaGraphInstantiate(&ge, g, 0);
+    cudaGraphDestroy(g);
+    CUDA_TRY(ci);
+    for (; k < n_updates; ++k) {
+      cudaError_t cl = cudaGraphLaunch(ge, st);
+      if (cl != cudaSuccess) { cudaGraphExecDestroy(ge); CUDA_TRY(cl); }
+      if (k) for (int i = 0; i < nodes; ++i) mopo_count_launch();
+      s->updates += 1;
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));              // the graph must outlive its launches
+    cudaGraphExecDestroy(ge);
   }
+  for (; k < n_updates; ++k) TRY(iteration(losses_out ? losses_out + 4 * k : nullptr));
   return MOPO_OK;
 }

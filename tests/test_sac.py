@@ -159,8 +159,13 @@ def test_sac_train_from_pools_equals_explicit_batches_and_exports_actor():
     a = SACUpdate(od, ad, device=0, seed=99)
     b = SACUpdate(od, ad, device=0, seed=99)                       # same seed -> same glorot init
     assert a.batch_sizes() == (12, 244)
-    K = 4
-    logs = a.train_from_pools(env_pool, model_pool, n_updates=K, return_losses=True)
+    K = 10
+    side = torch.cuda.Stream()                                     # a capturable stream: the 10 updates replay one CUDA graph
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        a.train_from_pools(env_pool, model_pool, n_updates=K - 2)
+    torch.cuda.synchronize()
+    logs = a.train_from_pools(env_pool, model_pool, n_updates=2, return_losses=True)     # direct launches, same sequence
     assert all(np.isfinite(v) for v in logs.values())
     for it in range(K):
         eb = env_pool.random_batch_device(12, seed=99, offset=2 * it)
