@@ -380,9 +380,7 @@ __global__ void gather_rows_kernel(const T* __restrict__ src, const int64_t* __r
     dst[i] = src[idx[j] * width + c];
   }
 }
-// d_step (optional): the offset lives on the device -- offset = 2 * (*d_step - 1) + offset (the SAC loop's captured graph)
-__global__ void philox_index_kernel(int64_t* idx, int64_t n, uint64_t seed, uint64_t offset, int64_t size, const uint64_t* d_step = nullptr) {
-  if (d_step) offset += 2 * (*d_step - 1);
+__global__ void philox_index_kernel(int64_t* idx, int64_t n, uint64_t seed, uint64_t offset, int64_t size) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     uint64_t c = offset + (uint64_t)i;
     Philox4 r = philox4x32_10((uint32_t)c, (uint32_t)(c >> 32), 0u, MOPO_STREAM_POOL, (uint32_t)seed, (uint32_t)(seed >> 32));
@@ -439,15 +437,6 @@ MOPO_API int mopo_pool_sample(const mopo_pool* p, int64_t n, uint64_t seed, uint
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(cudaSetDevice(p->device));
   MOPO_COUNT_LAUNCH, philox_index_kernel<<<grid_for(n), 256, 0, st>>>(idx_out, n, seed, offset, p->size);
-  CUDA_TRY(cudaGetLastError());
-  return pool_gather_impl(p, idx_out, n, obs, act, next_obs, rew, term, st);
-}
-
-// mopo_pool_sample with the draw offset 2 * (*d_step - 1) + which read on the device (sac.cu)
-int pool_sample_dev(const mopo_pool* p, int64_t n, uint64_t seed, const uint64_t* d_step, int which, int64_t* idx_out, float* obs,
-                    float* act, float* next_obs, float* rew, uint8_t* term, cudaStream_t st) {
-  REQUIRE(p->size > 0, MOPO_ESTATE, "mopo_sac_update_from_pools: pool is empty");
-  MOPO_COUNT_LAUNCH, philox_index_kernel<<<grid_for(n), 256, 0, st>>>(idx_out, n, seed, (uint64_t)which, p->size, d_step);
   CUDA_TRY(cudaGetLastError());
   return pool_gather_impl(p, idx_out, n, obs, act, next_obs, rew, term, st);
 }

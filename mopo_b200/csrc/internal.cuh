@@ -162,9 +162,6 @@ int launch_compact(const float* next_obs, const uint8_t* term, const int32_t* or
 int launch_term_only(int kind, const float* next_obs, int64_t n, int obs_dim, uint8_t* out, cudaStream_t st);
 int launch_exp(const float* lv, float* var, int64_t n, cudaStream_t st);
 
-int pool_sample_dev(const mopo_pool* p, int64_t n, uint64_t seed, const uint64_t* d_step, int which, int64_t* idx_out, float* obs,
-                    float* act, float* next_obs, float* rew, uint8_t* term, cudaStream_t st);
-
 // ---- policy (policy.cu): the SAC actor inside the rollout (mopo.py:292-312, 468-485) --------------------------
 struct mopo_policy {
   int obs_dim = 0, act_dim = 0, H = 0, device = 0, sm_count = 148;

@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(256) sac_loss_kernel(const float* __restrict__
                                                        const float* __restrict__ logp, const float* __restrict__ rew,
                                                        const uint8_t* __restrict__ term, const float* __restrict__ log_alpha,
                                                        int n, float reward_scale, float discount, float target_entropy,
-                                                       float* __restrict__ dQo, float* __restrict__ out) {
+                                                       float* __restrict__ dQo, float* __restrict__ out, float* __restrict__ g_alpha) {
   __shared__ float sh[8];
   const float la = *log_alpha, alpha = expf(la), inv_n = 1.0f / (float)n;
   float s1 = 0.f, s2 = 0.f, sp = 0.f, sa = 0.f;
@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(256) sac_loss_kernel(const float* __restrict__
   s1 = block_sum(s1, sh); s2 = block_sum(s2, sh); sp = block_sum(sp, sh); sa = block_sum(sa, sh);
   if (threadIdx.x == 0) {
     out[0] = 0.5f * s1 * inv_n; out[1] = 0.5f * s2 * inv_n; out[2] = sp * inv_n; out[3] = -la * sa * inv_n; out[4] = -sa * inv_n;
+    *g_alpha = -sa * inv_n;
   }
 }
 
@@ -124,6 +125,31 @@ __global__ void sac_pi_head_grad_kernel(const float* __restrict__ HD, const floa
     if (ls_raw < LOG_STD_MIN || ls_raw > LOG_STD_MAX) d_ls = 0.0f;      // tf.clip_by_value passes no gradient outside
     dHD[(int64_t)b * 2 * ad + d] = d_mu;
     dHD[(int64_t)b * 2 * ad + ad + d] = d_ls;
+  }
+}
+
+// _training_batch (mopo.py:801-821) in one launch: rows [0, n_env) from the env pool, [n_env, n) from the model pool, indices as
+// mopo_pool_sample draws them (Philox stream 2, counter = offset + row, offset = 2 (update index) + pool) -- all five fields.
+struct SacSample {
+  const float *obs[2], *act[2], *nobs[2], *rew[2]; const uint8_t* term[2];
+  int64_t size[2]; int n_env, n, od, ad;
+};
+__global__ void __launch_bounds__(256) sac_sample_kernel(SacSample a, uint64_t seed, const uint64_t* __restrict__ d_step,
+                                                         float* __restrict__ bo, float* __restrict__ ba, float* __restrict__ bno,
+                                                         float* __restrict__ br, uint8_t* __restrict__ bt, int64_t* __restrict__ bidx) {
+  const int W = 2 * a.od + a.ad + 2;
+  const uint64_t base = 2 * (*d_step - 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n * W; i += gridDim.x * blockDim.x) {
+    const int j = i / W, c = i % W;
+    const int w = j >= a.n_env;
+    const uint64_t ctr = base + (uint64_t)w + (uint64_t)(w ? j - a.n_env : j);
+    Philox4 r = philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, MOPO_STREAM_POOL, (uint32_t)seed, (uint32_t)(seed >> 32));
+    const int64_t idx = (int64_t)__umul64hi(((uint64_t)r.x << 32) | r.y, (uint64_t)a.size[w]);
+    if (c < a.od) bo[(int64_t)j * a.od + c] = a.obs[w][idx * a.od + c];
+    else if (c < 2 * a.od) bno[(int64_t)j * a.od + (c - a.od)] = a.nobs[w][idx * a.od + (c - a.od)];
+    else if (c < 2 * a.od + a.ad) ba[(int64_t)j * a.ad + (c - 2 * a.od)] = a.act[w][idx * a.ad + (c - 2 * a.od)];
+    else if (c == W - 2) { br[j] = a.rew[w][idx]; bidx[j] = idx; }
+    else bt[j] = a.term[w][idx];
   }
 }
 
@@ -178,8 +204,8 @@ struct mopo_sac {
   float *g[SAC_TENSORS] = {}, *m[SAC_TENSORS] = {}, *v[SAC_TENSORS] = {};
   int64_t* t = nullptr; float* lr_t = nullptr; float* out = nullptr;   // device: Adam step, {lr_pi_t, lr_q_t}, losses[5]
   int64_t updates = 0;
-  cudaStream_t side = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-  DevBuf bo, ba, br, bt, bno, bidx;                   // batch drawn from the pools
+  cudaStream_t side = nullptr, side2 = nullptr; cudaEvent_t ev_pi[4] = {}; cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
+  DevBuf ba, br, bt, bidx;                   // batch drawn from the pools
   DevBuf Xpi, H0p, H1p, HD, eps, logp, Xq, Xt, H0q, H1q, Qo, T0, T1, To, dQo, dZ1q, dZ0q, dXa, dHD, dZ1p, dZ0p;
   uint64_t* d_step = nullptr;                         // device Philox step id of the policy noise (advanced by sac_tick_kernel)
   size_t psize(int i) const {                         // elements of tensor i in SacAdam order
@@ -225,6 +251,10 @@ MOPO_API int mopo_sac_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, i
   CUDA_TRY(cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+  CUDA_TRY(cudaStreamCreateWithFlags(&s->side2, cudaStreamNonBlocking));
+  for (cudaEvent_t& e : s->ev_pi) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&s->ev_fork2, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&s->ev_join2, cudaEventDisableTiming));
   *out = s;
   return MOPO_OK;
 }
@@ -235,8 +265,10 @@ MOPO_API int mopo_sac_destroy(mopo_sac* s) {
   for (int i = 0; i < 3; ++i) { cudaFree(s->piW[i]); cudaFree(s->pib[i]); cudaFree(s->qW[i]); cudaFree(s->qb[i]); cudaFree(s->tW[i]); cudaFree(s->tb[i]); }
   for (int i = 0; i < SAC_TENSORS; ++i) { cudaFree(s->g[i]); cudaFree(s->m[i]); cudaFree(s->v[i]); }
   cudaFree(s->log_alpha); cudaFree(s->t); cudaFree(s->d_step); cudaFree(s->lr_t); cudaFree(s->out);
-  cudaEventDestroy(s->ev_fork); cudaEventDestroy(s->ev_join); cudaStreamDestroy(s->side);
-  DevBuf* bufs[] = {&s->bo, &s->ba, &s->br, &s->bt, &s->bno, &s->bidx, &s->Xpi, &s->H0p, &s->H1p, &s->HD, &s->eps, &s->logp, &s->Xq, &s->Xt,
+  cudaEventDestroy(s->ev_fork); cudaEventDestroy(s->ev_join); cudaEventDestroy(s->ev_fork2); cudaEventDestroy(s->ev_join2); cudaStreamDestroy(s->side);
+  for (cudaEvent_t e : s->ev_pi) cudaEventDestroy(e);
+  cudaStreamDestroy(s->side2);
+  DevBuf* bufs[] = {&s->ba, &s->br, &s->bt, &s->bidx, &s->Xpi, &s->H0p, &s->H1p, &s->HD, &s->eps, &s->logp, &s->Xq, &s->Xt,
                     &s->H0q, &s->H1q, &s->Qo, &s->T0, &s->T1, &s->To, &s->dQo, &s->dZ1q, &s->dZ0q, &s->dXa, &s->dHD, &s->dZ1p, &s->dZ0p};
   for (DevBuf* b : bufs) b->release();
   delete s;
@@ -377,8 +409,10 @@ static int sac_update_impl(mopo_sac* s, const float* obs, const float* act, cons
     sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
   }
   // policy on [s; s']
-  CUDA_TRY(cudaMemcpyAsync(Xpi, obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  CUDA_TRY(cudaMemcpyAsync(Xpi + (size_t)n * od, next_obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  if (obs != Xpi) {               // (the pools path samples straight into Xpi)
+    CUDA_TRY(cudaMemcpyAsync(Xpi, obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(Xpi + (size_t)n * od, next_obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  }
   const int n2 = 2 * n;
   gemm<4>(GemmP{Xpi, 0, od, 0, s->piW[0], 0, H, 0, H0p, 0, H, n2, H, od, s->pib[0], nullptr, nullptr}, 1, st);
   gemm<4>(GemmP{H0p, 0, H, 0, s->piW[1], 0, H, 0, H1p, 0, H, n2, H, H, s->pib[1], nullptr, nullptr}, 1, st);
@@ -388,17 +422,20 @@ static int sac_update_impl(mopo_sac* s, const float* obs, const float* act, cons
                                                        s->logp.as<float>(), Xq, Xt);
   // twin critics on [(s, a); (s, pi(s))] and their targets on (s', pi(s')): nets batched over blockIdx.z, inputs shared
   const int64_t sH2 = (int64_t)n2 * H, sH1 = (int64_t)n * H;
+  CUDA_TRY(cudaEventRecord(s->ev_fork2, st));
+  CUDA_TRY(cudaStreamWaitEvent(s->side, s->ev_fork2, 0));
+  gemm<4>(GemmP{Xt, 0, in_q, 0, s->tW[0], (int64_t)in_q * H, H, 0, T0, sH1, H, n, H, in_q, s->tb[0], nullptr, nullptr}, 2, s->side);
+  gemm<4>(GemmP{T0, sH1, H, 0, s->tW[1], (int64_t)H * H, H, 0, T1, sH1, H, n, H, H, s->tb[1], nullptr, nullptr}, 2, s->side);
+  gemm<2>(GemmP{T1, sH1, H, 0, s->tW[2], (int64_t)H, 1, 0, To, n, 1, n, 1, H, s->tb[2], nullptr, nullptr}, 2, s->side);
+  CUDA_TRY(cudaEventRecord(s->ev_join2, s->side));
   gemm<4>(GemmP{Xq, 0, in_q, 0, s->qW[0], (int64_t)in_q * H, H, 0, H0q, sH2, H, n2, H, in_q, s->qb[0], nullptr, nullptr}, 2, st);
   gemm<4>(GemmP{H0q, sH2, H, 0, s->qW[1], (int64_t)H * H, H, 0, H1q, sH2, H, n2, H, H, s->qb[1], nullptr, nullptr}, 2, st);
   gemm<2>(GemmP{H1q, sH2, H, 0, s->qW[2], (int64_t)H, 1, 0, Qo, n2, 1, n2, 1, H, s->qb[2], nullptr, nullptr}, 2, st);
-  gemm<4>(GemmP{Xt, 0, in_q, 0, s->tW[0], (int64_t)in_q * H, H, 0, T0, sH1, H, n, H, in_q, s->tb[0], nullptr, nullptr}, 2, st);
-  gemm<4>(GemmP{T0, sH1, H, 0, s->tW[1], (int64_t)H * H, H, 0, T1, sH1, H, n, H, H, s->tb[1], nullptr, nullptr}, 2, st);
-  gemm<2>(GemmP{T1, sH1, H, 0, s->tW[2], (int64_t)H, 1, 0, To, n, 1, n, 1, H, s->tb[2], nullptr, nullptr}, 2, st);
+  CUDA_TRY(cudaStreamWaitEvent(st, s->ev_join2, 0));            // target critics: beside the main critics (see above)
   MOPO_COUNT_LAUNCH;
   sac_loss_kernel<<<1, 256, 0, st>>>(Qo, To, s->logp.as<float>(), rew, term, s->log_alpha, n, s->hp.reward_scale, s->hp.discount,
-                                     s->hp.target_entropy, dQo, s->out);
+                                     s->hp.target_entropy, dQo, s->out, s->g[12]);
   if (losses_out) CUDA_TRY(cudaMemcpyAsync(losses_out, s->out, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  CUDA_TRY(cudaMemcpyAsync(s->g[12], s->out + 4, sizeof(float), cudaMemcpyDeviceToDevice, st));       // d alpha_loss / d log_alpha
   // critic backward over all 2n rows (data rows feed the critic gradients, pi rows the action gradient)
   gemm<5>(GemmP{dQo, n2, 1, 0, s->qW[2], (int64_t)H, 1, 1, dZ1q, sH2, H, n2, H, 1, nullptr, nullptr, H1q}, 2, st);
   gemm<5>(GemmP{dZ1q, sH2, H, 0, s->qW[1], (int64_t)H * H, H, 1, dZ0q, sH2, H, n2, H, H, nullptr, nullptr, H0q}, 2, st);
@@ -418,14 +455,24 @@ static int sac_update_impl(mopo_sac* s, const float* obs, const float* act, cons
                 nullptr, nullptr, nullptr}, 2, st);
   MOPO_COUNT_LAUNCH;
   sac_pi_head_grad_kernel<<<(n + 127) / 128, 128, 0, st>>>(HD, s->eps.as<float>(), dXa, s->log_alpha, n, ad, dHD);
-  gemm<0>(GemmP{H1p, 0, H, 1, dHD, 0, 2 * ad, 0, s->g[4], 0, 2 * ad, H, 2 * ad, n, nullptr, nullptr, nullptr}, 1, st);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((2 * ad + 31) / 32, 1), 256, 0, st>>>(dHD, s->g[5], n, 2 * ad, 0);
+  // actor backward: the chain dHD -> dZ1p -> dZ0p stays on the main stream, each stage's weight / bias gradients go to side2
+  cudaStream_t s2 = s->side2;
+  CUDA_TRY(cudaEventRecord(s->ev_pi[0], st));
   gemm<5>(GemmP{dHD, 0, 2 * ad, 0, s->piW[2], 0, 2 * ad, 1, dZ1p, 0, H, n, H, 2 * ad, nullptr, nullptr, H1p}, 1, st);
-  gemm<0>(GemmP{H0p, 0, H, 1, dZ1p, 0, H, 0, s->g[2], 0, H, H, H, n, nullptr, nullptr, nullptr}, 1, st);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 1), 256, 0, st>>>(dZ1p, s->g[3], n, H, 0);
+  CUDA_TRY(cudaEventRecord(s->ev_pi[1], st));
   gemm<5>(GemmP{dZ1p, 0, H, 0, s->piW[1], 0, H, 1, dZ0p, 0, H, n, H, H, nullptr, nullptr, H0p}, 1, st);
-  gemm<0>(GemmP{Xpi, 0, od, 1, dZ0p, 0, H, 0, s->g[0], 0, H, od, H, n, nullptr, nullptr, nullptr}, 1, st);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 1), 256, 0, st>>>(dZ0p, s->g[1], n, H, 0);
+  CUDA_TRY(cudaEventRecord(s->ev_pi[2], st));
+  CUDA_TRY(cudaStreamWaitEvent(s2, s->ev_pi[0], 0));
+  gemm<0>(GemmP{H1p, 0, H, 1, dHD, 0, 2 * ad, 0, s->g[4], 0, 2 * ad, H, 2 * ad, n, nullptr, nullptr, nullptr}, 1, s2);
+  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((2 * ad + 31) / 32, 1), 256, 0, s2>>>(dHD, s->g[5], n, 2 * ad, 0);
+  CUDA_TRY(cudaStreamWaitEvent(s2, s->ev_pi[1], 0));
+  gemm<0>(GemmP{H0p, 0, H, 1, dZ1p, 0, H, 0, s->g[2], 0, H, H, H, n, nullptr, nullptr, nullptr}, 1, s2);
+  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 1), 256, 0, s2>>>(dZ1p, s->g[3], n, H, 0);
+  CUDA_TRY(cudaStreamWaitEvent(s2, s->ev_pi[2], 0));
+  gemm<0>(GemmP{Xpi, 0, od, 1, dZ0p, 0, H, 0, s->g[0], 0, H, od, H, n, nullptr, nullptr, nullptr}, 1, s2);
+  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 1), 256, 0, s2>>>(dZ0p, s->g[1], n, H, 0);
+  CUDA_TRY(cudaEventRecord(s->ev_pi[3], s2));
+  CUDA_TRY(cudaStreamWaitEvent(st, s->ev_pi[3], 0));
   CUDA_TRY(cudaStreamWaitEvent(st, s->ev_join, 0));
   // the four Adam optimisers in one launch, then the Polyak update (every target_update_interval-th update, mopo.py:839-841)
   SacAdam ab;
@@ -477,20 +524,29 @@ MOPO_API int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, 
   CUDA_TRY(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int n = n_env + n_model, od = s->od, ad = s->ad;
-  TRY(s->bo.reserve((size_t)n * od * sizeof(float))); TRY(s->ba.reserve((size_t)n * ad * sizeof(float)));
-  TRY(s->br.reserve((size_t)n * sizeof(float))); TRY(s->bt.reserve((size_t)n)); TRY(s->bno.reserve((size_t)n * od * sizeof(float)));
+  TRY(sac_reserve(s, n));
+  TRY(s->ba.reserve((size_t)n * ad * sizeof(float)));
+  TRY(s->br.reserve((size_t)n * sizeof(float))); TRY(s->bt.reserve((size_t)n));
   TRY(s->bidx.reserve((size_t)n * sizeof(int64_t)));
-  float *bo = s->bo.as<float>(), *ba = s->ba.as<float>(), *br = s->br.as<float>(), *bno = s->bno.as<float>();
+  // observations / next observations are sampled straight into the actor's stacked input [s; s']
+  float *bo = s->Xpi.as<float>(), *ba = s->ba.as<float>(), *br = s->br.as<float>(), *bno = s->Xpi.as<float>() + (size_t)n * od;
   uint8_t* bt = s->bt.as<uint8_t>();
   int64_t* bidx = s->bidx.as<int64_t>();
+  REQUIRE((n_env == 0 || env_pool->size > 0) && (n_model == 0 || model_pool->size > 0), MOPO_ESTATE, "mopo_sac_update_from_pools: pool is empty");
+  const mopo_pool* pools[2] = {env_pool, n_model ? model_pool : env_pool};
+  SacSample smp;
+  for (int w = 0; w < 2; ++w) {
+    smp.obs[w] = pools[w]->obs; smp.act[w] = pools[w]->actions; smp.nobs[w] = pools[w]->next_obs; smp.rew[w] = pools[w]->rewards;
+    smp.term[w] = pools[w]->terminals; smp.size[w] = pools[w]->size;
+  }
+  smp.n_env = n_env; smp.n = n; smp.od = od; smp.ad = ad;
   const int interval = s->hp.target_update_interval > 0 ? s->hp.target_update_interval : 1;
   // one iteration: tick (update index, lr_t) -> draw env rows, draw model rows (offsets 2u, 2u + 1 read on the device) -> update
   auto iteration = [&](float* lo) -> int {
     MOPO_COUNT_LAUNCH;
     sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
-    if (n_env) TRY(pool_sample_dev(env_pool, n_env, seed, s->d_step, 0, bidx, bo, ba, bno, br, bt, st));
-    if (n_model) TRY(pool_sample_dev(model_pool, n_model, seed, s->d_step, 1, bidx + n_env, bo + (size_t)n_env * od, ba + (size_t)n_env * ad,
-                                     bno + (size_t)n_env * od, br + n_env, bt + n_env, st));
+    MOPO_COUNT_LAUNCH;
+    sac_sample_kernel<<<(n * (2 * od + ad + 2) + 255) / 256, 256, 0, st>>>(smp, seed, s->d_step, bo, ba, bno, br, bt, bidx);
     return sac_update_impl(s, bo, ba, br, bt, bno, n, nullptr, seed, lo, st, true);
   };
   int k = 0;
