@@ -5,13 +5,14 @@
 
 namespace {
 
-constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4;
+constexpr int BM = 64, BN = 64, BK = 32, TM = 4, TN = 4;
+constexpr int KQ = BK / 16;   // 16-deep k slices per tile: one 16-byte load per operand, slice and thread
 constexpr float ADAM_B1 = 0.9f, ADAM_B2 = 0.999f, ADAM_EPS = 1e-8f;
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
 __device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x))); }
 
-// C[e] (M x N) = opA(A[e]) (M x K) * opB(B[e]) (K x N), fp32 FFMA, 64 x 64 x 16 tiles, 4 x 4 per thread.
+// C[e] (M x N) = opA(A[e]) (M x K) * opB(B[e]) (K x N), fp32 FFMA, 64 x 64 x 32 tiles, 4 x 4 per thread.
 //   tA: A stored [K, M] (lda = M's row length);  tB: B stored [N, K].
 //   EPI 0: C = acc                                     (weight gradient)
 //   EPI 1: z = acc + bias[e,n]; Z = z; C = z sigmoid(z) (hidden layer forward; Z kept for the backward pass)
@@ -54,21 +55,31 @@ __global__ void __launch_bounds__(256) train_gemm_kernel(GemmP p) {
   // tile element owned by this thread for the global -> shared copy (4 along the contiguous dimension)
   const int a_r = p.tA ? tid / 16 : tid / 4, a_c = p.tA ? (tid % 16) * 4 : (tid % 4) * 4;   // tA: (k, m4)   else (m, k4)
   const int b_r = p.tB ? tid / 4 : tid / 16, b_c = p.tB ? (tid % 4) * 4 : (tid % 16) * 4;   // tB: (n, k4)   else (k, n4)
-  auto fetchA = [&](int k0) {
-    return p.tA ? load4(Ae, k0 + a_r, p.lda, m0 + a_c, p.K, p.M, vA) : load4(Ae, m0 + a_r, p.lda, k0 + a_c, p.M, p.K, vA);
+  // slice q of a tile covers k in [16 q, 16 q + 16)
+  auto fetchA = [&](int k0, int q) {
+    return p.tA ? load4(Ae, k0 + 16 * q + a_r, p.lda, m0 + a_c, p.K, p.M, vA) : load4(Ae, m0 + a_r, p.lda, k0 + 16 * q + a_c, p.M, p.K, vA);
   };
-  auto fetchB = [&](int k0) {
-    return p.tB ? load4(Be, n0 + b_r, p.ldb, k0 + b_c, p.N, p.K, vB) : load4(Be, k0 + b_r, p.ldb, n0 + b_c, p.K, p.N, vB);
+  auto fetchB = [&](int k0, int q) {
+    return p.tB ? load4(Be, n0 + b_r, p.ldb, k0 + 16 * q + b_c, p.N, p.K, vB) : load4(Be, k0 + 16 * q + b_r, p.ldb, n0 + b_c, p.K, p.N, vB);
   };
   float acc[TM][TN] = {};
-  float4 ra = fetchA(0), rb = fetchB(0);
+  float4 ra[KQ], rb[KQ];
+#pragma unroll
+  for (int q = 0; q < KQ; ++q) { ra[q] = fetchA(0, q); rb[q] = fetchB(0, q); }
   for (int k0 = 0; k0 < p.K; k0 += BK) {
-    if (p.tA) *reinterpret_cast<float4*>(&As[a_r][a_c]) = ra;
-    else { As[a_c][a_r] = ra.x; As[a_c + 1][a_r] = ra.y; As[a_c + 2][a_r] = ra.z; As[a_c + 3][a_r] = ra.w; }
-    if (p.tB) { Bs[b_c][b_r] = rb.x; Bs[b_c + 1][b_r] = rb.y; Bs[b_c + 2][b_r] = rb.z; Bs[b_c + 3][b_r] = rb.w; }
-    else *reinterpret_cast<float4*>(&Bs[b_r][b_c]) = rb;
+#pragma unroll
+    for (int q = 0; q < KQ; ++q) {
+      const int kq = 16 * q;
+      if (p.tA) *reinterpret_cast<float4*>(&As[kq + a_r][a_c]) = ra[q];
+      else { As[kq + a_c][a_r] = ra[q].x; As[kq + a_c + 1][a_r] = ra[q].y; As[kq + a_c + 2][a_r] = ra[q].z; As[kq + a_c + 3][a_r] = ra[q].w; }
+      if (p.tB) { Bs[kq + b_c][b_r] = rb[q].x; Bs[kq + b_c + 1][b_r] = rb[q].y; Bs[kq + b_c + 2][b_r] = rb[q].z; Bs[kq + b_c + 3][b_r] = rb[q].w; }
+      else *reinterpret_cast<float4*>(&Bs[kq + b_r][b_c]) = rb[q];
+    }
     __syncthreads();
-    if (k0 + BK < p.K) { ra = fetchA(k0 + BK); rb = fetchB(k0 + BK); }     // next tile in flight under this tile's FMAs
+    if (k0 + BK < p.K) {                                                  // next tile in flight under this tile's FMAs
+#pragma unroll
+      for (int q = 0; q < KQ; ++q) { ra[q] = fetchA(k0 + BK, q); rb[q] = fetchB(k0 + BK, q); }
+    }
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
       const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * TM]);
