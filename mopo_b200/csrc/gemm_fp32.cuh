@@ -5,14 +5,13 @@
 
 namespace {
 
-constexpr int BM = 64, BN = 64, BK = 32, TM = 4, TN = 4;
-constexpr int KQ = BK / 16;   // 16-deep k slices per tile: one 16-byte load per operand, slice and thread
+constexpr int TM = 4, TN = 4;
 constexpr float ADAM_B1 = 0.9f, ADAM_B2 = 0.999f, ADAM_EPS = 1e-8f;
 
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
 __device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x))); }
 
-// C[e] (M x N) = opA(A[e]) (M x K) * opB(B[e]) (K x N), fp32 FFMA, 64 x 64 x 32 tiles, 4 x 4 per thread.
+// C[e] (M x N) = opA(A[e]) (M x K) * opB(B[e]) (K x N), fp32 FFMA, 64 x 64 x 32 or 32 x 32 x 32 tiles, 4 x 4 per thread.
 //   tA: A stored [K, M] (lda = M's row length);  tB: B stored [N, K].
 //   EPI 0: C = acc                                     (weight gradient)
 //   EPI 1: z = acc + bias[e,n]; Z = z; C = z sigmoid(z) (hidden layer forward; Z kept for the backward pass)
@@ -41,44 +40,51 @@ __device__ __forceinline__ float4 load4(const float* __restrict__ base, int64_t 
   return v;
 }
 
-template <int EPI>
-__global__ void __launch_bounds__(256) train_gemm_kernel(GemmP p) {
+// Tile TB x TB x BK with (TB / 4)^2 threads, 4 x 4 outputs per thread: 64 x 64 x 32 (256 threads) when the grid fills the GPU,
+// 32 x 32 x 32 (64 threads, 4 x the CTAs) for the small grids of the latency-bound training steps.
+template <int EPI, int TB>
+__global__ void __launch_bounds__((TB / 4) * (TB / 4)) train_gemm_kernel(GemmP p) {
+  constexpr int BK = 32;                           // k depth of a tile (64 was slower for both tile sizes: measured)
+  constexpr int NT = (TB / 4) * (TB / 4);          // threads
+  constexpr int TX = TB / 4;                       // threads along n (and along m)
+  constexpr int NQ = TB * BK / 4 / NT;             // 16-byte loads per operand, tile and thread
   const int e = blockIdx.z;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-  __shared__ __align__(16) float As[BK][BM + 4];
-  __shared__ __align__(16) float Bs[BK][BN + 4];
+  const int m0 = blockIdx.y * TB, n0 = blockIdx.x * TB;
+  __shared__ __align__(16) float As[BK][TB + 4];
+  __shared__ __align__(16) float Bs[BK][TB + 4];
   const float* Ae = p.A + (int64_t)e * p.sA;
   const float* Be = p.B + (int64_t)e * p.sB;
-  const int tid = threadIdx.x, tx = tid % 16, ty = tid / 16;
+  const int tid = threadIdx.x, tx = tid % TX, ty = tid / TX;
   const bool vA = (p.lda % 4 == 0) && (p.sA % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0);
   const bool vB = (p.ldb % 4 == 0) && (p.sB % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0);
-  // tile element owned by this thread for the global -> shared copy (4 along the contiguous dimension)
-  const int a_r = p.tA ? tid / 16 : tid / 4, a_c = p.tA ? (tid % 16) * 4 : (tid % 4) * 4;   // tA: (k, m4)   else (m, k4)
-  const int b_r = p.tB ? tid / 4 : tid / 16, b_c = p.tB ? (tid % 4) * 4 : (tid % 16) * 4;   // tB: (n, k4)   else (k, n4)
-  // slice q of a tile covers k in [16 q, 16 q + 16)
-  auto fetchA = [&](int k0, int q) {
-    return p.tA ? load4(Ae, k0 + 16 * q + a_r, p.lda, m0 + a_c, p.K, p.M, vA) : load4(Ae, m0 + a_r, p.lda, k0 + 16 * q + a_c, p.M, p.K, vA);
+  // load q of this thread covers 4 elements along the operand's contiguous dimension:
+  //   k contiguous (A as stored [M, K], B stored [N, K]): (row, k4) = (f / (BK/4), 4 (f % (BK/4)))
+  //   k is the row (A stored [K, M], B as stored [K, N]):  (k, c4)  = (f / (TB/4), 4 (f % (TB/4)))      f = tid + NT q
+  auto fetch = [&](const float* base, int ld, bool t_is_kmajor, bool vec, int k0, int q, int o0, int o_lim) {
+    const int f = tid + NT * q;
+    if (t_is_kmajor) return load4(base, k0 + f / (TB / 4), ld, o0 + 4 * (f % (TB / 4)), p.K, o_lim, vec);
+    return load4(base, o0 + f / (BK / 4), ld, k0 + 4 * (f % (BK / 4)), o_lim, p.K, vec);
   };
-  auto fetchB = [&](int k0, int q) {
-    return p.tB ? load4(Be, n0 + b_r, p.ldb, k0 + 16 * q + b_c, p.N, p.K, vB) : load4(Be, k0 + 16 * q + b_r, p.ldb, n0 + b_c, p.K, p.N, vB);
+  auto stash = [&](float (*S)[TB + 4], bool t_is_kmajor, int q, const float4& v) {
+    const int f = tid + NT * q;
+    if (t_is_kmajor) *reinterpret_cast<float4*>(&S[f / (TB / 4)][4 * (f % (TB / 4))]) = v;
+    else {
+      const int r = f / (BK / 4), c = 4 * (f % (BK / 4));
+      S[c][r] = v.x; S[c + 1][r] = v.y; S[c + 2][r] = v.z; S[c + 3][r] = v.w;
+    }
   };
+  const bool ka = p.tA != 0, kb = p.tB == 0;       // operand stored with k as the row index
   float acc[TM][TN] = {};
-  float4 ra[KQ], rb[KQ];
+  float4 ra[NQ], rb[NQ];
 #pragma unroll
-  for (int q = 0; q < KQ; ++q) { ra[q] = fetchA(0, q); rb[q] = fetchB(0, q); }
+  for (int q = 0; q < NQ; ++q) { ra[q] = fetch(Ae, p.lda, ka, vA, 0, q, m0, p.M); rb[q] = fetch(Be, p.ldb, kb, vB, 0, q, n0, p.N); }
   for (int k0 = 0; k0 < p.K; k0 += BK) {
 #pragma unroll
-    for (int q = 0; q < KQ; ++q) {
-      const int kq = 16 * q;
-      if (p.tA) *reinterpret_cast<float4*>(&As[kq + a_r][a_c]) = ra[q];
-      else { As[kq + a_c][a_r] = ra[q].x; As[kq + a_c + 1][a_r] = ra[q].y; As[kq + a_c + 2][a_r] = ra[q].z; As[kq + a_c + 3][a_r] = ra[q].w; }
-      if (p.tB) { Bs[kq + b_c][b_r] = rb[q].x; Bs[kq + b_c + 1][b_r] = rb[q].y; Bs[kq + b_c + 2][b_r] = rb[q].z; Bs[kq + b_c + 3][b_r] = rb[q].w; }
-      else *reinterpret_cast<float4*>(&Bs[kq + b_r][b_c]) = rb[q];
-    }
+    for (int q = 0; q < NQ; ++q) { stash(As, ka, q, ra[q]); stash(Bs, kb, q, rb[q]); }
     __syncthreads();
     if (k0 + BK < p.K) {                                                  // next tile in flight under this tile's FMAs
 #pragma unroll
-      for (int q = 0; q < KQ; ++q) { ra[q] = fetchA(k0 + BK, q); rb[q] = fetchB(k0 + BK, q); }
+      for (int q = 0; q < NQ; ++q) { ra[q] = fetch(Ae, p.lda, ka, vA, k0 + BK, q, m0, p.M); rb[q] = fetch(Be, p.ldb, kb, vB, k0 + BK, q, n0, p.N); }
     }
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
@@ -123,9 +129,15 @@ __global__ void __launch_bounds__(256) train_gemm_kernel(GemmP p) {
 
 template <int EPI>
 int gemm(const GemmP& p, int E, cudaStream_t st) {
-  dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM, E);
   MOPO_COUNT_LAUNCH;
-  train_gemm_kernel<EPI><<<grid, 256, 0, st>>>(p);
+  const int big = ((p.N + 63) / 64) * ((p.M + 63) / 64) * E;
+  if (big >= 2 * 148) {
+    dim3 grid((p.N + 63) / 64, (p.M + 63) / 64, E);
+    train_gemm_kernel<EPI, 64><<<grid, 256, 0, st>>>(p);
+  } else {
+    dim3 grid((p.N + 31) / 32, (p.M + 31) / 32, E);
+    train_gemm_kernel<EPI, 32><<<grid, 64, 0, st>>>(p);
+  }
   return MOPO_OK;
 }
 
