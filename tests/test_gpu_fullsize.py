@@ -1,0 +1,131 @@
+"""BASELINE.json's full sizes (rollout_batch_size 50 000, h = 5) through size-independent properties of the path:
+pool accounting, step-to-step feedback (row j of step i+1 starts where row j of step i ended), reproducibility,
+shard invariance (the multi-GPU property: Philox is keyed by the global row id) and parity of a random row subset
+against the oracle rollout driven by the same Philox draws."""
+import numpy as np
+import pytest
+
+from oracle import ensemble as ens
+from oracle import philox
+from oracle.fake_env import FakeEnv as OracleEnv
+from oracle.pool import SimpleReplayPool as OraclePool
+from oracle.rollout import rollout_model as oracle_rollout
+from oracle.static_fns import StaticFns as OracleStatic
+
+pytestmark = pytest.mark.gpu
+B, H = 50000, 5
+
+
+def _model(p, prec):
+    from mopo_b200.models.constructor import construct_model
+    m = construct_model(obs_dim=p['obs_dim'], act_dim=p['act_dim'], separate_mean_var=True, name='t', device=0, precision=prec)
+    m.set_params(p['weights'], p['biases'], p['var_weights'], p['var_biases'], p['mu'], p['sigma'], p['max_logvar'], p['min_logvar'])
+    m._model_inds = [0, 1, 2, 3, 4]
+    return m
+
+
+def _run(m, domain, obs, acts, lo, hi, seed=77, max_size=None):
+    import torch
+    import mopo_b200.static as static
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    od, ad = obs.shape[1], acts[0].shape[1]
+    env = FakeEnv(m, static[domain], penalty_coeff=1.0, penalty_learned_var=True)
+    ro = ModelRollout(env, SimpleReplayPool(od, ad, 10), rollout_batch_size=hi - lo, rollout_schedule=(0, 1, H, H), seed=seed)
+    ro._set_rollout_length()
+    ro._model_pool = SimpleReplayPool(od, ad, max_size or (hi - lo) * H)
+    ro._rollout_model(hi - lo, start_obs=obs[lo:hi], actions=[a[lo:hi] for a in acts], origin_base=lo, quiet=True)
+    torch.cuda.synchronize()
+    return {k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()}, ro._last_steps_added, ro._model_pool
+
+
+@pytest.mark.parametrize('precision_name', ['bf16', 'fp32'])
+def test_fullsize_halfcheetah_rollout_properties(precision_name):
+    from mopo_b200 import _lib
+    prec = {'bf16': _lib.PREC_BF16, 'fp32': _lib.PREC_FP32}[precision_name]
+    p, obs, _ = ens.synthetic_case('halfcheetah', B, seed=0)
+    rng = np.random.RandomState(2)
+    acts = [np.tanh(rng.standard_normal((B, 6))).astype(np.float32) for _ in range(H)]
+    m = _model(p, prec)
+    full, steps, pool = _run(m, 'halfcheetah', obs, acts, 0, B)
+    # accounting (mopo.py:748-751, flexible_replay_pool.py:45-48)
+    assert steps == [B] * H and pool.size == B * H and pool._pointer == 0
+    assert not full['terminals'].any()
+    assert np.isfinite(full['next_observations']).all() and np.isfinite(full['rewards']).all()
+    for i in range(H):
+        assert np.array_equal(full['actions'][i * B:(i + 1) * B], acts[i])
+    # feedback without a host round trip (mopo.py:758): step i+1 starts from step i's next_obs, row for row
+    assert np.array_equal(full['observations'][:B], obs)
+    for i in range(H - 1):
+        assert np.array_equal(full['observations'][(i + 1) * B:(i + 2) * B], full['next_observations'][i * B:(i + 1) * B])
+    # reproducible bit for bit; a different seed changes the draws
+    again, _, _ = _run(m, 'halfcheetah', obs, acts, 0, B)
+    for k in full:
+        assert np.array_equal(full[k], again[k]), k
+    other, _, _ = _run(m, 'halfcheetah', obs, acts, 0, B, seed=78)
+    assert not np.array_equal(full['next_observations'], other['next_observations'])
+    # shard invariance: two ranks' shards (origin_base = first global row) hold exactly the rows of the unsharded run
+    half = B // 2
+    for lo, hi in ((0, half), (half, B)):
+        part, psteps, _ = _run(m, 'halfcheetah', obs, acts, lo, hi)
+        assert psteps == [hi - lo] * H
+        for i in range(H):
+            for k in ('observations', 'next_observations', 'rewards'):
+                assert np.array_equal(part[k][i * (hi - lo):(i + 1) * (hi - lo)], full[k][i * B + lo:i * B + hi]), (k, i, lo)
+    # a random subset of rows against the oracle rollout fed with the same Philox draws (elite pick, normal noise)
+    S = np.sort(np.random.RandomState(9).choice(B, 300, replace=False))
+    o_env = OracleEnv(ens.OracleModel(p), OracleStatic('halfcheetah'), penalty_coeff=1.0, penalty_learned_var=True)
+    o_pool = OraclePool(17, 6, len(S) * H)
+    elites = np.array([0, 1, 2, 3, 4])
+
+    def noise_fn(i, n):
+        z = philox.normals(S, i, 77, 18)                       # step id = (rollout id 0 << 16) ^ i
+        return np.tile(z[None], [7, 1, 1])
+
+    def inds_fn(i, n):
+        return elites[philox.elite_index(S, i, 77, 5)]
+
+    oracle_rollout(o_env, o_pool, obs[S], H, lambda i, o: acts[i][S], noise_fn=noise_fn, inds_fn=inds_fn)
+    tol = 1e-3 if precision_name == 'fp32' else None
+    for i in range(H):
+        rows = i * B + S
+        want_no = o_pool.fields['next_observations'][i * len(S):(i + 1) * len(S)]
+        want_r = o_pool.fields['rewards'][i * len(S):(i + 1) * len(S)]
+        if tol is not None:
+            np.testing.assert_allclose(full['next_observations'][rows], want_no, rtol=tol, atol=2e-4 * (i + 1))
+            np.testing.assert_allclose(full['rewards'][rows], want_r, rtol=tol, atol=2e-4 * (i + 1))
+        elif i == 0:                                            # bf16: reported separately -- first step within 2 % of the output scale
+            scale = np.abs(want_no).max()
+            assert np.abs(full['next_observations'][rows] - want_no).max() < 0.02 * scale
+
+
+def test_fullsize_hopper_termination_and_compaction():
+    """Terminating env at full size: the survivors of step i are exactly the rows of step i+1, in order, and the pool
+    holds sum(steps_added) rows; fp32 path so that the termination masks are the parity-grade ones."""
+    from mopo_b200 import _lib
+    p, obs, _ = ens.synthetic_case('hopper', B, seed=3)
+    p['max_logvar'][:] = -9.0                                   # low-noise ensemble: a fraction of the rows dies at every step
+    p['weights'][-1] = p['weights'][-1] * 0.02
+    p['biases'][-1] = p['biases'][-1] * 0.0
+    r0 = np.random.RandomState(77)
+    obs[:, 0] = r0.uniform(0.6, 1.5, B).astype(np.float32)
+    obs[:, 1] = r0.uniform(-0.25, 0.25, B).astype(np.float32)
+    rng = np.random.RandomState(4)
+    acts = [np.tanh(rng.standard_normal((B, 3))).astype(np.float32) for _ in range(H)]
+    m = _model(p, _lib.PREC_FP32)
+    full, steps, pool = _run(m, 'hopper', obs, acts, 0, B, max_size=B * H)
+    assert steps[0] == B and all(steps[i + 1] <= steps[i] for i in range(len(steps) - 1)) and steps[1] < B
+    assert pool.size == sum(steps)
+    off = 0
+    for i in range(len(steps) - 1):
+        n = steps[i]
+        term = full['terminals'][off:off + n, 0]
+        assert steps[i + 1] == int((~term).sum())
+        survivors = full['next_observations'][off:off + n][~term]
+        assert np.array_equal(full['observations'][off + n:off + n + steps[i + 1]], survivors)
+        # the termination mask is the static function of the stored next_obs (hopper.py:9-18), recomputed on the host
+        want = OracleStatic('hopper').termination_fn(full['observations'][off:off + n], full['actions'][off:off + n],
+                                                     full['next_observations'][off:off + n])[:, 0]
+        assert np.array_equal(term, want)
+        off += n
