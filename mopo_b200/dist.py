@@ -99,6 +99,24 @@ def gather_pool_rows(fields, n_rows, dst=0):
     return out if rank == dst else None
 
 
+def allgather_rows(fields):
+    """All-gather equally sized row blocks from every rank, rank-major: fields = dict name -> tensor [n, w] (same n on every
+    rank, e.g. the rows a never-terminating rollout just appended to this rank's model_pool shard).  Every rank receives the
+    concatenation -- the SAC sampler's view of the whole rollout (BASELINE.json: "gather model_pool shards")."""
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return dict(fields)
+    world = dist.get_world_size()
+    out = {}
+    for k, src in fields.items():
+        is_bool = src.dtype == torch.bool
+        src = (src.to(torch.uint8) if is_bool else src).contiguous()
+        bufs = [torch.empty_like(src) for _ in range(world)]
+        dist.all_gather(bufs, src)
+        cat = torch.cat(bufs, 0)
+        out[k] = cat.bool() if is_bool else cat
+    return out
+
+
 def max_over_ranks(value, device=None):
     if not dist.is_initialized() or dist.get_world_size() == 1:
         return float(value)

@@ -64,6 +64,9 @@ def _worker(rank, world, port, q):
     fields = {'observations': torch.arange(lo, hi, dtype=torch.float32)[:, None].repeat(1, 3),
               'terminals': (torch.arange(lo, hi) % 2 == 0)[:, None]}
     got = md.gather_pool_rows(fields, n, dst=0)
+    ag = md.allgather_rows({'observations': torch.full((4, 3), float(rank)), 'terminals': torch.full((4, 1), rank == 1)})
+    assert ag['observations'][:, 0].tolist() == [0.0] * 4 + [1.0] * 4
+    assert ag['terminals'].dtype == torch.bool and ag['terminals'][:, 0].tolist() == [False] * 4 + [True] * 4
     t = md.max_over_ranks(10.0 + rank, device='cpu')
     md.barrier()
     if rank == 0:

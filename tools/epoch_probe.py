@@ -63,14 +63,7 @@ def main():
             n_new = Bl * h
             ptr = shard_pool._pointer
             rows = (torch.arange(ptr - n_new, ptr, device=shard_pool.device) % shard_pool._max_size)
-            got = {}
-            for k in fields:
-                src = shard_pool.fields[k][rows]
-                src = src.to(torch.uint8) if src.dtype == torch.bool else src
-                bufs = [torch.empty_like(src) for _ in range(world)]
-                torch.distributed.all_gather(bufs, src.contiguous())
-                got[k] = torch.cat(bufs, 0)
-            got['terminals'] = got['terminals'].bool()
+            got = mdist.allgather_rows({k: shard_pool.fields[k][rows] for k in fields})
             full_pool.add_samples(got)
         sac.train_from_pools(env_pool, full_pool, n_updates=n_upd)
         sac.export_policy(pol)
