@@ -282,6 +282,11 @@ typedef struct {
  * rows to the pool in the reference's order, then synchronises once to read the counts back
  * (termination kinds that never terminate need no read-back: the call returns stream-ordered, without synchronising). */
 int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream);
+/* The same with HOST inputs, as MOPO calls it (NumPy arrays): a->start_obs [B,obs_dim] and every a->actions[i] [B,act_dim]
+ * are host pointers (pinned memory makes the copies asynchronous; a->action_events is ignored).  The call stages them on
+ * the device itself -- start states and step 0's actions on `stream`, the later steps' actions on an internal copy stream,
+ * each behind an event the rollout waits for only ahead of the first kernel that reads it.  noise / model_inds stay device. */
+int mopo_rollout_host(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream);
 
 /* ---- measurement ------------------------------------------------------------------------------- */
 /* CUDA-event timing of the ensemble-forward kernel (the dominant kernel of a step) as it runs inside

@@ -103,6 +103,7 @@ SYMBOLS = {
     'mopo_kernel_timing': (C.c_int, [C.c_void_p, C.c_int]),
     'mopo_kernel_time': (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
+    'mopo_rollout_host': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
     'mopo_sac_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(SacHParams), C.POINTER(C.c_void_p)]),
     'mopo_sac_destroy': (C.c_int, [C.c_void_p]),
     'mopo_sac_set_params': (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 6 + [C.c_float, C.c_void_p]),

@@ -10,6 +10,7 @@ maintainer can mix it into MOPO or call it standalone.  Two ways to supply actio
   * `get_action_meta(obs, hidden)` host callback as in the reference (mopo.py:734): per-step loop.
 """
 import ctypes as C
+import os
 import numpy as np
 import torch
 
@@ -126,8 +127,30 @@ class ModelRollout:
         env, model = self.fake_env, self.fake_env.model
         dev = model.device
         h = self._rollout_length
-        obs = torch.as_tensor(start_obs).to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
-        B = obs.shape[0]
+        # Host inputs (NumPy arrays / CPU tensors, as the reference's sampler and policy produce them) go to the C call as
+        # they are: mopo_rollout_host stages them on the device itself (start states + step 0's actions on the compute
+        # stream, later steps' actions on a copy stream behind per-step events), without per-array Python work.
+        def host_f32(x):
+            t = torch.as_tensor(x)
+            if t.is_cuda:
+                return None
+            return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.to(torch.float32).contiguous()
+
+        obs_h = host_f32(start_obs)
+        acts_h = None
+        if obs_h is not None and actions is not None:
+            acts_h = [host_f32(a) for a in actions[:h]]
+            if len(acts_h) < h or any(a is None or a.shape[0] < obs_h.shape[0] for a in acts_h):
+                acts_h = None
+        use_host = obs_h is not None and obs_h.dim() == 2 and (acts_h is not None or (actions is None and self._device_policy is not None))
+        if os.environ.get('MOPO_NO_HOST_ROLLOUT') == '1':        # A/B switch: stage through torch copies instead
+            use_host = False
+        if use_host:
+            obs, B = obs_h, obs_h.shape[0]
+            self._host_keep = (obs_h, acts_h)            # pinned sources of asynchronous copies stay alive until the next call
+        else:
+            obs = torch.as_tensor(start_obs).to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
+            B = obs.shape[0]
         keep = [obs]
 
         def ptr_array(seq, dtype):
@@ -142,7 +165,7 @@ class ModelRollout:
         # on the compute stream, the later steps' on a side stream with one event each, and the rollout waits for
         # event i only just before the first kernel that reads actions[i] -- the uploads overlap the earlier steps.
         act_events = None
-        if actions is not None and h > 1 and not all(torch.is_tensor(s) and s.is_cuda for s in actions[:h]):
+        if not use_host and actions is not None and h > 1 and not all(torch.is_tensor(s) and s.is_cuda for s in actions[:h]):
             cur = torch.cuda.current_stream(dev)
             if getattr(self, '_copy_stream', None) is None:
                 self._copy_stream = torch.cuda.Stream(dev)
@@ -165,7 +188,8 @@ class ModelRollout:
             act_events = (C.c_void_p * h)(*[e.cuda_event if e is not None else None for e in evs])
 
         steps = (C.c_int64 * max(h, 1))()
-        a = _lib.RolloutArgs(start_obs=obs.data_ptr(), B=B, rollout_length=h, actions=ptr_array(actions, torch.float32),
+        act_ptrs = (C.c_void_p * h)(*[t.data_ptr() for t in acts_h]) if (use_host and acts_h is not None) else ptr_array(actions, torch.float32)
+        a = _lib.RolloutArgs(start_obs=obs.data_ptr(), B=B, rollout_length=h, actions=act_ptrs,
                              term_kind=env.config.term_kind, penalty_kind=env.penalty_kind,
                              penalty_coeff=float(env.penalty_coeff), deterministic=int(bool(deterministic)),
                              precision=model.precision if precision is None else precision,
@@ -176,7 +200,8 @@ class ModelRollout:
                              rollout_random=int(bool(self._rollout_random)), policy_deterministic=0)
         self._rollout_count += 1
         model._ensure_handle()
-        _lib.check(_lib.load().mopo_rollout(model._handle, self._model_pool._handle, C.byref(a), _lib.stream_ptr(dev)))
+        call = _lib.load().mopo_rollout_host if use_host else _lib.load().mopo_rollout
+        _lib.check(call(model._handle, self._model_pool._handle, C.byref(a), _lib.stream_ptr(dev)))
         out = [int(steps[i]) for i in range(h)]
         while out and out[-1] == 0:          # the reference breaks out of the loop when nothing survives (mopo.py:754-756)
             out.pop()

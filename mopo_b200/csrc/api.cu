@@ -67,6 +67,10 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
   if (h->tc_img) cudaFree(h->tc_img);
   mopo_train_release(h);
+  for (cudaEvent_t e : h->act_ev) cudaEventDestroy(e);
+  if (h->ev_start) cudaEventDestroy(h->ev_start);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  h->st_obs.release(); h->st_act.release();
   for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
   DevBuf* bufs[] = {&h->sel, &h->selmv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
                     &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts, &h->ro_act};
@@ -589,4 +593,60 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   pool->pointer = (pool->pointer + total) % pool->max_size;      // == h successive add_samples calls
   pool->size = pool->size + total < pool->max_size ? pool->size + total : pool->max_size;
   return MOPO_OK;
+}
+
+// mopo_rollout with HOST inputs (the reference-facing call: MOPO hands NumPy arrays).  start_obs [B,obs] and every
+// actions[i] [B,act] are host pointers (pinned memory makes the copies asynchronous).  They are staged into device buffers
+// owned by the handle: the start states and step 0's actions on `stream`, the later steps' actions on an internal copy
+// stream behind one event each -- the rollout waits for event i only ahead of the first kernel that reads actions[i], so
+// those uploads overlap the earlier steps.  noise / model_inds (optional) stay device pointers.  Everything else as mopo_rollout.
+MOPO_API int mopo_rollout_host(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, void* stream) {
+  REQUIRE(h && pool && a, MOPO_EINVAL, "mopo_rollout_host: null argument");
+  REQUIRE(a->B >= 0 && a->B < (1ll << 31) && a->rollout_length >= 0 && a->rollout_length <= 1024, MOPO_EINVAL, "mopo_rollout_host: B=%lld h=%d", (long long)a->B, a->rollout_length);
+  const int H = a->rollout_length;
+  const int64_t B = a->B;
+  if (B == 0 || H == 0) return mopo_rollout(h, pool, a, stream);
+  REQUIRE(a->start_obs && (a->actions || a->policy), MOPO_EINVAL, "mopo_rollout_host: null start_obs/actions");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int od = h->cfg.obs_dim, ad = h->cfg.act_dim;
+  if (!h->copy_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&h->ev_start, cudaEventDisableTiming));
+  }
+  while ((int)h->act_ev.size() < H) {
+    cudaEvent_t e;
+    CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    h->act_ev.push_back(e);
+  }
+  const bool host_actions = a->actions != nullptr && !a->policy;
+  // growing a staging buffer frees the old one: wait for its readers first
+  if (h->st_obs.cap < sizeof(float) * B * od || (host_actions && h->st_act.cap < sizeof(float) * B * ad * H)) CUDA_TRY(cudaDeviceSynchronize());
+  TRY(h->st_obs.reserve(sizeof(float) * B * od));
+  if (host_actions) TRY(h->st_act.reserve(sizeof(float) * B * ad * H));
+  CUDA_TRY(cudaMemcpyAsync(h->st_obs.p, a->start_obs, sizeof(float) * B * od, cudaMemcpyHostToDevice, st));
+  std::vector<const float*> d_act(H, nullptr);
+  std::vector<void*> evs(H, nullptr);
+  if (host_actions) {
+    for (int i = 0; i < H; ++i) {
+      REQUIRE(a->actions[i], MOPO_EINVAL, "mopo_rollout_host: actions[%d] null", i);
+      float* dst = h->st_act.as<float>() + (size_t)i * B * ad;
+      d_act[i] = dst;
+      if (i == 0) {
+        CUDA_TRY(cudaMemcpyAsync(dst, a->actions[0], sizeof(float) * B * ad, cudaMemcpyHostToDevice, st));
+        // The copy stream starts behind step 0's inputs: they are on the critical path and get the whole link (uploads on
+        // two streams would share it), and behind the previous rollout on `st`, which may still read the staging buffers.
+        CUDA_TRY(cudaEventRecord(h->ev_start, st));
+        CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->ev_start, 0));
+      } else {
+        CUDA_TRY(cudaMemcpyAsync(dst, a->actions[i], sizeof(float) * B * ad, cudaMemcpyHostToDevice, h->copy_stream));
+        CUDA_TRY(cudaEventRecord(h->act_ev[i], h->copy_stream));
+        evs[i] = h->act_ev[i];
+      }
+    }
+  }
+  mopo_rollout_args b = *a;
+  b.start_obs = h->st_obs.as<float>();
+  if (host_actions) { b.actions = d_act.data(); b.action_events = evs.data(); }
+  return mopo_rollout(h, pool, &b, stream);
 }

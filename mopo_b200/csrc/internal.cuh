@@ -86,6 +86,11 @@ struct mopo_ens {
   DevBuf sel, selmv, pen2;         // fused-head step outputs
   DevBuf ro_obs[2], ro_origin[2], ro_counts, ro_act;
   mopo_train* tr = nullptr;
+  // mopo_rollout_host: device staging of host inputs, the upload stream and its per-step events
+  DevBuf st_obs, st_act;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_start = nullptr;
+  std::vector<cudaEvent_t> act_ev;
 };
 void mopo_train_release(mopo_ens* h);
 
