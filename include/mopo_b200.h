@@ -229,6 +229,9 @@ int mopo_sac_destroy(mopo_sac* s);
  * (target critics <- main, mopo.py:451-452) and resets the four Adam states. */
 int mopo_sac_set_params(mopo_sac* s, const float* const* pi_W, const float* const* pi_b, const float* const* q1_W,
                         const float* const* q1_b, const float* const* q2_W, const float* const* q2_b, float log_alpha, void* stream);
+/* Overwrite the target critics (HOST arrays, layout as q1_W / q1_b): restoring a checkpoint taken mid-training. */
+int mopo_sac_set_targets(mopo_sac* s, const float* const* q1t_W, const float* const* q1t_b, const float* const* q2t_W,
+                         const float* const* q2t_b, void* stream);
 /* The inverse (HOST outputs); q1t / q2t (target critics) may be NULL. */
 int mopo_sac_get_params(mopo_sac* s, float* const* pi_W, float* const* pi_b, float* const* q1_W, float* const* q1_b,
                         float* const* q2_W, float* const* q2_b, float* const* q1t_W, float* const* q1t_b,

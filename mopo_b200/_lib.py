@@ -108,6 +108,7 @@ SYMBOLS = {
     'mopo_sac_destroy': (C.c_int, [C.c_void_p]),
     'mopo_sac_set_params': (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 6 + [C.c_float, C.c_void_p]),
     'mopo_sac_get_params': (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 10 + [C.POINTER(C.c_float), C.c_void_p]),
+    'mopo_sac_set_targets': (C.c_int, [C.c_void_p] + [C.POINTER(C.c_void_p)] * 4 + [C.c_void_p]),
     'mopo_sac_update': (C.c_int, [C.c_void_p, C.POINTER(SacBatch), C.c_void_p]),
     'mopo_sac_update_from_pools': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.c_int32,
                                              C.c_void_p, C.c_void_p]),

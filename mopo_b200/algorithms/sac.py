@@ -94,6 +94,36 @@ class SACUpdate:
         out['log_alpha'] = float(la.value)
         return out
 
+    def save(self, path):
+        """Checkpoint of every variable (main + target networks, log_alpha) as one .npz (the reference checkpoints the TF
+        session; the optimiser moments are not part of it and restart from zero on load, like a fresh AdamOptimizer)."""
+        p = self.get_params()
+        flat = {'log_alpha': np.float32(p['log_alpha'])}
+        for name in ('pi', 'q1', 'q2', 'q1_targ', 'q2_targ'):
+            for k in ('W', 'b'):
+                for i, a in enumerate(p[name][k]):
+                    flat['%s/%s%d' % (name, k, i)] = a
+        np.savez(path, **flat)
+
+    def load(self, path):
+        d = np.load(path)
+        get = lambda name, k, n: [d['%s/%s%d' % (name, k, i)] for i in range(n)]
+        self.set_params(get('pi', 'W', 4), get('pi', 'b', 4), get('q1', 'W', 3), get('q1', 'b', 3), get('q2', 'W', 3), get('q2', 'b', 3),
+                        float(d['log_alpha']))
+        # set_params runs target_init; a checkpoint taken mid-training carries its own targets
+        self._set_targets(get('q1_targ', 'W', 3), get('q1_targ', 'b', 3), get('q2_targ', 'W', 3), get('q2_targ', 'b', 3))
+
+    def _set_targets(self, q1t_W, q1t_b, q2t_W, q2t_b):
+        keep = []
+
+        def pack(arrs):
+            a = [np.ascontiguousarray(np.asarray(x, np.float32)) for x in arrs]
+            keep.extend(a)
+            return (C.c_void_p * len(a))(*[x.ctypes.data for x in a])
+
+        _lib.check(_lib.load().mopo_sac_set_targets(self._handle, pack(q1t_W), pack(q1t_b), pack(q2t_W), pack(q2t_b),
+                                                    _lib.stream_ptr(self.device)))
+
     def export_policy(self, policy):
         """Push the actor (main/pi) into the rollout's GaussianPolicy handle, device to device."""
         _lib.check(_lib.load().mopo_sac_export_policy(self._handle, policy._handle, _lib.stream_ptr(self.device)))

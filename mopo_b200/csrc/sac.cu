@@ -323,6 +323,26 @@ MOPO_API int mopo_sac_set_params(mopo_sac* s, const float* const* pi_W, const fl
   return MOPO_OK;
 }
 
+MOPO_API int mopo_sac_set_targets(mopo_sac* s, const float* const* q1t_W, const float* const* q1t_b, const float* const* q2t_W,
+                                    const float* const* q2t_b, void* stream) {
+  REQUIRE(s && q1t_W && q1t_b && q2t_W && q2t_b, MOPO_EINVAL, "mopo_sac_set_targets: null argument");
+  REQUIRE(s->params_set, MOPO_ESTATE, "mopo_sac_set_targets: parameters not set");
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int H = s->H, in_q = s->od + s->ad;
+  const size_t wn[3] = {(size_t)in_q * H, (size_t)H * H, (size_t)H}, bn[3] = {(size_t)H, (size_t)H, 1};
+  const float* const* Ws[2] = {q1t_W, q2t_W};
+  const float* const* bs[2] = {q1t_b, q2t_b};
+  for (int e = 0; e < 2; ++e)
+    for (int l = 0; l < 3; ++l) {
+      REQUIRE(Ws[e][l] && bs[e][l], MOPO_EINVAL, "mopo_sac_set_targets: layer %d null", l);
+      TRY(sac_copy(s->tW[l] + e * wn[l], Ws[e][l], wn[l], cudaMemcpyHostToDevice, st));
+      TRY(sac_copy(s->tb[l] + e * bn[l], bs[e][l], bn[l], cudaMemcpyHostToDevice, st));
+    }
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return MOPO_OK;
+}
+
 // Inverse of mopo_sac_set_params, plus the target critics (q1t / q2t, may be NULL) and log_alpha; HOST outputs.
 MOPO_API int mopo_sac_get_params(mopo_sac* s, float* const* pi_W, float* const* pi_b, float* const* q1_W, float* const* q1_b,
                                    float* const* q2_W, float* const* q2_b, float* const* q1t_W, float* const* q1t_b,

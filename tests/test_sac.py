@@ -184,3 +184,60 @@ def test_sac_train_from_pools_equals_explicit_batches_and_exports_actor():
     act, _ = pol.get_action_meta(obs, None, deterministic=True)
     want, _, _ = opol.forward(pa['pi']['W'], pa['pi']['b'], obs, deterministic=True)
     np.testing.assert_allclose(act, want, rtol=1e-3, atol=2e-5)
+
+
+@pytest.mark.gpu
+def test_full_device_loop_and_checkpoint(tmp_path):
+    """Rows f1-f4 together, nothing leaving HBM: offline pool -> BNN.train -> elites -> actor-driven rollout into the model
+    pool -> SAC updates drawn from both pools -> actor exported -> next rollout uses the new actor; then the SAC variables
+    survive a save / load round trip (targets included) and training continues identically from the checkpoint."""
+    import torch
+    from mopo_b200 import _lib
+    import mopo_b200.static as static
+    from mopo_b200.models.constructor import construct_model
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    from mopo_b200.algorithms.sac import SACUpdate
+    from mopo_b200.policies import GaussianPolicy
+    od, ad, n = 11, 3, 4000
+    rng = np.random.RandomState(0)
+    data = _batch(rng, n, od, ad)
+    data['next_observations'] = (data['observations'] + 0.1 * np.tanh(data['observations'] @ rng.standard_normal((od, od)) * 0.3)).astype(np.float32)
+    data['terminals'] = np.zeros((n, 1), bool)
+    env_pool = SimpleReplayPool(od, ad, n)
+    env_pool.add_samples(data)
+    model = construct_model(obs_dim=od, act_dim=ad, num_networks=7, num_elites=5, separate_mean_var=True, precision=_lib.PREC_BF16, seed=1)
+    env = FakeEnv(model, static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=2)
+    pol = GaussianPolicy(od, ad, device=0, precision=_lib.PREC_BF16, seed=3)
+    sac = SACUpdate(od, ad, device=0, seed=4)
+    sac.export_policy(pol)
+    ro = ModelRollout(env, env_pool, rollout_batch_size=1000, rollout_schedule=(0, 1, 2, 2), epoch_length=1000, model_train_freq=1000,
+                      model_retain_epochs=2, policy=pol, seed=5)
+    ro._train_model(batch_size=256, max_epochs=3, holdout_ratio=0.2)
+    ro._set_rollout_length()
+    ro._reallocate_model_pool()
+    obs0 = data['observations'][:1000]
+    ro._rollout_model(1000, start_obs=obs0, quiet=True)
+    torch.cuda.synchronize()
+    a_before = ro._model_pool.fields['actions'][:1000].clone()
+    assert ro._model_pool.size == 2000
+    logs = sac.train_from_pools(env_pool, ro._model_pool, n_updates=20, return_losses=True)
+    assert all(np.isfinite(v) for v in logs.values())
+    sac.export_policy(pol)
+    ro._rollout_model(1000, start_obs=obs0, quiet=True)
+    torch.cuda.synchronize()
+    a_after = ro._model_pool.fields['actions'][2000:3000]
+    assert ro._model_pool.size == 4000 and not torch.equal(a_before, a_after)          # the updated actor drives the rollout
+    # checkpoint round trip
+    path = str(tmp_path / 'sac.npz')
+    sac.save(path)
+    clone = SACUpdate(od, ad, device=0, seed=4)
+    clone.load(path)
+    pa, pb = sac.get_params(), clone.get_params()
+    for name in ('pi', 'q1', 'q2', 'q1_targ', 'q2_targ'):
+        for k in ('W', 'b'):
+            for x, y in zip(pa[name][k], pb[name][k]):
+                assert np.array_equal(x, y), (name, k)
+    assert pa['log_alpha'] == pb['log_alpha']
+    assert not np.array_equal(pa['q1']['W'][0], pa['q1_targ']['W'][0])                  # targets lag the main critics
