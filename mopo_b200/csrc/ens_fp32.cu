@@ -29,8 +29,8 @@ ens_layer_fp32(const float* __restrict__ A, int64_t strideA, int lda,
   const int e = blockIdx.z;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
   if (m0 >= M) return;
-  __shared__ float As[BK][BM + 4];
-  __shared__ float Bs[BK][BN + 4];
+  __shared__ __align__(16) float As[BK][BM + 4];
+  __shared__ __align__(16) float Bs[BK][BN + 4];
   const float* Ae = A + (int64_t)e * strideA;
   const float* We = W + (int64_t)e * K * N;
   const int tid = threadIdx.x;
@@ -53,11 +53,9 @@ ens_layer_fp32(const float* __restrict__ A, int64_t strideA, int lda,
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
-      float a[TM], b[TN];
-#pragma unroll
-      for (int i = 0; i < TM; ++i) a[i] = As[k][ty * TM + i];
-#pragma unroll
-      for (int j = 0; j < TN; ++j) b[j] = Bs[k][tx * TN + j];
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * TM]);     // one 16-byte shared load per operand
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * TN]);
+      const float a[TM] = {a4.x, a4.y, a4.z, a4.w}, b[TN] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
       for (int i = 0; i < TM; ++i)
 #pragma unroll
