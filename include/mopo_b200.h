@@ -18,7 +18,7 @@
  *                                             + StaticFns.termination_fn, mopo/static/<env>.py
  *   mopo_pool_*                            <- SimpleReplayPool / FlexibleReplayPool,
  *                                             softlearning/replay_pools/flexible_replay_pool.py:39-161
- *   mopo_rollout                           <- MOPO._rollout_model, mopo/algorithms/mopo.py:723-765
+ *   mopo_rollout, mopo_rollout_host        <- MOPO._rollout_model, mopo/algorithms/mopo.py:723-765 (device / host inputs)
  *   mopo_sac_*                             <- the SAC update (actor, twin critics, alpha, Polyak targets): graph mopo.py:271-457,
  *                                             MOPO._do_training / _training_batch, mopo.py:801-843
  *   mopo_policy_*                          <- the SAC actor graph (mlp_gaussian_policy + apply_squashing_func,
