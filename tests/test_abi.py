@@ -46,6 +46,9 @@ def test_struct_layouts_match_header(lib):
     assert lib.RolloutArgs.actions.offset == 24 and lib.RolloutArgs.noise.offset == 56
     assert lib.RolloutArgs.action_events.offset == 104 and lib.RolloutArgs.policy.offset == 112 and C.sizeof(lib.RolloutArgs) == 128
     assert lib.PolicyArgs.noise.offset == 32 and lib.PolicyArgs.actions.offset == 72 and C.sizeof(lib.PolicyArgs) == 96
+    # mopo_sac_hparams: 6 float + 2 int32; mopo_sac_batch: 5 pointers, int64, pointer, uint64, pointer
+    assert C.sizeof(lib.SacHParams) == 32 and lib.SacHParams.target_update_interval.offset == 24
+    assert lib.SacBatch.n.offset == 40 and lib.SacBatch.seed.offset == 56 and C.sizeof(lib.SacBatch) == 72
 
 
 def test_null_handle_calls_fail_cleanly(lib):
