@@ -7,16 +7,18 @@
 // Layer 0 reads the scaled input shared by all nets (the 2-D einsum path, fc.py:98-99).
 // One launch per layer, activations [E,chunk,H] ping-pong through HBM: simple and exact;
 // the tensor-core path in ens_tc.cu is the fast one.
-#include "internal.cuh"
+#include "gemm_fp32.cuh"   // load4, softplus_f, TM / TN
 
 namespace {
 
-constexpr int BM = 64, BN = 64, BK = 16, TM = 4, TN = 4;
+constexpr int BM = 64, BN = 64;
 
 __device__ __forceinline__ float swish_f(float x) { return x / (1.0f + expf(-x)); }
-__device__ __forceinline__ float softplus_f(float x) { return fmaxf(x, 0.0f) + log1pf(expf(-fabsf(x))); }
 
 // MODE 0: swish -> C[e, m, n] (ldc = N);  MODE 1: head -> mean/lv [e, m, D1]
+// 64 x 64 x 32 tiles, 256 threads x (4 x 4) outputs; 16-byte global loads along each operand's contiguous dimension where
+// the pitch allows, the next k-tile's loads in flight under the current tile's FMAs, 16-byte shared-memory operand reads.
+// Every output is one fmaf chain over k = 0 .. K-1 in order: the result does not depend on the tiling.
 template <int MODE>
 __global__ void __launch_bounds__(256)
 ens_layer_fp32(const float* __restrict__ A, int64_t strideA, int lda,
@@ -25,6 +27,7 @@ ens_layer_fp32(const float* __restrict__ A, int64_t strideA, int lda,
                float* __restrict__ mean, float* __restrict__ lv, int64_t ld_out,
                const float* __restrict__ max_lv, const float* __restrict__ min_lv,
                int M_max, const int* __restrict__ d_n, int N, int K, int D1) {
+  constexpr int BK = 32, NQ = 2;
   const int M = d_n ? min(*d_n, M_max) : M_max;
   const int e = blockIdx.z;
   const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
@@ -35,25 +38,31 @@ ens_layer_fp32(const float* __restrict__ A, int64_t strideA, int lda,
   const float* We = W + (int64_t)e * K * N;
   const int tid = threadIdx.x;
   const int tx = tid % 16, ty = tid / 16;     // 16 x 16 threads, each TM x TN
+  const bool vA = (lda % 4 == 0) && (strideA % 4 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
+  const bool vB = (N % 4 == 0) && ((reinterpret_cast<uintptr_t>(W) & 15) == 0);
+  // A tile: row m = f / 8, k4 = 4 (f % 8);  W tile: row k = f / 16, n4 = 4 (f % 16);  f = tid + 256 q
+  auto fetchA = [&](int k0, int q) { const int f = tid + 256 * q; return load4(Ae, m0 + f / 8, lda, k0 + 4 * (f % 8), M, K, vA); };
+  auto fetchB = [&](int k0, int q) { const int f = tid + 256 * q; return load4(We, k0 + f / 16, N, n0 + 4 * (f % 16), K, N, vB); };
   float acc[TM][TN] = {};
+  float4 ra[NQ], rb[NQ];
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) { ra[q] = fetchA(0, q); rb[q] = fetchB(0, q); }
   for (int k0 = 0; k0 < K; k0 += BK) {
-    // A tile: BM x BK (row-major, K contiguous) -> As[k][m]
-    for (int i = tid; i < BM * BK; i += 256) {
-      int m = i / BK, k = i % BK;
-      float v = 0.f;
-      if (m0 + m < M && k0 + k < K) v = Ae[(int64_t)(m0 + m) * lda + k0 + k];
-      As[k][m] = v;
-    }
-    for (int i = tid; i < BK * BN; i += 256) {
-      int k = i / BN, n = i % BN;
-      float v = 0.f;
-      if (k0 + k < K && n0 + n < N) v = We[(int64_t)(k0 + k) * N + n0 + n];
-      Bs[k][n] = v;
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      const int f = tid + 256 * q;
+      const int r = f / 8, c = 4 * (f % 8);
+      As[c][r] = ra[q].x; As[c + 1][r] = ra[q].y; As[c + 2][r] = ra[q].z; As[c + 3][r] = ra[q].w;
+      *reinterpret_cast<float4*>(&Bs[f / 16][4 * (f % 16)]) = rb[q];
     }
     __syncthreads();
+    if (k0 + BK < K) {
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) { ra[q] = fetchA(k0 + BK, q); rb[q] = fetchB(k0 + BK, q); }
+    }
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
-      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * TM]);     // one 16-byte shared load per operand
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][ty * TM]);
       const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][tx * TN]);
       const float a[TM] = {a4.x, a4.y, a4.z, a4.w}, b[TN] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
