@@ -12,6 +12,7 @@
 // from the device replay pools inside the call (mopo_sac_update_from_pools: _training_batch, mopo.py:801-821).
 #include "gemm_fp32.cuh"
 #include "philox.cuh"
+#include <string.h>
 
 namespace {
 
@@ -208,6 +209,11 @@ struct mopo_sac {
   DevBuf ba, br, bt, bidx;                   // batch drawn from the pools
   DevBuf Xpi, H0p, H1p, HD, eps, logp, Xq, Xt, H0q, H1q, Qo, T0, T1, To, dQo, dZ1q, dZ0q, dXa, dHD, dZ1p, dZ0p;
   uint64_t* d_step = nullptr;                         // device Philox step id of the policy noise (advanced by sac_tick_kernel)
+  // the captured pools iteration (tick -> draw -> update), kept across calls: MOPO calls one update per environment step
+  // (_do_training_repeats, mopo.py:780-799), so the same pools / sizes recur until the next rollout grows the model pool
+  cudaGraphExec_t graph = nullptr; int g_nodes = 0; uint64_t g_seed = 0;
+  SacSample g_smp, last_smp; uint64_t last_seed = 0; bool have_last = false;
+  void drop_graph() { if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; } }
   size_t psize(int i) const {                         // elements of tensor i in SacAdam order
     const int in_q = od + ad;
     const size_t s[SAC_TENSORS] = {(size_t)od * H, (size_t)H, (size_t)H * H, (size_t)H, (size_t)H * 2 * ad, (size_t)2 * ad,
@@ -264,6 +270,7 @@ MOPO_API int mopo_sac_destroy(mopo_sac* s) {
   cudaSetDevice(s->device);
   for (int i = 0; i < 3; ++i) { cudaFree(s->piW[i]); cudaFree(s->pib[i]); cudaFree(s->qW[i]); cudaFree(s->qb[i]); cudaFree(s->tW[i]); cudaFree(s->tb[i]); }
   for (int i = 0; i < SAC_TENSORS; ++i) { cudaFree(s->g[i]); cudaFree(s->m[i]); cudaFree(s->v[i]); }
+  s->drop_graph();
   cudaFree(s->log_alpha); cudaFree(s->t); cudaFree(s->d_step); cudaFree(s->lr_t); cudaFree(s->out);
   cudaEventDestroy(s->ev_fork); cudaEventDestroy(s->ev_join); cudaEventDestroy(s->ev_fork2); cudaEventDestroy(s->ev_join2); cudaStreamDestroy(s->side);
   for (cudaEvent_t e : s->ev_pi) cudaEventDestroy(e);
@@ -410,7 +417,11 @@ static int sac_reserve(mopo_sac* s, int n) {
       {&s->Xq, 2 * N * in_q}, {&s->Xt, N * in_q}, {&s->H0q, 4 * N * H}, {&s->H1q, 4 * N * H}, {&s->Qo, 4 * N}, {&s->T0, 2 * N * H},
       {&s->T1, 2 * N * H}, {&s->To, 2 * N}, {&s->dQo, 4 * N}, {&s->dZ1q, 4 * N * H}, {&s->dZ0q, 4 * N * H}, {&s->dXa, 2 * N * ad},
       {&s->dHD, N * 2 * ad}, {&s->dZ1p, N * H}, {&s->dZ0p, N * H}};
-  for (auto& w : want) TRY(w.b->reserve(w.n * sizeof(float)));
+  for (auto& w : want) {
+    void* before = w.b->p;
+    TRY(w.b->reserve(w.n * sizeof(float)));
+    if (before != w.b->p) s->drop_graph();          // a moved buffer invalidates the captured iteration
+  }
   return MOPO_OK;
 }
 
@@ -555,6 +566,7 @@ MOPO_API int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, 
   REQUIRE((n_env == 0 || env_pool->size > 0) && (n_model == 0 || model_pool->size > 0), MOPO_ESTATE, "mopo_sac_update_from_pools: pool is empty");
   const mopo_pool* pools[2] = {env_pool, n_model ? model_pool : env_pool};
   SacSample smp;
+  memset(&smp, 0, sizeof(smp));                     // compared bytewise as the graph's key
   for (int w = 0; w < 2; ++w) {
     smp.obs[w] = pools[w]->obs; smp.act[w] = pools[w]->actions; smp.nobs[w] = pools[w]->next_obs; smp.rew[w] = pools[w]->rewards;
     smp.term[w] = pools[w]->terminals; smp.size[w] = pools[w]->size;
@@ -574,29 +586,38 @@ MOPO_API int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, 
   // per-update host-side variation: Polyak every update, no loss read-back)
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   if (st) CUDA_TRY(cudaStreamIsCapturing(st, &cap));
-  if (st && cap == cudaStreamCaptureStatusNone && !losses_out && interval == 1 && n_updates >= 8) {
+  const bool can_graph = st && cap == cudaStreamCaptureStatusNone && !losses_out && interval == 1 && n_updates > 0;
+  const bool key_match = s->graph && s->g_seed == seed && memcmp(&s->g_smp, &smp, sizeof(smp)) == 0;
+  const bool recurring = s->have_last && s->last_seed == seed && memcmp(&s->last_smp, &smp, sizeof(smp)) == 0;
+  s->last_smp = smp; s->last_seed = seed; s->have_last = true;
+  if (can_graph && (key_match || n_updates >= 8 || recurring)) {
     TRY(sac_reserve(s, n));
-    cudaGraph_t g = nullptr;
-    cudaGraphExec_t ge = nullptr;
-    const long long before = (long long)mopo_launch_count();
-    CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    int rc = iteration(nullptr);
-    cudaError_t ce = cudaStreamEndCapture(st, &g);
-    s->updates -= 1;                                  // the capture enqueued nothing
-    if (rc != MOPO_OK) { if (g) cudaGraphDestroy(g); return rc; }
-    CUDA_TRY(ce);
-    const int nodes = (int)((long long)mopo_launch_count() - before);
-    cudaError_t ci = cudaGraphInstantiate(&ge, g, 0);
-    cudaGraphDestroy(g);
-    CUDA_TRY(ci);
+    TRY(s->ba.reserve((size_t)n * ad * sizeof(float)));
+    bool fresh = false;
+    if (!(s->graph && s->g_seed == seed && memcmp(&s->g_smp, &smp, sizeof(smp)) == 0)) {
+      s->drop_graph();
+      cudaGraph_t g = nullptr;
+      const long long before = (long long)mopo_launch_count();
+      CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      int rc = iteration(nullptr);
+      cudaError_t ce = cudaStreamEndCapture(st, &g);
+      s->updates -= 1;                                // the capture enqueued nothing
+      if (rc != MOPO_OK) { if (g) cudaGraphDestroy(g); return rc; }
+      CUDA_TRY(ce);
+      s->g_nodes = (int)((long long)mopo_launch_count() - before);
+      cudaError_t ci = cudaGraphInstantiate(&s->graph, g, 0);
+      cudaGraphDestroy(g);
+      if (ci != cudaSuccess) s->graph = nullptr;
+      CUDA_TRY(ci);
+      s->g_smp = smp; s->g_seed = seed;
+      fresh = true;                                   // the launches counted during the capture stand for the first replay
+    }
     for (; k < n_updates; ++k) {
-      cudaError_t cl = cudaGraphLaunch(ge, st);
-      if (cl != cudaSuccess) { cudaGraphExecDestroy(ge); CUDA_TRY(cl); }
-      if (k) for (int i = 0; i < nodes; ++i) mopo_count_launch();
+      CUDA_TRY(cudaGraphLaunch(s->graph, st));
+      if (!(fresh && k == 0)) for (int i = 0; i < s->g_nodes; ++i) mopo_count_launch();
       s->updates += 1;
     }
-    CUDA_TRY(cudaStreamSynchronize(st));              // the graph must outlive its launches
-    cudaGraphExecDestroy(ge);
+    return MOPO_OK;
   }
   for (; k < n_updates; ++k) TRY(iteration(losses_out ? losses_out + 4 * k : nullptr));
   return MOPO_OK;

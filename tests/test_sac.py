@@ -167,6 +167,13 @@ def test_sac_train_from_pools_equals_explicit_batches_and_exports_actor():
     torch.cuda.synchronize()
     logs = a.train_from_pools(env_pool, model_pool, n_updates=2, return_losses=True)     # direct launches, same sequence
     assert all(np.isfinite(v) for v in logs.values())
+    # the per-environment-step pattern (_do_training_repeats, mopo.py:780-799): one update per call; from the second call
+    # with the same pools on, the captured iteration is kept and replayed across calls
+    with torch.cuda.stream(side):
+        for _ in range(5):
+            a.train_from_pools(env_pool, model_pool, n_updates=1)
+    torch.cuda.synchronize()
+    K += 5
     for it in range(K):
         eb = env_pool.random_batch_device(12, seed=99, offset=2 * it)
         mb = model_pool.random_batch_device(244, seed=99, offset=2 * it + 1)
