@@ -94,7 +94,7 @@ def _compare(got, st, atol):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('shape', [(17, 6, 256, 256), (11, 3, 64, 100), (5, 2, 32, 7)])
+@pytest.mark.parametrize('shape', [(17, 6, 256, 256), (11, 3, 64, 100), (5, 2, 32, 7), (45, 17, 30, 33)])   # last: odd pitches -> scalar-load fallbacks, 5 Philox blocks
 def test_sac_update_matches_oracle(shape):
     from mopo_b200.algorithms.sac import SACUpdate, LOSS_NAMES
     od, ad, H, n = shape
@@ -248,3 +248,31 @@ def test_full_device_loop_and_checkpoint(tmp_path):
                 assert np.array_equal(x, y), (name, k)
     assert pa['log_alpha'] == pb['log_alpha']
     assert not np.array_equal(pa['q1']['W'][0], pa['q1_targ']['W'][0])                  # targets lag the main critics
+
+
+@pytest.mark.gpu
+def test_sac_real_ratio_one_uses_only_the_env_pool():
+    """real_ratio == 1.0 (mopo.py:816-819): no model pool; the whole batch comes from the env pool."""
+    import torch
+    from mopo_b200.algorithms.sac import SACUpdate
+    from mopo_b200.replay_pools import SimpleReplayPool
+    od, ad = 11, 3
+    rng = np.random.RandomState(3)
+    env_pool = SimpleReplayPool(od, ad, 500)
+    env_pool.add_samples(_batch(rng, 500, od, ad))
+    a = SACUpdate(od, ad, hidden_sizes=(64, 64), device=0, real_ratio=1.0, batch_size=64, seed=5)
+    b = SACUpdate(od, ad, hidden_sizes=(64, 64), device=0, real_ratio=1.0, batch_size=64, seed=5)
+    assert a.batch_sizes() == (64, 0)
+    a.train_from_pools(env_pool, None, n_updates=3)
+    for it in range(3):
+        eb = env_pool.random_batch_device(64, seed=5, offset=2 * it)
+        b._do_training(it, {k: eb[k] for k in ('observations', 'actions', 'next_observations', 'rewards', 'terminals')}, return_losses=False)
+    torch.cuda.synchronize()
+    pa, pb = a.get_params(), b.get_params()
+    for name in ('pi', 'q1', 'q2', 'q1_targ', 'q2_targ'):
+        for k in ('W', 'b'):
+            for x, y in zip(pa[name][k], pb[name][k]):
+                assert np.array_equal(x, y), (name, k)
+    empty = SimpleReplayPool(od, ad, 10)
+    with pytest.raises(RuntimeError):                     # sampling an empty pool (np.random.randint(0, 0) raises in the reference)
+        a.train_from_pools(empty, None, n_updates=1)
