@@ -364,3 +364,28 @@ def test_train_model_then_rollout_stays_on_device():
     want = np.concatenate([samples['rewards'][:300], samples['next_observations'][:300] - samples['observations'][:300]], -1)
     base = (want ** 2).mean()
     assert ((mean - want) ** 2).mean() < 0.5 * base
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('cfg', [dict(num_networks=7, num_elites=5, separate_mean_var=False),
+                                 dict(num_networks=1, num_elites=1, separate_mean_var=True)])
+def test_bnn_train_other_layouts(cfg, tmp_path):
+    """BNN.train with the combined [mean | logvar] head (bnn.py:183-189) and with a single-net 'ensemble': the loop runs,
+    the holdout loss falls, and the trained host copies round-trip through save / load."""
+    import os
+    from mopo_b200.models.constructor import construct_model, format_samples_for_training
+    samples = _dynamics(3000, seed=4)
+    inputs, targets = format_samples_for_training(samples)
+    model = construct_model(obs_dim=11, act_dim=3, hidden_dim=200, seed=2, **cfg)
+    m0, _ = model.predict(inputs[:300], factored=True)
+    mse0 = ((m0 - targets[None, :300]) ** 2).mean()
+    metrics = model.train(inputs, targets, batch_size=256, max_epochs=15, holdout_ratio=0.2)
+    m1, v1 = model.predict(inputs[:300], factored=True)
+    assert ((m1 - targets[None, :300]) ** 2).mean() < 0.3 * mse0 and np.isfinite(metrics['val_loss'])
+    assert len(model._model_inds) == cfg['num_elites']
+    model.save(str(tmp_path), 0)
+    os.rename(os.path.join(str(tmp_path), 'BNN_0.mat'), os.path.join(str(tmp_path), 'BNN.mat'))
+    clone = construct_model(obs_dim=11, act_dim=3, hidden_dim=200, load_dir=str(tmp_path), **cfg)
+    m2, v2 = clone.predict(inputs[:300], factored=True)
+    np.testing.assert_array_equal(m2, m1)
+    np.testing.assert_array_equal(v2, v1)
