@@ -55,10 +55,13 @@ enum {
   MOPO_PEN_DISAGREEMENT = 2   /* max_e ||mean_e[1:] - mean_bar[1:]||_2 (fake_env.py:99-108) */
 };
 
-/* arithmetic of the ensemble contraction */
+/* arithmetic of the ensemble contraction (the reference contracts in fp32: fc.py:96-106) */
 enum {
-  MOPO_PREC_FP32 = 0,  /* fp32 FFMA path: the rtol-1e-3 parity path */
-  MOPO_PREC_BF16 = 1   /* tcgen05 kind::f16 (bf16 operands, fp32 accumulation in TMEM) */
+  MOPO_PREC_FP32 = 0,     /* fp32-accurate (the rtol-1e-3 parity path): tcgen05 kind::f16 with every operand split into a
+                             bf16 (hi, lo) pair, three MMAs per K step, fp32 accumulation in TMEM (ens_tc3.cu); shapes the
+                             tensor-core kernel does not cover (hidden_dim != 200, ...) run on the FFMA kernel */
+  MOPO_PREC_BF16 = 1,     /* tcgen05 kind::f16, plain bf16 operands, fp32 accumulation in TMEM */
+  MOPO_PREC_FP32_REF = 2  /* fp32 FFMA on the CUDA cores (ens_fp32.cu): kept as the on-device checker of the two above */
 };
 
 typedef struct mopo_ens  mopo_ens;

@@ -7,12 +7,12 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libmopo_b200.so')
+LIB_PATH = os.environ.get('MOPO_B200_LIB') or os.path.join(_HERE, 'libmopo_b200.so')   # override: developer builds (watchdog)
 
 OK, EINVAL, ESTATE, ECUDA, EUNSUPPORTED = 0, -1, -2, -3, -4
 TERM_NEVER, TERM_HOPPER, TERM_WALKER2D, TERM_ANT, TERM_HUMANOID = range(5)
 PEN_NONE, PEN_LEARNED_VAR, PEN_DISAGREEMENT = range(3)
-PREC_FP32, PREC_BF16 = 0, 1
+PREC_FP32, PREC_BF16, PREC_FP32_REF = 0, 1, 2
 F_ACTIONS, F_REWARDS, F_TERMINALS, F_OBS, F_NEXT_OBS = range(5)
 
 c_f32p = C.c_void_p  # device/host float*, passed as raw addresses

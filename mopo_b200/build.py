@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libmopo_b200.so')
-SOURCES = ['api.cu', 'ens_fp32.cu', 'ens_tc.cu', 'tail.cu', 'policy.cu', 'policy_tc.cu', 'train.cu', 'sac.cu', 'umma_probe.cu', 'microbench.cu']
+SOURCES = ['api.cu', 'ens_fp32.cu', 'ens_tc.cu', 'ens_tc3.cu', 'tail.cu', 'policy.cu', 'policy_tc.cu', 'train.cu', 'sac.cu', 'umma_probe.cu', 'microbench.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '--use_fast_math=false']
 

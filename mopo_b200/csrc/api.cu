@@ -66,6 +66,7 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   for (int l = 0; l < MOPO_MAX_LAYERS; ++l) { if (h->W[l]) cudaFree(h->W[l]); if (h->b[l]) cudaFree(h->b[l]); }
   cudaFree(h->mu); cudaFree(h->sigma); cudaFree(h->max_lv); cudaFree(h->min_lv); cudaFree(h->elites);
   if (h->tc_img) cudaFree(h->tc_img);
+  if (h->tc3_img) cudaFree(h->tc3_img);
   mopo_train_release(h);
   for (cudaEvent_t e : h->act_ev) cudaEventDestroy(e);
   if (h->ev_start) cudaEventDestroy(h->ev_start);
@@ -131,6 +132,7 @@ MOPO_API int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const
   TRY(upload(h->max_lv, max_logvar, D1, on_device, st));
   TRY(upload(h->min_lv, min_logvar, D1, on_device, st));
   if (tc_supported(h)) TRY(tc_build_images(h, st));
+  if (tc3_supported(h)) TRY(tc3_build_images(h, st));
   CUDA_TRY(cudaStreamSynchronize(st));
   h->params_set = true;
   return MOPO_OK;
@@ -147,15 +149,35 @@ MOPO_API int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n) 
   return MOPO_OK;
 }
 
+// Which kernel a precision request runs on.  MOPO_PREC_FP32: the fp32-accurate tcgen05 kernel (split bf16, ens_tc3.cu)
+// where the shape allows, else the FFMA kernel; MOPO_PREC_FP32_REF: always FFMA (the checker); MOPO_PREC_BF16: the
+// net-stationary bf16 kernel (ens_tc.cu), or the streamed-weights kernel in bf16 mode for wider shapes (ant, humanoid).
+enum { PATH_FFMA = 0, PATH_TC = 1, PATH_TC3 = 2, PATH_TC1 = 3, PATH_NONE = -1 };
+static int ens_path(const mopo_ens* h, int precision) {
+  static const bool no_tc3 = getenv("MOPO_NO_TC3") != nullptr;      // developer switch: MOPO_PREC_FP32 on the FFMA kernel
+  if (precision == MOPO_PREC_FP32_REF) return PATH_FFMA;
+  if (precision == MOPO_PREC_FP32) return (!no_tc3 && tc3_supported(h)) ? PATH_TC3 : PATH_FFMA;
+  if (precision == MOPO_PREC_BF16) return tc_supported(h) ? PATH_TC : tc3_supported(h) ? PATH_TC1 : PATH_NONE;
+  return PATH_NONE;
+}
+#define REQUIRE_PATH(path, precision)                                                                                   \
+  do {                                                                                                                  \
+    REQUIRE((precision) == MOPO_PREC_FP32 || (precision) == MOPO_PREC_BF16 || (precision) == MOPO_PREC_FP32_REF, MOPO_EINVAL, \
+            "unknown precision %d", (precision));                                                                       \
+    REQUIRE((path) != PATH_NONE, MOPO_EUNSUPPORTED,                                                                     \
+            "the tcgen05 paths support hidden_dim=200, n_hidden=4, obs+act<=63, 2*(obs+rew)<=96 only (use MOPO_PREC_FP32)"); \
+  } while (0)
+
 static int forward(mopo_ens* h, int precision, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
                    int64_t ldb, cudaStream_t st) {
-  if (precision == MOPO_PREC_FP32) return fp32_forward(h, xn, n_max, d_n, mean, lv, ldb, st);
-  if (precision == MOPO_PREC_BF16) {
-    REQUIRE(tc_supported(h), MOPO_EUNSUPPORTED, "bf16 tcgen05 path supports hidden_dim=200, n_hidden=4, in<=32, 2*D1<=48, E<=7 only");
-    return tc_forward(h, xn, n_max, d_n, mean, lv, ldb, st);
-  }
-  mopo_set_error("unknown precision %d", precision);
-  return MOPO_EINVAL;
+  const int path = ens_path(h, precision);
+  REQUIRE_PATH(path, precision);
+  if (path == PATH_FFMA) return fp32_forward(h, xn, n_max, d_n, mean, lv, ldb, st);
+  if (path == PATH_TC) return tc_forward(h, xn, n_max, d_n, mean, lv, ldb, st);
+  Tc3In x = {xn, nullptr, h->in, 0, false};
+  TcOut o = {};
+  o.mean = mean; o.lv = lv; o.ldb = ldb;
+  return tc3_launch(h, path == PATH_TC3 ? 3 : 1, x, n_max, d_n, o, st);
 }
 
 MOPO_API int mopo_ens_forward(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar, int precision, void* stream) {
@@ -244,8 +266,9 @@ static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_
                         uint64_t seed, uint64_t step_id, const int32_t* origin, int64_t origin_base,
                         TailArgs* t, cudaStream_t st, bool tiles_ready = false, bool pdl = false) {
   const int E = h->E, D1 = h->D1;
-  if (precision == MOPO_PREC_BF16) {
-    REQUIRE(tc_supported(h), MOPO_EUNSUPPORTED, "bf16 tcgen05 path supports hidden_dim=200, n_hidden=4 and shapes whose weights fit one CTA pair (in+2<=32, 2*D1<=48 at E<=74)");
+  const int path = ens_path(h, precision);
+  REQUIRE_PATH(path, precision);
+  if (path != PATH_FFMA) {
     const bool fused = !deterministic && !want_diag && penalty_kind != MOPO_PEN_DISAGREEMENT;
     TcPrep q = {};
     q.obs = obs; q.act = act; q.n_max = B; q.d_n = d_n; q.model_inds = model_inds;
@@ -265,11 +288,16 @@ static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_
       t->mean = o.mean; t->lv = o.lv;
     }
     t->ldb = B;
-    if (!tiles_ready) TRY(tc_tiles_from_step(h, q, st));       // else: written by the previous step's fused tail
     o.pdl = pdl && tiles_ready;                                // ... behind which this launch is a programmatic dependent
-    return tc_launch(h, B, d_n, o, st);
+    if (path == PATH_TC) {
+      if (!tiles_ready) TRY(tc_tiles_from_step(h, q, st));     // else: written by the previous step's fused tail
+      return tc_launch(h, B, d_n, o, st);
+    }
+    // streamed-weights kernel: reads obs / act itself (scaler and hi/lo split inside); only the elite picks come first
+    if (fused && !tiles_ready) TRY(tc3_pick(h, q.sel, model_inds, B, d_n, seed, step_id, origin, origin_base, st));
+    Tc3In x = {obs, act, h->cfg.obs_dim, h->cfg.act_dim, true};
+    return tc3_launch(h, path == PATH_TC3 ? 3 : 1, x, B, d_n, o, st);
   }
-  REQUIRE(precision == MOPO_PREC_FP32, MOPO_EINVAL, "unknown precision %d", precision);
   TRY(h->xn.reserve(sizeof(float) * B * h->in));
   TRY(h->mean.reserve(sizeof(float) * E * B * D1));
   TRY(h->lv.reserve(sizeof(float) * E * B * D1));
@@ -490,13 +518,15 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
   const int32_t* origin_cur = nullptr;
   // static rows on the fused tensor-core path: the tail of step i also tiles step i+1's inputs and picks its elites
   // (with a device policy, act[i+1] = policy(next_obs[i]) does not exist yet when the tail of step i runs: no chaining)
-  const bool chain = static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT && !a->policy;
+  const int path = ens_path(h, a->precision);
+  REQUIRE_PATH(path, a->precision);
+  const bool fused_ok = path != PATH_FFMA && !a->deterministic && a->penalty_kind != MOPO_PEN_DISAGREEMENT;
+  const bool streamed = path == PATH_TC3 || path == PATH_TC1;   // the forward reads obs / act itself: "tiles" = the elite picks
+  const bool chain = static_rows && fused_ok && !a->policy;
   if (a->policy) TRY(h->ro_act.reserve(sizeof(float) * B * ad));
   // terminating envs on the fused tensor-core path with supplied actions: the compaction tiles the next step's inputs
-  const bool compact_tiles = !static_rows && a->precision == MOPO_PREC_BF16 && !a->deterministic &&
-                             a->penalty_kind != MOPO_PEN_DISAGREEMENT && !a->policy && tc_supported(h);
-  const bool policy_tiles = a->policy && !a->rollout_random && a->precision == MOPO_PREC_BF16 && !a->deterministic &&
-                            a->penalty_kind != MOPO_PEN_DISAGREEMENT && tc_supported(h) && policy_tc_supported(a->policy);
+  const bool compact_tiles = !static_rows && fused_ok && !a->policy;
+  const bool policy_tiles = a->policy && !a->rollout_random && path == PATH_TC && fused_ok && policy_tc_supported(a->policy);
   // programmatic dependent launches between the chained kernels (not while per-kernel timing events sit between them)
   static const bool pdl_env = getenv("MOPO_NO_PDL") == nullptr;
   const bool pdl = chain && pdl_env && !h->timing && !h->timing_tail;
@@ -540,8 +570,10 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
                      (chain && i > 0) || tiles_done || (compact_tiles && i > 0), (pdl && !a->action_events) || (pdl_pol && tiles_done)));
     t.pdl = (chain && pdl) || (pdl_pol && tiles_done);
     if (chain && i + 1 < H) {
-      t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
-      t.K0 = (h->in + 2 + 15) / 16 * 16;
+      if (!streamed) {
+        t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
+        t.K0 = (h->in + 2 + 15) / 16 * 16;
+      }
       t.sel_next = h->sel.as<int32_t>(); t.model_inds_next = a->model_inds ? a->model_inds[i + 1] : nullptr;
       t.step_id_next = (a->rollout_id << 16) ^ (uint64_t)(i + 1);
     }
@@ -568,14 +600,16 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     if (static_rows) { obs_cur = obs_next; continue; }
     int32_t* origin_next = h->ro_origin[i & 1].as<int32_t>();
     CompactTiles ct = {};
-    if (compact_tiles && i + 1 < H) {                  // the compaction is also step i+1's tiling pass
-      int K0;
-      TRY(tc_reserve_xtiles(h, B, &K0));
+    if (compact_tiles && i + 1 < H) {                  // the compaction is also step i+1's tiling pass / elite pick
       TRY(h->sel.reserve(sizeof(int32_t) * B));
-      ct.xt = h->xtiles.as<uint4>(); ct.act_next = a->actions[i + 1]; ct.mu = h->mu; ct.sigma = h->sigma; ct.act_dim = ad; ct.K0 = K0;
+      if (!streamed) {
+        int K0;
+        TRY(tc_reserve_xtiles(h, B, &K0));
+        ct.xt = h->xtiles.as<uint4>(); ct.act_next = a->actions[i + 1]; ct.mu = h->mu; ct.sigma = h->sigma; ct.act_dim = ad; ct.K0 = K0;
+      }
       ct.sel = h->sel.as<int32_t>(); ct.model_inds = a->model_inds ? a->model_inds[i + 1] : nullptr;
       ct.elites = h->elites; ct.n_elites = h->n_elites; ct.seed = a->seed; ct.step_id = (a->rollout_id << 16) ^ (uint64_t)(i + 1);
-      if (a->action_events && a->action_events[i + 1]) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
+      if (!streamed && a->action_events && a->action_events[i + 1]) CUDA_TRY(cudaStreamWaitEvent(st, (cudaEvent_t)a->action_events[i + 1], 0));
     }
     TRY(launch_compact(nobs_dense, term_dense, origin_cur, a->origin_base, B, d_n, h->blk_counts.as<int>(), od,
                        obs_next, origin_next, d_counts + i + 1, d_pool_off, ct, st));

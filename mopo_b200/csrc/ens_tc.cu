@@ -33,6 +33,7 @@
 // critical resource, go straight from a tile's last hidden layer to the next tile's first.
 #include "internal.cuh"
 #include "tc_common.cuh"
+#include "tc_head.cuh"
 #include "philox.cuh"
 
 namespace {
@@ -258,13 +259,6 @@ struct Bars {
   uint32_t pad;
 };
 
-__device__ __forceinline__ float tanh_fast(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-// softplus(x) = max(x,0) + log(1 + exp(-|x|)); ex2/lg2-based: absolute error < 1e-6 over the clamp's range
-__device__ __forceinline__ float softplus_fast(float x) { return fmaxf(x, 0.0f) + __logf(1.0f + __expf(-fabsf(x))); }
 
 // swish of two accumulator columns (xh = x/2 already) -> packed bf16x2
 __device__ __forceinline__ uint32_t swish2(uint32_t a, uint32_t b) {
@@ -329,118 +323,6 @@ __device__ __forceinline__ void epi_hidden(uint32_t tlane, uint8_t* ay_row) {
   else fence_proxy_async_smem();
 }
 
-// head epilogue.  Soft clamp + exp of bnn.py:654-655/669-670,675 in closed form:
-//   lv1 = max - softplus(max - raw), lv = min + softplus(lv1 - min), var = exp(lv)
-//   =>  var = e^min + e^lv1 = e^min + 1 / (e^-max + e^-raw)                  (exp(softplus(y)) = 1 + e^y)
-// two MUFU ops per output dim instead of five.  sC[0][w*P+i] = e^min_d, sC[1][w*P+i] = e^-max_d for the dims of
-// warpgroup w (padding dims: 0 and +inf, so they contribute var = 0).
-// FUSED: pen2[w][e][row] = sum of var over this warpgroup's dims; rows whose chosen net is e (`mine`, prefetched by the
-//        caller) also store (mean, var) to selmv[d][row].
-// FULL : mean[e][row][d], lv[e][row][d] = log(var).
-template <bool FUSED>
-__device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const TcShape& s, const float* sC, const TcArgs& a,
-                                         int e, int64_t row, bool valid, bool mine) {
-  const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
-  const int d0 = wg * dh, nd = wg ? s.D1 - dh : dh;
-  const float* cmin = sC + wg * P;
-  const float* cnmax = sC + MOPO_MAX_D1 + wg * P;
-  float pen = 0.f;
-  for (int c = 0; c < P / 4; ++c) {
-    uint32_t mv[4], rv[4];
-    tmem_ld4(tblk + 4 * c, mv);
-    tmem_ld4(tblk + P + 4 * c, rv);
-    tmem_ld_wait();
-    float var[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      var[i] = cmin[4 * c + i] + __fdividef(1.0f, cnmax[4 * c + i] + __expf(-__uint_as_float(rv[i])));
-      pen += var[i];
-    }
-    if (FUSED) {
-      if (mine) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (4 * c + i < nd) a.selmv[(int64_t)(d0 + 4 * c + i) * a.ldb + row] = make_float2(__uint_as_float(mv[i]), var[i]);
-      }
-    } else if (valid) {
-      float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1 + d0;
-      float* lrow = a.lv + ((size_t)e * a.ldb + row) * s.D1 + d0;
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (4 * c + i < nd) { mrow[4 * c + i] = __uint_as_float(mv[i]); lrow[4 * c + i] = __logf(var[i]); }
-    }
-  }
-  if (FUSED && valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
-}
-
-// FMA-pipe exp2 and reciprocal for the head warps.  The MUFU is the forward kernel's saturated resource (one tanh per
-// hidden activation): head arithmetic that queues behind it holds a tile's head accumulator columns for thousands of
-// cycles, so the head uses the (idle) FMA / ALU pipes instead.
-//   2^y, |y| <= 60: y = n + f, n = rint(y), 2^f by a degree-5 polynomial on [-0.5, 0.5] (rel. error 3e-6), exponent add.
-__device__ __forceinline__ float exp2_fma(float y) {
-  y = fminf(fmaxf(y, -60.0f), 60.0f);
-  const float t = y + 12582912.0f;                       // 1.5 * 2^23: the integer part lands in the low mantissa bits
-  const float f = y - (t - 12582912.0f);
-  float p = 1.33335581e-3f;
-  p = fmaf(p, f, 9.61812911e-3f);
-  p = fmaf(p, f, 5.55041087e-2f);
-  p = fmaf(p, f, 2.40226507e-1f);
-  p = fmaf(p, f, 6.93147182e-1f);
-  p = fmaf(p, f, 1.0f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
-//   1/d, d in [2^-60, 2^61]: magic-constant seed (12 % error) + 3 Newton steps (error^2 each: 1.4e-2, 2e-4, 4e-8)
-__device__ __forceinline__ float rcp_fma(float d) {
-  float x = __int_as_float(0x7EF311C7 - __float_as_int(d));
-#pragma unroll
-  for (int it = 0; it < 3; ++it) x = fmaf(x, fmaf(-d, x, 1.0f), x);
-  return x;
-}
-
-// Fused head of one row with the column count known at compile time: the accumulator block is
-// [w = 0: mean x P | raw x P][w = 1: mean x P | raw x P], P = NHEAD / 4 (see build_image_kernel).  All tensor-memory
-// loads are issued before the one wait, the columns are handed back to the MMA warp (h_done) before any arithmetic or
-// global store, and the ex2 / rcp chains of all dims overlap.
-template <int NHEAD, int D1C>                  // D1C: D1 known at compile time (0 = use s.D1): branch-free, fully interleaved
-__device__ __forceinline__ void head_fused(uint32_t tblk, const TcShape& s, const float* sC, const TcArgs& a,
-                                           int e, int64_t row, bool valid, bool mine, uint64_t* done_bar, int lane) {
-  constexpr int P = NHEAD / 4;
-  uint32_t v[NHEAD];
-#pragma unroll
-  for (int c = 0; c < NHEAD / 16; ++c) tmem_ld16(tblk + 16 * c, reinterpret_cast<uint32_t (&)[16]>(v[16 * c]));
-  tmem_ld_wait();
-  tc_fence_before();
-  __syncwarp();
-  if (lane == 0) mbar_arrive_remote(done_bar, 0);
-  const int D1 = D1C ? D1C : s.D1;
-  const int dh = (D1 + 1) / 2;
-  float var[2][P], pen[2] = {0.f, 0.f};
-  // padding dims have cmin = 0 and a huge (finite) cnmax: their variance is ~0, no predicate needed
-#pragma unroll
-  for (int w = 0; w < 2; ++w)
-#pragma unroll
-    for (int i = 0; i < P; ++i) {
-      var[w][i] = sC[w * P + i] + rcp_fma(sC[MOPO_MAX_D1 + w * P + i] + exp2_fma(-1.44269504f * __uint_as_float(v[w * 2 * P + P + i])));
-      pen[w] += var[w][i];
-    }
-  if (valid) {
-    float* pp = a.pen2 + (size_t)e * a.ldb + row;
-    pp[0] = pen[0];
-    pp[(size_t)a.E * a.ldb] = pen[1];
-  }
-  if (mine) {
-#pragma unroll
-    for (int w = 0; w < 2; ++w) {
-      float2* dst = a.selmv + (int64_t)(w * dh) * a.ldb + row;
-      const int nd = w ? D1 - dh : dh;
-#pragma unroll
-      for (int i = 0; i < P; ++i) {
-        if (i < nd) *dst = make_float2(__uint_as_float(v[w * 2 * P + i]), var[w][i]);
-        dst += a.ldb;
-      }
-    }
-  }
-}
 
 constexpr int TRACE_CAP = 2048;   // events per role
 // timeline probe: role r (0 issuer, 1 epilogue WG0 warp 0, 2 epilogue WG1 warp 4, 3 loader, 4 head warp 12) of pair 0 / leader CTA
@@ -667,6 +549,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       const int q = warp & 3;
       const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
       const int rr = q * 32 + lane;
+      const HeadShape hs = {s.D1, s.NHEAD};
+      const HeadOut ho = {a.mean, a.lv, a.ldb, a.sel, a.selmv, a.pen2, a.E};
       for (int k = 0; k < n_super; ++k) {
         for (int t = 0; t < 2; ++t) {
           if (2 * k + t >= cnt) continue;
@@ -682,12 +566,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
           const uint32_t tblk = tlane + (t == 0 ? C_XD1 : C_YD1);
           bool arrived = false;
           if (a.sel) {
-            if (s.D1 == 18) { head_fused<48, 18>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }        // obs 17 (+1)
-            else if (s.D1 == 12) { head_fused<32, 12>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }   // obs 11 (+1)
-            else if (s.NHEAD == 48) { head_fused<48, 0>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }
-            else if (s.NHEAD == 32) { head_fused<32, 0>(tblk, s, sLv, a, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }
-            else { epi_head<true>(tblk, 0, s, sLv, a, e, row, valid, mine); epi_head<true>(tblk + s.NHEAD / 2, 1, s, sLv, a, e, row, valid, mine); }
-          } else { epi_head<false>(tblk, 0, s, sLv, a, e, row, valid, false); epi_head<false>(tblk + s.NHEAD / 2, 1, s, sLv, a, e, row, valid, false); }
+            if (s.D1 == 18) { head_fused<48, 18>(tblk, hs, sLv, ho, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }        // obs 17 (+1)
+            else if (s.D1 == 12) { head_fused<32, 12>(tblk, hs, sLv, ho, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }   // obs 11 (+1)
+            else if (s.NHEAD == 48) { head_fused<48, 0>(tblk, hs, sLv, ho, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }
+            else if (s.NHEAD == 32) { head_fused<32, 0>(tblk, hs, sLv, ho, e, row, valid, mine, &bars->h_done[t], lane); arrived = true; }
+            else { epi_head<true>(tblk, 0, hs, sLv, ho, e, row, valid, mine); epi_head<true>(tblk + s.NHEAD / 2, 1, hs, sLv, ho, e, row, valid, mine); }
+          } else { epi_head<false>(tblk, 0, hs, sLv, ho, e, row, valid, false); epi_head<false>(tblk + s.NHEAD / 2, 1, hs, sLv, ho, e, row, valid, false); }
           if (!arrived) {
             tc_fence_before();
             __syncwarp();

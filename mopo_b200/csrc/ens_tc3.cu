@@ -1,0 +1,555 @@
+// tcgen05 ensemble forward at fp32 accuracy (MOPO_PREC_FP32): BNN._compile_outputs (reference mopo/models/bnn.py:631-675,
+// fc.py:96-106) for all nets on the 5th-gen tensor cores, with every operand carried as a bf16 (hi, lo) pair.
+//
+// Arithmetic.  The reference contracts in fp32.  kind::f16 MMAs take 8-bit mantissas, so each fp32 operand x is split
+// x = hi + lo, hi = bf16(x), lo = bf16(x - hi) (16 significant bits) and a layer is THREE MMAs per K step into the same
+// fp32 accumulator in tensor memory:  Ah*Wh + Ah*Wl + Al*Wh  (the dropped Al*Wl term is 2^-16 relative).  Per-term error
+// ~1e-5 relative, ~1e-6 absolute on the outputs: inside the rtol-1e-3 parity bar that the FFMA checker path (ens_fp32.cu)
+// used to be the only one to meet.  swish is x * rcp(1 + ex2(-x log2 e)) (two MUFU ops, ~3 ulp), not tanh.approx (2^-11).
+// TERMS = 1 runs the same kernel as a plain bf16 forward (one MMA per K step, tanh-form swish) for shapes the
+// net-stationary bf16 kernel (ens_tc.cu) cannot hold resident (ant / humanoid: mopo/static/ant.py, humanoid.py).
+//
+// Design ("one tile per CTA pair, activations never leave tensor memory, weights streamed"):
+//   * A CTA PAIR (cluster of 2, cta_group::2, M = 256 rows per MMA) takes (net, 256-row tile) units, range-partitioned
+//     over the 74 pairs.  hi + lo weights of one net are 2 x 2 x 157 KB: they do not fit two SMs, so a unit STREAMS its
+//     net's five layers through a two-stage shared-memory ring (one layer per stage, 86.5 KB per CTA, bulk async copies
+//     from the L2-resident image, refilled as soon as tcgen05.commit reports the layer's MMAs retired).
+//   * Tensor memory holds the activations for the whole unit: two 208-column buffers ping-pong.  Layer j reads its A
+//     operand (TS-form MMA) from one buffer and accumulates into the other; the epilogue then converts the accumulator
+//     IN PLACE: the 16 fp32 columns of feature group g become [8 columns packed bf16x2 hi | 8 columns packed lo] of the
+//     same features, which is exactly the TS-form A operand of the next layer's K step g.  Column map (per CTA, 128 lanes):
+//         [  0,208) buffer 0 : D of layers 0, 2   ->  A of layers 1, 3
+//         [208,416) buffer 1 : D of layers 1, 3   ->  A of layer 2, head
+//         [416,416+NHEAD)    : head accumulator [mean | raw logvar] (owned by the head warps from h_full to h_done)
+//   * The N = 208 hidden width is issued as N = 112 + N = 96 with separate commits, and a layer's K loop runs over the
+//     first half's features first: the epilogue of half 1 runs under the MMAs of half 2, the epilogue of half 2 under
+//     the next layer's first 7 K groups (which only need half-1 features).  With one tile in flight the tensor pipe
+//     still only waits at the first and last layer of a unit.
+//   * Layer 0's A operand comes from shared memory (SS form): the head warps read the raw fp32 obs / act rows, apply the
+//     scaler (models/utils.py:96, true division as the reference), split and write the K-panel tile of the NEXT unit
+//     while the current one computes -- no tiling pass, no HBM round trip.
+//   * bias rides in the constant-1 K column (feature 200 of every hidden activation, k = in of the input tile).
+//
+// Warp roles (448 threads): warps 0-7 epilogue (each owns a 32-lane TMEM quadrant; warpgroup 0 takes groups 0-3 / 7-9,
+// warpgroup 1 groups 4-6 / 10-12), warp 8 of the leader CTA issues every MMA (elect.sync), warp 9 streams weights,
+// warps 10-13 produce input tiles and run the head stage (shared with ens_tc.cu: tc_head.cuh).
+#include "internal.cuh"
+#include "tc_common.cuh"
+#include "tc_head.cuh"
+#include "philox.cuh"
+
+namespace {
+
+using namespace tc;
+
+constexpr int H = 200;
+constexpr int KH = 208;                 // hidden K: 200 features + the constant-1 bias column + 7 zeros
+constexpr int NGRP = KH / 16;           // 13 feature groups (one K = 16 MMA step each)
+constexpr int KP = KH / 8;              // 26 K-panels
+constexpr int NH1 = 112, NH2 = 96;      // the two MMAs (N halves) of a hidden layer
+constexpr int G1 = NH1 / 16;            // groups 0..6 are half-1 features
+constexpr int WR = 104;                 // weight rows per CTA per hidden layer: 56 (half 1) + 48 (half 2)
+constexpr int WP = WR * 16;             // 1664 B: one K-panel of a CTA's weight block
+constexpr int WPART = KP * WP;          // 43264 B: the hi (or lo) part of one hidden layer
+constexpr int STAGE = 2 * WPART;        // 86528 B: one ring stage
+constexpr int XP = 128 * 16;            // 2048 B: one K-panel of a 128-row input block
+constexpr int NTHREADS = 448;
+constexpr int C_BUF0 = 0, C_BUF1 = 208, C_HEAD = 416;
+constexpr int MAX_IN = 64;
+
+struct S3 {
+  int in, D1, HO, K0, NHEAD;            // K0 = roundup(in + 1, 16), NHEAD = roundup(2*D1, 16)
+  __host__ __device__ int w0_part() const { return (K0 / 8) * WP; }
+  __host__ __device__ int head_part() const { return KP * (NHEAD / 2) * 16; }
+  __host__ __device__ int blob_bytes(int j) const { return j == 0 ? 2 * w0_part() : j < 4 ? STAGE : 2 * head_part(); }
+  __host__ __device__ int img_bytes() const { return 2 * w0_part() + 3 * STAGE + 2 * head_part(); }
+  __host__ __device__ int x_part() const { return (K0 / 8) * XP; }
+};
+
+__host__ __device__ inline S3 make_s3(int in, int D1) {
+  S3 s;
+  s.in = in; s.D1 = D1; s.HO = 2 * D1;
+  s.K0 = (in + 1 + 15) / 16 * 16;
+  s.NHEAD = (2 * D1 + 15) / 16 * 16;
+  return s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight image: [net e][cta rank r] -> blob 0 (layer 0) | blobs 1..3 (hidden) | blob 4 (head); a blob = [hi part | lo part],
+// each part in K-panel layout: element (row j, k) at byte (k/8) * (rows*16) + j*16 + (k%8)*2.
+// hidden-layer block of CTA r, local row j:  j < 56: output feature 56 r + j (half 1, N = 112);
+//   j >= 56: feature 112 + 48 r + (j - 56) of half 2 (N = 96: features 112..199, then 8 zero rows).
+// K index: k < Kin -> weight row k; k == Kin -> bias (the A operand carries a constant 1 there); else 0.
+// ---------------------------------------------------------------------------------------------
+struct ImgSrc3 {
+  const float* W[5];
+  const float* b[5];
+};
+
+__global__ void build_image3_kernel(ImgSrc3 src, __nv_bfloat16* __restrict__ img, S3 s, int E) {
+  const int per = s.img_bytes() / 2;
+  const int64_t total = (int64_t)E * 2 * per;
+  const int w0e = s.w0_part() / 2, hle = WPART / 2, hde = s.head_part() / 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(i / (2 * per));
+    const int r = (int)((i / per) % 2);
+    int o = (int)(i % per);
+    int layer, pe, rows;
+    if (o < 2 * w0e) { layer = 0; pe = w0e; rows = WR; }
+    else if (o < 2 * w0e + 6 * hle) { o -= 2 * w0e; layer = 1 + o / (2 * hle); o %= 2 * hle; pe = hle; rows = WR; }
+    else { o -= 2 * w0e + 6 * hle; layer = 4; pe = hde; rows = s.NHEAD / 2; }
+    const int part = o / pe;
+    o %= pe;
+    const int kc = o / (rows * 8), j = (o / 8) % rows, kk = o % 8;
+    const int k = kc * 8 + kk;
+    const int Kin = layer == 0 ? s.in : H;
+    const int Nout = layer == 4 ? s.HO : H;
+    int n;
+    if (layer == 4) {
+      // head rows of CTA r = head block r: [mean(d) x P | raw logvar(d) x P], d = r*dh + i, P = NHEAD/4 (see tc_head.cuh)
+      const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
+      const int hp = j / P, ii = j % P, d = r * dh + ii;
+      n = d < (r ? s.D1 : dh) ? hp * s.D1 + d : -1;
+    } else if (j < 56) n = 56 * r + j;
+    else {
+      n = 112 + 48 * r + (j - 56);
+      if (n >= H) n = -1;
+    }
+    float v = 0.f;
+    if (n >= 0 && n < Nout) {
+      if (k < Kin) v = src.W[layer][((int64_t)e * Kin + k) * Nout + n];
+      else if (k == Kin) v = src.b[layer][(int64_t)e * Nout + n];
+    }
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    img[i] = part == 0 ? hi : __float2bfloat16_rn(v - __bfloat162float(hi));
+  }
+}
+
+// per-row elite pick (bnn.py:342-344): supplied indices, or Philox over the elite list (same draw as prep_tiles_kernel)
+__global__ void pick_kernel(int32_t* __restrict__ sel, const int32_t* __restrict__ model_inds, const int32_t* __restrict__ elites,
+                            int n_elites, int64_t n_max, const int* __restrict__ d_n, uint64_t seed, uint64_t step_id,
+                            const int32_t* __restrict__ origin, int64_t origin_base) {
+  const int64_t n = d_n ? min((int64_t)*d_n, n_max) : n_max;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t orow = origin ? (uint32_t)origin[j] : (uint32_t)(origin_base + j);
+    sel[j] = model_inds ? model_inds[j] : elites[philox_elite(orow, (uint32_t)step_id, seed, (uint32_t)n_elites)];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward kernel
+// ---------------------------------------------------------------------------------------------
+struct T3Args {
+  const uint8_t* img;      // weight images [E][2][img_bytes]
+  const float *obs, *act;  // x = concat(obs [n, od], act [n, ad]) (fake_env.py:46); ad may be 0
+  const float *mu, *sigma; // scaler (models/utils.py:96), or nullptr: x is already scaled
+  int od, ad;
+  const float* max_lv;     // [D1]
+  const float* min_lv;     // [D1]
+  HeadOut out;
+  int n_max;
+  const int* d_n;
+  int E;
+  S3 s;
+};
+
+struct Bars3 {
+  uint64_t w_full[2];      // this CTA's ring stage has landed (tx)
+  uint64_t w_ready[2];     // leader: both CTAs' stage has landed                            (count 2)
+  uint64_t w_free[2];      // each CTA: the MMAs that read the stage have retired            (commit)
+  uint64_t x_full;         // leader: both CTAs' input block is in smem                      (count 8: head warps)
+  uint64_t x_free;         // each CTA: the layer-0 MMAs that read the input block retired   (commit)
+  uint64_t d_full[2];      // each CTA: half 1 / half 2 accumulator of the current layer     (commit)
+  uint64_t a_ready[2];     // leader: half 1 / half 2 of the next A operand is written       (count 16: epilogue warps)
+  uint64_t h_full;         // each CTA: head accumulator ready                               (commit)
+  uint64_t h_done;         // leader: the head warps have read it                            (count 8)
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+// swish (fc.py:21: x * sigmoid(x)).  TERMS == 3: ex2 + rcp, relative error ~3e-7.  TERMS == 1: tanh form, one MUFU op.
+template <int TERMS> __device__ __forceinline__ float swish_acc(float x) {
+  if constexpr (TERMS == 1) { const float xh = 0.5f * x; return fmaf(xh, tanh_fast(xh), xh); }
+  else return x * rcp_approx(1.0f + ex2_approx(-1.44269504f * x));
+}
+
+// N accumulator columns (N = 32 or 16: two or one feature group of this thread's row) at taddr -> swish -> split ->
+// the SAME columns as [hi x 8 | lo x 8] per group.  ONES: the chunk's last group is group 12, whose feature 200 is the
+// constant 1 of the bias row.
+template <int TERMS, int N, bool ONES>
+__device__ __forceinline__ void swish_split_store(uint32_t taddr, const uint32_t (&v)[32]) {
+  uint32_t o[N];
+#pragma unroll
+  for (int g = 0; g < N / 16; ++g) {
+    float sv[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) sv[i] = swish_acc<TERMS>(__uint_as_float(v[16 * g + i]));
+    if (ONES && g == N / 16 - 1) sv[8] = 1.0f;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const uint32_t hi = pack_bf16x2(sv[2 * p], sv[2 * p + 1]);
+      o[16 * g + p] = hi;
+      if constexpr (TERMS == 3) {
+        const float r0 = sv[2 * p] - __uint_as_float(hi << 16);
+        const float r1 = sv[2 * p + 1] - __uint_as_float(hi & 0xFFFF0000u);
+        o[16 * g + 8 + p] = pack_bf16x2(r0, r1);
+      } else o[16 * g + 8 + p] = 0u;
+    }
+  }
+  if constexpr (N == 32) tmem_st32(taddr, reinterpret_cast<const uint32_t (&)[32]>(o));
+  else tmem_st16(taddr, reinterpret_cast<const uint32_t (&)[16]>(o));
+}
+
+// one epilogue part of one warp: NC = 64 or 48 accumulator columns starting at taddr, software pipelined
+template <int TERMS, int NC, bool ONES>
+__device__ __forceinline__ void epi_part(uint32_t taddr) {
+  uint32_t va[32], vb[32];
+  tmem_ld32(taddr, va);
+  tmem_ld_wait();
+  if constexpr (NC == 64) tmem_ld32(taddr + 32, vb);
+  else tmem_ld16(taddr + 32, reinterpret_cast<uint32_t (&)[16]>(vb));
+  swish_split_store<TERMS, 32, false>(taddr, va);
+  tmem_ld_wait();
+  if constexpr (NC == 64) swish_split_store<TERMS, 32, ONES>(taddr + 32, vb);
+  else swish_split_store<TERMS, 16, ONES>(taddr + 32, vb);
+  tmem_st_wait();
+}
+
+// K groups [g0, g1) of one N half: D (+)= A[g] * B[g]^T with A from tensor memory (hi at column 16 g, lo at 16 g + 8)
+template <int TERMS>
+__device__ __forceinline__ void issue_ts(uint32_t d, uint32_t a_buf, uint32_t b_base, uint32_t b_lo, uint32_t bpanel,
+                                         uint32_t idesc, int g0, int g1) {
+  for (int g = g0; g < g1; ++g) {
+    const uint32_t ah = a_buf + 16 * g;
+    const uint32_t b = b_base + g * 2 * bpanel;
+    mma_ts<2>(d, ah, smem_desc(b, bpanel, 128), idesc, g > 0);
+    if constexpr (TERMS == 3) {
+      mma_ts<2>(d, ah, smem_desc(b + b_lo, bpanel, 128), idesc, 1);
+      mma_ts<2>(d, ah + 8, smem_desc(b, bpanel, 128), idesc, 1);
+    }
+  }
+}
+
+template <int TERMS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3_kernel(T3Args a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const S3 s = a.s;
+  uint8_t* sW = smem;                                   // two ring stages
+  uint8_t* sX = sW + 2 * STAGE;                         // input block: hi panels | lo panels
+  float* sLv = reinterpret_cast<float*>(sX + 2 * s.x_part());     // head constants (see tc_head.cuh)
+  float* sMu = sLv + 2 * MOPO_MAX_D1;
+  float* sSg = sMu + MAX_IN;
+  Bars3* bars = reinterpret_cast<Bars3*>(sSg + MAX_IN);
+
+  const int tid = threadIdx.x, lane = tid % 32;
+  const int warp = __shfl_sync(0xffffffffu, tid / 32, 0);
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x / 2, n_pairs = gridDim.x / 2;
+  const int n = __shfl_sync(0xffffffffu, a.d_n ? min(*a.d_n, a.n_max) : a.n_max, 0);
+  const int nT = (n + 255) / 256;
+  const int64_t U = (int64_t)a.E * nT;                  // (net, tile) units, net-major
+  const int u0 = (int)(U * pair / n_pairs), u1 = (int)(U * (pair + 1) / n_pairs);
+
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_ready[i], 2); mbar_init(&bars->w_free[i], 1);
+      mbar_init(&bars->d_full[i], 1); mbar_init(&bars->a_ready[i], 16);
+    }
+    mbar_init(&bars->x_full, 8); mbar_init(&bars->x_free, 1);
+    mbar_init(&bars->h_full, 1); mbar_init(&bars->h_done, 8);
+    fence_barrier_init();
+  }
+  for (int i = tid; i < 2 * (s.NHEAD / 4); i += NTHREADS) {          // head constants per head block (tc_head.cuh)
+    const int P = s.NHEAD / 4, dh = (s.D1 + 1) / 2;
+    const int w = i / P, d = w * dh + i % P;
+    const bool ok = d < (w ? s.D1 : dh);
+    sLv[w * P + i % P] = ok ? expf(a.min_lv[d]) : 0.0f;
+    sLv[MOPO_MAX_D1 + w * P + i % P] = ok ? fminf(expf(-a.max_lv[d]), 1e30f) : 1e30f;
+  }
+  for (int i = tid; i < MAX_IN; i += NTHREADS) {
+    const bool sc = a.mu != nullptr && i < s.in;
+    sMu[i] = sc ? a.mu[i] : 0.0f;
+    sSg[i] = sc ? a.sigma[i] : 1.0f;
+  }
+  if (warp == 8) { tmem_alloc<2>(&bars->tmem_base, 512); tmem_relinquish<2>(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tbase = __shfl_sync(0xffffffffu, bars->tmem_base, 0);
+  cluster_sync_all();                                   // both CTAs' barriers exist before any remote arrive / multicast commit
+
+  // PDL: see ens_tc.cu.  Everything the previous grid (the previous step's tail) writes -- obs, the elite picks -- and
+  // everything it reads that this grid writes (selmv / pen2) is touched by the head warps only, after pdl_wait().
+  pdl_launch_dependents();
+
+  if (warp == 9) {
+    // ===== weight streamer: blob j of the unit's net -> ring stage (load index & 1) =====
+    if (lane == 0) {
+      uint32_t li = 0;
+      for (int u = u0; u < u1; ++u) {
+        const int e = u / nT;
+        const uint8_t* src = a.img + ((size_t)e * 2 + rank) * s.img_bytes();
+        for (int j = 0; j < 5; ++j, ++li) {
+          const uint32_t st = li & 1;
+          if (li >= 2) mbar_wait(&bars->w_free[st], ((li >> 1) - 1) & 1, 1000 + j);
+          const uint32_t bytes = (uint32_t)s.blob_bytes(j);
+          mbar_expect_tx(&bars->w_full[st], bytes);
+          bulk_g2s(sW + st * STAGE, src, bytes / 2, &bars->w_full[st]);
+          bulk_g2s(sW + st * STAGE + bytes / 2, src + bytes / 2, bytes / 2, &bars->w_full[st]);
+          src += bytes;
+          mbar_wait(&bars->w_full[st], (li >> 1) & 1, 1100 + j);
+          mbar_arrive_remote(&bars->w_ready[st], 0);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 8) {
+    // ===== MMA issuer (leader CTA): all lanes run the loop, one elected lane issues =====
+    if (rank == 0) {
+      const uint32_t id1 = idesc_bf16(256, NH1), id2 = idesc_bf16(256, NH2), idh = idesc_bf16(256, s.NHEAD);
+      const uint32_t wa = smem_u32(sW), xa = smem_u32(sX);
+      const uint32_t hpanel = (uint32_t)(s.NHEAD / 2) * 16;
+      uint32_t li = 0, n_x = 0, n_a0 = 0, n_a1 = 0, n_h = 0;
+      for (int u = u0; u < u1; ++u) {
+        for (int j = 0; j < 5; ++j, ++li) {
+          const uint32_t st = li & 1;
+          const uint32_t wb = wa + st * STAGE;
+          mbar_wait_cluster(&bars->w_ready[st], (li >> 1) & 1, 10 * j);
+          if (j == 0) {
+            mbar_wait_cluster(&bars->x_full, n_x & 1, 1); ++n_x;
+            tc_fence_after();
+            if (elect_one()) {
+              const uint32_t wlo = (uint32_t)s.w0_part(), xlo = (uint32_t)s.x_part();
+              for (int hf = 0; hf < 2; ++hf) {
+                const uint32_t d = tbase + C_BUF0 + (hf ? NH1 : 0);
+                const uint32_t idesc = hf ? id2 : id1;
+                const uint32_t boff = hf ? 56 * 16 : 0;
+                for (int ks = 0; ks < s.K0 / 16; ++ks) {
+                  const uint32_t ax = xa + ks * 2 * XP, b = wb + boff + ks * 2 * WP;
+                  mma_ss<2>(d, smem_desc(ax, XP, 128), smem_desc(b, WP, 128), idesc, ks > 0);
+                  if constexpr (TERMS == 3) {
+                    mma_ss<2>(d, smem_desc(ax, XP, 128), smem_desc(b + wlo, WP, 128), idesc, 1);
+                    mma_ss<2>(d, smem_desc(ax + xlo, XP, 128), smem_desc(b, WP, 128), idesc, 1);
+                  }
+                }
+                mma_commit<2>(&bars->d_full[hf]);
+              }
+              mma_commit<2>(&bars->x_free);
+              mma_commit<2>(&bars->w_free[st]);
+            }
+            __syncwarp();
+          } else if (j < 4) {
+            const uint32_t abuf = tbase + (((j - 1) & 1) ? C_BUF1 : C_BUF0);
+            const uint32_t dbuf = tbase + ((j & 1) ? C_BUF1 : C_BUF0);
+            mbar_wait_cluster(&bars->a_ready[0], n_a0 & 1, 10 * j + 2); ++n_a0;
+            tc_fence_after();
+            if (elect_one()) issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, 0, G1);
+            __syncwarp();
+            mbar_wait_cluster(&bars->a_ready[1], n_a1 & 1, 10 * j + 3); ++n_a1;
+            tc_fence_after();
+            if (elect_one()) {
+              issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, G1, NGRP);
+              mma_commit<2>(&bars->d_full[0]);
+              issue_ts<TERMS>(dbuf + NH1, abuf, wb + 56 * 16, WPART, WP, id2, 0, NGRP);
+              mma_commit<2>(&bars->d_full[1]);
+              mma_commit<2>(&bars->w_free[st]);
+            }
+            __syncwarp();
+          } else {
+            mbar_wait_cluster(&bars->a_ready[0], n_a0 & 1, 42); ++n_a0;
+            mbar_wait_cluster(&bars->a_ready[1], n_a1 & 1, 43); ++n_a1;
+            // the head MMA overwrites the previous unit's head accumulator: the head warps must have read it
+            if (n_h > 0) mbar_wait_cluster(&bars->h_done, (n_h - 1) & 1, 44);
+            ++n_h;
+            tc_fence_after();
+            if (elect_one()) {
+              issue_ts<TERMS>(tbase + C_HEAD, tbase + C_BUF1, wb, (uint32_t)s.head_part(), hpanel, idh, 0, NGRP);
+              mma_commit<2>(&bars->h_full);
+              mma_commit<2>(&bars->w_free[st]);
+            }
+            __syncwarp();
+          }
+        }
+      }
+    }
+  } else if (warp < 8) {
+    // ===== epilogue warps: accumulator half -> swish -> (hi, lo) A operand, in place =====
+    const int wg = warp >> 2, q = warp & 3;
+    const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+    uint32_t n_d = 0;                                   // layers consumed (both halves flip once per layer)
+    for (int u = u0; u < u1; ++u) {
+      for (int j = 0; j < 4; ++j, ++n_d) {
+        const uint32_t buf = tlane + ((j & 1) ? C_BUF1 : C_BUF0);
+        mbar_wait(&bars->d_full[0], n_d & 1, 100 + j);
+        tc_fence_after();
+        if (wg == 0) epi_part<TERMS, 64, false>(buf);              // groups 0..3
+        else epi_part<TERMS, 48, false>(buf + 64);                 // groups 4..6
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_remote(&bars->a_ready[0], 0);
+        mbar_wait(&bars->d_full[1], n_d & 1, 110 + j);
+        tc_fence_after();
+        if (wg == 0) epi_part<TERMS, 48, false>(buf + 112);        // groups 7..9
+        else epi_part<TERMS, 48, true>(buf + 160);                 // groups 10..12 (feature 200 = 1)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_remote(&bars->a_ready[1], 0);
+      }
+    }
+  } else {
+    // ===== head warps (10-13, TMEM quadrant warp % 4): input tiles of the next unit, then the head stage =====
+    const int q = warp & 3;
+    const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
+    const int rr = q * 32 + lane;
+    const HeadShape hs = {s.D1, s.NHEAD};
+    constexpr bool PREC = TERMS == 3;
+    const int kcs = s.K0 / 8;
+    pdl_wait();
+    // x block of unit u: this thread's row -> K-panels (hi | lo) of the SS-form A operand of layer 0
+    auto produce_x = [&](int u) {
+      const int t = u % nT;
+      const int64_t row = 256 * (int64_t)t + (int64_t)rank * 128 + rr;
+      const bool ok = row < n;
+      const float* po = a.obs + row * a.od;
+      const float* pa = a.act + row * a.ad;
+      for (int kc = 0; kc < kcs; ++kc) {
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int k = kc * 8 + i;
+          float x = 0.0f;
+          if (ok) {
+            if (k < a.od) x = (po[k] - sMu[k]) / sSg[k];                      // models/utils.py:96
+            else if (k < s.in) x = (pa[k - a.od] - sMu[k]) / sSg[k];
+            else if (k == s.in) x = 1.0f;                                    // the bias row's constant
+          }
+          v[i] = x;
+        }
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          hi[p] = pack_bf16x2(v[2 * p], v[2 * p + 1]);
+          lo[p] = TERMS == 3 ? pack_bf16x2(v[2 * p] - __uint_as_float(hi[p] << 16), v[2 * p + 1] - __uint_as_float(hi[p] & 0xFFFF0000u)) : 0u;
+        }
+        st_shared_v4(sX + kc * XP + rr * 16, hi[0], hi[1], hi[2], hi[3]);
+        st_shared_v4(sX + s.x_part() + kc * XP + rr * 16, lo[0], lo[1], lo[2], lo[3]);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(&bars->x_full, 0);
+    };
+    if (u0 < u1) produce_x(u0);
+    uint32_t n_h = 0;
+    for (int u = u0; u < u1; ++u, ++n_h) {
+      const int e = u / nT, t = u - e * nT;
+      if (u + 1 < u1) {
+        mbar_wait(&bars->x_free, n_h & 1, 200);          // layer 0 of unit u has consumed the block
+        produce_x(u + 1);
+      }
+      const int64_t row = 256 * (int64_t)t + (int64_t)rank * 128 + rr;
+      const bool valid = row < n;
+      bool mine = false;
+      if (a.out.sel && valid) mine = a.out.sel[row] == e;
+      mbar_wait(&bars->h_full, n_h & 1, 210);
+      tc_fence_after();
+      const uint32_t tblk = tlane + C_HEAD;
+      bool arrived = false;
+      if (a.out.sel) {
+        if (s.D1 == 18) { head_fused<48, 18, PREC>(tblk, hs, sLv, a.out, e, row, valid, mine, &bars->h_done, lane); arrived = true; }
+        else if (s.D1 == 12) { head_fused<32, 12, PREC>(tblk, hs, sLv, a.out, e, row, valid, mine, &bars->h_done, lane); arrived = true; }
+        else if (s.NHEAD == 48) { head_fused<48, 0, PREC>(tblk, hs, sLv, a.out, e, row, valid, mine, &bars->h_done, lane); arrived = true; }
+        else if (s.NHEAD == 32) { head_fused<32, 0, PREC>(tblk, hs, sLv, a.out, e, row, valid, mine, &bars->h_done, lane); arrived = true; }
+        else { epi_head<true, PREC>(tblk, 0, hs, sLv, a.out, e, row, valid, mine); epi_head<true, PREC>(tblk + s.NHEAD / 2, 1, hs, sLv, a.out, e, row, valid, mine); }
+      } else { epi_head<false, PREC>(tblk, 0, hs, sLv, a.out, e, row, valid, false); epi_head<false, PREC>(tblk + s.NHEAD / 2, 1, hs, sLv, a.out, e, row, valid, false); }
+      if (!arrived) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_remote(&bars->h_done, 0);
+      }
+    }
+  }
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                   // peer smem / TMEM must outlive the leader's MMAs
+  if (warp == 8) tmem_dealloc<2>(tbase, 512);
+}
+
+size_t tc3_smem_bytes(const S3& s) {
+  return (size_t)2 * STAGE + 2 * s.x_part() + (2 * MOPO_MAX_D1 + 2 * MAX_IN) * sizeof(float) + sizeof(Bars3) + 128;
+}
+
+}  // namespace
+
+int tc3_supported(const mopo_ens* h) {
+  if (h->H != H || h->L != 4) return 0;
+  if (h->in + 1 > MAX_IN || h->HO > 96) return 0;
+  const S3 s = make_s3(h->in, h->D1);
+  return 2 * s.w0_part() <= STAGE && 2 * s.head_part() <= STAGE && tc3_smem_bytes(s) <= 227 * 1024;
+}
+
+int tc3_build_images(mopo_ens* h, cudaStream_t st) {
+  const S3 s = make_s3(h->in, h->D1);
+  const size_t bytes = (size_t)h->E * 2 * s.img_bytes();
+  if (h->tc3_img_bytes < bytes) {
+    if (h->tc3_img) cudaFree(h->tc3_img);
+    h->tc3_img = nullptr;
+    CUDA_TRY(cudaMalloc(&h->tc3_img, bytes));
+    h->tc3_img_bytes = bytes;
+  }
+  ImgSrc3 src;
+  for (int l = 0; l < 5; ++l) { src.W[l] = h->W[l]; src.b[l] = h->b[l]; }
+  MOPO_COUNT_LAUNCH, build_image3_kernel<<<592, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(h->tc3_img), s, h->E);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int tc3_pick(mopo_ens* h, int32_t* sel, const int32_t* model_inds, int64_t n_max, const int* d_n, uint64_t seed,
+             uint64_t step_id, const int32_t* origin, int64_t origin_base, cudaStream_t st) {
+  if (n_max == 0) return MOPO_OK;
+  const int64_t g64 = (n_max + 255) / 256;
+  MOPO_COUNT_LAUNCH, pick_kernel<<<(int)(g64 > 148 * 8 ? 148 * 8 : g64), 256, 0, st>>>(sel, model_inds, h->elites, h->n_elites, n_max, d_n,
+                                                                                  seed, step_id, origin, origin_base);
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}
+
+int tc3_launch(mopo_ens* h, int terms, const Tc3In& x, int64_t n_max, const int* d_n, const TcOut& o, cudaStream_t st) {
+  if (n_max == 0) return MOPO_OK;
+  if (!h->tc3_img) { mopo_set_error("tc3_launch: weight images not built"); return MOPO_ESTATE; }
+  T3Args a;
+  a.s = make_s3(h->in, h->D1);
+  a.img = reinterpret_cast<const uint8_t*>(h->tc3_img);
+  a.obs = x.obs; a.act = x.act ? x.act : x.obs; a.od = x.od; a.ad = x.ad;
+  a.mu = x.scale ? h->mu : nullptr; a.sigma = x.scale ? h->sigma : nullptr;
+  a.max_lv = h->max_lv; a.min_lv = h->min_lv;
+  a.out.mean = o.mean; a.out.lv = o.lv; a.out.ldb = o.ldb;
+  a.out.sel = o.sel; a.out.selmv = o.selmv; a.out.pen2 = o.pen2; a.out.E = h->E;
+  a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E;
+  const size_t smem = tc3_smem_bytes(a.s);
+  const int n_pairs = h->sm_count / 2;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  if (h->timing) {
+    if (h->ev_used + 2 > h->ev.size()) {
+      for (int i = 0; i < 2; ++i) { cudaEvent_t e; CUDA_TRY(cudaEventCreate(&e)); h->ev.push_back(e); }
+    }
+    ev0 = h->ev[h->ev_used]; ev1 = h->ev[h->ev_used + 1]; h->ev_used += 2;
+    CUDA_TRY(cudaEventRecord(ev0, st));
+  }
+  auto kern = terms == 3 ? ens_tc3_kernel<3> : ens_tc3_kernel<1>;
+  CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * n_pairs); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = o.pdl ? 1 : 0;          // rollout chain: behind the previous step's tail (see pdl_wait())
+  MOPO_COUNT_LAUNCH;
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, a));
+  if (ev1) CUDA_TRY(cudaEventRecord(ev1, st));
+  CUDA_TRY(cudaGetLastError());
+  return MOPO_OK;
+}

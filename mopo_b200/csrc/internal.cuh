@@ -75,6 +75,9 @@ struct mopo_ens {
   // bf16 UMMA-ready images for the tcgen05 path (built by tc_build_images).
   void* tc_img = nullptr;
   size_t tc_img_bytes = 0;
+  // (hi, lo) bf16 images for the fp32-accurate tcgen05 path (built by tc3_build_images).
+  void* tc3_img = nullptr;
+  size_t tc3_img_bytes = 0;
   // per-launch CUDA-event timing of the forward kernel (mopo_kernel_timing): events on the launching stream
   bool timing = false, timing_tail = false;
   std::vector<cudaEvent_t> ev;      // start/stop pairs of the launches since the last query
@@ -126,6 +129,19 @@ int tc_reserve_xtiles(mopo_ens* h, int64_t n_max, int* K0);
 int tc_tiles_from_xn(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, cudaStream_t st);
 int tc_tiles_from_step(mopo_ens* h, const TcPrep& q, cudaStream_t st);
 int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaStream_t st);
+
+// ---- tcgen05 split-bf16 forward at fp32 accuracy (ens_tc3.cu) -------------------------------------
+// terms = 3: every operand as a bf16 (hi, lo) pair, three MMAs per K step (MOPO_PREC_FP32); terms = 1: plain bf16 with
+// streamed weights (MOPO_PREC_BF16 for the shapes tc_supported rejects).  The kernel reads the raw rows itself.
+int tc3_supported(const mopo_ens* h);
+int tc3_build_images(mopo_ens* h, cudaStream_t st);
+struct Tc3In {
+  const float *obs, *act; int od, ad;     // x = concat(obs [n, od], act [n, ad]); ad == 0: obs is the whole input row
+  bool scale;                             // apply the handle's scaler (false: x is already scaled)
+};
+int tc3_pick(mopo_ens* h, int32_t* sel, const int32_t* model_inds, int64_t n_max, const int* d_n, uint64_t seed,
+             uint64_t step_id, const int32_t* origin, int64_t origin_base, cudaStream_t st);
+int tc3_launch(mopo_ens* h, int terms, const Tc3In& x, int64_t n_max, const int* d_n, const TcOut& o, cudaStream_t st);
 
 // ---- step tail / pool / compaction (tail.cu) ---------------------------------------------------
 struct TailArgs {

@@ -128,7 +128,7 @@ int policy_run(mopo_policy* p, const PolicyRun& r, cudaStream_t st) {
     REQUIRE(policy_tc_supported(p), MOPO_EUNSUPPORTED, "policy: the tcgen05 path supports hidden_dim=256, obs_dim+2<=64, 2*act_dim<=32");
     return policy_tc_launch(p, r, st);
   }
-  REQUIRE(r.precision == MOPO_PREC_FP32 || r.precision == MOPO_PREC_BF16, MOPO_EINVAL, "policy: unknown precision %d", r.precision);
+  REQUIRE(r.precision == MOPO_PREC_FP32 || r.precision == MOPO_PREC_BF16 || r.precision == MOPO_PREC_FP32_REF, MOPO_EINVAL, "policy: unknown precision %d", r.precision);
   return policy_fp32(p, r, st);
 }
 

@@ -434,9 +434,10 @@ compact_kernel(const float* __restrict__ next_obs, const uint8_t* __restrict__ t
         }
         ta.xt[((dst / TAIL_ROWS) * kcs + kc) * TAIL_ROWS + dst % TAIL_ROWS] = make_uint4(p[0], p[1], p[2], p[3]);
       }
+    }
+    if (ta.sel)
       ta.sel[dst] = ta.model_inds ? ta.model_inds[dst]
                                   : ta.elites[philox_elite((uint32_t)org, (uint32_t)ta.step_id, ta.seed, (uint32_t)ta.n_elites)];
-    }
   }
   if (blockIdx.x == gridDim.x - 1) {
     int tot = base;

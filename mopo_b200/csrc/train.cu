@@ -463,6 +463,7 @@ MOPO_API int mopo_ens_train_end(mopo_ens* h, void* stream) {
   CUDA_TRY(cudaSetDevice(h->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
   if (tc_supported(h)) TRY(tc_build_images(h, st));
+  if (tc3_supported(h)) TRY(tc3_build_images(h, st));
   CUDA_TRY(cudaStreamSynchronize(st));
   mopo_train_release(h);
   return MOPO_OK;

@@ -2,12 +2,16 @@
 
     python tests/golden/make_golden.py
 
-Imports /root/reference/mopo/models/fake_env.py (FakeEnv) and mopo/static/*.py unmodified
-(a stub ``tensorflow`` module satisfies fake_env.py:2; only step_ph uses it) and the
-reference's FlexibleReplayPool, drives FakeEnv.step with the oracle's NumPy forward
-(TensorFlow 1.14 is absent: the forward itself stays unpinned, see oracle/__init__.py),
-with np.random.normal / model.random_inds patched so the injected noise and elite indices
-are recorded.  The committed fixtures travel to the GPU box; /root/reference does not.
+Imports /root/reference/mopo/models/fake_env.py (FakeEnv), mopo/static/*.py, the reference's
+FlexibleReplayPool AND its model code -- mopo/models/constructor.py, bnn.py, fc.py, utils.py --
+all unmodified.  TensorFlow 1.14 is absent from this image, so ``tensorflow`` is
+tests/golden/tf_numpy_stub.py: a graph-mode stand-in that evaluates the dozen ops those files call
+in float32 NumPy.  FakeEnv.step is therefore driven by the reference's own BNN (construct_model ->
+finalize -> predict via sess.run), loaded with the seeded synthetic parameters, with
+np.random.normal / model.random_inds patched so the injected noise and elite indices are recorded.
+fwd_*.npz hold BNN.predict itself (2-D factored / aggregated, 3-D per-net inputs, both head modes).
+What stays third-party is the arithmetic inside TensorFlow's kernels.  The committed fixtures travel
+to the GPU box; /root/reference does not.
 """
 import os, sys, types, importlib.util
 import numpy as np
@@ -27,7 +31,10 @@ def _load(name, path):
 
 
 def load_reference():
-    sys.modules.setdefault('tensorflow', types.ModuleType('tensorflow'))
+    sys.path.insert(0, HERE)
+    import tf_numpy_stub
+    tf_numpy_stub.install()
+    sys.path.insert(0, REF)
     fe = _load('ref_fake_env', os.path.join(REF, 'mopo/models/fake_env.py'))
     static = {}
     for f in sorted(os.listdir(os.path.join(REF, 'mopo/static'))):
@@ -44,14 +51,46 @@ def load_reference():
     return fe.FakeEnv, static, pool.FlexibleReplayPool
 
 
+def reference_model(p, name):
+    """The reference's own BNN (constructor.py:7-43 -> bnn.py finalize), loaded with the parameter dict ``p``."""
+    from mopo.models.constructor import construct_model       # /root/reference, through the TF stand-in
+    import contextlib, io
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = construct_model(obs_dim=p['obs_dim'], act_dim=p['act_dim'], rew_dim=p['rew_dim'], hidden_dim=p['hidden_dim'],
+                            num_networks=p['num_networks'], num_elites=5, separate_mean_var=p['separate_mean_var'], name=name)
+    for layer, w, b in zip(m.layers, p['weights'], p['biases']):
+        layer.weights.load(w); layer.biases.load(b)
+    if p['separate_mean_var']:
+        m.var_layers[0].weights.load(p['var_weights']); m.var_layers[0].biases.load(p['var_biases'])
+    m.scaler.mu.load(p['mu']); m.scaler.sigma.load(p['sigma']); m.scaler.cache()
+    m.max_logvar.load(p['max_logvar']); m.min_logvar.load(p['min_logvar'])
+    return m
+
+
+def forward_case(domain, B, seed, separate):
+    """BNN.predict of the reference (bnn.py:508-546 over _compile_outputs, bnn.py:631-675): every input mode."""
+    p, obs, act = ens.synthetic_case(domain, B, seed=seed, separate_mean_var=separate)
+    m = reference_model(p, 'fwd_%s_%d' % (domain, seed))
+    x = np.concatenate([obs, act], -1)
+    rng = np.random.RandomState(seed + 3)
+    x3 = (x[None] + 0.1 * rng.standard_normal((p['num_networks'],) + x.shape)).astype(np.float32)
+    mean_fac, var_fac = m.predict(x, factored=True)
+    mean, var = m.predict(x, factored=False)
+    mean3, var3 = m.predict(x3, factored=True)
+    assert mean_fac.dtype == np.float32 and mean_fac.shape == (p['num_networks'], B, p['obs_dim'] + 1)
+    return dict(domain=domain, B=B, seed=seed, separate=separate, x3=x3, mean_fac=mean_fac, var_fac=var_fac,
+                mean=mean, var=var, mean3=mean3, var3=var3)
+
+
 def step_case(FakeEnv, static, domain, B, seed, learned_var, deterministic, coeff=1.0, separate=True, model_inds_set=None):
     p, obs, act = ens.synthetic_case(domain, B, seed=seed, separate_mean_var=separate)
-    model = ens.OracleModel(p, model_inds=model_inds_set)
+    model = reference_model(p, 'step_%s_%d' % (domain, seed))
+    model._model_inds = list(range(5)) if model_inds_set is None else list(model_inds_set)
     rng = np.random.RandomState(seed + 7)
     D1 = obs.shape[1] + 1
     noise = rng.standard_normal((model.num_nets, B, D1))
     inds = rng.choice(model._model_inds, size=B)
-    model.forced_inds = inds
+    model.random_inds = lambda batch_size: inds           # bnn.py:342-344 draws from global np.random: inject instead
     env = FakeEnv(model, static[domain], penalty_coeff=coeff, penalty_learned_var=learned_var)
     orig = np.random.normal
     np.random.normal = lambda size=None: noise.reshape(size)
@@ -134,6 +173,10 @@ def main():
     cases.append(step_case(FakeEnv, static, 'humanoid', B, seed=17, learned_var=False, deterministic=False, coeff=2.5))
     for i, c in enumerate(cases):
         np.savez_compressed(os.path.join(HERE, 'step_%02d_%s.npz' % (i, c['domain'])), **c)
+    fwd = [forward_case('halfcheetah', 64, 31, True), forward_case('hopper', 50, 32, False),
+           forward_case('humanoid', 40, 33, True), forward_case('walker2d', 33, 34, True)]
+    for i, c in enumerate(fwd):
+        np.savez_compressed(os.path.join(HERE, 'fwd_%02d_%s.npz' % (i, c['domain'])), **c)
     dims = {'halfcheetah': 17, 'hopper': 11, 'walker2d': 17, 'ant': 27, 'antangle': 27, 'humanoid': 45,
             'pendulum': 3, 'point2denv': 4}
     for i, (d, od) in enumerate(dims.items()):

@@ -56,6 +56,22 @@ def test_predict_matches_oracle(domain, sep):
     np.testing.assert_allclose(vv, v64.mean(0) + np.square(m64 - m64.mean(0)).mean(0), rtol=RTOL)
 
 
+@pytest.mark.parametrize('path', golden_files('fwd_'))
+def test_predict_matches_reference_bnn_fixture(path):
+    """The device forward against fixtures produced by the reference's own BNN.predict (tests/golden/make_golden.py runs
+    constructor.py / bnn.py / fc.py / utils.py unmodified over a NumPy TF stand-in): 2-D factored and aggregated."""
+    g = np.load(path)
+    p, obs, act = ens.synthetic_case(str(g['domain']), int(g['B']), seed=int(g['seed']), separate_mean_var=bool(g['separate']))
+    x = np.concatenate([obs, act], -1)
+    m = make_model(p)
+    mean, var = m.predict(x, factored=True)
+    np.testing.assert_allclose(mean, g['mean_fac'], rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(var, g['var_fac'], rtol=RTOL)
+    mm, vv = m.predict(x)
+    np.testing.assert_allclose(mm, g['mean'], rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(vv, g['var'], rtol=RTOL)
+
+
 def test_kat_zero_weights_device():
     p = ens.init_params(11, 3, seed=0)
     p['weights'] = [w * 0 for w in p['weights']]

@@ -33,6 +33,28 @@ def test_step_matches_reference(path):
         assert info['penalty'] is None
 
 
+@pytest.mark.parametrize('path', golden_files('fwd_'))
+def test_forward_matches_reference(path):
+    """oracle.ensemble.forward vs the reference's own BNN.predict (constructor.py -> bnn.py finalize / _compile_outputs,
+    fc.py compute_output_tensor, utils.py transform) run unmodified over the NumPy TF stand-in (tests/golden/make_golden.py):
+    2-D factored, 2-D aggregated (bnn.py:261-263), 3-D per-net inputs (fc.py:100-101), separate and combined heads."""
+    g = np.load(path)
+    p, obs, act = ens.synthetic_case(str(g['domain']), int(g['B']), seed=int(g['seed']), separate_mean_var=bool(g['separate']))
+    x = np.concatenate([obs, act], -1)
+    mean, var = ens.forward(p, x, np.float32)
+    np.testing.assert_allclose(mean, g['mean_fac'], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(var, g['var_fac'], rtol=1e-6)
+    m, v = ens.OracleModel(p).predict(x, factored=False)
+    np.testing.assert_allclose(m, g['mean'], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(v, g['var'], rtol=1e-6)
+    mean3, var3 = ens.forward(p, g['x3'], np.float32)
+    np.testing.assert_allclose(mean3, g['mean3'], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(var3, g['var3'], rtol=1e-6)
+    # and the float64 "truth" the device paths are held to stays within fp32 rounding of the reference's float32 run
+    m64, v64 = ens.forward(p, x, np.float64)
+    np.testing.assert_allclose(g['mean_fac'], m64, rtol=2e-4, atol=2e-5)
+
+
 @pytest.mark.parametrize('path', golden_files('term_'))
 def test_termination_matches_reference(path):
     g = np.load(path)
