@@ -80,6 +80,8 @@ typedef struct {
 
 const char* mopo_last_error(void);
 int mopo_version(void);
+/* SHA-256 prefix of the sources and flags this binary was built from (mopo_b200/build.py: tree_hash) */
+const char* mopo_build_hash(void);
 /* number of kernels this library has launched in this process (bench.py reports the delta) */
 int64_t mopo_launch_count(void);
 
@@ -97,6 +99,13 @@ int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const float* c
                         const float* mu, const float* sigma,
                         const float* max_logvar, const float* min_logvar,
                         int on_device, void* stream);
+
+/* Device address + element count of one fp32 master image (reference layout), for in-place device-to-device updates such as
+ * the NCCL broadcast of the ensemble after model training; call mopo_ens_refresh_images afterwards (rebuilds the tensor-core
+ * operand images from the fp32 masters). */
+enum { MOPO_IMG_W = 0, MOPO_IMG_B = 1, MOPO_IMG_MU = 2, MOPO_IMG_SIGMA = 3, MOPO_IMG_MAX_LOGVAR = 4, MOPO_IMG_MIN_LOGVAR = 5 };
+int mopo_ens_param_image(mopo_ens* h, int32_t which, int32_t layer, void** ptr, int64_t* count);
+int mopo_ens_refresh_images(mopo_ens* h, void* stream);
 
 /* Elite set = BNN._model_inds (host int32[n], each in [0,E)). */
 int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n);
@@ -158,10 +167,14 @@ void* mopo_pool_field(const mopo_pool* p, int32_t field);
 /* add_samples (flexible_replay_pool.py:57-83): device arrays of n rows, modular index, last write wins. */
 int mopo_pool_add(mopo_pool* p, const float* obs, const float* act, const float* next_obs,
                   const float* rew, const uint8_t* term, int64_t n, void* stream);
+/* Rows [pointer, pointer+n) of the field arrays were filled in place (a collective writing straight into mopo_pool_field
+ * memory): advance pointer / size as add_samples does (:45-48).  Requires pointer + n <= max_size. */
+int mopo_pool_advance(mopo_pool* p, int64_t n);
 /* batch_by_indices (:121-135): idx device int64[n]; outputs device arrays of n rows. */
 int mopo_pool_gather(const mopo_pool* p, const int64_t* idx, int64_t n, float* obs, float* act,
                      float* next_obs, float* rew, uint8_t* term, void* stream);
-/* random_batch (:85-92) with Philox indices in [0,size). */
+/* random_batch (:85-92) with Philox indices in [0,size): index i of the draw uses counter (i, offset) -- `offset` is the id of
+ * the draw, two draws with different offsets are independent (np.random.randint per batch). */
 int mopo_pool_sample(const mopo_pool* p, int64_t n, uint64_t seed, uint64_t offset, int64_t* idx_out,
                      float* obs, float* act, float* next_obs, float* rew, uint8_t* term, void* stream);
 
@@ -301,24 +314,6 @@ int mopo_rollout_host(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args* a, 
  * number of launches since then (synchronising on the events) and clears. bench.py's roofline uses it. */
 int mopo_kernel_timing(mopo_ens* h, int enable);
 int mopo_kernel_time(mopo_ens* h, double* ms_total, int64_t* launches);
-
-/* ---- debug ---------------------------------------------------------------------------------- */
-/* tcgen05 known-answer probe: D[M,N] = A[M,K] * B[N,K]^T (bf16 bit patterns in, fp32 out; device pointers),
- * cta_group 1|2, A operand from shared memory (0) or tensor memory (1).  Used by tests/test_gpu_umma.py. */
-int mopo_debug_umma_probe(int cta_group, int a_in_tmem, const uint16_t* A, const uint16_t* B, float* D,
-                          int M, int N, int K, void* stream);
-
-/* Timeline probe of the tcgen05 forward: runs mopo_ens_forward(bf16) once with per-role clock64 stamps of CTA
- * pair 0; trace = device uint64[5*2048] (role-major: 0 MMA issuer, 1/2 hidden-epilogue warpgroups, 3 input loader, 4 head warps),
- * entry = tag << 48 | clock.  tools/tc_timeline.py decodes it. */
-int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar,
-                        unsigned long long* trace, void* stream);
-/* Pipe-rate microbenchmark: kind 0 tanh.approx.f32, 1 tanh.approx.bf16x2, 2 ex2.approx.f32, 3 tanh.approx.f16x2,
- * 4 fma.bf16x2, 5 fma.f32; cycles_dev = device int64[n_blocks + 1] (per-block clock64 delta; last = scratch). */
-int mopo_debug_pipe_bench(int kind, int iters, long long* cycles_dev, int n_blocks, void* stream);
-/* tcgen05.mma rate probe: ksteps K=16 bf16 MMAs of (128*cta_group) x N over nacc round-robin accumulators, A from
- * TMEM (1) or shared memory (0); out_dev = device int64[2]: cycles to commit arrival, cycles to last issue. */
-int mopo_debug_mma_rate(int cta_group, int N, int nacc, int a_tmem, int ksteps, long long* out_dev, void* stream);
 
 #ifdef __cplusplus
 }

@@ -14,6 +14,7 @@ TERM_NEVER, TERM_HOPPER, TERM_WALKER2D, TERM_ANT, TERM_HUMANOID = range(5)
 PEN_NONE, PEN_LEARNED_VAR, PEN_DISAGREEMENT = range(3)
 PREC_FP32, PREC_BF16, PREC_FP32_REF = 0, 1, 2
 F_ACTIONS, F_REWARDS, F_TERMINALS, F_OBS, F_NEXT_OBS = range(5)
+IMG_W, IMG_B, IMG_MU, IMG_SIGMA, IMG_MAX_LOGVAR, IMG_MIN_LOGVAR = range(6)
 
 c_f32p = C.c_void_p  # device/host float*, passed as raw addresses
 
@@ -67,12 +68,15 @@ class SacBatch(C.Structure):
 SYMBOLS = {
     'mopo_last_error': (C.c_char_p, []),
     'mopo_version': (C.c_int, []),
+    'mopo_build_hash': (C.c_char_p, []),
     'mopo_launch_count': (C.c_int64, []),
     'mopo_ens_create': (C.c_int, [C.POINTER(EnsCfg), C.POINTER(C.c_void_p)]),
     'mopo_ens_destroy': (C.c_int, [C.c_void_p]),
     'mopo_ens_set_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_set_elites': (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32]),
+    'mopo_ens_param_image': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
+    'mopo_ens_refresh_images': (C.c_int, [C.c_void_p, C.c_void_p]),
     'mopo_ens_predict': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_train_begin': (C.c_int, [C.c_void_p, C.c_float, C.POINTER(C.c_float)]),
@@ -92,14 +96,11 @@ SYMBOLS = {
     'mopo_pool_pointer': (C.c_int64, [C.c_void_p]),
     'mopo_pool_max_size': (C.c_int64, [C.c_void_p]),
     'mopo_pool_field': (C.c_void_p, [C.c_void_p, C.c_int32]),
+    'mopo_pool_advance': (C.c_int, [C.c_void_p, C.c_int64]),
     'mopo_pool_add': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     'mopo_pool_gather': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mopo_pool_sample': (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    'mopo_debug_umma_probe': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
-    'mopo_debug_tc_trace': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    'mopo_debug_pipe_bench': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
-    'mopo_debug_mma_rate': (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'mopo_kernel_timing': (C.c_int, [C.c_void_p, C.c_int]),
     'mopo_kernel_time': (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     'mopo_rollout': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(RolloutArgs), C.c_void_p]),
@@ -119,7 +120,17 @@ SYMBOLS = {
     'mopo_policy_act': (C.c_int, [C.c_void_p, C.POINTER(PolicyArgs), C.c_void_p]),
 }
 
+# developer probes: only in libmopo_b200_dbg.so (include/mopo_b200_debug.h; python -m mopo_b200.build --probes)
+DEBUG_SYMBOLS = {
+    'mopo_debug_umma_probe': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    'mopo_debug_tc_trace': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'mopo_debug_tc3_trace': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    'mopo_debug_pipe_bench': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_debug_mma_rate': (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+}
+
 _lib = None
+_dbg = None
 
 
 def load():
@@ -138,13 +149,28 @@ def load():
     return lib
 
 
+def load_probes():
+    """The probe build of the library (all product symbols + mopo_debug_*): built on demand, never used by the product path."""
+    global _dbg
+    if _dbg is not None:
+        return _dbg
+    from . import build as _b
+    path = _b.build(probes=True)
+    lib = C.CDLL(path, mode=C.RTLD_LOCAL)
+    for name, (res, args) in list(SYMBOLS.items()) + list(DEBUG_SYMBOLS.items()):
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    _dbg = lib
+    return lib
+
+
 _EXC = {EINVAL: ValueError, ESTATE: RuntimeError, ECUDA: RuntimeError, EUNSUPPORTED: NotImplementedError}
 
 
-def check(rc):
+def check(rc, lib=None):
     """Re-raise a C status as the exception type the reference would raise."""
     if rc != OK:
-        msg = load().mopo_last_error()
+        msg = (lib or load()).mopo_last_error()
         raise _EXC.get(rc, RuntimeError)((msg or b'').decode() or 'mopo_b200 error %d' % rc)
 
 

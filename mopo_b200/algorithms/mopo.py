@@ -21,7 +21,7 @@ from ..replay_pools import SimpleReplayPool
 class ModelRollout:
     def __init__(self, fake_env, env_pool, rollout_batch_size=100000, rollout_schedule=(20, 100, 1, 1),
                  epoch_length=1000, model_train_freq=250, model_retain_epochs=20, deterministic=False,
-                 rollout_random=False, model_type='mlp', get_action_meta=None, policy=None, seed=0):
+                 rollout_random=False, model_type='mlp', get_action_meta=None, policy=None, seed=0, identity_terminal=0):
         self.fake_env = fake_env
         self._pool = env_pool                       # env (offline data) pool; `sampler.random_batch` delegates to it
         self.sampler = env_pool                     # simple_sampler.py:103-108
@@ -33,6 +33,7 @@ class ModelRollout:
         self._deterministic = deterministic
         self._rollout_random = rollout_random
         self._model_type = model_type
+        self._identity_terminal = identity_terminal          # mopo.py:743
         self._epoch = 0
         self._rollout_length = 1
         self._n_train_repeat = 1
@@ -110,8 +111,8 @@ class ModelRollout:
             batch = self.sampler.random_batch(rollout_batch_size)           # mopo.py:727
             start_obs = batch['observations']                               # mopo.py:728
         if self._model_type == 'identity':
-            raise NotImplementedError("identity model bypass (mopo.py:740-744) has no device work")
-        if actions is not None or self._device_policy is not None:
+            steps_added = self._rollout_identity(start_obs, actions)
+        elif actions is not None or self._device_policy is not None:
             steps_added = self._rollout_fused(start_obs, actions, noise, model_inds, deterministic, precision, origin_base)
         else:
             steps_added = self._rollout_callback(start_obs, deterministic, precision)
@@ -206,6 +207,30 @@ class ModelRollout:
         while out and out[-1] == 0:          # the reference breaks out of the loop when nothing survives (mopo.py:754-756)
             out.pop()
         return out
+
+    def _rollout_identity(self, obs, actions):
+        """model_type == 'identity' (mopo.py:740-744): the model is bypassed -- next_obs = obs, zero rewards, terminals =
+        identity_terminal -- but the loop, the pool appends and the early break are the reference's."""
+        steps_added = []
+        obs = np.asarray(obs.cpu() if torch.is_tensor(obs) else obs)
+        for i in range(self._rollout_length):
+            if actions is not None:
+                act = np.asarray(actions[i].cpu() if torch.is_tensor(actions[i]) else actions[i])[:len(obs)]
+            else:
+                act, _ = self.get_action_meta(obs, self.make_init_hidden(1))
+            if self._rollout_random:
+                act = np.random.uniform(low=-1, high=1, size=np.shape(act))
+            next_obs = obs
+            rew = np.zeros((len(obs), 1))
+            term = (np.ones((len(obs), 1)) * self._identity_terminal).astype(bool)
+            steps_added.append(len(obs))
+            self._model_pool.add_samples({'observations': obs, 'actions': act, 'next_observations': next_obs,
+                                          'rewards': rew, 'terminals': term})
+            nonterm_mask = ~term.squeeze(-1)
+            if nonterm_mask.sum() == 0:
+                break
+            obs = next_obs[nonterm_mask]
+        return steps_added
 
     def _rollout_callback(self, obs, deterministic, precision):
         """Literal per-step loop with a host policy callback (mopo.py:730-758)."""

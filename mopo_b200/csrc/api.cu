@@ -22,7 +22,11 @@ void mopo_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 MOPO_API int64_t mopo_launch_count(void) { return g_launches.load(); }
 
 MOPO_API const char* mopo_last_error(void) { return g_err; }
-MOPO_API int mopo_version(void) { return 100; }
+MOPO_API int mopo_version(void) { return 200; }
+#ifndef MOPO_BUILD_HASH
+#define MOPO_BUILD_HASH "unhashed"
+#endif
+MOPO_API const char* mopo_build_hash(void) { return MOPO_BUILD_HASH; }
 
 // ------------------------------------------------------------------------------------------
 // ensemble
@@ -138,6 +142,37 @@ MOPO_API int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const
   return MOPO_OK;
 }
 
+// Device addresses of the fp32 master images (reference layout), for in-place collectives (NCCL broadcast of the ensemble after
+// model training: mopo_b200/dist.py) -- followed by mopo_ens_refresh_images, which rebuilds the tensor-core images from them.
+MOPO_API int mopo_ens_param_image(mopo_ens* h, int32_t which, int32_t layer, void** ptr, int64_t* count) {
+  REQUIRE(h && ptr && count, MOPO_EINVAL, "mopo_ens_param_image: null argument");
+  const int E = h->E;
+  switch (which) {
+    case MOPO_IMG_W:
+      REQUIRE(layer >= 0 && layer <= h->L, MOPO_EINVAL, "mopo_ens_param_image: layer %d", layer);
+      *ptr = h->W[layer]; *count = (int64_t)E * (layer == 0 ? h->in : h->H) * (layer == h->L ? h->HO : h->H); return MOPO_OK;
+    case MOPO_IMG_B:
+      REQUIRE(layer >= 0 && layer <= h->L, MOPO_EINVAL, "mopo_ens_param_image: layer %d", layer);
+      *ptr = h->b[layer]; *count = (int64_t)E * (layer == h->L ? h->HO : h->H); return MOPO_OK;
+    case MOPO_IMG_MU: *ptr = h->mu; *count = h->in; return MOPO_OK;
+    case MOPO_IMG_SIGMA: *ptr = h->sigma; *count = h->in; return MOPO_OK;
+    case MOPO_IMG_MAX_LOGVAR: *ptr = h->max_lv; *count = h->D1; return MOPO_OK;
+    case MOPO_IMG_MIN_LOGVAR: *ptr = h->min_lv; *count = h->D1; return MOPO_OK;
+  }
+  mopo_set_error("mopo_ens_param_image: which=%d", which);
+  return MOPO_EINVAL;
+}
+
+MOPO_API int mopo_ens_refresh_images(mopo_ens* h, void* stream) {
+  REQUIRE(h, MOPO_EINVAL, "mopo_ens_refresh_images: null handle");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  if (tc_supported(h)) TRY(tc_build_images(h, st));
+  if (tc3_supported(h)) TRY(tc3_build_images(h, st));
+  h->params_set = true;
+  return MOPO_OK;
+}
+
 MOPO_API int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n) {
   REQUIRE(h && elites, MOPO_EINVAL, "mopo_ens_set_elites: null argument");
   REQUIRE(n >= 1 && n <= h->E, MOPO_EINVAL, "mopo_ens_set_elites: n=%d outside [1,%d]", n, h->E);
@@ -213,6 +248,7 @@ MOPO_API int mopo_kernel_time(mopo_ens* h, double* ms_total, int64_t* launches) 
   return MOPO_OK;
 }
 
+#ifdef MOPO_DEBUG_PROBES
 __global__ void fill_mod_kernel(int32_t* p, int64_t n, int m) {   // m > 0: i % m ; m <= 0: the constant -m
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = m > 0 ? (int32_t)(i % m) : -m;
 }
@@ -241,6 +277,31 @@ MOPO_API int mopo_debug_tc_trace(mopo_ens* h, const float* xn, int64_t B, float*
   h->tc_trace = nullptr;
   return rc;
 }
+
+// the same for the streamed-weights kernel (ens_tc3.cu): precision MOPO_PREC_FP32 (three-term) or MOPO_PREC_BF16 on a shape
+// the resident kernel rejects; roles 0 MMA issuer, 1/2 epilogue warps 0 / 4, 3 weight streamer, 4 head warp 12
+MOPO_API int mopo_debug_tc3_trace(mopo_ens* h, const float* xn, int64_t B, float* mean, float* logvar, int terms,
+                                  unsigned long long* trace, void* stream) {
+  REQUIRE(h && xn && trace && B > 0 && (terms == 1 || terms == 3), MOPO_EINVAL, "mopo_debug_tc3_trace: bad argument");
+  REQUIRE(h->params_set && tc3_supported(h), MOPO_ESTATE, "mopo_debug_tc3_trace: streamed tensor-core path unavailable");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemsetAsync(trace, 0, sizeof(unsigned long long) * 5 * 2048, st));
+  h->tc_trace = trace;
+  Tc3In x = {xn, nullptr, h->in, 0, false};
+  TcOut o = {};
+  int rc = MOPO_OK;
+  if (mean && logvar) { o.mean = mean; o.lv = logvar; o.ldb = B; }
+  else {
+    rc = h->sel.reserve(sizeof(int32_t) * B);
+    if (!rc) rc = h->selmv.reserve(sizeof(float2) * B * h->D1);
+    if (!rc) rc = h->pen2.reserve(sizeof(float) * 2 * h->E * B);
+    if (!rc) { fill_mod_kernel<<<148, 256, 0, st>>>(h->sel.as<int32_t>(), B, 5); o.sel = h->sel.as<int32_t>(); o.selmv = h->selmv.as<float2>(); o.pen2 = h->pen2.as<float>(); o.ldb = B; }
+  }
+  if (!rc) rc = tc3_launch(h, terms, x, B, nullptr, o, st);
+  h->tc_trace = nullptr;
+  return rc;
+}
+#endif  // MOPO_DEBUG_PROBES
 
 MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, int precision, void* stream) {
   REQUIRE(h && (B == 0 || (x && mean && var)), MOPO_EINVAL, "mopo_ens_predict: null argument");
@@ -414,8 +475,9 @@ __global__ void gather_rows_kernel(const T* __restrict__ src, const int64_t* __r
 }
 __global__ void philox_index_kernel(int64_t* idx, int64_t n, uint64_t seed, uint64_t offset, int64_t size) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    uint64_t c = offset + (uint64_t)i;
-    Philox4 r = philox4x32_10((uint32_t)c, (uint32_t)(c >> 32), 0u, MOPO_STREAM_POOL, (uint32_t)seed, (uint32_t)(seed >> 32));
+    // counter = (row of this draw, draw id): two draws with different `offset` share no counter, so their index sets are
+    // independent (np.random.randint per batch, flexible_replay_pool.py:85-87)
+    Philox4 r = philox_pool_draw((uint32_t)i, offset, seed);
     uint64_t u = ((uint64_t)r.x << 32) | r.y;
     idx[i] = (int64_t)__umul64hi(u, (uint64_t)size);     // floor(u * size / 2^64): np.random.randint(0, size)
   }
@@ -438,6 +500,16 @@ MOPO_API int mopo_pool_add(mopo_pool* p, const float* obs, const float* act, con
   MOPO_COUNT_LAUNCH, ring_scatter_kernel<<<grid_for((n - skip) * p->obs_dim), 256, 0, st>>>(next_obs, p->next_obs, n, skip, p->obs_dim, p->pointer, p->max_size);
   CUDA_TRY(cudaGetLastError());
   p->pointer = (p->pointer + n) % p->max_size;                 // flexible_replay_pool.py:45-48
+  p->size = p->size + n < p->max_size ? p->size + n : p->max_size;
+  return MOPO_OK;
+}
+
+// Rows [pointer, pointer + n) were written in place (e.g. by an NCCL all-gather straight into the field arrays): advance
+// the ring exactly as add_samples would (flexible_replay_pool.py:45-48).  The caller keeps pointer + n <= max_size.
+MOPO_API int mopo_pool_advance(mopo_pool* p, int64_t n) {
+  REQUIRE(p && n >= 0 && p->pointer + n <= p->max_size, MOPO_EINVAL, "mopo_pool_advance: n=%lld from pointer %lld exceeds max_size %lld",
+          (long long)n, p ? (long long)p->pointer : 0ll, p ? (long long)p->max_size : 0ll);
+  p->pointer = (p->pointer + n) % p->max_size;
   p->size = p->size + n < p->max_size ? p->size + n : p->max_size;
   return MOPO_OK;
 }

@@ -550,7 +550,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc_
       const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
       const int rr = q * 32 + lane;
       const HeadShape hs = {s.D1, s.NHEAD};
-      const HeadOut ho = {a.mean, a.lv, a.ldb, a.sel, a.selmv, a.pen2, a.E};
+      const HeadOut ho = {1.0f, a.mean, a.lv, a.ldb, a.sel, a.selmv, a.pen2, a.E};
       for (int k = 0; k < n_super; ++k) {
         for (int t = 0; t < 2; ++t) {
           if (2 * k + t >= cnt) continue;
@@ -682,10 +682,13 @@ int tc_launch(mopo_ens* h, int64_t n_max, const int* d_n, const TcOut& o, cudaSt
     ev0 = h->ev[h->ev_used]; ev1 = h->ev[h->ev_used + 1]; h->ev_used += 2;
     CUDA_TRY(cudaEventRecord(ev0, st));
   }
-  if (a.trace) {
+#ifdef MOPO_DEBUG_PROBES
+  if (a.trace) {                                        // timeline variant: only in the probe build (mopo_debug_tc_trace)
     CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     MOPO_COUNT_LAUNCH, ens_tc_kernel<true><<<2 * n_pairs, NTHREADS, smem, st>>>(a);
-  } else {
+  } else
+#endif
+  {
     CUDA_TRY(cudaFuncSetAttribute(ens_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     if (o.pdl) {
       // programmatic dependent launch behind the previous step's tail (static-row rollouts): see pdl_wait() in the kernel

@@ -1,11 +1,13 @@
 // tcgen05 ensemble forward at fp32 accuracy (MOPO_PREC_FP32): BNN._compile_outputs (reference mopo/models/bnn.py:631-675,
-// fc.py:96-106) for all nets on the 5th-gen tensor cores, with every operand carried as a bf16 (hi, lo) pair.
+// fc.py:96-106) for all nets on the 5th-gen tensor cores, with every operand carried as an fp16 (hi, lo) pair.
 //
-// Arithmetic.  The reference contracts in fp32.  kind::f16 MMAs take 8-bit mantissas, so each fp32 operand x is split
-// x = hi + lo, hi = bf16(x), lo = bf16(x - hi) (16 significant bits) and a layer is THREE MMAs per K step into the same
-// fp32 accumulator in tensor memory:  Ah*Wh + Ah*Wl + Al*Wh  (the dropped Al*Wl term is 2^-16 relative).  Per-term error
-// ~1e-5 relative, ~1e-6 absolute on the outputs: inside the rtol-1e-3 parity bar that the FFMA checker path (ens_fp32.cu)
-// used to be the only one to meet.  swish is x * rcp(1 + ex2(-x log2 e)) (two MUFU ops, ~3 ulp), not tanh.approx (2^-11).
+// Arithmetic.  The reference contracts in fp32.  kind::f16 MMAs take 11-bit significands (fp16), so each fp32 operand
+// x is split x = hi + lo, hi = f16(x), lo = f16(x - hi) (22 significant bits) and a layer is THREE MMAs per K step into
+// the same fp32 accumulator in tensor memory:  Ah*Wh + Ah*Wl + Al*Wh  (the dropped Al*Wl term is 2^-22 relative).
+// Weights and biases are stored x 64 (a power of two: exact) so that the lo parts of small weights stay normal fp16
+// numbers; the epilogue multiplies the accumulator by 1/64.  Activations saturate at +-65504 (cvt.satfinite) instead
+// of overflowing.  Measured against the float64 oracle the outputs agree to ~1e-6 absolute, as the FFMA checker path
+// (ens_fp32.cu) does.  swish is x * rcp(1 + ex2(-x log2 e)) (two MUFU ops, ~3 ulp), not tanh.approx (2^-11).
 // TERMS = 1 runs the same kernel as a plain bf16 forward (one MMA per K step, tanh-form swish) for shapes the
 // net-stationary bf16 kernel (ens_tc.cu) cannot hold resident (ant / humanoid: mopo/static/ant.py, humanoid.py).
 //
@@ -56,6 +58,7 @@ constexpr int XP = 128 * 16;            // 2048 B: one K-panel of a 128-row inpu
 constexpr int NTHREADS = 448;
 constexpr int C_BUF0 = 0, C_BUF1 = 208, C_HEAD = 416;
 constexpr int MAX_IN = 64;
+constexpr float W_SCALE = 64.0f;         // TERMS == 3: weight / bias images are stored x 64 (see the header comment)
 
 struct S3 {
   int in, D1, HO, K0, NHEAD;            // K0 = roundup(in + 1, 16), NHEAD = roundup(2*D1, 16)
@@ -86,7 +89,8 @@ struct ImgSrc3 {
   const float* b[5];
 };
 
-__global__ void build_image3_kernel(ImgSrc3 src, __nv_bfloat16* __restrict__ img, S3 s, int E) {
+// one image per mode: [0] fp16 (hi, lo) x 64 for TERMS == 3, [1] bf16 (hi, unused lo = 0) for TERMS == 1
+__global__ void build_image3_kernel(ImgSrc3 src, uint16_t* __restrict__ img3, uint16_t* __restrict__ img1, S3 s, int E) {
   const int per = s.img_bytes() / 2;
   const int64_t total = (int64_t)E * 2 * per;
   const int w0e = s.w0_part() / 2, hle = WPART / 2, hde = s.head_part() / 2;
@@ -120,8 +124,10 @@ __global__ void build_image3_kernel(ImgSrc3 src, __nv_bfloat16* __restrict__ img
       if (k < Kin) v = src.W[layer][((int64_t)e * Kin + k) * Nout + n];
       else if (k == Kin) v = src.b[layer][(int64_t)e * Nout + n];
     }
-    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
-    img[i] = part == 0 ? hi : __float2bfloat16_rn(v - __bfloat162float(hi));
+    const float vs = v * W_SCALE;
+    const __half hi = __float2half_rn(vs);
+    img3[i] = __half_as_ushort(part == 0 ? hi : __float2half_rn(vs - __half2float(hi)));
+    img1[i] = part == 0 ? __bfloat16_as_ushort(__float2bfloat16_rn(v)) : (uint16_t)0;
   }
 }
 
@@ -151,6 +157,7 @@ struct T3Args {
   const int* d_n;
   int E;
   S3 s;
+  unsigned long long* trace;   // debug timeline (mopo_debug_tc3_trace, probe build only) or nullptr
 };
 
 struct Bars3 {
@@ -176,6 +183,19 @@ template <int TERMS> __device__ __forceinline__ float swish_acc(float x) {
   else return x * rcp_approx(1.0f + ex2_approx(-1.44269504f * x));
 }
 
+// operand formats: TERMS == 3 -> fp16 pairs, TERMS == 1 -> bf16
+template <int TERMS> __device__ __forceinline__ uint32_t pack2(float a, float b) {
+  if constexpr (TERMS == 3) return pack_f16x2(a, b); else return pack_bf16x2(a, b);
+}
+template <int TERMS> __device__ __forceinline__ uint32_t idesc_of(uint32_t M, uint32_t N) {
+  return TERMS == 3 ? idesc_f16(M, N) : idesc_bf16(M, N);
+}
+// (hi, lo) split of two values: hi = f16x2(a, b), lo = f16x2(a - hi.a, b - hi.b)
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  hi = pack_f16x2(a, b);
+  lo = pack_f16x2(a - f16lo_to_f32(hi), b - f16hi_to_f32(hi));
+}
+
 // N accumulator columns (N = 32 or 16: two or one feature group of this thread's row) at taddr -> swish -> split ->
 // the SAME columns as [hi x 8 | lo x 8] per group.  ONES: the chunk's last group is group 12, whose feature 200 is the
 // constant 1 of the bias row.
@@ -186,17 +206,12 @@ __device__ __forceinline__ void swish_split_store(uint32_t taddr, const uint32_t
   for (int g = 0; g < N / 16; ++g) {
     float sv[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) sv[i] = swish_acc<TERMS>(__uint_as_float(v[16 * g + i]));
+    for (int i = 0; i < 16; ++i) sv[i] = swish_acc<TERMS>((TERMS == 3 ? 1.0f / W_SCALE : 1.0f) * __uint_as_float(v[16 * g + i]));
     if (ONES && g == N / 16 - 1) sv[8] = 1.0f;
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
-      const uint32_t hi = pack_bf16x2(sv[2 * p], sv[2 * p + 1]);
-      o[16 * g + p] = hi;
-      if constexpr (TERMS == 3) {
-        const float r0 = sv[2 * p] - __uint_as_float(hi << 16);
-        const float r1 = sv[2 * p + 1] - __uint_as_float(hi & 0xFFFF0000u);
-        o[16 * g + 8 + p] = pack_bf16x2(r0, r1);
-      } else o[16 * g + 8 + p] = 0u;
+      if constexpr (TERMS == 3) split2(sv[2 * p], sv[2 * p + 1], o[16 * g + p], o[16 * g + 8 + p]);
+      else { o[16 * g + p] = pack_bf16x2(sv[2 * p], sv[2 * p + 1]); o[16 * g + 8 + p] = 0u; }
     }
   }
   if constexpr (N == 32) tmem_st32(taddr, reinterpret_cast<const uint32_t (&)[32]>(o));
@@ -233,8 +248,18 @@ __device__ __forceinline__ void issue_ts(uint32_t d, uint32_t a_buf, uint32_t b_
   }
 }
 
-template <int TERMS>
+constexpr int TRACE_CAP = 2048;   // events per role
+// timeline probe: role r (0 issuer, 1 epilogue warp 0, 2 epilogue warp 4, 3 weight streamer, 4 head warp 12) of pair 0 / leader CTA
+#define TR(role, tag)                                                                                   \
+  do {                                                                                                  \
+    if (TRACE && a.trace && pair == 0 && rank == 0 && lane == 0 && tr_n < TRACE_CAP)                    \
+      a.trace[(role) * TRACE_CAP + tr_n++] = ((unsigned long long)(tag) << 48) | ((unsigned long long)clock64() & 0xFFFFFFFFFFFFull); \
+  } while (0)
+
+template <int TERMS, bool TRACE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3_kernel(T3Args a) {
+  int tr_n = 0;
+  (void)tr_n;
   extern __shared__ __align__(128) uint8_t smem[];
   const S3 s = a.s;
   uint8_t* sW = smem;                                   // two ring stages
@@ -295,12 +320,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         for (int j = 0; j < 5; ++j, ++li) {
           const uint32_t st = li & 1;
           if (li >= 2) mbar_wait(&bars->w_free[st], ((li >> 1) - 1) & 1, 1000 + j);
+          TR(3, 70 + j);
           const uint32_t bytes = (uint32_t)s.blob_bytes(j);
           mbar_expect_tx(&bars->w_full[st], bytes);
           bulk_g2s(sW + st * STAGE, src, bytes / 2, &bars->w_full[st]);
           bulk_g2s(sW + st * STAGE + bytes / 2, src + bytes / 2, bytes / 2, &bars->w_full[st]);
           src += bytes;
           mbar_wait(&bars->w_full[st], (li >> 1) & 1, 1100 + j);
+          TR(3, 80 + j);
           mbar_arrive_remote(&bars->w_ready[st], 0);
         }
       }
@@ -309,7 +336,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
   } else if (warp == 8) {
     // ===== MMA issuer (leader CTA): all lanes run the loop, one elected lane issues =====
     if (rank == 0) {
-      const uint32_t id1 = idesc_bf16(256, NH1), id2 = idesc_bf16(256, NH2), idh = idesc_bf16(256, s.NHEAD);
+      if (TRACE && a.trace && pair == 0 && lane == 0) {          // wall clock beside the cycle counter: the SM clock under this load
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        a.trace[5 * TRACE_CAP - 4] = (unsigned long long)clock64();
+        a.trace[5 * TRACE_CAP - 3] = ns;
+      }
+      const uint32_t id1 = idesc_of<TERMS>(256, NH1), id2 = idesc_of<TERMS>(256, NH2), idh = idesc_of<TERMS>(256, s.NHEAD);
       const uint32_t wa = smem_u32(sW), xa = smem_u32(sX);
       const uint32_t hpanel = (uint32_t)(s.NHEAD / 2) * 16;
       uint32_t li = 0, n_x = 0, n_a0 = 0, n_a1 = 0, n_h = 0;
@@ -318,9 +351,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
           const uint32_t st = li & 1;
           const uint32_t wb = wa + st * STAGE;
           mbar_wait_cluster(&bars->w_ready[st], (li >> 1) & 1, 10 * j);
+          TR(0, 10 * j);
           if (j == 0) {
             mbar_wait_cluster(&bars->x_full, n_x & 1, 1); ++n_x;
             tc_fence_after();
+            TR(0, 1);
             if (elect_one()) {
               const uint32_t wlo = (uint32_t)s.w0_part(), xlo = (uint32_t)s.x_part();
               for (int hf = 0; hf < 2; ++hf) {
@@ -346,10 +381,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
             const uint32_t dbuf = tbase + ((j & 1) ? C_BUF1 : C_BUF0);
             mbar_wait_cluster(&bars->a_ready[0], n_a0 & 1, 10 * j + 2); ++n_a0;
             tc_fence_after();
+            TR(0, 10 * j + 1);
             if (elect_one()) issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, 0, G1);
             __syncwarp();
             mbar_wait_cluster(&bars->a_ready[1], n_a1 & 1, 10 * j + 3); ++n_a1;
             tc_fence_after();
+            TR(0, 10 * j + 2);
             if (elect_one()) {
               issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, G1, NGRP);
               mma_commit<2>(&bars->d_full[0]);
@@ -358,6 +395,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
               mma_commit<2>(&bars->w_free[st]);
             }
             __syncwarp();
+            TR(0, 10 * j + 3);
           } else {
             mbar_wait_cluster(&bars->a_ready[0], n_a0 & 1, 42); ++n_a0;
             mbar_wait_cluster(&bars->a_ready[1], n_a1 & 1, 43); ++n_a1;
@@ -365,6 +403,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
             if (n_h > 0) mbar_wait_cluster(&bars->h_done, (n_h - 1) & 1, 44);
             ++n_h;
             tc_fence_after();
+            TR(0, 42);
             if (elect_one()) {
               issue_ts<TERMS>(tbase + C_HEAD, tbase + C_BUF1, wb, (uint32_t)s.head_part(), hpanel, idh, 0, NGRP);
               mma_commit<2>(&bars->h_full);
@@ -373,6 +412,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
             __syncwarp();
           }
         }
+      }
+      if (TRACE && a.trace && pair == 0 && lane == 0) {
+        unsigned long long ns;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        a.trace[5 * TRACE_CAP - 2] = (unsigned long long)clock64();
+        a.trace[5 * TRACE_CAP - 1] = ns;
       }
     }
   } else if (warp < 8) {
@@ -383,20 +428,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     for (int u = u0; u < u1; ++u) {
       for (int j = 0; j < 4; ++j, ++n_d) {
         const uint32_t buf = tlane + ((j & 1) ? C_BUF1 : C_BUF0);
+        if (q == 0) TR(1 + wg, 100 + 10 * j);
         mbar_wait(&bars->d_full[0], n_d & 1, 100 + j);
         tc_fence_after();
+        if (q == 0) TR(1 + wg, 200 + 10 * j);
         if (wg == 0) epi_part<TERMS, 64, false>(buf);              // groups 0..3
         else epi_part<TERMS, 48, false>(buf + 64);                 // groups 4..6
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_remote(&bars->a_ready[0], 0);
+        if (q == 0) TR(1 + wg, 300 + 10 * j);
         mbar_wait(&bars->d_full[1], n_d & 1, 110 + j);
         tc_fence_after();
+        if (q == 0) TR(1 + wg, 200 + 10 * j + 1);
         if (wg == 0) epi_part<TERMS, 48, false>(buf + 112);        // groups 7..9
         else epi_part<TERMS, 48, true>(buf + 160);                 // groups 10..12 (feature 200 = 1)
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_remote(&bars->a_ready[1], 0);
+        if (q == 0) TR(1 + wg, 300 + 10 * j + 1);
       }
     }
   } else {
@@ -431,8 +481,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         uint32_t hi[4], lo[4];
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-          hi[p] = pack_bf16x2(v[2 * p], v[2 * p + 1]);
-          lo[p] = TERMS == 3 ? pack_bf16x2(v[2 * p] - __uint_as_float(hi[p] << 16), v[2 * p + 1] - __uint_as_float(hi[p] & 0xFFFF0000u)) : 0u;
+          if constexpr (TERMS == 3) split2(v[2 * p], v[2 * p + 1], hi[p], lo[p]);
+          else { hi[p] = pack_bf16x2(v[2 * p], v[2 * p + 1]); lo[p] = 0u; }
         }
         st_shared_v4(sX + kc * XP + rr * 16, hi[0], hi[1], hi[2], hi[3]);
         st_shared_v4(sX + s.x_part() + kc * XP + rr * 16, lo[0], lo[1], lo[2], lo[3]);
@@ -447,7 +497,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
       const int e = u / nT, t = u - e * nT;
       if (u + 1 < u1) {
         mbar_wait(&bars->x_free, n_h & 1, 200);          // layer 0 of unit u has consumed the block
+        if (q == 0) TR(4, 150);
         produce_x(u + 1);
+        if (q == 0) TR(4, 250);
       }
       const int64_t row = 256 * (int64_t)t + (int64_t)rank * 128 + rr;
       const bool valid = row < n;
@@ -455,6 +507,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
       if (a.out.sel && valid) mine = a.out.sel[row] == e;
       mbar_wait(&bars->h_full, n_h & 1, 210);
       tc_fence_after();
+      if (q == 0) TR(4, 240);
       const uint32_t tblk = tlane + C_HEAD;
       bool arrived = false;
       if (a.out.sel) {
@@ -469,6 +522,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         __syncwarp();
         if (lane == 0) mbar_arrive_remote(&bars->h_done, 0);
       }
+      if (q == 0) TR(4, 340);
     }
   }
   __syncwarp();
@@ -493,7 +547,8 @@ int tc3_supported(const mopo_ens* h) {
 
 int tc3_build_images(mopo_ens* h, cudaStream_t st) {
   const S3 s = make_s3(h->in, h->D1);
-  const size_t bytes = (size_t)h->E * 2 * s.img_bytes();
+  const size_t one = (size_t)h->E * 2 * s.img_bytes();
+  const size_t bytes = 2 * one;                         // [fp16 (hi, lo) image | bf16 image]
   if (h->tc3_img_bytes < bytes) {
     if (h->tc3_img) cudaFree(h->tc3_img);
     h->tc3_img = nullptr;
@@ -502,7 +557,8 @@ int tc3_build_images(mopo_ens* h, cudaStream_t st) {
   }
   ImgSrc3 src;
   for (int l = 0; l < 5; ++l) { src.W[l] = h->W[l]; src.b[l] = h->b[l]; }
-  MOPO_COUNT_LAUNCH, build_image3_kernel<<<592, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(h->tc3_img), s, h->E);
+  MOPO_COUNT_LAUNCH, build_image3_kernel<<<592, 256, 0, st>>>(src, reinterpret_cast<uint16_t*>(h->tc3_img),
+                                                              reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(h->tc3_img) + one), s, h->E);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -522,13 +578,15 @@ int tc3_launch(mopo_ens* h, int terms, const Tc3In& x, int64_t n_max, const int*
   if (!h->tc3_img) { mopo_set_error("tc3_launch: weight images not built"); return MOPO_ESTATE; }
   T3Args a;
   a.s = make_s3(h->in, h->D1);
-  a.img = reinterpret_cast<const uint8_t*>(h->tc3_img);
+  a.img = reinterpret_cast<const uint8_t*>(h->tc3_img) + (terms == 3 ? 0 : (size_t)h->E * 2 * a.s.img_bytes());
   a.obs = x.obs; a.act = x.act ? x.act : x.obs; a.od = x.od; a.ad = x.ad;
   a.mu = x.scale ? h->mu : nullptr; a.sigma = x.scale ? h->sigma : nullptr;
   a.max_lv = h->max_lv; a.min_lv = h->min_lv;
+  a.out.acc_scale = terms == 3 ? 1.0f / W_SCALE : 1.0f;
   a.out.mean = o.mean; a.out.lv = o.lv; a.out.ldb = o.ldb;
   a.out.sel = o.sel; a.out.selmv = o.selmv; a.out.pen2 = o.pen2; a.out.E = h->E;
   a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E;
+  a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
   const size_t smem = tc3_smem_bytes(a.s);
   const int n_pairs = h->sm_count / 2;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -539,7 +597,10 @@ int tc3_launch(mopo_ens* h, int terms, const Tc3In& x, int64_t n_max, const int*
     ev0 = h->ev[h->ev_used]; ev1 = h->ev[h->ev_used + 1]; h->ev_used += 2;
     CUDA_TRY(cudaEventRecord(ev0, st));
   }
-  auto kern = terms == 3 ? ens_tc3_kernel<3> : ens_tc3_kernel<1>;
+  auto kern = terms == 3 ? ens_tc3_kernel<3, false> : ens_tc3_kernel<1, false>;
+#ifdef MOPO_DEBUG_PROBES
+  if (a.trace) kern = terms == 3 ? ens_tc3_kernel<3, true> : ens_tc3_kernel<1, true>;
+#endif
   CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * n_pairs); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;

@@ -2,10 +2,14 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <string>
 #include <vector>
 #include "../../include/mopo_b200.h"
+#ifdef MOPO_DEBUG_PROBES
+#include "../../include/mopo_b200_debug.h"
+#endif
 
 #define MOPO_MAX_LAYERS 8
 #define MOPO_MAX_D1 64
@@ -19,6 +23,7 @@ void mopo_count_launch();
   do {                                                                                  \
     cudaError_t _e = (expr);                                                            \
     if (_e != cudaSuccess) {                                                            \
+      (void)cudaGetLastError(); /* clear the (non-sticky) error so that later calls do not report it again */ \
       mopo_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
       return MOPO_ECUDA;                                                                \
     }                                                                                   \

@@ -38,6 +38,13 @@ __host__ __device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t 
 // uniform in (0,1): 24 high bits + half an ulp
 __host__ __device__ __forceinline__ float mopo_u01(uint32_t x) { return ((float)(x >> 8) + 0.5f) * (1.0f / 16777216.0f); }
 
+// one replay-pool index draw (np.random.randint(0, size), flexible_replay_pool.py:85-87): counter = (row i of the draw,
+// the 64-bit id of the draw) -- draws with different ids (mopo_pool_sample's `offset`; the SAC update index and pool) are
+// disjoint counter planes, i.e. independent.  index = floor(u64 * size / 2^64) with u64 = (x << 32) | y.
+__host__ __device__ __forceinline__ Philox4 philox_pool_draw(uint32_t i, uint64_t draw, uint64_t seed) {
+  return philox4x32_10(i, (uint32_t)draw, (uint32_t)(draw >> 32), MOPO_STREAM_POOL, (uint32_t)seed, (uint32_t)(seed >> 32));
+}
+
 #ifdef __CUDACC__
 // 4 standard normals from one Philox block (two Box-Muller pairs).
 __device__ __forceinline__ void philox_normal4(uint32_t row, uint32_t step, uint32_t blk, uint64_t seed, float out[4],

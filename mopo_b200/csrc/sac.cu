@@ -130,7 +130,8 @@ __global__ void sac_pi_head_grad_kernel(const float* __restrict__ HD, const floa
 }
 
 // _training_batch (mopo.py:801-821) in one launch: rows [0, n_env) from the env pool, [n_env, n) from the model pool, indices as
-// mopo_pool_sample draws them (Philox stream 2, counter = offset + row, offset = 2 (update index) + pool) -- all five fields.
+// mopo_pool_sample draws them (Philox stream 2, counter = (row, offset), offset = 2 (update index) + pool: every update and
+// each pool has its own counter plane, so consecutive minibatches are independent draws, mopo.py:801-821) -- all five fields.
 struct SacSample {
   const float *obs[2], *act[2], *nobs[2], *rew[2]; const uint8_t* term[2];
   int64_t size[2]; int n_env, n, od, ad;
@@ -143,8 +144,7 @@ __global__ void __launch_bounds__(256) sac_sample_kernel(SacSample a, uint64_t s
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n * W; i += gridDim.x * blockDim.x) {
     const int j = i / W, c = i % W;
     const int w = j >= a.n_env;
-    const uint64_t ctr = base + (uint64_t)w + (uint64_t)(w ? j - a.n_env : j);
-    Philox4 r = philox4x32_10((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, MOPO_STREAM_POOL, (uint32_t)seed, (uint32_t)(seed >> 32));
+    Philox4 r = philox_pool_draw((uint32_t)(w ? j - a.n_env : j), base + (uint64_t)w, seed);
     const int64_t idx = (int64_t)__umul64hi(((uint64_t)r.x << 32) | r.y, (uint64_t)a.size[w]);
     if (c < a.od) bo[(int64_t)j * a.od + c] = a.obs[w][idx * a.od + c];
     else if (c < 2 * a.od) bno[(int64_t)j * a.od + (c - a.od)] = a.nobs[w][idx * a.od + (c - a.od)];

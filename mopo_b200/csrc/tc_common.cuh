@@ -244,4 +244,25 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return r;
 }
 
+// kind::f16 instruction descriptor with fp16 operands (formats 0): D = f32, A = B = f16, both K-major.
+__host__ __device__ constexpr uint32_t idesc_f16(uint32_t M, uint32_t N) {
+  return (1u << 4) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+// pack two fp32 into f16x2 (lo = a, hi = b), round to nearest even, saturating to +-65504 instead of inf
+__device__ __forceinline__ uint32_t pack_f16x2(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+__device__ __forceinline__ float f16lo_to_f32(uint32_t p) {
+  float f;
+  asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %1;\n\tcvt.f32.f16 %0, l;\n\t}" : "=f"(f) : "r"(p));
+  return f;
+}
+__device__ __forceinline__ float f16hi_to_f32(uint32_t p) {
+  float f;
+  asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %1;\n\tcvt.f32.f16 %0, h;\n\t}" : "=f"(f) : "r"(p));
+  return f;
+}
+
 }  // namespace tc

@@ -9,6 +9,7 @@ namespace tc {
 
 struct HeadShape { int D1, NHEAD; };     // NHEAD = roundup(2*D1, 16): accumulator columns of the fused [mean | raw logvar] head
 struct HeadOut {
+  float acc_scale;         // accumulator -> output units (the fp32-accurate kernel stores its weights x 64; else 1)
   // FULL output (sel == nullptr): everything BNN.predict returns
   float* mean;             // [E, ldb, D1]
   float* lv;               // [E, ldb, D1]
@@ -53,22 +54,22 @@ __device__ __forceinline__ void epi_head(uint32_t tblk, int wg, const HeadShape&
     float var[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      if constexpr (PRECISE) var[i] = cmin[4 * c + i] + 1.0f / (cnmax[4 * c + i] + expf(-__uint_as_float(rv[i])));
-      else var[i] = cmin[4 * c + i] + __fdividef(1.0f, cnmax[4 * c + i] + __expf(-__uint_as_float(rv[i])));
+      if constexpr (PRECISE) var[i] = cmin[4 * c + i] + 1.0f / (cnmax[4 * c + i] + expf(-a.acc_scale * __uint_as_float(rv[i])));
+      else var[i] = cmin[4 * c + i] + __fdividef(1.0f, cnmax[4 * c + i] + __expf(-a.acc_scale * __uint_as_float(rv[i])));
       pen += var[i];
     }
     if (FUSED) {
       if (mine) {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          if (4 * c + i < nd) a.selmv[(int64_t)(d0 + 4 * c + i) * a.ldb + row] = make_float2(__uint_as_float(mv[i]), var[i]);
+          if (4 * c + i < nd) a.selmv[(int64_t)(d0 + 4 * c + i) * a.ldb + row] = make_float2(PRECISE ? a.acc_scale * __uint_as_float(mv[i]) : __uint_as_float(mv[i]), var[i]);
       }
     } else if (valid) {
       float* mrow = a.mean + ((size_t)e * a.ldb + row) * s.D1 + d0;
       float* lrow = a.lv + ((size_t)e * a.ldb + row) * s.D1 + d0;
 #pragma unroll
       for (int i = 0; i < 4; ++i)
-        if (4 * c + i < nd) { mrow[4 * c + i] = __uint_as_float(mv[i]); lrow[4 * c + i] = PRECISE ? logf(var[i]) : __logf(var[i]); }
+        if (4 * c + i < nd) { mrow[4 * c + i] = PRECISE ? a.acc_scale * __uint_as_float(mv[i]) : __uint_as_float(mv[i]); lrow[4 * c + i] = PRECISE ? logf(var[i]) : __logf(var[i]); }
     }
   }
   if (FUSED && valid) a.pen2[((size_t)wg * a.E + e) * a.ldb + row] = pen;
@@ -121,7 +122,7 @@ __device__ __forceinline__ void head_fused(uint32_t tblk, const HeadShape& s, co
   for (int w = 0; w < 2; ++w)
 #pragma unroll
     for (int i = 0; i < P; ++i) {
-      if constexpr (PRECISE) var[w][i] = sC[w * P + i] + 1.0f / (sC[MOPO_MAX_D1 + w * P + i] + expf(-__uint_as_float(v[w * 2 * P + P + i])));
+      if constexpr (PRECISE) var[w][i] = sC[w * P + i] + 1.0f / (sC[MOPO_MAX_D1 + w * P + i] + expf(-a.acc_scale * __uint_as_float(v[w * 2 * P + P + i])));
       else var[w][i] = sC[w * P + i] + rcp_fma(sC[MOPO_MAX_D1 + w * P + i] + exp2_fma(-1.44269504f * __uint_as_float(v[w * 2 * P + P + i])));
       pen[w] += var[w][i];
     }
@@ -137,7 +138,7 @@ __device__ __forceinline__ void head_fused(uint32_t tblk, const HeadShape& s, co
       const int nd = w ? D1 - dh : dh;
 #pragma unroll
       for (int i = 0; i < P; ++i) {
-        if (i < nd) *dst = make_float2(__uint_as_float(v[w * 2 * P + i]), var[w][i]);
+        if (i < nd) *dst = make_float2(PRECISE ? a.acc_scale * __uint_as_float(v[w * 2 * P + i]) : __uint_as_float(v[w * 2 * P + i]), var[w][i]);
         dst += a.ldb;
       }
     }

@@ -37,9 +37,34 @@ def param_list(model):
     return model._all_vars()
 
 
-def broadcast_params(model, src=0, device=None):
-    """Broadcast every ensemble parameter (and the elite list) from `src`; one flat buffer, one collective."""
+def broadcast_params(model, src=0, device=None, sync_host=True):
+    """Broadcast every ensemble parameter (and the elite list) from `src`: one flat buffer, one collective.
+
+    NCCL + a device model (mopo_b200.models.bnn.BNN): the fp32 master images are packed device-to-device, broadcast, unpacked
+    in place on the receivers and the tensor-core operand images are rebuilt there -- nothing crosses PCIe on the collective's
+    path (sync_host=True then refreshes the host mirrors that save() reads; False leaves that to the caller).
+    Otherwise (gloo / host models, the CPU tests): the same flat buffer built from the host arrays."""
     if not dist.is_initialized() or dist.get_world_size() == 1:
+        return
+    if dist.get_backend() == 'nccl' and hasattr(model, '_device_images'):
+        views = model._device_images()
+        elites = torch.full((model.num_nets,), -1.0, dtype=torch.float32, device=views[0].device)
+        if hasattr(model, '_model_inds_list'):
+            elites[:len(model._model_inds_list)] = torch.tensor(model._model_inds_list, dtype=torch.float32)
+        if dist.get_rank() == src:
+            flat = torch.cat([v for v in views] + [elites])
+        else:
+            flat = torch.empty(sum(v.numel() for v in views) + model.num_nets, dtype=torch.float32, device=views[0].device)
+        dist.broadcast(flat, src=src)
+        if dist.get_rank() != src:
+            off = 0
+            for v in views:
+                v.copy_(flat[off:off + v.numel()])
+                off += v.numel()
+            model._after_device_update(sync_host=sync_host)
+            el = [int(e) for e in flat[off:].tolist() if e >= 0]
+            if el:
+                model._model_inds = el
         return
     arrs = param_list(model)
     flat = np.concatenate([np.asarray(a, np.float32).ravel() for a in arrs])
@@ -115,6 +140,34 @@ def allgather_rows(fields):
         cat = torch.cat(bufs, 0)
         out[k] = cat.bool() if is_bool else cat
     return out
+
+
+def allgather_new_rows(shard_pool, full_pool, n_new):
+    """The pool gather of BASELINE.json: every rank's newest `n_new` rows (the rows its rollout shard just appended; the same
+    count on every rank, as for never-terminating envs) land in EVERY rank's `full_pool`, rank-major, exactly where
+    `full_pool.add_samples(concat over ranks)` would have put them -- but written by the collective itself: one
+    all_gather_into_tensor per field straight into the field arrays at the ring offset (no staging concat, no host bounce),
+    then the ring is advanced.  Falls back to a gathered index + add_samples when either span wraps around its ring."""
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    ptr, cap = shard_pool._pointer, shard_pool._max_size
+    lo = (ptr - n_new) % cap
+    src_contig = lo + n_new <= cap
+    dptr, dcap = full_pool._pointer, full_pool._max_size
+    if world == 1:
+        rows = (torch.arange(lo, lo + n_new, device=shard_pool.fields['rewards'].device) % cap)
+        full_pool.add_samples({k: v[rows] for k, v in shard_pool.fields.items()})
+        return
+    if src_contig and dptr + world * n_new <= dcap and hasattr(full_pool, 'advance'):
+        for k, v in shard_pool.fields.items():
+            src = v[lo:lo + n_new]
+            dst = full_pool.fields[k][dptr:dptr + world * n_new]
+            if src.dtype == torch.bool:
+                src, dst = src.view(torch.uint8), dst.view(torch.uint8)
+            dist.all_gather_into_tensor(dst, src)
+        full_pool.advance(world * n_new)
+        return
+    rows = (torch.arange(lo, lo + n_new, device=shard_pool.fields['rewards'].device) % cap)
+    full_pool.add_samples(allgather_rows({k: v[rows] for k, v in shard_pool.fields.items()}))
 
 
 def max_over_ranks(value, device=None):

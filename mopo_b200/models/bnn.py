@@ -279,6 +279,39 @@ class BNN:
             self._epochs_since_update += 1
         return self._epochs_since_update > self._max_epochs_since_update
 
+    # ---- device master images (in-place collectives: mopo_b200/dist.py) -----------------------------
+    def _device_images(self):
+        """torch views of the fp32 master images in HBM, fixed order: mu, sigma, (W_l, b_l) for l = 0..L (the head image is
+        the fused [mean | logvar] head), max_logvar, min_logvar."""
+        from ..replay_pools import _RawDevArray
+        self._ensure_handle()
+        lib = _lib.load()
+        specs = [(_lib.IMG_MU, 0), (_lib.IMG_SIGMA, 0)]
+        for l in range(len(self.layers)):
+            specs += [(_lib.IMG_W, l), (_lib.IMG_B, l)]
+        specs += [(_lib.IMG_MAX_LOGVAR, 0), (_lib.IMG_MIN_LOGVAR, 0)]
+        views = []
+        with torch.cuda.device(self.device):
+            for which, layer in specs:
+                ptr, cnt = C.c_void_p(), C.c_int64()
+                _lib.check(lib.mopo_ens_param_image(self._handle, which, layer, C.byref(ptr), C.byref(cnt)))
+                views.append(torch.as_tensor(_RawDevArray(ptr.value, (cnt.value,), '<f4'), device=self.device))
+        return views
+
+    def param_bytes(self):
+        return 4 * sum(int(np.prod(np.shape(a))) for a in self._all_vars())
+
+    def _after_device_update(self, sync_host=True):
+        """The master images were overwritten on the device: rebuild the tensor-core operand images and (optionally) refresh
+        the host mirrors that save() / the scaler read."""
+        _lib.check(_lib.load().mopo_ens_refresh_images(self._handle, _lib.stream_ptr(self.device)))
+        if sync_host:
+            self._pull_params()
+            v = self._device_images()
+            self.scaler._on_change = None
+            self.scaler.load(v[0].cpu().numpy().reshape(1, -1), v[1].cpu().numpy().reshape(1, -1))
+            self.scaler._on_change = self._sync_device
+
     def _weight_decays(self):
         """Per-layer rates for the C trainer: hidden layers, mean head, log-variance head (fc.py:155-156)."""
         d = [l.weight_decay or 0.0 for l in self.layers]

@@ -72,6 +72,10 @@ class SimpleReplayPool:
         _lib.check(_lib.load().mopo_pool_add(self._handle, obs.data_ptr(), act.data_ptr(), nobs.data_ptr(),
                                              rew.data_ptr(), term.data_ptr(), n, _lib.stream_ptr(self.device)))
 
+    def advance(self, n):
+        """Rows [pointer, pointer + n) of `fields` were filled in place (dist.allgather_new_rows): move the ring forward."""
+        _lib.check(_lib.load().mopo_pool_advance(self._handle, int(n)))
+
     def add_sample(self, sample):
         self.add_samples({k: (v[None, ...]) for k, v in sample.items()})
 

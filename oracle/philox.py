@@ -64,3 +64,13 @@ def uniforms_pm1(rows, step_id, seed, d):
         for u in range(4):
             out[:, 4 * blk + u] = np.float32(2.0) * u01(r[u]).astype(np.float32) - np.float32(1.0)
     return out[:, :d]
+
+
+def pool_indices(n, size, seed, offset):
+    """mopo_pool_sample / the SAC sampler: n indices in [0, size) for draw id ``offset`` (philox_pool_draw): counter =
+    (row, offset lo, offset hi, STREAM_POOL), index = floor(((x << 32) | y) * size / 2^64).  Draws with different offsets
+    share no counter, as np.random.randint per batch (flexible_replay_pool.py:85-87) shares no state."""
+    r = philox4x32_10(np.arange(n, dtype=np.uint32), np.uint32(offset & 0xFFFFFFFF), np.uint32((offset >> 32) & 0xFFFFFFFF),
+                      STREAM_POOL, seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    u = [(int(x) << 32) | int(y) for x, y in zip(r[0], r[1])]
+    return np.asarray([(v * int(size)) >> 64 for v in u], np.int64)

@@ -33,8 +33,22 @@ def test_every_declared_symbol_is_exported(lib):
 
 def test_version_and_error_string(lib):
     h = lib.load()
-    assert h.mopo_version() >= 100
+    assert h.mopo_version() >= 200
     assert isinstance(h.mopo_last_error(), bytes)
+
+
+def test_loaded_library_was_built_from_this_tree(lib):
+    """The binary that travels to the GPU box is the one these sources produce: its embedded hash (sources + headers + flags)
+    equals the tree's; the product library exports no developer probe."""
+    from mopo_b200 import build as b
+    h = lib.load()
+    assert h.mopo_build_hash().decode() == b.tree_hash()
+    assert not b.needs_build()
+    for name in lib.DEBUG_SYMBOLS:
+        assert not hasattr(h, name), name
+    dbg = open(os.path.join(ROOT, 'include', 'mopo_b200_debug.h')).read()
+    for name in lib.DEBUG_SYMBOLS:
+        assert name in dbg
 
 
 def test_struct_layouts_match_header(lib):

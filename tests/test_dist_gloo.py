@@ -47,6 +47,28 @@ class _FakeModel:
     def _model_inds(self, v): self._model_inds_list = list(v)
 
 
+class _FakePool:
+    """CPU ring pool with the attributes dist.allgather_new_rows touches."""
+    def __init__(self, cap, w=3):
+        self._max_size, self._pointer, self.size = cap, 0, 0
+        self.fields = {'observations': torch.zeros(cap, w), 'rewards': torch.zeros(cap, 1), 'terminals': torch.zeros(cap, 1, dtype=torch.bool)}
+
+    def add_samples(self, s):
+        n = len(s['rewards'])
+        idx = (torch.arange(self._pointer, self._pointer + n) % self._max_size)
+        for k in self.fields:
+            self.fields[k][idx] = torch.as_tensor(s[k]).to(self.fields[k].dtype)
+        self.advance_wrapped(n)
+
+    def advance_wrapped(self, n):
+        self._pointer = (self._pointer + n) % self._max_size
+        self.size = min(self.size + n, self._max_size)
+
+    def advance(self, n):
+        assert self._pointer + n <= self._max_size
+        self.advance_wrapped(n)
+
+
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
@@ -67,6 +89,19 @@ def _worker(rank, world, port, q):
     ag = md.allgather_rows({'observations': torch.full((4, 3), float(rank)), 'terminals': torch.full((4, 1), rank == 1)})
     assert ag['observations'][:, 0].tolist() == [0.0] * 4 + [1.0] * 4
     assert ag['terminals'].dtype == torch.bool and ag['terminals'][:, 0].tolist() == [False] * 4 + [True] * 4
+    # pool gather straight into the destination ring (in-place collective), then the wrapped fallback
+    shard, full, want = _FakePool(10), _FakePool(17), _FakePool(17)
+    for it in range(3):
+        for r in range(world):
+            rows = {'observations': torch.full((4, 3), float(10 * it + r)), 'rewards': torch.arange(4.0)[:, None] + 100 * r + it,
+                    'terminals': torch.full((4, 1), (r + it) % 2 == 0)}
+            if r == rank:
+                shard.add_samples(rows)
+            want.add_samples(rows)                       # what add_samples(concat over ranks) gives
+        md.allgather_new_rows(shard, full, 4)
+        assert full._pointer == want._pointer and full.size == want.size
+        for k in full.fields:
+            assert torch.equal(full.fields[k], want.fields[k]), (it, k)
     t = md.max_over_ranks(10.0 + rank, device='cpu')
     md.barrier()
     if rank == 0:

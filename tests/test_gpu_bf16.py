@@ -57,13 +57,31 @@ def test_predict_bf16_matches_oracle(domain, B, sep):
     np.testing.assert_allclose(var, v64, rtol=BF16_VAR_RTOL)
 
 
-def test_bf16_unsupported_shape_raises():
-    """No silent fallback: a shape whose weights do not fit one CTA pair's shared memory raises (use PREC_FP32)."""
+@pytest.mark.parametrize('domain,B', [('ant', 700), ('humanoid', 300)])
+def test_bf16_wide_shapes_run_on_the_streamed_kernel(domain, B):
+    """ant (in 35, D1 28) and humanoid (in 62, D1 46) -- mopo/static/ant.py, humanoid.py -- do not fit the net-stationary
+    bf16 kernel's shared memory; MOPO_PREC_BF16 runs them on the streamed-weights tcgen05 kernel in bf16 mode (ens_tc3.cu,
+    TERMS = 1): same bf16 bar as the other shapes, predict and the fused step."""
     from mopo_b200 import _lib
-    p, obs, act = ens.synthetic_case('ant', 8, seed=1)
+    from mopo_b200.models.fake_env import FakeEnv
+    import mopo_b200.static as static
+    p, obs, act = ens.synthetic_case(domain, B, seed=1)
+    x = np.concatenate([obs, act], -1)
     m = make_model(p, _lib.PREC_BF16)
-    with pytest.raises(NotImplementedError):
-        m.predict(np.concatenate([obs, act], -1), factored=True)
+    mean, var = m.predict(x, factored=True)
+    m64, v64 = ens.forward(p, x, np.float64)
+    assert norm_err(mean, m64) < BF16_NORM_ERR
+    np.testing.assert_allclose(var, v64, rtol=BF16_VAR_RTOL)
+    rng = np.random.RandomState(3)
+    noise = rng.standard_normal((7, B, obs.shape[1] + 1))
+    inds = rng.choice(5, size=B)
+    o_env = OracleEnv(ens.OracleModel(p), OracleStatic(domain), penalty_coeff=1.0, penalty_learned_var=True)
+    r_nobs, r_rew, r_term, r_info = o_env.step(obs, act, noise=noise, model_inds=inds)
+    env = FakeEnv(m, static[domain], penalty_coeff=1.0, penalty_learned_var=True)
+    nobs, rew, term, info = env.step(obs, act, noise=noise, model_inds=inds, diagnostics=False)
+    assert (info['model_inds'] == inds).all()
+    assert norm_err(nobs, r_nobs) < BF16_NORM_ERR and norm_err(rew, r_rew) < BF16_NORM_ERR
+    np.testing.assert_allclose(info['penalty'], r_info['penalty'], rtol=BF16_VAR_RTOL)
 
 
 def test_predict_bf16_close_to_fp32_path():

@@ -16,10 +16,8 @@ def _bf16_bits(x):
                                        (2, 0, 208, 208), (2, 1, 208, 208), (2, 1, 112, 208), (2, 1, 96, 208),
                                        (2, 0, 112, 32), (2, 1, 48, 208), (2, 0, 96, 32)])
 def test_umma_probe(cg, ts, N, K):
-    import __graft_entry__ as ge
-    ge.build()
     from mopo_b200 import _lib
-    lib = _lib.load()
+    lib = _lib.load_probes()          # the probe build (libmopo_b200_dbg.so, include/mopo_b200_debug.h): not the product library
     M = 512
     rng = np.random.RandomState(N * 7 + K + cg)
     a_bits, a = _bf16_bits(rng.standard_normal((M, K)))
@@ -27,7 +25,7 @@ def test_umma_probe(cg, ts, N, K):
     dA, dB = a_bits.cuda(), b_bits.cuda()
     D = torch.full((M, N), float('nan'), device='cuda')
     _lib.check(lib.mopo_debug_umma_probe(cg, ts, dA.data_ptr(), dB.data_ptr(), D.data_ptr(), M, N, K,
-                                         torch.cuda.current_stream().cuda_stream))
+                                         torch.cuda.current_stream().cuda_stream), lib)
     torch.cuda.synchronize()
     ref = a.astype(np.float64) @ b.astype(np.float64).T
     np.testing.assert_allclose(D.cpu().numpy(), ref, rtol=1e-4, atol=1e-3)

@@ -100,3 +100,58 @@ def test_fc_spec_mirrors_reference_repr_and_init_law():
     assert abs(l.weights.std() - 0.88 * std) < 0.05 * std and not l.biases.any()
     with pytest.raises(RuntimeError):
         FC(10).construct_vars(np.random.RandomState(0))
+
+
+def test_offline_loader_formats(tmp_path, capsys):
+    """mopo/off_policy/loader.py:8-126 on the host side (the pool here is the oracle's NumPy ring; the GPU tests run the same
+    loader into the device pool): contiguous matrix, BEAR pickle with its three extra keys, softlearning checkpoint
+    directory (ascending epochs, stop at max_size, the 250k rule, the saved pool + return statistics), bad widths."""
+    import gzip, os, pickle
+    from mopo_b200.off_policy import loader
+    from oracle.pool import SimpleReplayPool
+    od, ad, n = 5, 2, 300
+    rng = np.random.RandomState(4)
+    fields = {'observations': rng.standard_normal((n, od)), 'actions': rng.standard_normal((n, ad)),
+              'next_observations': rng.standard_normal((n, od)), 'rewards': rng.standard_normal((n, 1)),
+              'terminals': rng.uniform(size=(n, 1)) < 0.02}
+    mat = np.concatenate([fields[k].astype(np.float64) for k in ('observations', 'actions', 'next_observations', 'rewards', 'terminals')], 1)
+    want = SimpleReplayPool(od, ad, 1000); want.add_samples(fields)
+
+    def same(pool):
+        return pool.size == want.size and all(np.array_equal(pool.fields[k], want.fields[k]) for k in want.fields)
+
+    # contiguous
+    p_npy = str(tmp_path / 'pool.npy'); np.save(p_npy, mat)
+    pool = SimpleReplayPool(od, ad, 1000); loader.restore_pool(pool, p_npy, max_size=1000)
+    assert same(pool)
+    parsed = loader.parse_contiguous(mat, od, ad)
+    assert parsed['terminals'].dtype == bool and parsed['actions'].shape == (n, ad)
+    with pytest.raises(AssertionError, match='Expected 14 dimensions, found 13'):
+        loader.parse_contiguous(mat[:, :-1], od, ad)
+    # BEAR: a gzip pickle that np.load rejects -> second format; extras dropped
+    p_bear = str(tmp_path / 'bear.pkl')
+    with gzip.open(p_bear, 'wb') as f:
+        pickle.dump(dict(fields, log_pis=np.zeros(n), data_policy_mean=np.zeros((n, ad)), data_policy_logvar=np.zeros((n, ad))), f)
+    pool = SimpleReplayPool(od, ad, 1000); loader.restore_pool(pool, p_bear, max_size=1000)
+    assert same(pool)
+    assert 'BEAR pool' in capsys.readouterr().out
+    # softlearning checkpoints: epochs out of lexical order, 100 rows each
+    root = tmp_path / 'run'
+    for ep, lo in ((2, 0), (10, 100), (30, 200)):
+        d = root / ('checkpoint_%d' % ep); d.mkdir(parents=True)
+        with gzip.open(str(d / 'replay_pool.pkl'), 'wb') as f:
+            pickle.dump({k: v[lo:lo + 100] for k, v in fields.items()}, f)
+    assert [os.path.basename(os.path.dirname(p)) for p in loader.checkpoint_files(str(root), 1000)] == ['checkpoint_2', 'checkpoint_10', 'checkpoint_30']
+    assert len(loader.checkpoint_files(str(root), 250e3)) == 1
+    out = tmp_path / 'out'; out.mkdir()
+    pool = SimpleReplayPool(od, ad, 1000); loader.restore_pool(pool, str(root), max_size=1000, save_path=str(out))
+    assert same(pool)
+    stats = pickle.load(open(str(out / 'pool_stat_300.pkl'), 'rb'))
+    ends = [i for i in range(n) if fields['terminals'][i, 0]]
+    paths, s = [], 0
+    for e in ends: paths.append(fields['rewards'][s:e + 1].astype(np.float32).sum()); s = e + 1
+    assert np.isclose(stats['buffer_max'], max(paths), rtol=1e-5) and np.isclose(stats['avg_return'], fields['rewards'].astype(np.float32).sum() / len(paths), rtol=1e-4)
+    saved = pickle.load(open(str(out / 'pool_300.pkl'), 'rb'))
+    assert np.array_equal(saved['observations'], want.fields['observations'][:n])
+    pool = SimpleReplayPool(od, ad, 1000); loader.restore_pool(pool, str(root), max_size=150)      # stops after two checkpoints
+    assert pool.size == 200

@@ -153,3 +153,21 @@ def test_philox_streams_statistics():
     e = philox.elite_index(rows, 3, 12345, 5)
     assert e.min() == 0 and e.max() == 4
     assert np.abs(np.bincount(e, minlength=5) / len(rows) - 0.2).max() < 5e-3
+
+
+def test_pool_draws_with_different_offsets_are_independent():
+    """The replay-pool sampler (mopo_pool_sample, the SAC sampler): draws with different ids share no Philox counter, so
+    consecutive minibatches share only what chance gives (the reference draws np.random.randint per batch,
+    flexible_replay_pool.py:85-87; mopo.py:801-821).  Guards the round-1 counter layout where update u+1 replayed update
+    u's rows shifted by two."""
+    from oracle import philox
+    size, n = 1_000_000, 244
+    draws = [philox.pool_indices(n, size, seed=99, offset=o) for o in range(8)]
+    for a in range(8):
+        assert draws[a].min() >= 0 and draws[a].max() < size
+        for b in range(a + 1, 8):
+            assert len(np.intersect1d(draws[a], draws[b])) <= 2            # expectation n^2 / size = 0.06
+            assert not np.array_equal(draws[a][2:], draws[b][:-2])
+    # uniformity over a small range (floor(u * size / 2^64))
+    small = philox.pool_indices(70000, 7, seed=1, offset=5)
+    assert np.all(np.abs(np.bincount(small, minlength=7) - 10000) < 400)

@@ -194,6 +194,29 @@ def test_sac_train_from_pools_equals_explicit_batches_and_exports_actor():
 
 
 @pytest.mark.gpu
+def test_pool_sampler_matches_oracle_and_draws_are_independent():
+    """mopo_pool_sample's indices equal the NumPy restatement bit for bit, and batches of consecutive draw ids (what
+    consecutive SAC updates use) share no rows beyond chance."""
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from oracle import philox
+    rng = np.random.default_rng(3)
+    pool = SimpleReplayPool(5, 2, 50000, device=0)
+    n = 40000
+    pool.add_samples({'observations': rng.standard_normal((n, 5)).astype(np.float32), 'actions': rng.standard_normal((n, 2)).astype(np.float32),
+                      'next_observations': rng.standard_normal((n, 5)).astype(np.float32), 'rewards': np.arange(n, dtype=np.float32)[:, None],
+                      'terminals': np.zeros((n, 1), bool)})
+    seen = []
+    for off in (0, 1, 2, 3, (1 << 33) + 5):
+        b = pool.random_batch_device(244, seed=99, offset=off)
+        idx = b['rewards'].cpu().numpy()[:, 0].astype(np.int64)           # rewards hold the row id
+        assert np.array_equal(idx, philox.pool_indices(244, n, 99, off))
+        seen.append(idx)
+    for a in range(len(seen)):
+        for c in range(a + 1, len(seen)):
+            assert len(np.intersect1d(seen[a], seen[c])) <= 8                # expectation 244^2 / 40000 = 1.5
+
+
+@pytest.mark.gpu
 def test_full_device_loop_and_checkpoint(tmp_path):
     """Rows f1-f4 together, nothing leaving HBM: offline pool -> BNN.train -> elites -> actor-driven rollout into the model
     pool -> SAC updates drawn from both pools -> actor exported -> next rollout uses the new actor; then the SAC variables

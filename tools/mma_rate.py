@@ -5,7 +5,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from mopo_b200 import _lib
-lib = _lib.load()
+lib = _lib.load_probes()
 st = torch.cuda.current_stream().cuda_stream
 out = torch.zeros(2, dtype=torch.int64, device='cuda')
 print('cg  N   nacc a_tmem ksteps | cyc/kstep(total) cyc/kstep(issue) | ideal N/2')

@@ -12,12 +12,12 @@ from mopo_b200.models.constructor import construct_model
 from oracle import ensemble as ens
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 50000
-lib = _lib.load()
+lib = _lib.load_probes()
 dev = torch.device('cuda', 0)
 st = torch.cuda.current_stream(dev)
 
 names = {0: 'tanh.f32', 1: 'tanh.bf16x2', 2: 'ex2.f32', 3: 'tanh.f16x2', 4: 'fma.bf16x2', 5: 'fma.f32'}
-for kind in range(6):
+for kind in (range(6) if os.environ.get('TL_PIPES', '1') == '1' else ()):
     nb, iters = 148, 2000
     cyc = torch.zeros(nb + 1, dtype=torch.int64, device=dev)
     for _ in range(2):
@@ -39,10 +39,18 @@ lv = torch.empty_like(mean)
 trace = torch.zeros(5 * 2048, dtype=torch.int64, device=dev)
 fused = os.environ.get('TL_FUSED', '0') == '1'
 print('mode:', 'fused head' if fused else 'full outputs')
-for _ in range(2):
-    _lib.check(lib.mopo_debug_tc_trace(model._handle, xn.data_ptr(), B, None if fused else mean.data_ptr(), None if fused else lv.data_ptr(), trace.data_ptr(), st.cuda_stream))
+tc3 = int(os.environ.get('TL_TC3', '0'))          # 3 / 1: the streamed-weights kernel (ens_tc3.cu) in fp32-accurate / bf16 mode
+for _ in range(int(os.environ.get('TL_REPS', '2'))):
+    if tc3:
+        _lib.check(lib.mopo_debug_tc3_trace(model._handle, xn.data_ptr(), B, None if fused else mean.data_ptr(), None if fused else lv.data_ptr(), tc3, trace.data_ptr(), st.cuda_stream), lib)
+    else:
+        _lib.check(lib.mopo_debug_tc_trace(model._handle, xn.data_ptr(), B, None if fused else mean.data_ptr(), None if fused else lv.data_ptr(), trace.data_ptr(), st.cuda_stream), lib)
 torch.cuda.synchronize()
 t = trace.cpu().numpy().astype(np.uint64).reshape(5, 2048)
+if tc3 and t[4, -1]:
+    cyc, ns = int(t[4, -2]) - int(t[4, -4]), int(t[4, -1]) - int(t[4, -3])
+    print('issuer loop of pair 0: %d cycles in %d ns -> SM clock %.0f MHz under this load' % (cyc, ns, cyc / max(ns, 1) * 1e3))
+    t[4, -4:] = 0
 ev = []
 for role in range(5):
     for v in t[role]:
