@@ -28,6 +28,13 @@ int mopo_debug_pipe_bench(int kind, int iters, long long* cycles_dev, int n_bloc
  * TMEM (1) or shared memory (0); out_dev = device int64[2]: cycles to commit arrival, cycles to last issue. */
 int mopo_debug_mma_rate(int cta_group, int N, int nacc, int a_tmem, int ksteps, long long* out_dev, void* stream);
 
+/* Interference probe: the cta_group::2 MMA loop (N = 112 | 96, ksteps K=16 steps into one accumulator) while n_warps
+ * other warps per CTA run an epilogue-like loop: imode 0 idle, 1 ex2 + rcp in registers, 2 tcgen05.ld/st x16, 3 the
+ * fp32-accurate kernel's group body (ld, swish, fp16 hi/lo split, st).  with_mma = 0 runs the interferers alone for the
+ * same nominal duration.  out_dev = device int64[8]: [0] MMA cycles to commit, [1] issue cycles, [2] interferer group
+ * iterations completed by the leader CTA's warps. */
+int mopo_debug_mma_interference(int N, int a_tmem, int ksteps, int imode, int n_warps, int with_mma, long long* out_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

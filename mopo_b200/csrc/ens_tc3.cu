@@ -32,9 +32,9 @@
 //     while the current one computes -- no tiling pass, no HBM round trip.
 //   * bias rides in the constant-1 K column (feature 200 of every hidden activation, k = in of the input tile).
 //
-// Warp roles (448 threads): warps 0-7 epilogue (each owns a 32-lane TMEM quadrant; warpgroup 0 takes groups 0-3 / 7-9,
-// warpgroup 1 groups 4-6 / 10-12), warp 8 of the leader CTA issues every MMA (elect.sync), warp 9 streams weights,
-// warps 10-13 produce input tiles and run the head stage (shared with ens_tc.cu: tc_head.cuh).
+// Warp roles (576 threads): warps 0-11 epilogue (three per SM sub-partition, each owns a 32-lane TMEM quadrant and a share
+// of each half's feature groups), warp 12 of the leader CTA issues every MMA (elect.sync), warp 13 streams weights,
+// warps 14-17 produce input tiles and run the head stage (shared with ens_tc.cu: tc_head.cuh).
 #include "internal.cuh"
 #include "tc_common.cuh"
 #include "tc_head.cuh"
@@ -55,9 +55,21 @@ constexpr int WP = WR * 16;             // 1664 B: one K-panel of a CTA's weight
 constexpr int WPART = KP * WP;          // 43264 B: the hi (or lo) part of one hidden layer
 constexpr int STAGE = 2 * WPART;        // 86528 B: one ring stage
 constexpr int XP = 128 * 16;            // 2048 B: one K-panel of a 128-row input block
-constexpr int NTHREADS = 448;
+constexpr int EPI_WG = 3;                // epilogue warpgroups: 3 warps per SM sub-partition keep the MUFU fed (2 left it ~35 % idle)
+constexpr int EPI_WARPS = 4 * EPI_WG;    // warps 0 .. EPI_WARPS-1; then the MMA issuer, the weight streamer, 4 head warps
+// Epilogue rounds: round r converts feature groups 3r .. 3r+2 (one per warpgroup; round 2 is group 6 alone, the last of half 1;
+// rounds 3, 4 are half 2) and signals r_ready[r]: the next layer's K loop follows the epilogue round by round.
+constexpr int NROUND = 5;
+static_assert(EPI_WG == 3, "the round table below deals one feature group per warpgroup and round");
+__host__ __device__ constexpr int round_g0(int r) { return r < 2 ? 3 * r : r == 2 ? 6 : 7 + 3 * (r - 3); }
+__host__ __device__ constexpr int round_n(int r) { return r == 2 ? 1 : 3; }
+constexpr int W_ISSUE = EPI_WARPS, W_LOAD = EPI_WARPS + 1, W_HEAD = EPI_WARPS + 2;
+constexpr int NTHREADS = 32 * (EPI_WARPS + 6);
 constexpr int C_BUF0 = 0, C_BUF1 = 208, C_HEAD = 416;
 constexpr int MAX_IN = 64;
+#ifndef MOPO_TC3_POLL_NS
+#define MOPO_TC3_POLL_NS 32     // back-off between mbarrier polls of the issuer and the epilogue warps (see tc_common.cuh)
+#endif
 constexpr float W_SCALE = 64.0f;         // TERMS == 3: weight / bias images are stored x 64 (see the header comment)
 
 struct S3 {
@@ -166,8 +178,10 @@ struct Bars3 {
   uint64_t w_free[2];      // each CTA: the MMAs that read the stage have retired            (commit)
   uint64_t x_full;         // leader: both CTAs' input block is in smem                      (count 8: head warps)
   uint64_t x_free;         // each CTA: the layer-0 MMAs that read the input block retired   (commit)
-  uint64_t d_full[2];      // each CTA: half 1 / half 2 accumulator of the current layer     (commit)
-  uint64_t a_ready[2];     // leader: half 1 / half 2 of the next A operand is written       (count 16: epilogue warps)
+  uint64_t d_full[2];      // each CTA: half 1 / half 2 accumulator of hidden layer 1..3     (commit)
+  uint64_t r_ready[NROUND];// leader: the feature groups of epilogue round r are written as the next A operand (count: ROUND_CNT)
+  uint64_t d0_full[2];     // the same for layer 0, whose MMAs are issued a unit early (ahead of the previous unit's head):
+  uint64_t r0_ready[NROUND]; // own barriers, so that its phases cannot lap or mix with layer 3's
   uint64_t h_full;         // each CTA: head accumulator ready                               (commit)
   uint64_t h_done;         // leader: the head warps have read it                            (count 8)
   uint32_t tmem_base;
@@ -177,10 +191,21 @@ struct Bars3 {
 __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-// swish (fc.py:21: x * sigmoid(x)).  TERMS == 3: ex2 + rcp, relative error ~3e-7.  TERMS == 1: tanh form, one MUFU op.
-template <int TERMS> __device__ __forceinline__ float swish_acc(float x) {
+// swish (fc.py:21: x * sigmoid(x)).  TERMS == 3: x * rcp(1 + ex2(-x log2 e)), two MUFU results, relative error ~3e-7.
+// (Measured and rejected, profiles/r02_tc3_timeline_v2_newton.txt: taking every second reciprocal on the FMA pipe -- magic
+// seed + 3 Newton steps -- to balance MUFU against issue slots made the epilogue 1.6x SLOWER: with two epilogue warps per
+// SM sub-partition the dependent FMA chains are not hidden, as round 1 found for the bf16 kernel.)  TERMS == 1: tanh form.
+template <int TERMS, bool NEWTON = false> __device__ __forceinline__ float swish_acc(float x) {
   if constexpr (TERMS == 1) { const float xh = 0.5f * x; return fmaf(xh, tanh_fast(xh), xh); }
-  else return x * rcp_approx(1.0f + ex2_approx(-1.44269504f * x));
+  else if constexpr (!NEWTON) return x * rcp_approx(1.0f + ex2_approx(-1.44269504f * x));
+  else {
+    // reciprocal on the FMA pipe: magic-constant seed (12 %) + 3 Newton steps (4e-8); d in [1, 2^100] keeps the seed finite
+    const float d = 1.0f + ex2_approx(fminf(-1.44269504f * x, 100.0f));
+    float r = __int_as_float(0x7EF311C7 - __float_as_int(d));
+#pragma unroll
+    for (int it = 0; it < 3; ++it) r = fmaf(r, fmaf(-d, r, 1.0f), r);
+    return x * r;
+  }
 }
 
 // operand formats: TERMS == 3 -> fp16 pairs, TERMS == 1 -> bf16
@@ -196,41 +221,28 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
   lo = pack_f16x2(a - f16lo_to_f32(hi), b - f16hi_to_f32(hi));
 }
 
-// N accumulator columns (N = 32 or 16: two or one feature group of this thread's row) at taddr -> swish -> split ->
-// the SAME columns as [hi x 8 | lo x 8] per group.  ONES: the chunk's last group is group 12, whose feature 200 is the
-// constant 1 of the bias row.
-template <int TERMS, int N, bool ONES>
-__device__ __forceinline__ void swish_split_store(uint32_t taddr, const uint32_t (&v)[32]) {
-  uint32_t o[N];
+// One feature group (16 accumulator columns of this thread's row) at taddr -> swish -> split -> the SAME 16 columns as
+// [hi x 8 | lo x 8].  ones: this is group 12, whose feature 200 is the constant 1 of the bias row.
+// The epilogue is a LOOP over groups with this one body (two inlined copies, ~5 KB of code) shared by every warp, layer and
+// half: the first version unrolled each (warpgroup, half) part on its own -- 40 KB of straight-line epilogue code that each
+// warp ran once per layer -- and a quarter of all warp stall samples were instruction-fetch stalls on exactly those FMUL /
+// MUFU / F2FP lines (profiles/r02_tc3_v3_ncu_stalls.txt; the L1.5 instruction cache is 32 KB).
+template <int TERMS>
+__device__ __forceinline__ void group_store(uint32_t taddr, const uint32_t (&v)[16], bool ones) {
+  // Written pair by pair (swish of two features, then their split) so that the fp16 split of one pair sits between the
+  // MUFU instructions of the following pairs in the instruction stream: with all 16 swishes first and all 8 splits after
+  // them every warp had a ~60-instruction tail without a single MUFU, and the warps of a round run in phase.
+  uint32_t o[16];
 #pragma unroll
-  for (int g = 0; g < N / 16; ++g) {
-    float sv[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) sv[i] = swish_acc<TERMS>((TERMS == 3 ? 1.0f / W_SCALE : 1.0f) * __uint_as_float(v[16 * g + i]));
-    if (ONES && g == N / 16 - 1) sv[8] = 1.0f;
-#pragma unroll
-    for (int p = 0; p < 8; ++p) {
-      if constexpr (TERMS == 3) split2(sv[2 * p], sv[2 * p + 1], o[16 * g + p], o[16 * g + 8 + p]);
-      else { o[16 * g + p] = pack_bf16x2(sv[2 * p], sv[2 * p + 1]); o[16 * g + 8 + p] = 0u; }
-    }
+  for (int p = 0; p < 8; ++p) {
+    const float sc = TERMS == 3 ? 1.0f / W_SCALE : 1.0f;
+    float s0 = swish_acc<TERMS>(sc * __uint_as_float(v[2 * p]));
+    const float s1 = swish_acc<TERMS>(sc * __uint_as_float(v[2 * p + 1]));
+    if (p == 4 && ones) s0 = 1.0f;
+    if constexpr (TERMS == 3) split2(s0, s1, o[p], o[8 + p]);
+    else { o[p] = pack_bf16x2(s0, s1); o[8 + p] = 0u; }
   }
-  if constexpr (N == 32) tmem_st32(taddr, reinterpret_cast<const uint32_t (&)[32]>(o));
-  else tmem_st16(taddr, reinterpret_cast<const uint32_t (&)[16]>(o));
-}
-
-// one epilogue part of one warp: NC = 64 or 48 accumulator columns starting at taddr, software pipelined
-template <int TERMS, int NC, bool ONES>
-__device__ __forceinline__ void epi_part(uint32_t taddr) {
-  uint32_t va[32], vb[32];
-  tmem_ld32(taddr, va);
-  tmem_ld_wait();
-  if constexpr (NC == 64) tmem_ld32(taddr + 32, vb);
-  else tmem_ld16(taddr + 32, reinterpret_cast<uint32_t (&)[16]>(vb));
-  swish_split_store<TERMS, 32, false>(taddr, va);
-  tmem_ld_wait();
-  if constexpr (NC == 64) swish_split_store<TERMS, 32, ONES>(taddr + 32, vb);
-  else swish_split_store<TERMS, 16, ONES>(taddr + 32, vb);
-  tmem_st_wait();
+  tmem_st16(taddr, o);
 }
 
 // K groups [g0, g1) of one N half: D (+)= A[g] * B[g]^T with A from tensor memory (hi at column 16 g, lo at 16 g + 8)
@@ -281,8 +293,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_ready[i], 2); mbar_init(&bars->w_free[i], 1);
-      mbar_init(&bars->d_full[i], 1); mbar_init(&bars->a_ready[i], 16);
+      mbar_init(&bars->d_full[i], 1); mbar_init(&bars->d0_full[i], 1);
     }
+    for (int r = 0; r < NROUND; ++r) { mbar_init(&bars->r_ready[r], 8 * round_n(r)); mbar_init(&bars->r0_ready[r], 8 * round_n(r)); }
     mbar_init(&bars->x_full, 8); mbar_init(&bars->x_free, 1);
     mbar_init(&bars->h_full, 1); mbar_init(&bars->h_done, 8);
     fence_barrier_init();
@@ -299,7 +312,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     sMu[i] = sc ? a.mu[i] : 0.0f;
     sSg[i] = sc ? a.sigma[i] : 1.0f;
   }
-  if (warp == 8) { tmem_alloc<2>(&bars->tmem_base, 512); tmem_relinquish<2>(); }
+  if (warp == W_ISSUE) { tmem_alloc<2>(&bars->tmem_base, 512); tmem_relinquish<2>(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -310,143 +323,207 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
   // everything it reads that this grid writes (selmv / pen2) is touched by the head warps only, after pdl_wait().
   pdl_launch_dependents();
 
-  if (warp == 9) {
-    // ===== weight streamer: blob j of the unit's net -> ring stage (load index & 1) =====
+  if (warp == W_LOAD) {
+    // ===== weight streamer.  Ring stage = load index & 1.  Loads: a prologue [W0 of the first unit], then per unit
+    // W1, W2, W3 and ONE stage holding [head of this unit | W0 of the next unit] (an even number of loads per unit keeps
+    // every load at least one layer ahead of its use; with five the second layer's weights could only be requested
+    // once the previous unit's head had retired and arrived ~1500 cycles late, profiles/r02_tc3_timeline_first.txt) =====
     if (lane == 0) {
       uint32_t li = 0;
+      const uint32_t hw_w0 = 2 * (uint32_t)s.head_part();            // offset of the W0 blob inside a [head | W0] stage
+      const size_t off_w0 = 0, off_h = 2 * (size_t)s.w0_part() + 3 * (size_t)STAGE;
+      auto img_of = [&](int u) { return a.img + ((size_t)(u / nT) * 2 + rank) * s.img_bytes(); };
+      auto stage_wait = [&](int tag) {
+        const uint32_t st = li & 1;
+        if (li >= 2) mbar_wait_relaxed(&bars->w_free[st], ((li >> 1) - 1) & 1, 1000 + tag);
+        TR(3, 70 + tag);
+        return st;
+      };
+      auto stage_done = [&](uint32_t st, int tag) {
+        mbar_wait_relaxed(&bars->w_full[st], (li >> 1) & 1, 1100 + tag);
+        TR(3, 80 + tag);
+        mbar_arrive_remote(&bars->w_ready[st], 0);
+        ++li;
+      };
+      if (u0 < u1) {                                                  // prologue: W0 of the first unit
+        const uint32_t st = stage_wait(0);
+        mbar_expect_tx(&bars->w_full[st], 2 * (uint32_t)s.w0_part());
+        bulk_g2s(sW + st * STAGE + hw_w0, img_of(u0) + off_w0, 2 * (uint32_t)s.w0_part(), &bars->w_full[st]);
+        stage_done(st, 0);
+      }
       for (int u = u0; u < u1; ++u) {
-        const int e = u / nT;
-        const uint8_t* src = a.img + ((size_t)e * 2 + rank) * s.img_bytes();
-        for (int j = 0; j < 5; ++j, ++li) {
-          const uint32_t st = li & 1;
-          if (li >= 2) mbar_wait(&bars->w_free[st], ((li >> 1) - 1) & 1, 1000 + j);
-          TR(3, 70 + j);
-          const uint32_t bytes = (uint32_t)s.blob_bytes(j);
-          mbar_expect_tx(&bars->w_full[st], bytes);
-          bulk_g2s(sW + st * STAGE, src, bytes / 2, &bars->w_full[st]);
-          bulk_g2s(sW + st * STAGE + bytes / 2, src + bytes / 2, bytes / 2, &bars->w_full[st]);
-          src += bytes;
-          mbar_wait(&bars->w_full[st], (li >> 1) & 1, 1100 + j);
-          TR(3, 80 + j);
-          mbar_arrive_remote(&bars->w_ready[st], 0);
+        const uint8_t* src = img_of(u);
+        for (int j = 1; j < 4; ++j) {
+          const uint32_t st = stage_wait(j);
+          mbar_expect_tx(&bars->w_full[st], STAGE);
+          const uint8_t* g = src + 2 * (size_t)s.w0_part() + (size_t)(j - 1) * STAGE;
+          bulk_g2s(sW + st * STAGE, g, WPART, &bars->w_full[st]);
+          bulk_g2s(sW + st * STAGE + WPART, g + WPART, WPART, &bars->w_full[st]);
+          stage_done(st, j);
         }
+        const uint32_t st = stage_wait(4);
+        const bool more = u + 1 < u1;
+        mbar_expect_tx(&bars->w_full[st], 2 * (uint32_t)s.head_part() + (more ? 2 * (uint32_t)s.w0_part() : 0u));
+        bulk_g2s(sW + st * STAGE, src + off_h, 2 * (uint32_t)s.head_part(), &bars->w_full[st]);
+        if (more) bulk_g2s(sW + st * STAGE + hw_w0, img_of(u + 1) + off_w0, 2 * (uint32_t)s.w0_part(), &bars->w_full[st]);
+        stage_done(st, 4);
       }
     }
     __syncwarp();
-  } else if (warp == 8) {
+  } else if (warp == W_ISSUE) {
     // ===== MMA issuer (leader CTA): all lanes run the loop, one elected lane issues =====
     if (rank == 0) {
-      if (TRACE && a.trace && pair == 0 && lane == 0) {          // wall clock beside the cycle counter: the SM clock under this load
+      if (TRACE && a.trace && lane == 0) {                       // wall clock beside the cycle counter: the SM clock under this load
         unsigned long long ns;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
-        a.trace[5 * TRACE_CAP - 4] = (unsigned long long)clock64();
-        a.trace[5 * TRACE_CAP - 3] = ns;
+        if (pair == 0) { a.trace[5 * TRACE_CAP - 4] = (unsigned long long)clock64(); a.trace[5 * TRACE_CAP - 3] = ns; }
+        if (pair < 256) a.trace[4 * TRACE_CAP + 1024 + 2 * pair] = ns;       // every pair: start / end of its issuer loop
       }
       const uint32_t id1 = idesc_of<TERMS>(256, NH1), id2 = idesc_of<TERMS>(256, NH2), idh = idesc_of<TERMS>(256, s.NHEAD);
       const uint32_t wa = smem_u32(sW), xa = smem_u32(sX);
       const uint32_t hpanel = (uint32_t)(s.NHEAD / 2) * 16;
-      uint32_t li = 0, n_x = 0, n_a0 = 0, n_a1 = 0, n_h = 0;
+      uint32_t li = 0, n_x = 0, n_r = 0, n_h = 0, n_u = 0;   // n_r / n_u: epilogue passes over hidden-layer / layer-0 accumulators consumed
+      const uint32_t hw_w0 = 2 * (uint32_t)s.head_part();
+      // layer 0 of a unit: A = the input block in shared memory (SS form), B = the W0 blob at wb, D -> buffer 0
+      auto issue_l0 = [&](uint32_t wb) {
+        mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&bars->x_full, n_x & 1, 1); ++n_x;
+        tc_fence_after();
+        TR(0, 1);
+        if (elect_one()) {
+          const uint32_t wlo = (uint32_t)s.w0_part(), xlo = (uint32_t)s.x_part();
+          for (int hf = 0; hf < 2; ++hf) {
+            const uint32_t d = tbase + C_BUF0 + (hf ? NH1 : 0);
+            const uint32_t idesc = hf ? id2 : id1;
+            const uint32_t boff = hf ? 56 * 16 : 0;
+            for (int ks = 0; ks < s.K0 / 16; ++ks) {
+              const uint32_t ax = xa + ks * 2 * XP, b = wb + boff + ks * 2 * WP;
+              mma_ss<2>(d, smem_desc(ax, XP, 128), smem_desc(b, WP, 128), idesc, ks > 0);
+              if constexpr (TERMS == 3) {
+                mma_ss<2>(d, smem_desc(ax, XP, 128), smem_desc(b + wlo, WP, 128), idesc, 1);
+                mma_ss<2>(d, smem_desc(ax + xlo, XP, 128), smem_desc(b, WP, 128), idesc, 1);
+              }
+            }
+            mma_commit<2>(&bars->d0_full[hf]);
+          }
+          mma_commit<2>(&bars->x_free);
+        }
+        __syncwarp();
+      };
+      if (u0 < u1) {                                    // prologue: layer 0 of the first unit
+        mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&bars->w_ready[0], 0, 0);
+        TR(0, 0);
+        issue_l0(wa + hw_w0);
+        if (elect_one()) mma_commit<2>(&bars->w_free[0]);
+        __syncwarp();
+        ++li;
+      }
       for (int u = u0; u < u1; ++u) {
-        for (int j = 0; j < 5; ++j, ++li) {
+        for (int j = 1; j < 5; ++j, ++li) {
           const uint32_t st = li & 1;
           const uint32_t wb = wa + st * STAGE;
-          mbar_wait_cluster(&bars->w_ready[st], (li >> 1) & 1, 10 * j);
+          mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&bars->w_ready[st], (li >> 1) & 1, 10 * j);
           TR(0, 10 * j);
-          if (j == 0) {
-            mbar_wait_cluster(&bars->x_full, n_x & 1, 1); ++n_x;
-            tc_fence_after();
-            TR(0, 1);
-            if (elect_one()) {
-              const uint32_t wlo = (uint32_t)s.w0_part(), xlo = (uint32_t)s.x_part();
-              for (int hf = 0; hf < 2; ++hf) {
-                const uint32_t d = tbase + C_BUF0 + (hf ? NH1 : 0);
-                const uint32_t idesc = hf ? id2 : id1;
-                const uint32_t boff = hf ? 56 * 16 : 0;
-                for (int ks = 0; ks < s.K0 / 16; ++ks) {
-                  const uint32_t ax = xa + ks * 2 * XP, b = wb + boff + ks * 2 * WP;
-                  mma_ss<2>(d, smem_desc(ax, XP, 128), smem_desc(b, WP, 128), idesc, ks > 0);
-                  if constexpr (TERMS == 3) {
-                    mma_ss<2>(d, smem_desc(ax, XP, 128), smem_desc(b + wlo, WP, 128), idesc, 1);
-                    mma_ss<2>(d, smem_desc(ax + xlo, XP, 128), smem_desc(b, WP, 128), idesc, 1);
-                  }
-                }
-                mma_commit<2>(&bars->d_full[hf]);
-              }
-              mma_commit<2>(&bars->x_free);
-              mma_commit<2>(&bars->w_free[st]);
-            }
-            __syncwarp();
-          } else if (j < 4) {
+          // the A operand of layer j / the head = what the epilogue makes of layer j-1's accumulator, round by round
+          uint64_t* rr = j == 1 ? bars->r0_ready : bars->r_ready;
+          const uint32_t par = (j == 1 ? n_u : n_r) & 1;
+          if (j < 4) {
             const uint32_t abuf = tbase + (((j - 1) & 1) ? C_BUF1 : C_BUF0);
             const uint32_t dbuf = tbase + ((j & 1) ? C_BUF1 : C_BUF0);
-            mbar_wait_cluster(&bars->a_ready[0], n_a0 & 1, 10 * j + 2); ++n_a0;
-            tc_fence_after();
-            TR(0, 10 * j + 1);
-            if (elect_one()) issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, 0, G1);
-            __syncwarp();
-            mbar_wait_cluster(&bars->a_ready[1], n_a1 & 1, 10 * j + 3); ++n_a1;
-            tc_fence_after();
-            TR(0, 10 * j + 2);
-            if (elect_one()) {
-              issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, G1, NGRP);
-              mma_commit<2>(&bars->d_full[0]);
-              issue_ts<TERMS>(dbuf + NH1, abuf, wb + 56 * 16, WPART, WP, id2, 0, NGRP);
-              mma_commit<2>(&bars->d_full[1]);
-              mma_commit<2>(&bars->w_free[st]);
+            for (int r = 0; r < NROUND; ++r) {
+              mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&rr[r], par, 10 * j + r);
+              tc_fence_after();
+              TR(0, 50 + 10 * j + r);
+              if (elect_one()) {
+                issue_ts<TERMS>(dbuf, abuf, wb, WPART, WP, id1, round_g0(r), round_g0(r) + round_n(r));
+                if (r == NROUND - 1) {
+                  mma_commit<2>(&bars->d_full[0]);
+                  issue_ts<TERMS>(dbuf + NH1, abuf, wb + 56 * 16, WPART, WP, id2, 0, NGRP);
+                  mma_commit<2>(&bars->d_full[1]);
+                  mma_commit<2>(&bars->w_free[st]);
+                }
+              }
+              __syncwarp();
             }
-            __syncwarp();
             TR(0, 10 * j + 3);
           } else {
-            mbar_wait_cluster(&bars->a_ready[0], n_a0 & 1, 42); ++n_a0;
-            mbar_wait_cluster(&bars->a_ready[1], n_a1 & 1, 43); ++n_a1;
+            // [head | W0'] stage.  Layer 0 of the NEXT unit goes to the tensor pipe first: it writes buffer 0 (free since
+            // layer 3's MMAs were issued) while the epilogue still turns layer 3's accumulator (buffer 1) into the head's
+            // A operand, and its own epilogue then runs under the head MMA.
+            if (u + 1 < u1) issue_l0(wb + hw_w0);
             // the head MMA overwrites the previous unit's head accumulator: the head warps must have read it
-            if (n_h > 0) mbar_wait_cluster(&bars->h_done, (n_h - 1) & 1, 44);
+            if (n_h > 0) mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&bars->h_done, (n_h - 1) & 1, 44);
             ++n_h;
-            tc_fence_after();
-            TR(0, 42);
-            if (elect_one()) {
-              issue_ts<TERMS>(tbase + C_HEAD, tbase + C_BUF1, wb, (uint32_t)s.head_part(), hpanel, idh, 0, NGRP);
-              mma_commit<2>(&bars->h_full);
-              mma_commit<2>(&bars->w_free[st]);
+            for (int r = 0; r < NROUND; ++r) {
+              mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&rr[r], par, 40 + r);
+              tc_fence_after();
+              if (r == 0) TR(0, 42);
+              if (elect_one()) {
+                issue_ts<TERMS>(tbase + C_HEAD, tbase + C_BUF1, wb, (uint32_t)s.head_part(), hpanel, idh, round_g0(r), round_g0(r) + round_n(r));
+                if (r == NROUND - 1) {
+                  mma_commit<2>(&bars->h_full);
+                  mma_commit<2>(&bars->w_free[st]);
+                }
+              }
+              __syncwarp();
             }
-            __syncwarp();
           }
+          if (j == 1) ++n_u; else ++n_r;
         }
       }
-      if (TRACE && a.trace && pair == 0 && lane == 0) {
+      if (TRACE && a.trace && lane == 0) {
         unsigned long long ns;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
-        a.trace[5 * TRACE_CAP - 2] = (unsigned long long)clock64();
-        a.trace[5 * TRACE_CAP - 1] = ns;
+        if (pair == 0) { a.trace[5 * TRACE_CAP - 2] = (unsigned long long)clock64(); a.trace[5 * TRACE_CAP - 1] = ns; }
+        if (pair < 256) a.trace[4 * TRACE_CAP + 1024 + 2 * pair + 1] = ns;
       }
     }
-  } else if (warp < 8) {
+  } else if (warp < EPI_WARPS) {
     // ===== epilogue warps: accumulator half -> swish -> (hi, lo) A operand, in place =====
     const int wg = warp >> 2, q = warp & 3;
     const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
-    uint32_t n_d = 0;                                   // layers consumed (both halves flip once per layer)
-    for (int u = u0; u < u1; ++u) {
-      for (int j = 0; j < 4; ++j, ++n_d) {
+    uint32_t n_d = 0, n_u = 0;                          // hidden layers 1..3 / units consumed (every barrier flips once per layer)
+    uint32_t va[16], vb[16];
+    for (int u = u0; u < u1; ++u, ++n_u) {
+      for (int j = 0; j < 4; ++j) {
         const uint32_t buf = tlane + ((j & 1) ? C_BUF1 : C_BUF0);
-        if (q == 0) TR(1 + wg, 100 + 10 * j);
-        mbar_wait(&bars->d_full[0], n_d & 1, 100 + j);
-        tc_fence_after();
-        if (q == 0) TR(1 + wg, 200 + 10 * j);
-        if (wg == 0) epi_part<TERMS, 64, false>(buf);              // groups 0..3
-        else epi_part<TERMS, 48, false>(buf + 64);                 // groups 4..6
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_remote(&bars->a_ready[0], 0);
-        if (q == 0) TR(1 + wg, 300 + 10 * j);
-        mbar_wait(&bars->d_full[1], n_d & 1, 110 + j);
-        tc_fence_after();
-        if (q == 0) TR(1 + wg, 200 + 10 * j + 1);
-        if (wg == 0) epi_part<TERMS, 48, false>(buf + 112);        // groups 7..9
-        else epi_part<TERMS, 48, true>(buf + 160);                 // groups 10..12 (feature 200 = 1)
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_remote(&bars->a_ready[1], 0);
-        if (q == 0) TR(1 + wg, 300 + 10 * j + 1);
+        uint64_t* dfull = j == 0 ? bars->d0_full : bars->d_full;
+        uint64_t* rready = j == 0 ? bars->r0_ready : bars->r_ready;
+        const uint32_t par = (j == 0 ? n_u : n_d) & 1;
+        // round r: group round_g0(r) + wg (round 2 only has warpgroup 0's group 6).  Rounds alternate between the two
+        // register sets so that the tcgen05.ld of this warp's next group is in flight while the current one is converted.
+        bool pre = false;                                  // the current round's group is already on its way into registers
+#pragma unroll 1
+        for (int r = 0; r < NROUND; r += 2) {
+#pragma unroll
+          for (int ab = 0; ab < 2; ++ab) {
+            const int rd = r + ab;
+            if (rd >= NROUND) break;
+            uint32_t (&cur)[16] = ab ? vb : va;
+            uint32_t (&nxt)[16] = ab ? va : vb;
+            const bool mine = wg < round_n(rd);
+            if (rd == 0 || rd == 3) {                      // first round of a half: its accumulator must have been committed
+              if (q == 0 && wg < 2) TR(1 + wg, 100 + 10 * j + (rd == 3));
+              mbar_wait_backoff<MOPO_TC3_POLL_NS>(&dfull[rd == 3], par, 100 + 10 * j + rd);
+              tc_fence_after();
+              if (q == 0 && wg < 2) TR(1 + wg, 200 + 10 * j + (rd == 3));
+            }
+            if (mine) {
+              const uint32_t t_cur = buf + 16 * (round_g0(rd) + wg);
+              if (!pre) tmem_ld16(t_cur, cur);
+              tmem_ld_wait();
+              pre = rd + 1 < NROUND && rd + 1 != 3 && wg < round_n(rd + 1);      // same half, and this warpgroup has a group there
+              if (pre) tmem_ld16(buf + 16 * (round_g0(rd + 1) + wg), nxt);
+              group_store<TERMS>(t_cur, cur, round_g0(rd) + wg == NGRP - 1);
+              tmem_st_wait();
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_remote(&rready[rd], 0);
+              if (q == 0 && wg < 2) TR(1 + wg, 400 + 10 * j + rd);
+            } else pre = false;
+            if ((rd == 2 || rd == 4) && q == 0 && wg < 2) TR(1 + wg, 300 + 10 * j + (rd == 4));
+          }
+        }
+        if (j > 0) ++n_d;
       }
     }
   } else {
@@ -496,7 +573,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     for (int u = u0; u < u1; ++u, ++n_h) {
       const int e = u / nT, t = u - e * nT;
       if (u + 1 < u1) {
-        mbar_wait(&bars->x_free, n_h & 1, 200);          // layer 0 of unit u has consumed the block
+        mbar_wait_relaxed(&bars->x_free, n_h & 1, 200);          // layer 0 of unit u has consumed the block
         if (q == 0) TR(4, 150);
         produce_x(u + 1);
         if (q == 0) TR(4, 250);
@@ -505,7 +582,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
       const bool valid = row < n;
       bool mine = false;
       if (a.out.sel && valid) mine = a.out.sel[row] == e;
-      mbar_wait(&bars->h_full, n_h & 1, 210);
+      mbar_wait_relaxed(&bars->h_full, n_h & 1, 210);
       tc_fence_after();
       if (q == 0) TR(4, 240);
       const uint32_t tblk = tlane + C_HEAD;
@@ -529,7 +606,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                                   // peer smem / TMEM must outlive the leader's MMAs
-  if (warp == 8) tmem_dealloc<2>(tbase, 512);
+  if (warp == W_ISSUE) tmem_dealloc<2>(tbase, 512);
 }
 
 size_t tc3_smem_bytes(const S3& s) {

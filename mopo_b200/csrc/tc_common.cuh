@@ -69,6 +69,33 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ct
   MOPO_WATCHDOG_DECL
   while (!mbar_try_wait(bar, parity)) { MOPO_WATCHDOG_CHECK(bar, parity) }
 }
+// Waits with a back-off between polls.  mbarrier.try_wait goes through the SM's MIO queue, the same queue that feeds the
+// MUFU and tcgen05.ld/st: in the fp32-accurate kernel the polls of waiting warps were half as many MIO instructions as
+// the epilogue's MUFU work and held it at 2/3 of the special-function rate (383 vs 256 cycles per feature group,
+// profiles/r02_tc3_timeline_v8.txt vs tools/mma_interference.py).  NS = 0: poll back to back.
+template <int NS>
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity, int ctx = 0) {
+  (void)ctx;
+  MOPO_WATCHDOG_DECL
+  while (!mbar_try_wait(bar, parity)) { if (NS > 0) __nanosleep(NS); MOPO_WATCHDOG_CHECK(bar, parity) }
+}
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, int ctx = 0) { mbar_wait_backoff<128>(bar, parity, ctx); }
+template <int NS>
+__device__ __forceinline__ void mbar_wait_cluster_backoff(uint64_t* bar, uint32_t parity, int ctx = 0) {
+  (void)ctx;
+  uint32_t ok = 0;
+  MOPO_WATCHDOG_DECL
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (ok) break;
+    if (NS > 0) __nanosleep(NS);
+    MOPO_WATCHDOG_CHECK(bar, parity)
+  }
+}
 // acquire at cluster scope (pairs with mbar_arrive_cluster from the peer CTA)
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity, int ctx = 0) {
   (void)ctx;

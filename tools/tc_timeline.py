@@ -16,8 +16,8 @@ lib = _lib.load_probes()
 dev = torch.device('cuda', 0)
 st = torch.cuda.current_stream(dev)
 
-names = {0: 'tanh.f32', 1: 'tanh.bf16x2', 2: 'ex2.f32', 3: 'tanh.f16x2', 4: 'fma.bf16x2', 5: 'fma.f32'}
-for kind in (range(6) if os.environ.get('TL_PIPES', '1') == '1' else ()):
+names = {0: 'tanh.f32', 1: 'tanh.bf16x2', 2: 'ex2.f32', 3: 'tanh.f16x2', 4: 'fma.bf16x2', 5: 'fma.f32', 6: 'rcp.f32', 7: 'swish(ex2+rcp)', 8: 'cvt.f16x2.f32', 9: 'cvt.f32.f16+sub'}
+for kind in (range(10) if os.environ.get('TL_PIPES', '1') == '1' else ()):
     nb, iters = 148, 2000
     cyc = torch.zeros(nb + 1, dtype=torch.int64, device=dev)
     for _ in range(2):
@@ -51,6 +51,15 @@ if tc3 and t[4, -1]:
     cyc, ns = int(t[4, -2]) - int(t[4, -4]), int(t[4, -1]) - int(t[4, -3])
     print('issuer loop of pair 0: %d cycles in %d ns -> SM clock %.0f MHz under this load' % (cyc, ns, cyc / max(ns, 1) * 1e3))
     t[4, -4:] = 0
+    pp = t[4, 1024:1024 + 512].astype(np.int64).reshape(-1, 2)
+    pp = pp[pp[:, 1] > 0]
+    if len(pp):
+        base = pp[:, 0].min()
+        print('per-pair issuer loops (ns from the first start): start min/median/max %d/%d/%d, end min/median/max %d/%d/%d, duration min/median/max %d/%d/%d' % (
+            (pp[:, 0] - base).min(), np.median(pp[:, 0] - base), (pp[:, 0] - base).max(), (pp[:, 1] - base).min(), np.median(pp[:, 1] - base), (pp[:, 1] - base).max(),
+            (pp[:, 1] - pp[:, 0]).min(), np.median(pp[:, 1] - pp[:, 0]), (pp[:, 1] - pp[:, 0]).max()))
+        print('per-pair durations (us):', ' '.join('%.0f' % (d / 1e3) for d in (pp[:, 1] - pp[:, 0])))
+    t[4, 1024:1024 + 512] = 0
 ev = []
 for role in range(5):
     for v in t[role]:
