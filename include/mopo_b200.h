@@ -114,6 +114,10 @@ int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n);
 int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var,
                      int precision, void* stream);
 
+/* BNN.predict with 3-D inputs (bnn.py:541-545; fc.py:100-101: net e sees x[e]): x [E,B,in] device fp32 -> mean, var [E,B,D1]. */
+int mopo_ens_predict3d(mopo_ens* h, const float* x, int64_t B, float* mean, float* var,
+                       int precision, void* stream);
+
 /* The contraction alone (BNN._compile_outputs(ret_log_var=True), bnn.py:631-673) on ALREADY SCALED inputs
  * xn = (x - mu) / sigma [B,in]: -> mean [E,B,D1], clamped logvar [E,B,D1].  This is the kernel the roofline
  * is quoted on (bench.py times it alone). */
@@ -205,10 +209,15 @@ typedef struct {
 int mopo_policy_act(mopo_policy* p, const mopo_policy_args* a, void* stream);
 
 /* ---- BNN.train (bnn.py:369-503): the optimiser loop on the device -------------------------- */
-/* Start a training run: allocates Adam state (tf.train.AdamOptimizer defaults beta1 .9, beta2 .999, eps 1e-8,
+/* Start a training run: allocates (first call) or keeps the Adam state (tf.train.AdamOptimizer defaults beta1 .9, beta2 .999, eps 1e-8,
  * constructor.py:40 learning_rate 1e-3) and the per-net snapshot store.  weight_decays: HOST array of n_hidden + 2
  * rates -- hidden layers, mean head, log-variance head (constructor.py:31-36; combined head: pass the same rate twice). */
 int mopo_ens_train_begin(mopo_ens* h, float lr, const float* weight_decays);
+/* The optimiser state lives on the handle from the first mopo_ens_train_begin on (the reference builds ONE AdamOptimizer in
+ * finalize, bnn.py:180, 252: moments and step count carry over between BNN.train() calls); mopo_ens_train_reset drops it.
+ * mopo_ens_train_set_deterministic(h, 1): the deterministic training loss of bnn.py:246-247 (MSE + decays). */
+int mopo_ens_train_reset(mopo_ens* h);
+int mopo_ens_train_set_deterministic(mopo_ens* h, int32_t deterministic);
 /* ceil(n_cols / batch_size) Adam updates (bnn.py:421-427): batch k trains net e on rows idx[e*ld_idx + k*bs .. +bs) of
  * inputs [n_rows, obs+act] (raw; the handle's scaler is applied) / targets [n_rows, obs+rew]; all device pointers.
  * loss_out: optional device float[ceil(n_cols/bs)], train_loss (bnn.py:242-244) of each batch before its update.
@@ -223,7 +232,7 @@ int mopo_ens_train_mse(mopo_ens* h, const float* inputs, const float* targets, c
  * reference's KeyError).  max/min_logvar are not part of the saved state, as in the reference. */
 int mopo_ens_train_snapshot(mopo_ens* h, int32_t net, void* stream);
 int mopo_ens_train_restore(mopo_ens* h, void* stream);
-/* Finish: rebuild the bf16 tensor-core images from the trained fp32 weights, free the optimiser state (synchronises). */
+/* Finish: rebuild the tensor-core operand images from the trained fp32 weights (synchronises); the optimiser state stays. */
 int mopo_ens_train_end(mopo_ens* h, void* stream);
 /* Device parameters -> HOST arrays in the reference layout (the inverse of mopo_ens_set_params; synchronises). */
 int mopo_ens_get_params(mopo_ens* h, float* const* weights, float* const* biases, float* var_w, float* var_b,

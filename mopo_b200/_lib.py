@@ -78,8 +78,11 @@ SYMBOLS = {
     'mopo_ens_param_image': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     'mopo_ens_refresh_images': (C.c_int, [C.c_void_p, C.c_void_p]),
     'mopo_ens_predict': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_ens_predict3d': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_train_begin': (C.c_int, [C.c_void_p, C.c_float, C.POINTER(C.c_float)]),
+    'mopo_ens_train_reset': (C.c_int, [C.c_void_p]),
+    'mopo_ens_train_set_deterministic': (C.c_int, [C.c_void_p, C.c_int32]),
     'mopo_ens_train_batches': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
                                          C.c_int32, C.c_void_p, C.c_void_p]),
     'mopo_ens_train_mse': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]),

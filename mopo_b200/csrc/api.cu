@@ -35,7 +35,9 @@ MOPO_API int mopo_ens_create(const mopo_ens_cfg* cfg, mopo_ens** out) {
   REQUIRE(cfg && out, MOPO_EINVAL, "mopo_ens_create: null argument");
   REQUIRE(cfg->obs_dim > 0 && cfg->act_dim > 0 && cfg->rew_dim >= 0 && cfg->hidden_dim > 0, MOPO_EINVAL,
           "mopo_ens_create: bad dims obs=%d act=%d rew=%d hidden=%d", cfg->obs_dim, cfg->act_dim, cfg->rew_dim, cfg->hidden_dim);
-  REQUIRE(cfg->n_hidden >= 1 && cfg->n_hidden < MOPO_MAX_LAYERS - 1, MOPO_EINVAL, "mopo_ens_create: n_hidden=%d unsupported", cfg->n_hidden);
+  REQUIRE(cfg->n_hidden >= 0 && cfg->n_hidden < MOPO_MAX_LAYERS - 1, MOPO_EINVAL, "mopo_ens_create: n_hidden=%d unsupported", cfg->n_hidden);
+  // n_hidden == 0 is construct_model(model_type='linear') (constructor.py:25-27): one FC whose output finalize() doubles (bnn.py:185)
+  REQUIRE(cfg->n_hidden >= 1 || !cfg->separate_mean_var, MOPO_EINVAL, "mopo_ens_create: a linear model has no hidden activation for a separate variance head");
   REQUIRE(cfg->num_networks >= 1 && cfg->num_networks <= MOPO_MAX_E, MOPO_EINVAL, "mopo_ens_create: num_networks=%d (max %d)", cfg->num_networks, MOPO_MAX_E);
   REQUIRE(cfg->num_elites >= 1 && cfg->num_elites <= cfg->num_networks, MOPO_EINVAL, "mopo_ens_create: num_elites=%d", cfg->num_elites);
   REQUIRE(cfg->obs_dim + cfg->rew_dim <= MOPO_MAX_D1, MOPO_EINVAL, "mopo_ens_create: obs_dim+rew_dim > %d", MOPO_MAX_D1);
@@ -114,7 +116,7 @@ MOPO_API int mopo_ens_set_params(mopo_ens* h, const float* const* weights, const
   }
   REQUIRE(weights[h->L] && biases[h->L], MOPO_EINVAL, "mopo_ens_set_params: head null");
   if (!h->cfg.separate_mean_var) {                       // bnn.py:185: last layer already 2*D1 wide
-    TRY(upload(h->W[h->L], weights[h->L], (size_t)E * H * h->HO, on_device, st));
+    TRY(upload(h->W[h->L], weights[h->L], (size_t)E * (h->L == 0 ? h->in : H) * h->HO, on_device, st));
     TRY(upload(h->b[h->L], biases[h->L], (size_t)E * h->HO, on_device, st));
   } else {                                               // bnn.py:657-667: both heads read the last hidden activation
     TRY(h->misc.reserve(sizeof(float) * ((size_t)E * H * D1 + (size_t)E * D1)));
@@ -317,6 +319,32 @@ MOPO_API int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mea
   TRY(forward(h, precision, h->xn.as<float>(), B, nullptr, mean, h->lv.as<float>(), B, st));
   TRY(launch_exp(h->lv.as<float>(), var, (int64_t)h->E * B * h->D1, st));
   return MOPO_OK;
+}
+
+// BNN.predict with 3-D inputs (bnn.py:541-545 -> fc.py:100-101): net e sees its own rows x[e].  x [E,B,in] device fp32 ->
+// mean / var [E,B,D1].  The scaler runs over all E*B rows, the contraction reads them with a per-net stride.
+MOPO_API int mopo_ens_predict3d(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, int precision, void* stream) {
+  REQUIRE(h && (B == 0 || (x && mean && var)), MOPO_EINVAL, "mopo_ens_predict3d: null argument");
+  REQUIRE(B >= 0 && (int64_t)h->E * B < (1ll << 31), MOPO_EINVAL, "mopo_ens_predict3d: B=%lld", (long long)B);
+  REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_predict3d: parameters not set");
+  if (B == 0) return MOPO_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  int path = ens_path(h, precision);
+  if (path == PATH_TC) path = tc3_supported(h) ? PATH_TC1 : PATH_NONE;     // the net-stationary kernel tiles ONE input for all nets
+  REQUIRE_PATH(path, precision);
+  const int64_t rows = (int64_t)h->E * B;
+  TRY(h->xn.reserve(sizeof(float) * rows * h->in));
+  TRY(launch_prep(x, x, h->mu, h->sigma, h->xn.as<float>(), rows, nullptr, h->in, 0, st));
+  TRY(h->lv.reserve(sizeof(float) * rows * h->D1));
+  if (path == PATH_FFMA) TRY(fp32_forward(h, h->xn.as<float>(), B, nullptr, mean, h->lv.as<float>(), B, st, B * (int64_t)h->in));
+  else {
+    Tc3In in = {h->xn.as<float>(), nullptr, h->in, 0, false, B};
+    TcOut o = {};
+    o.mean = mean; o.lv = h->lv.as<float>(); o.ldb = B;
+    TRY(tc3_launch(h, path == PATH_TC3 ? 3 : 1, in, B, nullptr, o, st));
+  }
+  return launch_exp(h->lv.as<float>(), var, rows * h->D1, st);
 }
 
 // One ensemble pass of a FakeEnv.step: scaler + forward.  On the tensor-core path a stochastic step with the

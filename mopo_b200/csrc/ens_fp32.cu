@@ -101,7 +101,7 @@ ens_layer_fp32(const float* __restrict__ A, int64_t strideA, int lda,
 }  // namespace
 
 int fp32_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
-                 int64_t ldb, cudaStream_t st) {
+                 int64_t ldb, cudaStream_t st, int64_t x_net_stride) {
   if (n_max == 0) return MOPO_OK;
   const int E = h->E, H = h->H;
   TRY(h->actA.reserve((size_t)E * n_max * H * sizeof(float)));
@@ -110,7 +110,7 @@ int fp32_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, fl
   const int64_t strideAct = n_max * (int64_t)H;
   dim3 blk(256);
   const float* A = xn;
-  int64_t strideA = 0;
+  int64_t strideA = x_net_stride;        // 0: every net reads the same rows (fc.py:98-99); else per-net inputs (fc.py:100-101)
   int lda = h->in, K = h->in;
   for (int l = 0; l < h->L; ++l) {
     dim3 grid((H + BN - 1) / BN, (unsigned)((n_max + BM - 1) / BM), E);

@@ -162,6 +162,7 @@ struct T3Args {
   const float *obs, *act;  // x = concat(obs [n, od], act [n, ad]) (fake_env.py:46); ad may be 0
   const float *mu, *sigma; // scaler (models/utils.py:96), or nullptr: x is already scaled
   int od, ad;
+  int64_t net_stride;      // rows between consecutive nets' inputs (3-D predict, fc.py:100-101), 0: shared rows
   const float* max_lv;     // [D1]
   const float* min_lv;     // [D1]
   HeadOut out;
@@ -540,8 +541,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
       const int t = u % nT;
       const int64_t row = 256 * (int64_t)t + (int64_t)rank * 128 + rr;
       const bool ok = row < n;
-      const float* po = a.obs + row * a.od;
-      const float* pa = a.act + row * a.ad;
+      const int64_t src_row = row + (int64_t)(u / nT) * a.net_stride;
+      const float* po = a.obs + src_row * a.od;
+      const float* pa = a.act + src_row * a.ad;
       for (int kc = 0; kc < kcs; ++kc) {
         float v[8];
 #pragma unroll
@@ -656,7 +658,7 @@ int tc3_launch(mopo_ens* h, int terms, const Tc3In& x, int64_t n_max, const int*
   T3Args a;
   a.s = make_s3(h->in, h->D1);
   a.img = reinterpret_cast<const uint8_t*>(h->tc3_img) + (terms == 3 ? 0 : (size_t)h->E * 2 * a.s.img_bytes());
-  a.obs = x.obs; a.act = x.act ? x.act : x.obs; a.od = x.od; a.ad = x.ad;
+  a.obs = x.obs; a.act = x.act ? x.act : x.obs; a.od = x.od; a.ad = x.ad; a.net_stride = x.net_stride;
   a.mu = x.scale ? h->mu : nullptr; a.sigma = x.scale ? h->sigma : nullptr;
   a.max_lv = h->max_lv; a.min_lv = h->min_lv;
   a.out.acc_scale = terms == 3 ? 1.0f / W_SCALE : 1.0f;

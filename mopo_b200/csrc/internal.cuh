@@ -111,8 +111,9 @@ struct mopo_pool {
 
 // ---- fp32 FFMA forward (ens_fp32.cu) --------------------------------------------------------
 // xn [n_max,in] -> mean [E,ldb,D1], lv [E,ldb,D1]; rows >= *d_n (if d_n) are skipped.
+// x_net_stride (floats): 0 = all nets read the same xn rows; n_max * in = per-net inputs xn [E, n_max, in].
 int fp32_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, float* mean, float* lv,
-                 int64_t ldb, cudaStream_t st);
+                 int64_t ldb, cudaStream_t st, int64_t x_net_stride = 0);
 
 // ---- tcgen05 bf16 forward (ens_tc.cu) ---------------------------------------------------------
 int tc_supported(const mopo_ens* h);
@@ -143,6 +144,7 @@ int tc3_build_images(mopo_ens* h, cudaStream_t st);
 struct Tc3In {
   const float *obs, *act; int od, ad;     // x = concat(obs [n, od], act [n, ad]); ad == 0: obs is the whole input row
   bool scale;                             // apply the handle's scaler (false: x is already scaled)
+  int64_t net_stride = 0;                 // rows between consecutive nets' inputs (0: every net reads the same rows)
 };
 int tc3_pick(mopo_ens* h, int32_t* sel, const int32_t* model_inds, int64_t n_max, const int* d_n, uint64_t seed,
              uint64_t step_id, const int32_t* origin, int64_t origin_base, cudaStream_t st);

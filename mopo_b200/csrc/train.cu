@@ -37,13 +37,22 @@ __global__ void gather_scale_kernel(const float* __restrict__ inputs, const floa
 // contributions to the loss and to d max_logvar / d min_logvar in part [3][E,n,D1] (reduced by head_reduce_kernel).
 __global__ void head_grad_kernel(const float* __restrict__ out, const float* __restrict__ tg,
                                  const float* __restrict__ max_lv, const float* __restrict__ min_lv, int E, int n, int D1,
-                                 float* __restrict__ dOut, float* __restrict__ part) {
+                                 float* __restrict__ dOut, float* __restrict__ part, int deterministic) {
   const int64_t tot = (int64_t)E * n * D1;
   const float c = 1.0f / ((float)n * (float)D1);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
     int d = (int)(i % D1);
     int64_t eb = i / D1;
     float mean = out[eb * 2 * D1 + d], raw = out[eb * 2 * D1 + D1 + d], t = tg[i];
+    if (deterministic) {                               // bnn.py:246-247: the loss is the plain MSE; the log-variance half gets no gradient
+      const float diff = mean - t;
+      dOut[eb * 2 * D1 + d] = 2.0f * diff * c;
+      dOut[eb * 2 * D1 + D1 + d] = 0.0f;
+      part[i] = diff * diff * c;
+      part[tot + i] = 0.0f;
+      part[2 * tot + i] = 0.0f;
+      continue;
+    }
     float mx = max_lv[d], mn = min_lv[d];
     float l1 = mx - softplus_f(mx - raw);
     float lv = mn + softplus_f(l1 - mn);
@@ -60,7 +69,7 @@ __global__ void head_grad_kernel(const float* __restrict__ out, const float* __r
 
 // blocks [0, D1): g_lv[d] = 0.01 + sum_{e,b} part1, g_lv[D1 + d] = -0.01 + sum part2;  blocks [D1, D1 + E): loss_e
 __global__ void __launch_bounds__(256) head_reduce_kernel(const float* __restrict__ part, int E, int n, int D1,
-                                                          float* __restrict__ g_lv, float* __restrict__ loss_e) {
+                                                          float* __restrict__ g_lv, float* __restrict__ loss_e, float bound_grad) {
   __shared__ float sh[8];
   const int64_t tot = (int64_t)E * n * D1;
   if ((int)blockIdx.x < D1) {
@@ -72,7 +81,7 @@ __global__ void __launch_bounds__(256) head_reduce_kernel(const float* __restric
     }
     a = block_sum(a, sh);
     b = block_sum(b, sh);
-    if (threadIdx.x == 0) { g_lv[d] = a + 0.01f; g_lv[D1 + d] = b - 0.01f; }
+    if (threadIdx.x == 0) { g_lv[d] = a + bound_grad; g_lv[D1 + d] = b - bound_grad; }
   } else {
     const int e = blockIdx.x - D1;
     float a = 0.f;
@@ -114,13 +123,13 @@ __global__ void __launch_bounds__(1024) sumsq_kernel(const float* __restrict__ w
 // total = sum(loss_e) + sum(decay terms) + 0.01 (sum max_lv - sum min_lv)
 __global__ void loss_total_kernel(const float* __restrict__ loss_e, int E, const float* __restrict__ decay_terms, int nd,
                                   const float* __restrict__ max_lv, const float* __restrict__ min_lv, int D1,
-                                  float* __restrict__ out) {
+                                  float* __restrict__ out, float bound_coeff) {
   float t = 0.f;
   for (int e = 0; e < E; ++e) t += loss_e[e];
   for (int i = 0; i < nd; ++i) t += decay_terms[i];
   float a = 0.f, b = 0.f;
   for (int d = 0; d < D1; ++d) { a += max_lv[d]; b += min_lv[d]; }
-  *out = t + 0.01f * a - 0.01f * b;
+  *out = t + bound_coeff * a - bound_coeff * b;
 }
 
 // Per-batch bookkeeping on the device: ctr = {next batch's first column, Adam step t, this batch's first column};
@@ -184,6 +193,7 @@ struct mopo_train {
   float *sW[MOPO_MAX_LAYERS] = {}, *sb[MOPO_MAX_LAYERS] = {};   // per-net snapshots (bnn.py:287-290)
   float *g_lv = nullptr, *m_lv = nullptr, *v_lv = nullptr;   // [2 D1]: max | min
   bool snap[MOPO_MAX_E] = {};
+  bool deterministic = false;  // bnn.py:246-247: MSE + decays instead of the Gaussian NLL + log-variance bounds
   DevBuf x, tg, Z, Hh, out, dA, dB, part, scal;
   cudaStream_t side = nullptr;   // weight / bias gradients run here, beside the data-gradient chain
   cudaEvent_t ev_fork[MOPO_MAX_LAYERS] = {}, ev_join = nullptr;
@@ -223,7 +233,18 @@ MOPO_API int mopo_ens_train_begin(mopo_ens* h, float lr, const float* weight_dec
   REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_train_begin: parameters not set");
   REQUIRE(lr > 0.f, MOPO_EINVAL, "mopo_ens_train_begin: lr=%g", (double)lr);
   CUDA_TRY(cudaSetDevice(h->cfg.device));
-  mopo_train_release(h);
+  // The optimiser lives as long as the model: the reference builds ONE tf.train.AdamOptimizer in finalize() (bnn.py:180, 252),
+  // so its moments and step count carry over from one BNN.train() call to the next (periodic model training,
+  // model_train_freq); only mopo_ens_train_reset / mopo_ens_destroy drop them.  A new run just clears the snapshot store.
+  if (h->tr) {
+    bool same = h->tr->lr == lr;
+    for (int l = 0; l < h->L + 2; ++l) same = same && h->tr->decay[l] == weight_decays[l];
+    h->tr->lr = lr;
+    for (int l = 0; l < h->L + 2; ++l) h->tr->decay[l] = weight_decays[l];
+    for (int e = 0; e < MOPO_MAX_E; ++e) h->tr->snap[e] = false;
+    if (!same && h->tr->graph) { cudaGraphExecDestroy(h->tr->graph); h->tr->graph = nullptr; }   // lr / decays are baked into the captured nodes
+    return MOPO_OK;
+  }
   mopo_train* tr = new mopo_train();
   h->tr = tr;
   tr->lr = lr;
@@ -305,9 +326,9 @@ static int train_one_batch(mopo_ens* h, const float* inputs, const float* target
   float* dOut = tr->dA.as<float>();
   MOPO_COUNT_LAUNCH;
   head_grad_kernel<<<grid1d((int64_t)rows * D1), 256, 0, st>>>(tr->out.as<float>(), tr->tg.as<float>(), h->max_lv, h->min_lv, E, n,
-                                                             D1, dOut, tr->part.as<float>());
+                                                             D1, dOut, tr->part.as<float>(), tr->deterministic ? 1 : 0);
   MOPO_COUNT_LAUNCH;
-  head_reduce_kernel<<<D1 + E, 256, 0, st>>>(tr->part.as<float>(), E, n, D1, tr->g_lv, scal);
+  head_reduce_kernel<<<D1 + E, 256, 0, st>>>(tr->part.as<float>(), E, n, D1, tr->g_lv, scal, tr->deterministic ? 0.0f : 0.01f);
   if (loss_out) {
     for (int l = 0; l < L; ++l) {
       MOPO_COUNT_LAUNCH;
@@ -318,7 +339,7 @@ static int train_one_batch(mopo_ens* h, const float* inputs, const float* target
     MOPO_COUNT_LAUNCH;
     sumsq_kernel<<<1, 1024, 0, st>>>(h->W[L], (int64_t)E * H, HO, D1, HO, 0.5f * tr->decay[L + 1], scal + E + L + 1);
     MOPO_COUNT_LAUNCH;
-    loss_total_kernel<<<1, 1, 0, st>>>(scal, E, scal + E, L + 2, h->max_lv, h->min_lv, D1, loss_out);
+    loss_total_kernel<<<1, 1, 0, st>>>(scal, E, scal + E, L + 2, h->max_lv, h->min_lv, D1, loss_out, tr->deterministic ? 0.0f : 0.01f);
   }
   // backward.  dZ_l feeds three independent consumers: gW_l = In_l^T dZ_l, gb_l = colsum(dZ_l) (side stream) and the
   // chain dZ_{l-1} = (dZ_l W_l^T) .* swish'(Z_{l-1}) (main stream); every dZ_l has its own buffer so the branches overlap.
@@ -465,7 +486,20 @@ MOPO_API int mopo_ens_train_end(mopo_ens* h, void* stream) {
   if (tc_supported(h)) TRY(tc_build_images(h, st));
   if (tc3_supported(h)) TRY(tc3_build_images(h, st));
   CUDA_TRY(cudaStreamSynchronize(st));
+  return MOPO_OK;             // the optimiser state stays on the handle (see mopo_ens_train_begin)
+}
+
+MOPO_API int mopo_ens_train_reset(mopo_ens* h) {
+  REQUIRE(h, MOPO_EINVAL, "mopo_ens_train_reset: null argument");
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
   mopo_train_release(h);
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_ens_train_set_deterministic(mopo_ens* h, int32_t deterministic) {
+  REQUIRE(h && h->tr, MOPO_ESTATE, "mopo_ens_train_set_deterministic: call mopo_ens_train_begin first");
+  if (h->tr->deterministic != (deterministic != 0) && h->tr->graph) { cudaGraphExecDestroy(h->tr->graph); h->tr->graph = nullptr; }
+  h->tr->deterministic = deterministic != 0;
   return MOPO_OK;
 }
 

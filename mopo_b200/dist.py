@@ -21,7 +21,10 @@ def init_from_env(backend=None):
             backend = 'nccl' if torch.cuda.is_available() else 'gloo'
         if backend == 'nccl':
             torch.cuda.set_device(local)
-        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+        # a long timeout: under torch.distributed only rank 0 trains the ensemble while the others wait in broadcast_params, and a
+        # full-dataset BNN.train (max_epochs=None over 1-2 M rows) outlasts NCCL's default 10-minute collective timeout
+        import datetime
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, timeout=datetime.timedelta(hours=6))
     return rank, world, local
 
 

@@ -122,9 +122,9 @@ class BNN:
         if self.finalized:
             raise RuntimeError("Can only finalize a network once.")
         hidden = self.layers[:-1]
-        if not hidden or any(l.activation != 'swish' for l in hidden) or len({l.output_dim for l in hidden}) != 1:
-            raise NotImplementedError("mopo_b200 builds the construct_model 'mlp' architecture only "
-                                      "(equal-width swish hidden layers + linear head)")
+        if any(l.activation != 'swish' for l in hidden) or len({l.output_dim for l in hidden}) > 1 or self.layers[-1].activation is not None:
+            raise NotImplementedError("mopo_b200 builds the construct_model architectures only: 'mlp' (equal-width swish "
+                                      "hidden layers + linear head) and 'linear' (the head alone)")
         if not self.separate_mean_var:                                  # bnn.py:183-189
             self.layers[-1].set_output_dim(2 * self.layers[-1].get_output_dim())
             self.end_act_name = self.layers[-1].get_activation(as_func=False)
@@ -136,7 +136,7 @@ class BNN:
                 raise NotImplementedError("separate_mean_var expects one linear var head on the last hidden activation")
         self.in_dim = self.layers[0].get_input_dim()
         self.out_dim = d1
-        self.hidden_dim = hidden[0].output_dim
+        self.hidden_dim = hidden[0].output_dim if hidden else 1          # 'linear': no hidden layer (constructor.py:25-27)
         rng = np.random.RandomState(self.seed)
         self.scaler = TensorStandardScaler(self.in_dim)
         self.max_logvar = np.ones([1, d1], np.float32) / 2.                # bnn.py:196-199
@@ -239,17 +239,18 @@ class BNN:
     def predict(self, inputs, factored=False, *args, **kwargs):
         is_np = not torch.is_tensor(inputs)
         x = torch.as_tensor(inputs)
-        if x.dim() != 2:
-            raise NotImplementedError("3-D (per-net) inputs are the training path (bnn.py:541-545); not on the rollout hot path")
-        if x.shape[1] != self.in_dim:
+        if x.dim() not in (2, 3) or (x.dim() == 3 and x.shape[0] != self.num_nets) or x.shape[-1] != self.in_dim:
             raise ValueError("Invalid input dimension.")                   # fc.py:103
         x = x.to(device=self.device, dtype=torch.float32).contiguous()
-        B = x.shape[0]
+        B = x.shape[-2]
         mean = torch.empty((self.num_nets, B, self.out_dim), dtype=torch.float32, device=self.device)
         var = torch.empty_like(mean)
         self._ensure_handle()
-        _lib.check(_lib.load().mopo_ens_predict(self._handle, x.data_ptr(), B, mean.data_ptr(), var.data_ptr(),
-                                               kwargs.get('precision', self.precision), _lib.stream_ptr(self.device)))
+        lib, prec = _lib.load(), kwargs.get('precision', self.precision)
+        if x.dim() == 3:                                                   # bnn.py:541-545: net e sees inputs[e]; always factored
+            _lib.check(lib.mopo_ens_predict3d(self._handle, x.data_ptr(), B, mean.data_ptr(), var.data_ptr(), prec, _lib.stream_ptr(self.device)))
+            return (mean.cpu().numpy(), var.cpu().numpy()) if is_np else (mean, var)
+        _lib.check(lib.mopo_ens_predict(self._handle, x.data_ptr(), B, mean.data_ptr(), var.data_ptr(), prec, _lib.stream_ptr(self.device)))
         if not factored:                                                   # bnn.py:261-263
             m = mean.mean(0)
             mean, var = m, var.mean(0) + (mean - m).square().mean(0)
@@ -348,8 +349,8 @@ class BNN:
         otherwise they come from a device generator seeded with the model's seed."""
         import itertools, time
         from collections import OrderedDict
-        if self.deterministic:
-            raise NotImplementedError("deterministic=True training loss (bnn.py:246-247) is not built; MOPO trains the probabilistic model")
+        if len(self.layers) < 2:
+            raise NotImplementedError("training the 'linear' model on the device is not built (predict / FakeEnv.step are)")
         self._max_epochs_since_update = max_epochs_since_update
         self._start_train()
         break_train = False
@@ -392,7 +393,11 @@ class BNN:
         with torch.cuda.stream(self._train_stream):
             st = _lib.stream_ptr(dev)
             self._ensure_handle()
+            for t_ in (inputs, targets, holdout_inputs, holdout_targets, idxs):    # allocated on the caller's stream, used on this one
+                t_.record_stream(self._train_stream)
+            idxs = idxs.clone()                                            # a buffer this call owns (shuffled in place every epoch)
             _lib.check(lib.mopo_ens_train_begin(self._handle, 1e-3 if not hasattr(self, '_lr') else self._lr, self._weight_decays()))
+            _lib.check(lib.mopo_ens_train_set_deterministic(self._handle, int(bool(self.deterministic))))     # bnn.py:242-247
             mse_dev = torch.empty(2 * self.num_nets, dtype=torch.float32, device=dev)
             n_cols = idxs.shape[1]
             t0 = time.time()
@@ -402,7 +407,7 @@ class BNN:
                     _lib.check(lib.mopo_ens_train_batches(self._handle, inputs.data_ptr(), targets.data_ptr(), N, idxs.data_ptr(),
                                                           n_cols, n_cols, batch_size, None, st))        # bnn.py:421-427
                     grad_updates += int(np.ceil(n_cols / batch_size))
-                    idxs = shuffle_rows(idxs)                                  # bnn.py:429
+                    idxs.copy_(shuffle_rows(idxs))                             # bnn.py:429; in place: the captured graph is keyed on this buffer
                     if not hide_progress:
                         n_log = min(max_logging, n_cols)
                         _lib.check(lib.mopo_ens_train_mse(self._handle, inputs.data_ptr(), targets.data_ptr(), idxs.data_ptr(),

@@ -22,7 +22,8 @@ def construct_model(obs_dim=11, act_dim=3, rew_dim=1, hidden_dim=200, num_networ
     if model_type == 'identity':                                       # constructor.py:23-24
         return
     elif model_type == 'linear':
-        raise NotImplementedError("model_type='linear' (constructor.py:25-27) is not on the D4RL hot path")
+        print('[ BNN ] Training linear model')                          # constructor.py:25-27
+        model.add(FC(obs_dim + rew_dim, input_dim=obs_dim + act_dim, weight_decay=0.000025))
     elif model_type == 'mlp':                                          # constructor.py:28-36
         print('[ BNN ] Training non-linear model | Obs: {} | Act: {} | Rew: {}'.format(obs_dim, act_dim, rew_dim))
         model.add(FC(hidden_dim, input_dim=obs_dim + act_dim, activation="swish", weight_decay=0.000025))

@@ -39,7 +39,7 @@ def init_params(obs_dim, act_dim, rew_dim=1, hidden_dim=200, num_networks=7, n_h
         weights.append(_trunc_normal(rng, (E, dims[i], dims[i + 1]), 1.0 / (2.0 * np.sqrt(dims[i]))))
         biases.append((rng.standard_normal((E, 1, dims[i + 1])) * bias_std).astype(np.float32))
     out_last = D1 if separate_mean_var else 2 * D1
-    weights.append(_trunc_normal(rng, (E, hidden_dim, out_last), 1.0 / (2.0 * np.sqrt(hidden_dim))))
+    weights.append(_trunc_normal(rng, (E, dims[-1], out_last), 1.0 / (2.0 * np.sqrt(dims[-1]))))
     biases.append((rng.standard_normal((E, 1, out_last)) * bias_std).astype(np.float32))
     p = {
         'obs_dim': obs_dim, 'act_dim': act_dim, 'rew_dim': rew_dim, 'hidden_dim': hidden_dim,

@@ -76,19 +76,25 @@ def mse(params, v, x, t):
     return ((mean - t) ** 2).mean(-1).mean(-1)
 
 
-def loss(params, v, x, t, decays=DECAYS_MLP, decay_var=DECAY_VAR):
-    """bnn.py:242-245 train_loss (scalar)."""
+def loss(params, v, x, t, decays=DECAYS_MLP, decay_var=DECAY_VAR, deterministic=False):
+    """bnn.py:242-245 train_loss (scalar); deterministic (bnn.py:246-247): sum over nets of the plain MSE + the decays (TF
+    minimises the [E] loss vector, i.e. its sum), no log-variance bound terms."""
     mean, lv, _ = _forward(v, scale(params, x))
-    per_net = ((mean - t) ** 2 * np.exp(-lv)).mean(-1).mean(-1) + lv.mean(-1).mean(-1)
+    if deterministic:
+        per_net = ((mean - t) ** 2).mean(-1).mean(-1)
+    else:
+        per_net = ((mean - t) ** 2 * np.exp(-lv)).mean(-1).mean(-1) + lv.mean(-1).mean(-1)
     tot = per_net.sum()
     for w, d in zip(v['weights'], decays):
         tot += d * 0.5 * (w ** 2).sum()
     if 'var_weights' in v:
         tot += decay_var * 0.5 * (v['var_weights'] ** 2).sum()
+    if deterministic:
+        return tot
     return tot + 0.01 * v['max_logvar'].sum() - 0.01 * v['min_logvar'].sum()
 
 
-def grads(params, v, x, t, decays=DECAYS_MLP, decay_var=DECAY_VAR):
+def grads(params, v, x, t, decays=DECAYS_MLP, decay_var=DECAY_VAR, deterministic=False):
     """Analytic gradient of `loss` w.r.t. every entry of `v` (same dict structure)."""
     xn = scale(params, x)
     mean, lv, (hs, zs, raw, l1) = _forward(v, xn)
@@ -104,6 +110,10 @@ def grads(params, v, x, t, decays=DECAYS_MLP, decay_var=DECAY_VAR):
     g = {'weights': [None] * (L + 1), 'biases': [None] * (L + 1)}
     g['max_logvar'] = (d_lv * s_min * (1.0 - s_max)).sum((0, 1)).reshape(1, -1) + 0.01
     g['min_logvar'] = (d_lv * (1.0 - s_min)).sum((0, 1)).reshape(1, -1) - 0.01
+    if deterministic:                                            # the loss does not see the log-variance at all
+        d_mean = 2.0 * (mean - t) * c
+        d_raw = np.zeros_like(d_raw)
+        g['max_logvar'], g['min_logvar'] = np.zeros_like(g['max_logvar']), np.zeros_like(g['min_logvar'])
     hT = np.swapaxes(hs[-1], 1, 2)
     if 'var_weights' in v:
         g['weights'][L] = hT @ d_mean + decays[L] * v['weights'][L]
@@ -150,15 +160,16 @@ def adam_step(v, g, st, lr=1e-3):
         pc[pk] = pc[pk] - lr_t * mc[mk] / (np.sqrt(vc[vk]) + EPS)
 
 
-def train_batches(params, v, st, inputs, targets, idxs, batch_size, lr=1e-3, decays=DECAYS_MLP, decay_var=DECAY_VAR):
+def train_batches(params, v, st, inputs, targets, idxs, batch_size, lr=1e-3, decays=DECAYS_MLP, decay_var=DECAY_VAR,
+                  deterministic=False):
     """One epoch's inner loop (bnn.py:421-427): batch k trains net e on rows idxs[e, k*bs:(k+1)*bs].  Returns the
     train_loss of every batch evaluated BEFORE its update."""
     losses = []
     for k in range(int(np.ceil(idxs.shape[-1] / batch_size))):
         bi = idxs[:, k * batch_size:(k + 1) * batch_size]
         x, t = np.asarray(inputs, np.float64)[bi], np.asarray(targets, np.float64)[bi]
-        losses.append(loss(params, v, x, t, decays, decay_var))
-        adam_step(v, grads(params, v, x, t, decays, decay_var), st, lr)
+        losses.append(loss(params, v, x, t, decays, decay_var, deterministic))
+        adam_step(v, grads(params, v, x, t, decays, decay_var, deterministic), st, lr)
     return np.array(losses)
 
 

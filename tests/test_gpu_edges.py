@@ -90,3 +90,26 @@ def test_errors_follow_the_reference_exception_types():
         small = construct_model(obs_dim=17, act_dim=6, hidden_dim=64, separate_mean_var=True, device=0, precision=_lib.PREC_BF16)
         small._model_inds = [0, 1, 2, 3, 4]
         FakeEnv(small, static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True).step(obs, act)
+
+
+def test_identity_model_type_bypasses_the_model():
+    """model_type == 'identity' (mopo.py:740-744): next_obs = obs, zero rewards, terminals = identity_terminal; the pool
+    appends, steps_added and the early break are the reference loop's."""
+    from mopo_b200.algorithms.mopo import ModelRollout
+    from mopo_b200.replay_pools import SimpleReplayPool
+    rng = np.random.RandomState(0)
+    obs = rng.standard_normal((50, 17)).astype(np.float32)
+    acts = [np.tanh(rng.standard_normal((50, 6))).astype(np.float32) for _ in range(3)]
+    for ident_term, want_steps in ((0, [50, 50, 50]), (1, [50])):
+        ro = ModelRollout(None, SimpleReplayPool(17, 6, 10), rollout_batch_size=50, rollout_schedule=(0, 1, 3, 3),
+                          model_type='identity', identity_terminal=ident_term)
+        ro._set_rollout_length()
+        ro._model_pool = SimpleReplayPool(17, 6, 200)
+        stats = ro._rollout_model(50, start_obs=obs, actions=acts, quiet=True)
+        assert ro._last_steps_added == want_steps and stats['mean_rollout_length'] == len(want_steps)
+        f = {k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()}
+        n = 50 * len(want_steps)
+        assert ro._model_pool.size == n
+        assert np.array_equal(f['next_observations'][:n], f['observations'][:n]) and np.array_equal(f['observations'][:50], obs)
+        assert not f['rewards'][:n].any() and f['terminals'][:n].all() == bool(ident_term)
+        assert np.array_equal(f['actions'][:50], acts[0])

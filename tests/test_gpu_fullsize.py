@@ -100,10 +100,13 @@ def test_fullsize_halfcheetah_rollout_properties(precision_name):
             assert np.abs(full['next_observations'][rows] - want_no).max() < 0.02 * scale
 
 
-def test_fullsize_hopper_termination_and_compaction():
-    """Terminating env at full size: the survivors of step i are exactly the rows of step i+1, in order, and the pool
-    holds sum(steps_added) rows; fp32 path so that the termination masks are the parity-grade ones."""
+@pytest.mark.parametrize('precision_name', ['fp32', 'bf16'])
+def test_fullsize_hopper_termination_and_compaction(precision_name):
+    """Terminating env at full size on both tensor-core paths (fp32-accurate: compaction + elite picks; bf16: compaction that
+    also rewrites the next step's input tiles): the survivors of step i are exactly the rows of step i+1, in order, the pool
+    holds sum(steps_added) rows, and every stored termination flag is hopper.py:9-18 of the stored next_obs."""
     from mopo_b200 import _lib
+    prec = {'bf16': _lib.PREC_BF16, 'fp32': _lib.PREC_FP32}[precision_name]
     p, obs, _ = ens.synthetic_case('hopper', B, seed=3)
     p['max_logvar'][:] = -9.0                                   # low-noise ensemble: a fraction of the rows dies at every step
     p['weights'][-1] = p['weights'][-1] * 0.02
@@ -113,7 +116,7 @@ def test_fullsize_hopper_termination_and_compaction():
     obs[:, 1] = r0.uniform(-0.25, 0.25, B).astype(np.float32)
     rng = np.random.RandomState(4)
     acts = [np.tanh(rng.standard_normal((B, 3))).astype(np.float32) for _ in range(H)]
-    m = _model(p, _lib.PREC_FP32)
+    m = _model(p, prec)
     full, steps, pool = _run(m, 'hopper', obs, acts, 0, B, max_size=B * H)
     assert steps[0] == B and all(steps[i + 1] <= steps[i] for i in range(len(steps) - 1)) and steps[1] < B
     assert pool.size == sum(steps)
@@ -129,3 +132,56 @@ def test_fullsize_hopper_termination_and_compaction():
                                                      full['next_observations'][off:off + n])[:, 0]
         assert np.array_equal(term, want)
         off += n
+
+
+@pytest.mark.parametrize('precision_name', ['fp32', 'bf16'])
+def test_fullsize_walker2d_single_step(precision_name):
+    """BASELINE.json config 3: Walker2d-shaped, B = 50 000, h = 1, both precisions.  Pool accounting, the stored termination
+    flags against walker2d.py:9-17 of the stored next_obs (bit-exact on either path), and a 300-row subset against the oracle
+    step fed with the same Philox draws: fp32-accurate path rtol 1e-3 with identical termination flags; bf16 path within 2 %
+    of the output scale, termination flips only where the oracle's height / angle sits within that error of a threshold."""
+    import torch
+    import mopo_b200.static as static
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    prec = {'bf16': _lib.PREC_BF16, 'fp32': _lib.PREC_FP32}[precision_name]
+    p, obs, _ = ens.synthetic_case('walker2d', B, seed=5)
+    p['max_logvar'][:] = -6.0                                    # gentle ensemble: next_obs stays near obs, so the four
+    p['weights'][-1] = p['weights'][-1] * 0.02                   # thresholds cut through the batch instead of ending every row
+    p['biases'][-1] = p['biases'][-1] * 0.0
+    r0 = np.random.RandomState(11)
+    obs[:, 0] = r0.uniform(0.7, 2.1, B).astype(np.float32)          # heights and angles around all four thresholds
+    obs[:, 1] = r0.uniform(-1.1, 1.1, B).astype(np.float32)
+    act = np.tanh(np.random.RandomState(6).standard_normal((B, 6))).astype(np.float32)
+    m = _model(p, prec)
+    env = FakeEnv(m, static['walker2d'], penalty_coeff=1.0, penalty_learned_var=True)
+    ro = ModelRollout(env, SimpleReplayPool(17, 6, 10), rollout_batch_size=B, rollout_schedule=(0, 1, 1, 1), seed=77)
+    ro._set_rollout_length()
+    ro._model_pool = SimpleReplayPool(17, 6, B)
+    ro._rollout_model(B, start_obs=obs, actions=[act], quiet=True)
+    torch.cuda.synchronize()
+    full = {k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()}
+    assert ro._last_steps_added == [B] and ro._model_pool.size == B
+    assert np.array_equal(full['observations'], obs) and np.array_equal(full['actions'], act)
+    want_term = OracleStatic('walker2d').termination_fn(full['observations'], full['actions'], full['next_observations'])
+    assert np.array_equal(full['terminals'], want_term)
+    assert 0.05 < full['terminals'].mean() < 0.95
+    S = np.sort(np.random.RandomState(9).choice(B, 300, replace=False))
+    o_env = OracleEnv(ens.OracleModel(p), OracleStatic('walker2d'), penalty_coeff=1.0, penalty_learned_var=True)
+    elites = np.array([0, 1, 2, 3, 4])
+    z = philox.normals(S, 0, 77, 18)
+    r_nobs, r_rew, r_term, _ = o_env.step(obs[S], act[S], noise=np.tile(z[None], [7, 1, 1]), model_inds=elites[philox.elite_index(S, 0, 77, 5)])
+    got_no, got_r, got_t = full['next_observations'][S], full['rewards'][S], full['terminals'][S]
+    flips = np.flatnonzero(got_t.ravel() != r_term.ravel())
+    if precision_name == 'fp32':
+        np.testing.assert_allclose(got_no, r_nobs, rtol=1e-3, atol=2e-4)
+        np.testing.assert_allclose(got_r, r_rew, rtol=1e-3, atol=2e-4)
+        assert flips.size == 0
+    else:
+        tol = 0.02 * np.abs(r_nobs).max()
+        assert np.abs(got_no - r_nobs).max() < tol and np.abs(got_r - r_rew).max() < 0.02 * max(np.abs(r_rew).max(), 1.0)
+        for j in flips:                                       # reported, and bounded: only rows within the bf16 error of a threshold
+            assert any(abs(r_nobs[j, c] - v) < tol for c, v in ((0, 0.8), (0, 2.0), (1, -1.0), (1, 1.0))), (j, r_nobs[j, :2])
+        print('bf16 walker2d termination flips on the 300-row subset: %d' % flips.size)

@@ -70,6 +70,47 @@ def test_predict_matches_reference_bnn_fixture(path):
     mm, vv = m.predict(x)
     np.testing.assert_allclose(mm, g['mean'], rtol=RTOL, atol=ATOL)
     np.testing.assert_allclose(vv, g['var'], rtol=RTOL)
+    # 3-D inputs: net e sees x3[e] (bnn.py:541-545, fc.py:100-101) -- on the fp32-accurate tensor-core path and on the FFMA checker
+    from mopo_b200 import _lib
+    for prec in (_lib.PREC_FP32, _lib.PREC_FP32_REF):
+        m3, v3 = m.predict(g['x3'], factored=True, precision=prec)
+        np.testing.assert_allclose(m3, g['mean3'], rtol=RTOL, atol=ATOL)
+        np.testing.assert_allclose(v3, g['var3'], rtol=RTOL)
+    with pytest.raises(ValueError):
+        m.predict(g['x3'][:3])                          # leading dimension != ensemble size (fc.py:100-103)
+
+
+def test_linear_model_predict_and_step():
+    """construct_model(model_type='linear') (constructor.py:25-27): one FC whose output finalize() doubles into [mean | logvar]
+    (bnn.py:185); predict and FakeEnv.step against the oracle."""
+    from mopo_b200.models.constructor import construct_model
+    from mopo_b200.models.fake_env import FakeEnv
+    import mopo_b200.static as static
+    od, ad, B = 11, 3, 257
+    p = ens.init_params(od, ad, n_hidden=0, separate_mean_var=False, seed=4, bias_std=0.1)
+    rng = np.random.RandomState(5)
+    obs = (rng.standard_normal((B, od)) * 0.05).astype(np.float32); obs[:, 0] += 1.25
+    act = np.tanh(rng.standard_normal((B, ad))).astype(np.float32)
+    ens.fit_scaler(p, np.concatenate([obs, act], -1))
+    m = construct_model(obs_dim=od, act_dim=ad, model_type='linear', separate_mean_var=False, name='lin', device=0)
+    assert len(m.layers) == 1 and m.layers[0].get_output_dim() == 2 * (od + 1)
+    m.set_params(p['weights'], p['biases'], None, None, p['mu'], p['sigma'], p['max_logvar'], p['min_logvar'])
+    m._model_inds = [0, 1, 2, 3, 4]
+    x = np.concatenate([obs, act], -1)
+    mean, var = m.predict(x, factored=True)
+    m64, v64 = ens.forward(p, x, np.float64)
+    np.testing.assert_allclose(mean, m64, rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(var, v64, rtol=RTOL)
+    noise = rng.standard_normal((7, B, od + 1))
+    inds = rng.choice(5, size=B)
+    o_env = OracleEnv(ens.OracleModel(p), OracleStatic('hopper'), penalty_coeff=1.0, penalty_learned_var=True)
+    r_nobs, r_rew, r_term, r_info = o_env.step(obs, act, noise=noise, model_inds=inds)
+    nobs, rew, term, info = FakeEnv(m, static['hopper'], penalty_coeff=1.0, penalty_learned_var=True).step(obs, act, noise=noise, model_inds=inds)
+    np.testing.assert_allclose(nobs, r_nobs, rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(rew, r_rew, rtol=RTOL, atol=ATOL)
+    assert np.array_equal(term, r_term)
+    with pytest.raises(RuntimeError):                   # bnn.py:175-176: a separate variance head needs var layers, 'linear' adds none
+        construct_model(obs_dim=od, act_dim=ad, model_type='linear', separate_mean_var=True, name='lin2', device=0)
 
 
 def test_kat_zero_weights_device():

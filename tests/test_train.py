@@ -162,6 +162,46 @@ def test_train_batches_match_oracle(shape, sep):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize('sep', [True, False])
+def test_train_deterministic_loss_and_persistent_adam_state(sep):
+    """(1) deterministic=True (bnn.py:246-247): the loss is MSE + decays, the log-variance half and max/min_logvar get no
+    gradient.  (2) The optimiser belongs to the model, not to a train() call (one AdamOptimizer built in finalize, bnn.py:180,
+    252): a second begin/batches/end run continues with the first run's moments and step count -- the oracle is run as ONE
+    sequence over both runs' batches."""
+    import torch
+    from mopo_b200 import _lib
+    od, ad, H, E, bs, n_cols = 11, 3, 200, 7, 64, 192
+    p, inputs, targets, rng = _problem(od, ad, H, E, sep, 500, seed=3)
+    idx = rng.randint(500, size=(E, 2 * n_cols)).astype(np.int32)
+    lib, h = _handle(p)
+    d_in, d_tg = torch.as_tensor(inputs).cuda(), torch.as_tensor(targets).cuda()
+    nb = n_cols // bs
+    got_loss = []
+    for run, det in ((0, 1), (1, 0)):                       # a deterministic run, then a probabilistic one on the same optimiser
+        d_idx = torch.as_tensor(np.ascontiguousarray(idx[:, run * n_cols:(run + 1) * n_cols])).cuda()
+        d_loss = torch.zeros(nb, device='cuda')
+        _lib.check(lib.mopo_ens_train_begin(h, 1e-3, _decays(p)))
+        _lib.check(lib.mopo_ens_train_set_deterministic(h, det))
+        _lib.check(lib.mopo_ens_train_batches(h, d_in.data_ptr(), d_tg.data_ptr(), 500, d_idx.data_ptr(), n_cols, n_cols, bs,
+                                              d_loss.data_ptr(), None))
+        _lib.check(lib.mopo_ens_train_end(h, None))
+        got_loss.append(d_loss.cpu().numpy())
+    got = _get_params(lib, h, p)
+    v = otr.trainable(p)
+    mx0, mn0 = v['max_logvar'].copy(), v['min_logvar'].copy()
+    st = otr.adam_init(v)
+    want0 = otr.train_batches(p, v, st, inputs, targets, idx[:, :n_cols], bs, deterministic=True)
+    assert np.array_equal(v['max_logvar'], mx0) and np.array_equal(v['min_logvar'], mn0)     # untouched by the deterministic loss
+    want1 = otr.train_batches(p, v, st, inputs, targets, idx[:, n_cols:], bs)                  # same Adam state: t continues at nb + 1
+    np.testing.assert_allclose(got_loss[0], want0, rtol=2e-4)
+    np.testing.assert_allclose(got_loss[1], want1, rtol=2e-4)
+    _compare_params(got, v, 2e-5 * 2 * nb)
+    # a fresh optimiser gives different parameters: the state did carry over
+    _lib.check(lib.mopo_ens_train_reset(h))
+    lib.mopo_ens_destroy(h)
+
+
+@pytest.mark.gpu
 def test_train_mse_snapshot_restore():
     import torch
     from mopo_b200 import _lib
