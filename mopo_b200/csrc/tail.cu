@@ -181,8 +181,10 @@ constexpr int TQ = 4;
 // sqrt.approx (MUFU.RSQ based, ~1 ulp): the bf16 tensor-core path's variances carry ~3 significant digits
 __device__ __forceinline__ float sqrt_fast(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 // contiguous span copy, 16 bytes per thread when both ends are 16-byte aligned (n floats, NT threads)
+// __noinline__: ten call sites x (vector path + scalar path) inlined made the fused tail 100 KB of code that every CTA runs
+// once -- a fifth of its stall samples were instruction fetch (profiles/r01_step_tail_final_ncu_stalls.txt)
 template <int NT>
-__device__ __forceinline__ void span_copy(float* __restrict__ dst, const float* __restrict__ src, int n, int tid) {
+__device__ __noinline__ void span_copy(float* __restrict__ dst, const float* __restrict__ src, int n, int tid) {
   if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0) {
     const int n4 = n >> 2;
     for (int i = tid; i < n4; i += NT) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i];
