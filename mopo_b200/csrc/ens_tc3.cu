@@ -18,23 +18,26 @@
 //     from the L2-resident image, refilled as soon as tcgen05.commit reports the layer's MMAs retired).
 //   * Tensor memory holds the activations for the whole unit: two 208-column buffers ping-pong.  Layer j reads its A
 //     operand (TS-form MMA) from one buffer and accumulates into the other; the epilogue then converts the accumulator
-//     IN PLACE: the 16 fp32 columns of feature group g become [8 columns packed bf16x2 hi | 8 columns packed lo] of the
+//     IN PLACE: the 16 fp32 columns of feature group g become [8 columns packed f16x2 hi | 8 columns packed lo] of the
 //     same features, which is exactly the TS-form A operand of the next layer's K step g.  Column map (per CTA, 128 lanes):
 //         [  0,208) buffer 0 : D of layers 0, 2   ->  A of layers 1, 3
 //         [208,416) buffer 1 : D of layers 1, 3   ->  A of layer 2, head
 //         [416,416+NHEAD)    : head accumulator [mean | raw logvar] (owned by the head warps from h_full to h_done)
-//   * The N = 208 hidden width is issued as N = 112 + N = 96 with separate commits, and a layer's K loop runs over the
-//     first half's features first: the epilogue of half 1 runs under the MMAs of half 2, the epilogue of half 2 under
-//     the next layer's first 7 K groups (which only need half-1 features).  With one tile in flight the tensor pipe
-//     still only waits at the first and last layer of a unit.
+//   * The N = 208 hidden width is issued as N = 112 + N = 96 with separate commits, and the 13 feature groups are dealt to
+//     three epilogue warpgroups in five ROUNDS (groups 0-2 | 3-5 | 6 | 7-9 | 10-12); round r signals r_ready[r] and the MMA
+//     issuer follows the epilogue through the next layer's K loop round by round: half 1's epilogue runs under half 2's
+//     MMAs, the next layer's first K groups under half 2's epilogue.
 //   * Layer 0's A operand comes from shared memory (SS form): the head warps read the raw fp32 obs / act rows, apply the
 //     scaler (models/utils.py:96, true division as the reference), split and write the K-panel tile of the NEXT unit
-//     while the current one computes -- no tiling pass, no HBM round trip.
+//     while the current one computes -- no tiling pass, no HBM round trip.  Layer 0 of unit u+1 is issued ahead of unit
+//     u's head MMA (it only needs buffer 0), on its own barrier set.
+//   * Ring loads per unit: W1, W2, W3, [head | W0 of the next unit] -- an even count keeps every load a layer ahead.
 //   * bias rides in the constant-1 K column (feature 200 of every hidden activation, k = in of the input tile).
 //
-// Warp roles (576 threads): warps 0-11 epilogue (three per SM sub-partition, each owns a 32-lane TMEM quadrant and a share
-// of each half's feature groups), warp 12 of the leader CTA issues every MMA (elect.sync), warp 13 streams weights,
+// Warp roles (576 threads): warps 0-11 epilogue (three per SM sub-partition, each owns a 32-lane TMEM quadrant and one
+// feature group per round), warp 12 of the leader CTA issues every MMA (elect.sync), warp 13 streams weights,
 // warps 14-17 produce input tiles and run the head stage (shared with ens_tc.cu: tc_head.cuh).
+// Measurements, what was tried and what limits it: DESIGN.md 4.1b.
 #include "internal.cuh"
 #include "tc_common.cuh"
 #include "tc_head.cuh"

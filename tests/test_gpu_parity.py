@@ -80,6 +80,23 @@ def test_predict_matches_reference_bnn_fixture(path):
         m.predict(g['x3'][:3])                          # leading dimension != ensemble size (fc.py:100-103)
 
 
+@pytest.mark.parametrize('E,B', [(1, 300), (3, 1000), (12, 257)])
+def test_predict_other_ensemble_sizes_on_the_tensor_core_path(E, B):
+    """(net, tile) units are range-partitioned over the CTA pairs for any ensemble size: 1 net (fewer units than pairs), 3, 12."""
+    from mopo_b200.models.constructor import construct_model
+    p = ens.init_params(17, 6, num_networks=E, seed=E, bias_std=0.1)
+    ens.scale_weights(p, 3.0)
+    rng = np.random.RandomState(E)
+    x = rng.standard_normal((B, 23)).astype(np.float32)
+    ens.fit_scaler(p, x)
+    m = construct_model(obs_dim=17, act_dim=6, num_networks=E, num_elites=1, separate_mean_var=True, name='e', device=0)
+    m.set_params(p['weights'], p['biases'], p['var_weights'], p['var_biases'], p['mu'], p['sigma'], p['max_logvar'], p['min_logvar'])
+    mean, var = m.predict(x, factored=True)
+    m64, v64 = ens.forward(p, x, np.float64)
+    np.testing.assert_allclose(mean, m64, rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(var, v64, rtol=RTOL)
+
+
 def test_linear_model_predict_and_step():
     """construct_model(model_type='linear') (constructor.py:25-27): one FC whose output finalize() doubles into [mean | logvar]
     (bnn.py:185); predict and FakeEnv.step against the oracle."""
