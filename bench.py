@@ -555,24 +555,38 @@ def run_ours(args):
     r = measure(cx, main_case, args.steps, args.warmup, clocks=True)
     extras = {}
     if not args.no_extras:
+        # every rank runs the same sequence (the records are whole-job numbers); a failing extra is reported in the line, it
+        # does not take the headline record with it
+        def extra(name, fn):
+            try:
+                return fn()
+            except Exception as e:                                  # noqa: BLE001
+                import traceback
+                sys.stderr.write('bench extra %s failed:\n%s' % (name, traceback.format_exc()))
+                return {'error': '%s: %s' % (type(e).__name__, str(e)[:200])}
+
         ksteps = max(5, min(args.steps, 10))
-        extras['path_error'] = {args.precision: path_error(cx, main_case)}
         other = 'bf16' if args.precision == 'fp32' else 'fp32'
-        oc = quiet(make_case, cx, args.workload, other, B, h, policy=args.policy == 'device')
-        orec = measure(cx, oc, ksteps, 3)
-        extras['%s_path' % other] = dict(brief(orec), dtype=DTYPE_NOTE[other])
-        extras['path_error'][other] = path_error(cx, oc)
-        del oc
+        extras['path_error'] = {args.precision: extra('path_error', lambda: path_error(cx, main_case))}
+
+        def other_path():
+            oc = quiet(make_case, cx, args.workload, other, B, h, policy=args.policy == 'device')
+            rec = dict(brief(measure(cx, oc, ksteps, 3)), dtype=DTYPE_NOTE[other])
+            extras['path_error'][other] = path_error(cx, oc)
+            return rec
+        extras['%s_path' % other] = extra('%s_path' % other, other_path)
         cfgs = {}
         for name, wl, prec, hh in (('hopper_h5', 'hopper', 'fp32', 5), ('hopper_h5_bf16', 'hopper', 'bf16', 5),
                                    ('walker2d_h1_parity', 'walker2d', 'fp32', 1), ('walker2d_h1_bf16', 'walker2d', 'bf16', 1)):
-            cc = quiet(make_case, cx, wl, prec, B, hh)
-            cfgs[name] = brief(measure(cx, cc, ksteps, 3))
-            cfgs[name]['path_error'] = path_error(cx, cc)
-            del cc
-        cfgs['epoch_loop'] = quiet(epoch_loop, cx, B, 5, 1000, 2)
+            def one(wl=wl, prec=prec, hh=hh):
+                cc = quiet(make_case, cx, wl, prec, B, hh)
+                rec = brief(measure(cx, cc, ksteps, 3))
+                rec['path_error'] = path_error(cx, cc)
+                return rec
+            cfgs[name] = extra(name, one)
+        cfgs['epoch_loop'] = extra('epoch_loop', lambda: quiet(epoch_loop, cx, B, 5, 1000, 2))
         extras['configs'] = cfgs
-        extras['strong_scaling'] = strong_scaling(cx, args.precision, 1000000, 5, 5)
+        extras['strong_scaling'] = extra('strong_scaling', lambda: strong_scaling(cx, args.precision, 1000000, 5, 5))
     if cx.rank != 0:
         return
     cores = os.cpu_count()
