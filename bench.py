@@ -191,12 +191,9 @@ class Ctx:
 
 def quiet(fn, *a, **k):
     """The shims print like the reference; keep stdout to ONE json line."""
-    devnull = open(os.devnull, 'w')
-    stdout, sys.stdout = sys.stdout, devnull
-    try:
+    import contextlib
+    with open(os.devnull, 'w') as devnull, contextlib.redirect_stdout(devnull):
         return fn(*a, **k)
-    finally:
-        sys.stdout = stdout
 
 
 def make_case(cx, workload, precision, B, h, pool_rows=None, policy=False, seed_rank=True):

@@ -33,7 +33,7 @@ int mopo_debug_mma_rate(int cta_group, int N, int nacc, int a_tmem, int ksteps, 
  * fp32-accurate kernel's group body (ld, swish, fp16 hi/lo split, st).  with_mma = 0 runs the interferers alone for the
  * same nominal duration.  out_dev = device int64[8]: [0] MMA cycles to commit, [1] issue cycles, [2] interferer group
  * iterations completed by the leader CTA's warps. */
-int mopo_debug_mma_interference(int N, int a_tmem, int ksteps, int imode, int n_warps, int with_mma, long long* out_dev, void* stream);
+int mopo_debug_mma_interference(int N, int a_tmem, int ksteps, int imode, int n_warps, int with_mma, int icol, long long* out_dev, void* stream);   /* icol: first TMEM column of the interferers' groups (the accumulator is [0, N), the A operand [408, 512)) */
 
 #ifdef __cplusplus
 }

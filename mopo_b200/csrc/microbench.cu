@@ -212,20 +212,20 @@ __device__ __forceinline__ void interferer_iter(uint32_t taddr, uint32_t (&v)[16
 }
 
 template <int N, int A_TMEM, int IMODE>
-__global__ void __launch_bounds__(640) mma_interf_kernel(int reps, int with_mma, long long* out) {
+__global__ void __launch_bounds__(640) mma_interf_kernel(int reps, int with_mma, int icol, long long* out) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int rows = N / 2;
   uint8_t* sB = smem;
   uint8_t* sA = sB + 26 * 256 * 16;
   uint64_t* bar = reinterpret_cast<uint64_t*>(sA + 26 * 128 * 16);
-  uint32_t* tptr = reinterpret_cast<uint32_t*>(bar + 1);
+  uint32_t* tptr = reinterpret_cast<uint32_t*>(bar + 8);
   volatile int* stop = reinterpret_cast<volatile int*>(tptr + 1);
   int* iters = const_cast<int*>(stop) + 1;
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid / 32, 0), lane = tid % 32;
   const uint32_t rank = cluster_ctarank();
   for (int i = tid; i < (26 * 256 * 16 + 26 * 128 * 16) / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
   if (warp == 0) { tmem_alloc<2>(tptr, 512); tmem_relinquish<2>(); }
-  if (tid == 0) { mbar_init(bar, 1); fence_barrier_init(); *stop = 0; *iters = 0; }
+  if (tid == 0) { mbar_init(bar, 1); for (int i = 4; i < 8; ++i) mbar_init(bar + i, (1 << 20) - 1); fence_barrier_init(); *stop = 0; *iters = 0; }
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(640) mma_interf_kernel(int reps, int with_mma,
   const uint32_t tbase = __shfl_sync(0xffffffffu, *tptr, 0);
   if (warp < 4) {
     uint32_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int c = 208; c < 512; c += 8) tmem_st8(tbase + ((uint32_t)(warp * 32) << 16) + c, z);
+    for (int c = 112; c < 512; c += 8) tmem_st8(tbase + ((uint32_t)(warp * 32) << 16) + c, z);
     tmem_st_wait();
     tc_fence_before();
   }
@@ -271,12 +271,42 @@ __global__ void __launch_bounds__(640) mma_interf_kernel(int reps, int with_mma,
     }
     if (lane == 0) *stop = 1;
   } else if (warp >= 4) {
-    const uint32_t taddr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + 208 + 16 * ((warp - 4) >> 2);
+    const uint32_t taddr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + icol + 16 * ((warp - 4) >> 2);
     uint32_t v[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = 0x3c003c00u + tid + i;
     int n = 0;
-    while (!*stop) { interferer_iter<IMODE>(taddr, v); ++n; }
+    if (IMODE == 4) {
+      // the fp32-accurate kernel's epilogue control flow: per "layer" a few rounds on consecutive groups, the next group's
+      // tcgen05.ld in flight during the current group's conversion, and per round wait::st + fence + an mbarrier arrive
+      uint32_t w[16];
+      uint64_t* rbar = bar + 4 + (warp & 3);                 // nobody waits on it: arrivals only
+      while (!*stop) {
+        tmem_ld16(taddr, v);
+#pragma unroll 1
+        for (int r = 0; r < 4; r += 2) {
+          tmem_ld_wait();
+          tmem_ld16(taddr + 64 * ((r + 1) & 1), w);
+          interferer_iter<1>(taddr, v);
+          tmem_st16(taddr, v);
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(rbar, 0);
+          tmem_ld_wait();
+          if (r + 2 < 4) tmem_ld16(taddr, v);
+          interferer_iter<1>(taddr, w);
+          tmem_st16(taddr + 64, w);
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_remote(rbar, 0);
+          n += 2;
+        }
+      }
+    } else {
+      while (!*stop) { interferer_iter<IMODE>(taddr, v); ++n; }
+    }
     uint32_t sink = 0;
 #pragma unroll
     for (int i = 0; i < 16; ++i) sink ^= v[i];
@@ -291,7 +321,7 @@ __global__ void __launch_bounds__(640) mma_interf_kernel(int reps, int with_mma,
 }
 
 template <int N, int A_TMEM, int IMODE>
-int launch_interf(int reps, int with_mma, int n_warps, long long* out_dev, cudaStream_t st) {
+int launch_interf(int reps, int with_mma, int n_warps, int icol, long long* out_dev, cudaStream_t st) {
   const size_t smem = 26 * 256 * 16 + 26 * 128 * 16 + 128;
   CUDA_TRY(cudaFuncSetAttribute(mma_interf_kernel<N, A_TMEM, IMODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
@@ -300,7 +330,7 @@ int launch_interf(int reps, int with_mma, int n_warps, long long* out_dev, cudaS
   at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
   MOPO_COUNT_LAUNCH;
-  CUDA_TRY(cudaLaunchKernelEx(&cfg, mma_interf_kernel<N, A_TMEM, IMODE>, reps, with_mma, out_dev));
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, mma_interf_kernel<N, A_TMEM, IMODE>, reps, with_mma, icol, out_dev));
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
@@ -308,14 +338,15 @@ int launch_interf(int reps, int with_mma, int n_warps, long long* out_dev, cudaS
 
 // N in {112, 96}; imode 0..3; n_warps 0..16 interferer warps per CTA; with_mma 0 = the interferers alone for the same duration
 extern "C" __attribute__((visibility("default")))
-int mopo_debug_mma_interference(int N, int a_tmem, int ksteps, int imode, int n_warps, int with_mma, long long* out_dev, void* stream) {
+int mopo_debug_mma_interference(int N, int a_tmem, int ksteps, int imode, int n_warps, int with_mma, int icol, long long* out_dev, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   const int reps = ksteps / 13;
+  if (icol < N || icol + 16 * ((n_warps + 3) / 4) > 408 || (icol & 3)) { mopo_set_error("mopo_debug_mma_interference: icol=%d", icol); return MOPO_EINVAL; }
   if (n_warps < 0 || n_warps > 16) { mopo_set_error("mopo_debug_mma_interference: n_warps=%d", n_warps); return MOPO_EINVAL; }
-#define INTERF_CASE(n, t, m) if (N == n && a_tmem == t && imode == m) return launch_interf<n, t, m>(reps, with_mma, n_warps, out_dev, st);
+#define INTERF_CASE(n, t, m) if (N == n && a_tmem == t && imode == m) return launch_interf<n, t, m>(reps, with_mma, n_warps, icol, out_dev, st);
   INTERF_CASE(112, 1, 0) INTERF_CASE(112, 1, 1) INTERF_CASE(112, 1, 2) INTERF_CASE(112, 1, 3)
   INTERF_CASE(96, 1, 0) INTERF_CASE(96, 1, 1) INTERF_CASE(96, 1, 2) INTERF_CASE(96, 1, 3)
-  INTERF_CASE(112, 0, 0) INTERF_CASE(112, 0, 3)
+  INTERF_CASE(112, 0, 0) INTERF_CASE(112, 0, 3) INTERF_CASE(112, 1, 4) INTERF_CASE(96, 1, 4)
 #undef INTERF_CASE
   mopo_set_error("mopo_debug_mma_interference: unsupported combination N=%d a_tmem=%d imode=%d", N, a_tmem, imode);
   return MOPO_EINVAL;

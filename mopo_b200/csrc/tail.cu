@@ -493,12 +493,8 @@ int launch_tail(const TailArgs& a, cudaStream_t st) {
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = a.pdl ? 1 : 0;      // rollout chain: may be scheduled while the forward kernel drains
-    if (smem > 48 * 1024) {                           // wide shapes (humanoid: obs 45, act 17 -> 65 KB): opt in once
-      static bool big_ok = false;
-      if (!big_ok) {
-        CUDA_TRY(cudaFuncSetAttribute(step_tail_fused_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        big_ok = true;
-      }
+    if (smem > 48 * 1024) {                           // wide shapes (humanoid: obs 45, act 17 -> 65 KB): opt in
+      CUDA_TRY(cudaFuncSetAttribute(step_tail_fused_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));   // per device: set on every such launch
       REQUIRE(smem <= 96 * 1024, MOPO_EUNSUPPORTED, "step tail: obs_dim %d / act_dim %d need %zu B of shared memory", a.obs_dim, a.act_dim, smem);
     }
     MOPO_COUNT_LAUNCH;
