@@ -547,27 +547,40 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
       const int64_t src_row = row + (int64_t)(u / nT) * a.net_stride;
       const float* po = a.obs + src_row * a.od;
       const float* pa = a.act + src_row * a.ad;
-      for (int kc = 0; kc < kcs; ++kc) {
-        float v[8];
+      // four K-panels (32 input columns) per pass, all their loads issued before the first use: the first block of a launch
+      // is produced behind pdl_wait() with nothing to hide its latency (one L2 round trip instead of one per panel)
+      for (int kc0 = 0; kc0 < kcs; kc0 += 4) {
+        float raw[32];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int k = kc * 8 + i;
-          float x = 0.0f;
-          if (ok) {
-            if (k < a.od) x = (po[k] - sMu[k]) / sSg[k];                      // models/utils.py:96
-            else if (k < s.in) x = (pa[k - a.od] - sMu[k]) / sSg[k];
-            else if (k == s.in) x = 1.0f;                                    // the bias row's constant
+        for (int i = 0; i < 32; ++i) {
+          const int k = kc0 * 8 + i;
+          raw[i] = 0.0f;
+          if (ok && k < s.in) raw[i] = k < a.od ? po[k] : pa[k - a.od];
+        }
+#pragma unroll
+        for (int pnl = 0; pnl < 4; ++pnl) {
+          const int kc = kc0 + pnl;
+          if (kc >= kcs) break;
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int k = kc * 8 + i;
+            float x = 0.0f;
+            if (ok) {
+              if (k < s.in) x = (raw[pnl * 8 + i] - sMu[k]) / sSg[k];          // models/utils.py:96
+              else if (k == s.in) x = 1.0f;                                    // the bias row's constant
+            }
+            v[i] = x;
           }
-          v[i] = x;
-        }
-        uint32_t hi[4], lo[4];
+          uint32_t hi[4], lo[4];
 #pragma unroll
-        for (int p = 0; p < 4; ++p) {
-          if constexpr (TERMS == 3) split2(v[2 * p], v[2 * p + 1], hi[p], lo[p]);
-          else { hi[p] = pack_bf16x2(v[2 * p], v[2 * p + 1]); lo[p] = 0u; }
+          for (int p = 0; p < 4; ++p) {
+            if constexpr (TERMS == 3) split2(v[2 * p], v[2 * p + 1], hi[p], lo[p]);
+            else { hi[p] = pack_bf16x2(v[2 * p], v[2 * p + 1]); lo[p] = 0u; }
+          }
+          st_shared_v4(sX + kc * XP + rr * 16, hi[0], hi[1], hi[2], hi[3]);
+          st_shared_v4(sX + s.x_part() + kc * XP + rr * 16, lo[0], lo[1], lo[2], lo[3]);
         }
-        st_shared_v4(sX + kc * XP + rr * 16, hi[0], hi[1], hi[2], hi[3]);
-        st_shared_v4(sX + s.x_part() + kc * XP + rr * 16, lo[0], lo[1], lo[2], lo[3]);
       }
       fence_proxy_async_smem();
       __syncwarp();
