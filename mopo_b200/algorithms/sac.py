@@ -165,8 +165,7 @@ class SACUpdate:
         if model_pool is None:                                             # real_ratio == 1.0 (mopo.py:816-819)
             n_env, n_model = n_env + n_model, 0
         losses = torch.empty((n_updates, 4), dtype=torch.float32, device=self.device) if return_losses else None
-        # on a side stream: the ~45 launches of an update are captured once and replayed as a CUDA graph (stream capture is
-        # not possible on the legacy default stream)
+        # on a side stream, so that the n_updates one-kernel updates queue behind each other beside the caller's stream
         cur = torch.cuda.current_stream(self.device)
         if getattr(self, '_stream', None) is None:
             self._stream = torch.cuda.Stream(self.device)

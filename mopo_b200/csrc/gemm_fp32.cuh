@@ -141,6 +141,181 @@ int gemm(const GemmP& p, int E, cudaStream_t st) {
   return MOPO_OK;
 }
 
+// ---- the same contraction as a device function, for the one-kernel update steps (sac.cu) ---------------------------------------
+// One 512-thread CTA per SM owns one 32 x 32 output tile at a time: its eight 64-thread groups each take an eighth of the k range
+// (4 x 4 outputs per thread), staged in shared memory FKD deep in one go; the partial tiles meet in shared memory and are summed in
+// a fixed order, then the epilogue runs once.  What counts here is the length of one thread's instruction stream (the steps are
+// chains of tiles a few microseconds long), hence the k split and the straight-line fast path.  Operands may have been written
+// earlier in the SAME kernel by other CTAs (behind a grid barrier): loads are ld.global.cg.
+constexpr int FT = 32, FKS = 8, FPITCH = FT + 4, FKD = 32, FUSED_THREADS = 64 * FKS;
+struct FusedSmem { float As[FKS][FKD + 1][FPITCH]; float Bs[FKS][FKD + 1][FPITCH]; };   // 76 032 B (dynamic)
+enum { GF_VA = 1, GF_VB = 2, GF_VC = 4 };     // host-checked: 16-byte pieces of A / B / (C, Zin, Zout, bias) are aligned
+
+__device__ __forceinline__ void group_bar(int g) { asm volatile("bar.sync %0, 64;" ::"r"(g + 1) : "memory"); }            // ids 1..8
+
+// grid barrier on a counter that only grows: `target` is the count at which this barrier opens (kept by the caller)
+__device__ __forceinline__ void grid_bar(unsigned* ctr, unsigned target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+    unsigned v;
+    do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory"); } while ((int)(v - target) < 0);
+  }
+  __syncthreads();
+}
+
+// four 16-byte pieces of one operand's [32 k] x [32] slab for this thread: piece q is row row0 + rstep q, columns col0..col0+3
+//   k is the row (A stored [K, M], B stored [K, N]): (k, c4) = (tid / 8 + 8 q, 4 (tid % 8));  k contiguous: (row, k4) = (tid / 8 + 8 q, 4 (tid % 8))
+__device__ __forceinline__ void slab_load(const float* base, int ld, bool kmajor, bool vec_ok, int tid, int k0, int kend, int o0, int o_lim,
+                                          float4 (&r)[4]) {
+  const int row0 = (kmajor ? k0 : o0) + (tid >> 3), col0 = (kmajor ? o0 : k0) + 4 * (tid & 7);
+  const int row_lim = kmajor ? kend : o_lim, col_lim = kmajor ? o_lim : kend;
+  const float* p = base + (int64_t)row0 * ld + col0;
+  const int64_t step = (int64_t)8 * ld;
+  if (vec_ok && row0 + 24 < row_lim && col0 + 3 < col_lim) {              // the whole column of pieces is inside: straight line
+#pragma unroll
+    for (int q = 0; q < 4; ++q) r[q] = __ldcg(reinterpret_cast<const float4*>(p + step * q));
+    return;
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row0 + 8 * q < row_lim) {
+      const float* pq = p + step * q;
+      if (vec_ok && col0 + 3 < col_lim) v = __ldcg(reinterpret_cast<const float4*>(pq));
+      else {
+        if (col0 < col_lim) v.x = __ldcg(pq);
+        if (col0 + 1 < col_lim) v.y = __ldcg(pq + 1);
+        if (col0 + 2 < col_lim) v.z = __ldcg(pq + 2);
+        if (col0 + 3 < col_lim) v.w = __ldcg(pq + 3);
+      }
+    }
+    r[q] = v;
+  }
+}
+__device__ __forceinline__ void slab_stash(float (*S)[FPITCH], bool kmajor, int tid, const float4 (&r)[4]) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (kmajor) *reinterpret_cast<float4*>(&S[(tid >> 3) + 8 * q][4 * (tid & 7)]) = r[q];
+    else { const int rr = (tid >> 3) + 8 * q, c = 4 * (tid & 7); S[c][rr] = r[q].x; S[c + 1][rr] = r[q].y; S[c + 2][rr] = r[q].z; S[c + 3][rr] = r[q].w; }
+  }
+}
+
+// One output tile by the CTA: unit u of the op's (net, m tile, n tile) grid, tn = n tiles, tmn = tiles per net.
+__device__ __forceinline__ void tile_unit(FusedSmem& sm, const GemmP& p, int epi, int flags, int tn, int tmn, int u) {
+  const int e = u / tmn, r0 = u - e * tmn, mt = r0 / tn;
+  const int m0 = mt * FT, n0 = (r0 - mt * tn) * FT;
+  const int g = threadIdx.x >> 6, tid = threadIdx.x & 63, tx = tid & 7, ty = tid >> 3;
+  float (*As)[FPITCH] = sm.As[g];
+  float (*Bs)[FPITCH] = sm.Bs[g];
+  const int K = p.K;
+  const int ksl = (((K + FKS - 1) / FKS) + 3) & ~3;        // k range of a group, a multiple of 4 (16-byte loads stay aligned)
+  const int kb = g * ksl, ke = min(K, kb + ksl);
+  const float* Ae = p.A + (int64_t)e * p.sA;
+  const float* Be = p.B + (int64_t)e * p.sB;
+  const bool ka = p.tA != 0, kbm = p.tB == 0;              // operand stored with k as the row index
+  // the epilogue's operands of this thread's two outputs (row r, columns c2, c2 + 1), requested before the contraction
+  const int r = threadIdx.x >> 4, c2 = (threadIdx.x & 15) * 2;
+  const int m = m0 + r, n = n0 + c2;
+  const int64_t o = (int64_t)e * p.sC + (int64_t)m * p.ldc + n;
+  const bool pair = (flags & GF_VC) && n + 1 < p.N;        // both columns exist and the 8-byte accesses are aligned
+  float bias2[2] = {0.f, 0.f}, zin2[2] = {0.f, 0.f};
+  if (m < p.M && n < p.N) {
+    if (epi == 1 || epi == 2 || epi == 4) {
+      if (pair) { const float2 t = __ldcg(reinterpret_cast<const float2*>(p.bias + (int64_t)e * p.N + n)); bias2[0] = t.x; bias2[1] = t.y; }
+      else { bias2[0] = __ldcg(p.bias + (int64_t)e * p.N + n); if (n + 1 < p.N) bias2[1] = __ldcg(p.bias + (int64_t)e * p.N + n + 1); }
+    } else if (epi == 3 || epi == 5) {
+      if (pair) { const float2 t = __ldcg(reinterpret_cast<const float2*>(p.Zin + o)); zin2[0] = t.x; zin2[1] = t.y; }
+      else { zin2[0] = __ldcg(p.Zin + o); if (n + 1 < p.N) zin2[1] = __ldcg(p.Zin + o + 1); }
+    }
+  }
+  float acc[TM][TN] = {};
+  for (int k0 = kb; k0 < ke; k0 += FKD) {
+    const int kd = min(FKD, ke - k0), kend = k0 + kd;
+    float4 ra[4], rb[4];
+    slab_load(Ae, p.lda, ka, flags & GF_VA, tid, k0, kend, m0, p.M, ra);
+    slab_load(Be, p.ldb, kbm, flags & GF_VB, tid, k0, kend, n0, p.N, rb);
+    slab_stash(As, ka, tid, ra);
+    slab_stash(Bs, kbm, tid, rb);
+    group_bar(g);
+    float4 a4 = *reinterpret_cast<const float4*>(&As[0][ty * TM]);
+    float4 b4 = *reinterpret_cast<const float4*>(&Bs[0][tx * TN]);
+#pragma unroll 8
+    for (int k = 0; k < kd; ++k) {
+      const float4 an = *reinterpret_cast<const float4*>(&As[k + 1][ty * TM]);   // row FKD exists (never summed)
+      const float4 bn = *reinterpret_cast<const float4*>(&Bs[k + 1][tx * TN]);
+      const float a[TM] = {a4.x, a4.y, a4.z, a4.w}, b[TN] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      a4 = an; b4 = bn;
+    }
+    group_bar(g);
+  }
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+    *reinterpret_cast<float4*>(&As[ty * TM + i][tx * TN]) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+  __syncthreads();
+  if (m < p.M && n < p.N) {
+    float v[2] = {0.f, 0.f};
+#pragma unroll
+    for (int s = 0; s < FKS; ++s) {
+      const float2 t = *reinterpret_cast<const float2*>(&sm.As[s][r][c2]);
+      v[0] += t.x; v[1] += t.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      float x = v[j];
+      if (epi == 1) { x += bias2[j]; v[j] = x; x = x * sigmoid_f(x); }          // v keeps z for Zout
+      else if (epi == 2) x += bias2[j];
+      else if (epi == 3) { const float z = zin2[j], sg = sigmoid_f(z); x *= sg + z * sg * (1.0f - sg); }
+      else if (epi == 4) x = fmaxf(x + bias2[j], 0.0f);
+      else if (epi == 5) x = zin2[j] > 0.0f ? x : 0.0f;
+      bias2[j] = x;                                                            // (reused as the output pair)
+    }
+    if (pair) {
+      if (epi == 1) *reinterpret_cast<float2*>(p.Zout + o) = make_float2(v[0], v[1]);
+      *reinterpret_cast<float2*>(p.C + o) = make_float2(bias2[0], bias2[1]);
+    } else {
+      if (epi == 1) { p.Zout[o] = v[0]; if (n + 1 < p.N) p.Zout[o + 1] = v[1]; }
+      p.C[o] = bias2[0]; if (n + 1 < p.N) p.C[o + 1] = bias2[1];
+    }
+  }
+  __syncthreads();
+}
+// host side: the alignment flags of an op
+inline int gemm_flags(const GemmP& p) {
+  auto al = [](const void* q, int bytes) { return q == nullptr || (reinterpret_cast<uintptr_t>(q) % bytes) == 0; };
+  int f = 0;
+  if (p.lda % 4 == 0 && p.sA % 4 == 0 && al(p.A, 16)) f |= GF_VA;
+  if (p.ldb % 4 == 0 && p.sB % 4 == 0 && al(p.B, 16)) f |= GF_VB;
+  if (p.ldc % 2 == 0 && p.sC % 2 == 0 && p.N % 2 == 0 && al(p.C, 8) && al(p.Zin, 8) && al(p.Zout, 8) && al(p.bias, 8)) f |= GF_VC;
+  return f;
+}
+
+// colsum_kernel's block (bx, e) as one CTA-wide unit: 32 columns x 16 row groups
+__device__ __forceinline__ void colsum_unit(FusedSmem& sm, const float* dZ, float* db, int n, int N, int64_t stride, int u) {
+  const int nbx = (N + 31) / 32, e = u / nbx, bx = u - e * nbx;
+  float (*sh)[FPITCH] = sm.Bs[0];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int c = bx * 32 + lane;
+  float s = 0.f;
+  if (c < N) {
+    const float* q = dZ + (int64_t)e * stride + c;
+    for (int b = w; b < n; b += FUSED_THREADS / 32) s += __ldcg(q + (int64_t)b * N);
+  }
+  sh[w][lane] = s;
+  __syncthreads();
+  if (w == 0 && c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < FUSED_THREADS / 32; ++i) t += sh[i][lane];
+    db[(int64_t)e * N + c] = t;
+  }
+  __syncthreads();
+}
+
 // db[e, c] = sum_{b<n} dZ[e*stride + b*N + c]: 32 columns x 8 row groups per block, fixed summation order (deterministic)
 __global__ void __launch_bounds__(256) colsum_kernel(const float* __restrict__ dZ, float* __restrict__ db, int n, int N, int64_t stride) {
   __shared__ float sh[8][33];

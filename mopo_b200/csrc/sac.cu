@@ -19,74 +19,107 @@ namespace {
 constexpr float LOG_STD_MAX = 2.0f, LOG_STD_MIN = -20.0f, PI_EPS = 1e-8f;
 constexpr int SAC_MAX_ACT = 32;
 
-// t += 1; lr_t[0] = policy lr, lr_t[1] = Q lr for the step being applied (tf.train.AdamOptimizer)
-__global__ void sac_tick_kernel(int64_t* __restrict__ t, uint64_t* __restrict__ step, float* __restrict__ lr_t, float lr_pi, float lr_q) {
-  const int64_t k = ++t[0];
-  ++step[0];                                   // Philox step id of this update's policy noise
-  const double c = sqrt(1.0 - pow((double)ADAM_B2, (double)k)) / (1.0 - pow((double)ADAM_B1, (double)k));
-  lr_t[0] = (float)((double)lr_pi * c);
-  lr_t[1] = (float)((double)lr_q * c);
+// ---- the update as ONE cooperative kernel --------------------------------------------------------------------------------------
+// Stages separated by grid barriers; inside a stage every CTA takes work units (32 x 32 GEMM tiles with a 4-way k split inside the
+// CTA, bias-gradient column sums, 256-row blocks of the per-row maps) round robin over all the stage's ops, so the weight gradients
+// run beside the next link of the data-gradient chain.
+struct SacSample {
+  const float *obs[2], *act[2], *nobs[2], *rew[2]; const uint8_t* term[2];
+  int64_t size[2]; int n_env, n, od, ad;
+};
+constexpr int SAC_TENSORS = 13;   // pi 3 W + 3 b, q 3 W + 3 b (twins stacked), log_alpha
+// the update's program: ops in stage order, a grid barrier after every stage (the host writes it, sac_program below)
+enum { OP_GEMM = 0, OP_COLSUM, OP_OUTER, OP_SAMPLE, OP_PI_HEAD, OP_LOSS, OP_PI_GRAD };
+struct FOp { GemmP g; int kind, epi, stage, units, tn, tmn, flags; };
+constexpr int SAC_MAX_OPS = 40;
+struct SacFused {
+  int n, od, ad, adp, H, sample, polyak;        // adp: lanes per policy row (power of two >= ad)
+  SacSample smp; uint64_t seed;
+  int64_t* t; uint64_t* d_step; float* lr_t; float lr_pi, lr_q;
+  float reward_scale, discount, target_entropy, tau;
+  const float* eps_in;
+  const float* act; const float* rew; const uint8_t* term;          // batch fields (the pools path: ba / br / bt, written by stage 0)
+  float* ba; float* br; uint8_t* bt; int64_t* bidx;
+  float *piW[3], *pib[3], *qW[3], *qb[3], *tW[3], *tb[3], *log_alpha;
+  float *g[SAC_TENSORS], *m[SAC_TENSORS], *v[SAC_TENSORS]; int64_t psize[SAC_TENSORS];
+  float *par[SAC_TENSORS], *targ[SAC_TENSORS]; int64_t cpref[SAC_TENSORS + 1];   // variables, their Polyak targets (or null), 4-element chunk prefix
+  float *Xpi, *H0p, *H1p, *HD, *eps, *logp, *Xq, *Xt, *H0q, *H1q, *Qo, *T0, *T1, *To, *dQo, *dZ1q, *dZ0q, *dXa, *dHD, *dZ1p, *dZ0p;
+  float* out;
+  unsigned long long* trace;
+  unsigned* bar; unsigned bar_base;          // grid barrier counter (only grows) and its value when this launch starts
+  int n_ops; FOp ops[SAC_MAX_OPS];
+};
+
+// _training_batch (mopo.py:801-821): rows [0, n_env) from the env pool, [n_env, n) from the model pool, indices as
+// mopo_pool_sample draws them (Philox stream 2, counter = (row, offset), offset = 2 (update index) + pool: every update and
+// each pool has its own counter plane, so consecutive minibatches are independent draws) -- all five fields.
+__device__ __forceinline__ void sac_sample(const SacFused& a, uint64_t step) {
+  const SacSample& sp = a.smp;
+  const int W = 2 * sp.od + sp.ad + 2;
+  const uint64_t base = 2 * (step - 1);
+  float* bo = a.Xpi; float* bno = a.Xpi + (size_t)sp.n * sp.od;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < sp.n * W; i += gridDim.x * blockDim.x) {
+    const int j = i / W, c = i % W;
+    const int w = j >= sp.n_env;
+    Philox4 r = philox_pool_draw((uint32_t)(w ? j - sp.n_env : j), base + (uint64_t)w, a.seed);
+    const int64_t idx = (int64_t)__umul64hi(((uint64_t)r.x << 32) | r.y, (uint64_t)sp.size[w]);
+    if (c < sp.od) bo[(int64_t)j * sp.od + c] = sp.obs[w][idx * sp.od + c];
+    else if (c < 2 * sp.od) bno[(int64_t)j * sp.od + (c - sp.od)] = sp.nobs[w][idx * sp.od + (c - sp.od)];
+    else if (c < 2 * sp.od + sp.ad) a.ba[(int64_t)j * sp.ad + (c - 2 * sp.od)] = sp.act[w][idx * sp.ad + (c - 2 * sp.od)];
+    else if (c == W - 2) { a.br[j] = sp.rew[w][idx]; a.bidx[j] = idx; }
+    else a.bt[j] = sp.term[w][idx];
+  }
 }
 
-// One thread per policy row r of [s; s'] (2n rows): head [mu | log_std] -> u = mu + eps std, a = tanh(u), logp
-// (gaussian_likelihood + squashing correction, mopo.py:281-296); writes the critic inputs:
-//   r <  n: Xq[r] = (s_r, a_data_r),  Xq[n + r] = (s_r, a)      r >= n: Xt[r - n] = (s'_r, a)
-__global__ void sac_pi_head_kernel(const float* __restrict__ HD, const float* __restrict__ eps_in, uint64_t seed,
-                                   const uint64_t* __restrict__ d_step,
-                                   const float* __restrict__ obs, const float* __restrict__ act, const float* __restrict__ next_obs,
-                                   int n, int od, int ad, float* __restrict__ eps_out, float* __restrict__ logp,
-                                   float* __restrict__ Xq, float* __restrict__ Xt) {
-  const int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= 2 * n) return;
+// adp lanes (a power of two >= act_dim) per policy row r of [s; s'] (2n rows), lane d owns action dimension d: head
+// [mu | log_std] -> u = mu + eps std, a = tanh(u), logp (gaussian_likelihood + squashing correction, mopo.py:281-296); writes the
+// critic inputs:   r <  n: Xq[r] = (s_r, a_data_r),  Xq[n + r] = (s_r, a)      r >= n: Xt[r - n] = (s'_r, a)
+__device__ __forceinline__ void sac_pi_head(const SacFused& a, uint64_t step64, int unit) {
+  const int n = a.n, od = a.od, ad = a.ad, adp = a.adp;
+  const int r = unit * (FUSED_THREADS / adp) + (int)threadIdx.x / adp, d = (int)threadIdx.x % adp;
+  const bool on = r < 2 * n && d < ad;
   const int in_q = od + ad;
-  float z[SAC_MAX_ACT];
-  if (eps_in) {
-    for (int d = 0; d < ad; ++d) z[d] = eps_in[(int64_t)r * ad + d];
-  } else {
-    const uint32_t step = (uint32_t)*d_step;
-    for (int d0 = 0; d0 < ad; d0 += 4) {
-      float gg[4];
-      philox_normal4((uint32_t)r, step, (uint32_t)(d0 >> 2), seed, gg, MOPO_STREAM_SAC);
-      for (int j = 0; j < 4 && d0 + j < ad; ++j) z[d0 + j] = gg[j];
+  float lp = 0.f;
+  if (r < 2 * n) {
+    const float* s = a.Xpi + (int64_t)r * od;                        // [s; s'] stacked
+    float* xo = r < n ? a.Xq + (int64_t)(n + r) * in_q : a.Xt + (int64_t)(r - n) * in_q;
+    float* xd = a.Xq + (int64_t)r * in_q;
+    for (int k = d; k < od; k += adp) { const float sv = s[k]; xo[k] = sv; if (r < n) xd[k] = sv; }
+    if (on) {
+      float z;
+      if (a.eps_in) z = a.eps_in[(int64_t)r * ad + d];
+      else {
+        float gg[4];
+        philox_normal4((uint32_t)r, (uint32_t)step64, (uint32_t)(d >> 2), a.seed, gg, MOPO_STREAM_SAC);
+        z = gg[d & 3];
+      }
+      if (r < n) xd[od + d] = a.act[(int64_t)r * ad + d];
+      const float mu = __ldcg(a.HD + (int64_t)r * 2 * ad + d);
+      const float ls = fminf(fmaxf(__ldcg(a.HD + (int64_t)r * 2 * ad + ad + d), LOG_STD_MIN), LOG_STD_MAX);
+      const float sd = expf(ls);
+      const float u = mu + z * sd;
+      const float q = z * sd / (sd + PI_EPS);        // (u - mu) / (std + EPS) with u - mu = eps std exactly
+      lp = -0.5f * (q * q + 2.0f * ls + 1.8378770664093453f) - 2.0f * (0.6931471805599453f - u - softplus_f(-2.0f * u));
+      xo[od + d] = tanhf(u);
+      a.eps[(int64_t)r * ad + d] = z;
     }
   }
-  const float* s = r < n ? obs + (int64_t)r * od : next_obs + (int64_t)(r - n) * od;
-  float* xo = r < n ? Xq + (int64_t)(n + r) * in_q : Xt + (int64_t)(r - n) * in_q;
-  for (int k = 0; k < od; ++k) xo[k] = s[k];
-  if (r < n) {
-    float* xd = Xq + (int64_t)r * in_q;
-    for (int k = 0; k < od; ++k) xd[k] = s[k];
-    for (int d = 0; d < ad; ++d) xd[od + d] = act[(int64_t)r * ad + d];
-  }
-  float lp = 0.f;
-  for (int d = 0; d < ad; ++d) {
-    const float mu = HD[(int64_t)r * 2 * ad + d];
-    const float ls = fminf(fmaxf(HD[(int64_t)r * 2 * ad + ad + d], LOG_STD_MIN), LOG_STD_MAX);
-    const float sd = expf(ls);
-    const float u = mu + z[d] * sd;
-    const float q = z[d] * sd / (sd + PI_EPS);        // (u - mu) / (std + EPS) with u - mu = eps std exactly
-    lp += -0.5f * (q * q + 2.0f * ls + 1.8378770664093453f);
-    lp -= 2.0f * (0.6931471805599453f - u - softplus_f(-2.0f * u));
-    xo[od + d] = tanhf(u);
-    eps_out[(int64_t)r * ad + d] = z[d];
-  }
-  logp[r] = lp;
+  for (int o = adp >> 1; o > 0; o >>= 1) lp += __shfl_xor_sync(0xffffffffu, lp, o);   // over the row's lanes, fixed order
+  if (r < 2 * n && d == 0) a.logp[r] = lp;
 }
 
-// One block: q targets, dQ for the stacked critic rows, the four losses and d alpha_loss / d log_alpha.
+// One CTA: q targets, dQ for the stacked critic rows, the four losses and d alpha_loss / d log_alpha.
 //   Qo [2, 2n]: twin e, rows [0,n) = q_e(s, a), [n,2n) = q_e(s, pi(s));  To [2, n] = target twins on (s', pi(s'))
 //   out[0..3] = q1_loss, q2_loss, policy_loss, alpha_loss;  out[4] = d alpha_loss / d log_alpha
-__global__ void __launch_bounds__(256) sac_loss_kernel(const float* __restrict__ Qo, const float* __restrict__ To,
-                                                       const float* __restrict__ logp, const float* __restrict__ rew,
-                                                       const uint8_t* __restrict__ term, const float* __restrict__ log_alpha,
-                                                       int n, float reward_scale, float discount, float target_entropy,
-                                                       float* __restrict__ dQo, float* __restrict__ out, float* __restrict__ g_alpha) {
-  __shared__ float sh[8];
-  const float la = *log_alpha, alpha = expf(la), inv_n = 1.0f / (float)n;
+__device__ __forceinline__ void sac_loss(const SacFused& a, float* sh) {
+  const int n = a.n;
+  const float *Qo = a.Qo, *To = a.To, *logp = a.logp;
+  float* dQo = a.dQo;
+  const float la = *a.log_alpha, alpha = expf(la), inv_n = 1.0f / (float)n;
   float s1 = 0.f, s2 = 0.f, sp = 0.f, sa = 0.f;
   for (int b = threadIdx.x; b < n; b += blockDim.x) {
     const float next_value = fminf(To[b], To[n + b]) - alpha * logp[n + b];
-    const float y = reward_scale * rew[b] + discount * (term[b] ? 0.0f : 1.0f) * next_value;
+    const float y = a.reward_scale * a.rew[b] + a.discount * (a.term[b] ? 0.0f : 1.0f) * next_value;
     const float q1 = Qo[b], q2 = Qo[2 * n + b], q1p = Qo[n + b], q2p = Qo[3 * n + b];
     dQo[b] = (q1 - y) * inv_n;
     dQo[2 * n + b] = (q2 - y) * inv_n;
@@ -96,89 +129,132 @@ __global__ void __launch_bounds__(256) sac_loss_kernel(const float* __restrict__
     s1 += (q1 - y) * (q1 - y);
     s2 += (q2 - y) * (q2 - y);
     sp += alpha * logp[b] - fminf(q1p, q2p);
-    sa += logp[b] + target_entropy;
+    sa += logp[b] + a.target_entropy;
   }
   s1 = block_sum(s1, sh); s2 = block_sum(s2, sh); sp = block_sum(sp, sh); sa = block_sum(sa, sh);
   if (threadIdx.x == 0) {
-    out[0] = 0.5f * s1 * inv_n; out[1] = 0.5f * s2 * inv_n; out[2] = sp * inv_n; out[3] = -la * sa * inv_n; out[4] = -sa * inv_n;
-    *g_alpha = -sa * inv_n;
+    a.out[0] = 0.5f * s1 * inv_n; a.out[1] = 0.5f * s2 * inv_n; a.out[2] = sp * inv_n; a.out[3] = -la * sa * inv_n; a.out[4] = -sa * inv_n;
+    *a.g[12] = -sa * inv_n;
   }
 }
 
-// d policy_loss / d [mu | log_std_raw] for the n rows of s (thread per row); dXa [2, n, ad] = d(-min q)/d a per twin.
-__global__ void sac_pi_head_grad_kernel(const float* __restrict__ HD, const float* __restrict__ eps, const float* __restrict__ dXa,
-                                        const float* __restrict__ log_alpha, int n, int ad, float* __restrict__ dHD) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= n) return;
-  const float c = expf(*log_alpha) / (float)n;
-  for (int d = 0; d < ad; ++d) {
-    const float mu = HD[(int64_t)b * 2 * ad + d], ls_raw = HD[(int64_t)b * 2 * ad + ad + d];
-    const float ls = fminf(fmaxf(ls_raw, LOG_STD_MIN), LOG_STD_MAX);
-    const float sd = expf(ls), z = eps[(int64_t)b * ad + d];
-    const float u = mu + z * sd, a = tanhf(u);
-    const float den = sd + PI_EPS;
-    const float dev = z * sd;                          // u - mu
-    const float r2 = dev / (den * den);
-    const float d_a = dXa[(int64_t)b * ad + d] + dXa[((int64_t)n + b) * ad + d];
-    const float g_u = c * (-r2 + 2.0f * a) + d_a * (1.0f - a * a);
-    const float d_mu = g_u + c * r2;
-    float d_ls = g_u * (z * sd) + c * (dev * dev * sd / (den * den * den) - 1.0f);
-    if (ls_raw < LOG_STD_MIN || ls_raw > LOG_STD_MAX) d_ls = 0.0f;      // tf.clip_by_value passes no gradient outside
-    dHD[(int64_t)b * 2 * ad + d] = d_mu;
-    dHD[(int64_t)b * 2 * ad + ad + d] = d_ls;
-  }
+// d policy_loss / d [mu | log_std_raw], one thread per (row b of s, action dimension d); dXa [2, n, ad] = d(-min q)/d a per twin.
+__device__ __forceinline__ void sac_pi_head_grad(const SacFused& a, int i) {
+  const int n = a.n, ad = a.ad;
+  if (i >= n * ad) return;
+  const int b = i / ad, d = i - b * ad;
+  const float c = expf(*a.log_alpha) / (float)n;
+  const float mu = a.HD[(int64_t)b * 2 * ad + d], ls_raw = a.HD[(int64_t)b * 2 * ad + ad + d];
+  const float ls = fminf(fmaxf(ls_raw, LOG_STD_MIN), LOG_STD_MAX);
+  const float sd = expf(ls), z = a.eps[i];
+  const float u = mu + z * sd, av = tanhf(u);
+  const float den = sd + PI_EPS;
+  const float dev = z * sd;                          // u - mu
+  const float r2 = dev / (den * den);
+  const float d_a = __ldcg(a.dXa + i) + __ldcg(a.dXa + (int64_t)n * ad + i);
+  const float g_u = c * (-r2 + 2.0f * av) + d_a * (1.0f - av * av);
+  const float d_mu = g_u + c * r2;
+  float d_ls = g_u * (z * sd) + c * (dev * dev * sd / (den * den * den) - 1.0f);
+  if (ls_raw < LOG_STD_MIN || ls_raw > LOG_STD_MAX) d_ls = 0.0f;      // tf.clip_by_value passes no gradient outside
+  a.dHD[(int64_t)b * 2 * ad + d] = d_mu;
+  a.dHD[(int64_t)b * 2 * ad + ad + d] = d_ls;
 }
 
-// _training_batch (mopo.py:801-821) in one launch: rows [0, n_env) from the env pool, [n_env, n) from the model pool, indices as
-// mopo_pool_sample draws them (Philox stream 2, counter = (row, offset), offset = 2 (update index) + pool: every update and
-// each pool has its own counter plane, so consecutive minibatches are independent draws, mopo.py:801-821) -- all five fields.
-struct SacSample {
-  const float *obs[2], *act[2], *nobs[2], *rew[2]; const uint8_t* term[2];
-  int64_t size[2]; int n_env, n, od, ad;
-};
-__global__ void __launch_bounds__(256) sac_sample_kernel(SacSample a, uint64_t seed, const uint64_t* __restrict__ d_step,
-                                                         float* __restrict__ bo, float* __restrict__ ba, float* __restrict__ bno,
-                                                         float* __restrict__ br, uint8_t* __restrict__ bt, int64_t* __restrict__ bidx) {
-  const int W = 2 * a.od + a.ad + 2;
-  const uint64_t base = 2 * (*d_step - 1);
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n * W; i += gridDim.x * blockDim.x) {
-    const int j = i / W, c = i % W;
-    const int w = j >= a.n_env;
-    Philox4 r = philox_pool_draw((uint32_t)(w ? j - a.n_env : j), base + (uint64_t)w, seed);
-    const int64_t idx = (int64_t)__umul64hi(((uint64_t)r.x << 32) | r.y, (uint64_t)a.size[w]);
-    if (c < a.od) bo[(int64_t)j * a.od + c] = a.obs[w][idx * a.od + c];
-    else if (c < 2 * a.od) bno[(int64_t)j * a.od + (c - a.od)] = a.nobs[w][idx * a.od + (c - a.od)];
-    else if (c < 2 * a.od + a.ad) ba[(int64_t)j * a.ad + (c - 2 * a.od)] = a.act[w][idx * a.ad + (c - 2 * a.od)];
-    else if (c == W - 2) { br[j] = a.rew[w][idx]; bidx[j] = idx; }
-    else bt[j] = a.term[w][idx];
-  }
+// C[e, m, n] = x[e, m] w[e, n] (Zin[e, m, n] > 0): the data gradient through a one-unit head (K = 1) as an elementwise map;
+// GemmP fields: A = x (stride sA per net), B = w (stride sB), C / Zin [E, M, N] contiguous rows (ldc = N), four columns per thread
+__device__ __forceinline__ void outer_unit(const GemmP& p, int u) {
+  const int nq = p.N >> 2;                                   // host guarantees N % 4 == 0 and 16-byte alignment
+  const int64_t i = (int64_t)u * FUSED_THREADS + threadIdx.x;
+  const int64_t rows = i / nq; const int c = (int)(i - rows * nq) * 4;
+  const int e = (int)(rows / p.M); const int m = (int)(rows - (int64_t)e * p.M);
+  if (e >= p.K) return;                                      // (K carries the net count here)
+  const float x = __ldcg(p.A + (int64_t)e * p.sA + m);
+  const float4 w = __ldcg(reinterpret_cast<const float4*>(p.B + (int64_t)e * p.sB + c));
+  const int64_t o = (int64_t)e * p.sC + (int64_t)m * p.ldc + c;
+  const float4 z = __ldcg(reinterpret_cast<const float4*>(p.Zin + o));
+  *reinterpret_cast<float4*>(p.C + o) = make_float4(z.x > 0.f ? x * w.x : 0.f, z.y > 0.f ? x * w.y : 0.f, z.z > 0.f ? x * w.z : 0.f, z.w > 0.f ? x * w.w : 0.f);
 }
 
-constexpr int SAC_TENSORS = 13;   // pi 3 W + 3 b, q 3 W + 3 b (twins stacked), log_alpha
-struct SacAdam {
-  float* p[SAC_TENSORS]; const float* g[SAC_TENSORS]; float* m[SAC_TENSORS]; float* v[SAC_TENSORS];
-  int64_t n[SAC_TENSORS]; int which_lr[SAC_TENSORS];
-  const float* lr_t;
-};
-__global__ void __launch_bounds__(256) sac_adam_kernel(SacAdam a) {
-  const int t = blockIdx.y;
-  const float lr_t = a.lr_t[a.which_lr[t]];
-  float* __restrict__ p = a.p[t]; const float* __restrict__ g = a.g[t];
-  float* __restrict__ m = a.m[t]; float* __restrict__ v = a.v[t];
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n[t]; i += (int64_t)gridDim.x * blockDim.x) {
-    const float gi = g[i];
-    const float mi = ADAM_B1 * m[i] + (1.0f - ADAM_B1) * gi;
-    const float vi = ADAM_B2 * v[i] + (1.0f - ADAM_B2) * gi * gi;
-    m[i] = mi; v[i] = vi;
-    p[i] = p[i] - lr_t * mi / (sqrtf(vi) + ADAM_EPS);
-  }
+// units [off, off + count) of a stage go to the CTAs (one per SM) round robin; f(u) runs unit u of this op on the calling CTA
+template <class F>
+__device__ __forceinline__ void stage_units(int& off, int count, F f) {
+  const int G = gridDim.x;
+  for (int u = ((int)blockIdx.x - off % G + G) % G; u < count; u += G) f(u);
+  off += count;
 }
 
-struct SacPolyak { float* targ[6]; const float* main[6]; int64_t n[6]; float tau; };
-__global__ void __launch_bounds__(256) sac_polyak_kernel(SacPolyak a) {
-  const int t = blockIdx.y;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n[t]; i += (int64_t)gridDim.x * blockDim.x)
-    a.targ[t][i] = (1.0f - a.tau) * a.targ[t][i] + a.tau * a.main[t][i];
+__global__ void __launch_bounds__(FUSED_THREADS, 1) sac_fused_kernel(const __grid_constant__ SacFused a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FusedSmem& sm = *reinterpret_cast<FusedSmem*>(smem_raw);
+  __shared__ float s_lr[2];
+  const int64_t k_adam = *a.t + 1;                 // tf.train.AdamOptimizer's step being applied
+  const uint64_t step = *a.d_step + 1;             // Philox step id of this update's draws
+  if (threadIdx.x == 0) {                          // lr_t of both optimiser families (sqrt(1 - b2^k) / (1 - b1^k))
+    const double c = sqrt(1.0 - pow((double)ADAM_B2, (double)k_adam)) / (1.0 - pow((double)ADAM_B1, (double)k_adam));
+    s_lr[0] = (float)((double)a.lr_pi * c); s_lr[1] = (float)((double)a.lr_q * c);
+  }
+  unsigned bar_target = a.bar_base;
+  int tr_i = 0;
+  auto TRC = [&]() { if (a.trace && blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); a.trace[tr_i] = t; } ++tr_i; };
+  TRC();
+  int i = 0;
+  while (i < a.n_ops) {
+    const int stage = a.ops[i].stage;
+    int off = 0;
+    for (; i < a.n_ops && a.ops[i].stage == stage; ++i) {
+      const FOp& op = a.ops[i];
+      switch (op.kind) {
+        case OP_GEMM: stage_units(off, op.units, [&](int u) { tile_unit(sm, op.g, op.epi, op.flags, op.tn, op.tmn, u); }); break;
+        case OP_COLSUM: stage_units(off, op.units, [&](int u) { colsum_unit(sm, op.g.A, op.g.C, op.g.M, op.g.N, op.g.sA, u); }); break;
+        case OP_OUTER: stage_units(off, op.units, [&](int u) { outer_unit(op.g, u); }); break;
+        case OP_SAMPLE: sac_sample(a, step); break;
+        case OP_PI_HEAD: stage_units(off, op.units, [&](int u) { sac_pi_head(a, step, u); }); break;
+        case OP_LOSS: stage_units(off, 1, [&](int) { sac_loss(a, &sm.Bs[0][0][0]); }); break;
+        case OP_PI_GRAD: stage_units(off, op.units, [&](int u) { sac_pi_head_grad(a, u * FUSED_THREADS + (int)threadIdx.x); }); break;
+        default: break;
+      }
+    }
+    bar_target += gridDim.x;
+    grid_bar(a.bar, bar_target); TRC();
+    if (stage == 0 && blockIdx.x == 0 && threadIdx.x == 0) { *a.t = k_adam; *a.d_step = step; a.lr_t[0] = s_lr[0]; a.lr_t[1] = s_lr[1]; }
+  }
+  // last: the four Adam optimisers, and target <- (1 - tau) target + tau main on the freshly written critic variables; all 13
+  // tensors as one list of 4-element chunks, so that a thread's loads of one chunk are the only round trip
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, gn = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t c = gtid; c < a.cpref[SAC_TENSORS]; c += gn) {
+    int t = 0;
+    while (c >= a.cpref[t + 1]) ++t;
+    const int64_t j0 = (c - a.cpref[t]) * 4;
+    const int cnt = (int)min((int64_t)4, a.psize[t] - j0);
+    const float lr_t = s_lr[(t < 6 || t == 12) ? 0 : 1];
+    float* p = a.par[t] + j0; float* targ = a.polyak && a.targ[t] ? a.targ[t] + j0 : nullptr;
+    const float* g = a.g[t] + j0; float* m = a.m[t] + j0; float* v = a.v[t] + j0;
+    float gi[4], mi[4], vi[4], pi[4], ti[4] = {0.f, 0.f, 0.f, 0.f};
+    if (cnt == 4) {
+      const float4 g4 = *reinterpret_cast<const float4*>(g), m4 = *reinterpret_cast<const float4*>(m), v4 = *reinterpret_cast<const float4*>(v),
+                   p4 = *reinterpret_cast<const float4*>(p);
+      gi[0] = g4.x; gi[1] = g4.y; gi[2] = g4.z; gi[3] = g4.w; mi[0] = m4.x; mi[1] = m4.y; mi[2] = m4.z; mi[3] = m4.w;
+      vi[0] = v4.x; vi[1] = v4.y; vi[2] = v4.z; vi[3] = v4.w; pi[0] = p4.x; pi[1] = p4.y; pi[2] = p4.z; pi[3] = p4.w;
+      if (targ) { const float4 t4 = *reinterpret_cast<const float4*>(targ); ti[0] = t4.x; ti[1] = t4.y; ti[2] = t4.z; ti[3] = t4.w; }
+    } else {
+      for (int j = 0; j < cnt; ++j) { gi[j] = g[j]; mi[j] = m[j]; vi[j] = v[j]; pi[j] = p[j]; if (targ) ti[j] = targ[j]; }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mi[j] = ADAM_B1 * mi[j] + (1.0f - ADAM_B1) * gi[j];
+      vi[j] = ADAM_B2 * vi[j] + (1.0f - ADAM_B2) * gi[j] * gi[j];
+      pi[j] = pi[j] - lr_t * mi[j] / (sqrtf(vi[j]) + ADAM_EPS);
+      ti[j] = (1.0f - a.tau) * ti[j] + a.tau * pi[j];
+    }
+    if (cnt == 4) {
+      *reinterpret_cast<float4*>(m) = make_float4(mi[0], mi[1], mi[2], mi[3]); *reinterpret_cast<float4*>(v) = make_float4(vi[0], vi[1], vi[2], vi[3]);
+      *reinterpret_cast<float4*>(p) = make_float4(pi[0], pi[1], pi[2], pi[3]);
+      if (targ) *reinterpret_cast<float4*>(targ) = make_float4(ti[0], ti[1], ti[2], ti[3]);
+    } else {
+      for (int j = 0; j < cnt; ++j) { m[j] = mi[j]; v[j] = vi[j]; p[j] = pi[j]; if (targ) targ[j] = ti[j]; }
+    }
+  }
+  TRC();
 }
 
 // dst[r, c0 + c] = src[r, c] / dst[r, c] = src[r, c0 + c]: the fused [mu | log_std] head <-> the reference's two dense layers
@@ -205,15 +281,11 @@ struct mopo_sac {
   float *g[SAC_TENSORS] = {}, *m[SAC_TENSORS] = {}, *v[SAC_TENSORS] = {};
   int64_t* t = nullptr; float* lr_t = nullptr; float* out = nullptr;   // device: Adam step, {lr_pi_t, lr_q_t}, losses[5]
   int64_t updates = 0;
-  cudaStream_t side = nullptr, side2 = nullptr; cudaEvent_t ev_pi[4] = {}; cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
   DevBuf ba, br, bt, bidx;                   // batch drawn from the pools
   DevBuf Xpi, H0p, H1p, HD, eps, logp, Xq, Xt, H0q, H1q, Qo, T0, T1, To, dQo, dZ1q, dZ0q, dXa, dHD, dZ1p, dZ0p;
-  uint64_t* d_step = nullptr;                         // device Philox step id of the policy noise (advanced by sac_tick_kernel)
-  // the captured pools iteration (tick -> draw -> update), kept across calls: MOPO calls one update per environment step
-  // (_do_training_repeats, mopo.py:780-799), so the same pools / sizes recur until the next rollout grows the model pool
-  cudaGraphExec_t graph = nullptr; int g_nodes = 0; uint64_t g_seed = 0;
-  SacSample g_smp, last_smp; uint64_t last_seed = 0; bool have_last = false;
-  void drop_graph() { if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; } }
+  uint64_t* d_step = nullptr;                         // device Philox step id of the policy noise (advanced by the update kernel)
+  int grid = 0;                                       // CTAs of sac_fused_kernel: one per SM (cooperative launch)
+  unsigned* bar = nullptr; unsigned bar_count = 0;    // its grid barrier counter and the arrivals launched so far
   size_t psize(int i) const {                         // elements of tensor i in SacAdam order
     const int in_q = od + ad;
     const size_t s[SAC_TENSORS] = {(size_t)od * H, (size_t)H, (size_t)H * H, (size_t)H, (size_t)H * 2 * ad, (size_t)2 * ad,
@@ -254,13 +326,13 @@ MOPO_API int mopo_sac_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, i
   CUDA_TRY(cudaMalloc(&s->d_step, sizeof(uint64_t))); CUDA_TRY(cudaMemset(s->d_step, 0, sizeof(uint64_t)));
   CUDA_TRY(cudaMalloc(&s->lr_t, 2 * sizeof(float)));
   CUDA_TRY(cudaMalloc(&s->out, 8 * sizeof(float)));
-  CUDA_TRY(cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking));
-  CUDA_TRY(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
-  CUDA_TRY(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
-  CUDA_TRY(cudaStreamCreateWithFlags(&s->side2, cudaStreamNonBlocking));
-  for (cudaEvent_t& e : s->ev_pi) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-  CUDA_TRY(cudaEventCreateWithFlags(&s->ev_fork2, cudaEventDisableTiming));
-  CUDA_TRY(cudaEventCreateWithFlags(&s->ev_join2, cudaEventDisableTiming));
+  int per_sm = 0, sms = 0;
+  CUDA_TRY(cudaFuncSetAttribute(sac_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FusedSmem)));
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sac_fused_kernel, FUSED_THREADS, sizeof(FusedSmem)));
+  CUDA_TRY(cudaMalloc(&s->bar, sizeof(unsigned))); CUDA_TRY(cudaMemset(s->bar, 0, sizeof(unsigned)));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  REQUIRE(per_sm > 0 && sms > 0, MOPO_ECUDA, "mopo_sac_create: the update kernel does not fit on an SM");
+  s->grid = sms;
   *out = s;
   return MOPO_OK;
 }
@@ -270,11 +342,7 @@ MOPO_API int mopo_sac_destroy(mopo_sac* s) {
   cudaSetDevice(s->device);
   for (int i = 0; i < 3; ++i) { cudaFree(s->piW[i]); cudaFree(s->pib[i]); cudaFree(s->qW[i]); cudaFree(s->qb[i]); cudaFree(s->tW[i]); cudaFree(s->tb[i]); }
   for (int i = 0; i < SAC_TENSORS; ++i) { cudaFree(s->g[i]); cudaFree(s->m[i]); cudaFree(s->v[i]); }
-  s->drop_graph();
-  cudaFree(s->log_alpha); cudaFree(s->t); cudaFree(s->d_step); cudaFree(s->lr_t); cudaFree(s->out);
-  cudaEventDestroy(s->ev_fork); cudaEventDestroy(s->ev_join); cudaEventDestroy(s->ev_fork2); cudaEventDestroy(s->ev_join2); cudaStreamDestroy(s->side);
-  for (cudaEvent_t e : s->ev_pi) cudaEventDestroy(e);
-  cudaStreamDestroy(s->side2);
+  cudaFree(s->log_alpha); cudaFree(s->t); cudaFree(s->d_step); cudaFree(s->lr_t); cudaFree(s->out); cudaFree(s->bar);
   DevBuf* bufs[] = {&s->ba, &s->br, &s->bt, &s->bidx, &s->Xpi, &s->H0p, &s->H1p, &s->HD, &s->eps, &s->logp, &s->Xq, &s->Xt,
                     &s->H0q, &s->H1q, &s->Qo, &s->T0, &s->T1, &s->To, &s->dQo, &s->dZ1q, &s->dZ0q, &s->dXa, &s->dHD, &s->dZ1p, &s->dZ0p};
   for (DevBuf* b : bufs) b->release();
@@ -418,118 +486,127 @@ static int sac_reserve(mopo_sac* s, int n) {
       {&s->T1, 2 * N * H}, {&s->To, 2 * N}, {&s->dQo, 4 * N}, {&s->dZ1q, 4 * N * H}, {&s->dZ0q, 4 * N * H}, {&s->dXa, 2 * N * ad},
       {&s->dHD, N * 2 * ad}, {&s->dZ1p, N * H}, {&s->dZ0p, N * H}};
   for (auto& w : want) {
-    void* before = w.b->p;
     TRY(w.b->reserve(w.n * sizeof(float)));
-    if (before != w.b->p) s->drop_graph();          // a moved buffer invalidates the captured iteration
   }
   return MOPO_OK;
 }
 
-// One _do_training step on a batch already in device memory.
-static int sac_update_impl(mopo_sac* s, const float* obs, const float* act, const float* rew, const uint8_t* term, const float* next_obs,
-                           int n, const float* eps_in, uint64_t seed, float* losses_out, cudaStream_t st, bool ticked = false) {
-  const int od = s->od, ad = s->ad, H = s->H, in_q = od + ad;
+// One _do_training step: ONE cooperative launch.  smp != nullptr: the batch is drawn from the pools inside the kernel
+// (into Xpi / ba / br / bt); else obs / next_obs are already in Xpi or copied there, act / rew / term are read in place.
+static int sac_update_impl(mopo_sac* s, const SacSample* smp, const float* obs, const float* act, const float* rew, const uint8_t* term,
+                           const float* next_obs, int n, const float* eps_in, uint64_t seed, float* losses_out, cudaStream_t st) {
+  const int od = s->od;
   TRY(sac_reserve(s, n));
-  float *Xpi = s->Xpi.as<float>(), *H0p = s->H0p.as<float>(), *H1p = s->H1p.as<float>(), *HD = s->HD.as<float>();
-  float *Xq = s->Xq.as<float>(), *Xt = s->Xt.as<float>(), *H0q = s->H0q.as<float>(), *H1q = s->H1q.as<float>(), *Qo = s->Qo.as<float>();
-  float *T0 = s->T0.as<float>(), *T1 = s->T1.as<float>(), *To = s->To.as<float>(), *dQo = s->dQo.as<float>();
-  float *dZ1q = s->dZ1q.as<float>(), *dZ0q = s->dZ0q.as<float>(), *dXa = s->dXa.as<float>(), *dHD = s->dHD.as<float>();
-  float *dZ1p = s->dZ1p.as<float>(), *dZ0p = s->dZ0p.as<float>();
-  if (!ticked) {
-    MOPO_COUNT_LAUNCH;
-    sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
-  }
-  // policy on [s; s']
-  if (obs != Xpi) {               // (the pools path samples straight into Xpi)
+  SacFused a;
+  memset(&a, 0, sizeof(a));
+  a.n = n; a.od = od; a.ad = s->ad; a.H = s->H;
+  a.adp = 1; while (a.adp < s->ad) a.adp *= 2;
+  a.seed = seed; a.t = s->t; a.d_step = s->d_step; a.lr_t = s->lr_t; a.lr_pi = s->hp.policy_lr; a.lr_q = s->hp.q_lr;
+  a.reward_scale = s->hp.reward_scale; a.discount = s->hp.discount; a.target_entropy = s->hp.target_entropy; a.tau = s->hp.tau;
+  a.eps_in = eps_in;
+  float* Xpi = s->Xpi.as<float>();
+  if (smp) {
+    a.sample = 1; a.smp = *smp;
+    a.ba = s->ba.as<float>(); a.br = s->br.as<float>(); a.bt = s->bt.as<uint8_t>(); a.bidx = s->bidx.as<int64_t>();
+    a.act = a.ba; a.rew = a.br; a.term = a.bt;
+  } else {
     CUDA_TRY(cudaMemcpyAsync(Xpi, obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(Xpi + (size_t)n * od, next_obs, (size_t)n * od * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    a.act = act; a.rew = rew; a.term = term;
   }
-  const int n2 = 2 * n;
-  gemm<4>(GemmP{Xpi, 0, od, 0, s->piW[0], 0, H, 0, H0p, 0, H, n2, H, od, s->pib[0], nullptr, nullptr}, 1, st);
-  gemm<4>(GemmP{H0p, 0, H, 0, s->piW[1], 0, H, 0, H1p, 0, H, n2, H, H, s->pib[1], nullptr, nullptr}, 1, st);
-  gemm<2>(GemmP{H1p, 0, H, 0, s->piW[2], 0, 2 * ad, 0, HD, 0, 2 * ad, n2, 2 * ad, H, s->pib[2], nullptr, nullptr}, 1, st);
-  MOPO_COUNT_LAUNCH;
-  sac_pi_head_kernel<<<(n2 + 127) / 128, 128, 0, st>>>(HD, eps_in, seed, s->d_step, obs, act, next_obs, n, od, ad, s->eps.as<float>(),
-                                                       s->logp.as<float>(), Xq, Xt);
-  // twin critics on [(s, a); (s, pi(s))] and their targets on (s', pi(s')): nets batched over blockIdx.z, inputs shared
-  const int64_t sH2 = (int64_t)n2 * H, sH1 = (int64_t)n * H;
-  CUDA_TRY(cudaEventRecord(s->ev_fork2, st));
-  CUDA_TRY(cudaStreamWaitEvent(s->side, s->ev_fork2, 0));
-  gemm<4>(GemmP{Xt, 0, in_q, 0, s->tW[0], (int64_t)in_q * H, H, 0, T0, sH1, H, n, H, in_q, s->tb[0], nullptr, nullptr}, 2, s->side);
-  gemm<4>(GemmP{T0, sH1, H, 0, s->tW[1], (int64_t)H * H, H, 0, T1, sH1, H, n, H, H, s->tb[1], nullptr, nullptr}, 2, s->side);
-  gemm<2>(GemmP{T1, sH1, H, 0, s->tW[2], (int64_t)H, 1, 0, To, n, 1, n, 1, H, s->tb[2], nullptr, nullptr}, 2, s->side);
-  CUDA_TRY(cudaEventRecord(s->ev_join2, s->side));
-  gemm<4>(GemmP{Xq, 0, in_q, 0, s->qW[0], (int64_t)in_q * H, H, 0, H0q, sH2, H, n2, H, in_q, s->qb[0], nullptr, nullptr}, 2, st);
-  gemm<4>(GemmP{H0q, sH2, H, 0, s->qW[1], (int64_t)H * H, H, 0, H1q, sH2, H, n2, H, H, s->qb[1], nullptr, nullptr}, 2, st);
-  gemm<2>(GemmP{H1q, sH2, H, 0, s->qW[2], (int64_t)H, 1, 0, Qo, n2, 1, n2, 1, H, s->qb[2], nullptr, nullptr}, 2, st);
-  CUDA_TRY(cudaStreamWaitEvent(st, s->ev_join2, 0));            // target critics: beside the main critics (see above)
-  MOPO_COUNT_LAUNCH;
-  sac_loss_kernel<<<1, 256, 0, st>>>(Qo, To, s->logp.as<float>(), rew, term, s->log_alpha, n, s->hp.reward_scale, s->hp.discount,
-                                     s->hp.target_entropy, dQo, s->out, s->g[12]);
-  if (losses_out) CUDA_TRY(cudaMemcpyAsync(losses_out, s->out, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  // critic backward over all 2n rows (data rows feed the critic gradients, pi rows the action gradient)
-  gemm<5>(GemmP{dQo, n2, 1, 0, s->qW[2], (int64_t)H, 1, 1, dZ1q, sH2, H, n2, H, 1, nullptr, nullptr, H1q}, 2, st);
-  gemm<5>(GemmP{dZ1q, sH2, H, 0, s->qW[1], (int64_t)H * H, H, 1, dZ0q, sH2, H, n2, H, H, nullptr, nullptr, H0q}, 2, st);
-  // fork: critic parameter gradients (first n rows of every net) on the side stream
-  CUDA_TRY(cudaEventRecord(s->ev_fork, st));
-  CUDA_TRY(cudaStreamWaitEvent(s->side, s->ev_fork, 0));
-  cudaStream_t sd = s->side;
-  gemm<0>(GemmP{H1q, sH2, H, 1, dQo, n2, 1, 0, s->g[10], (int64_t)H, 1, H, 1, n, nullptr, nullptr, nullptr}, 2, sd);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3(1, 2), 256, 0, sd>>>(dQo, s->g[11], n, 1, (int64_t)n2);
-  gemm<0>(GemmP{H0q, sH2, H, 1, dZ1q, sH2, H, 0, s->g[8], (int64_t)H * H, H, H, H, n, nullptr, nullptr, nullptr}, 2, sd);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 2), 256, 0, sd>>>(dZ1q, s->g[9], n, H, sH2);
-  gemm<0>(GemmP{Xq, 0, in_q, 1, dZ0q, sH2, H, 0, s->g[6], (int64_t)in_q * H, H, in_q, H, n, nullptr, nullptr, nullptr}, 2, sd);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 2), 256, 0, sd>>>(dZ0q, s->g[7], n, H, sH2);
-  CUDA_TRY(cudaEventRecord(s->ev_join, sd));
-  // main: d(-min q)/d a of the pi rows -> policy head gradient -> policy backward
-  gemm<0>(GemmP{dZ0q + (size_t)n * H, sH2, H, 0, s->qW[0] + (size_t)od * H, (int64_t)in_q * H, H, 1, dXa, (int64_t)n * ad, ad, n, ad, H,
-                nullptr, nullptr, nullptr}, 2, st);
-  MOPO_COUNT_LAUNCH;
-  sac_pi_head_grad_kernel<<<(n + 127) / 128, 128, 0, st>>>(HD, s->eps.as<float>(), dXa, s->log_alpha, n, ad, dHD);
-  // actor backward: the chain dHD -> dZ1p -> dZ0p stays on the main stream, each stage's weight / bias gradients go to side2
-  cudaStream_t s2 = s->side2;
-  CUDA_TRY(cudaEventRecord(s->ev_pi[0], st));
-  gemm<5>(GemmP{dHD, 0, 2 * ad, 0, s->piW[2], 0, 2 * ad, 1, dZ1p, 0, H, n, H, 2 * ad, nullptr, nullptr, H1p}, 1, st);
-  CUDA_TRY(cudaEventRecord(s->ev_pi[1], st));
-  gemm<5>(GemmP{dZ1p, 0, H, 0, s->piW[1], 0, H, 1, dZ0p, 0, H, n, H, H, nullptr, nullptr, H0p}, 1, st);
-  CUDA_TRY(cudaEventRecord(s->ev_pi[2], st));
-  CUDA_TRY(cudaStreamWaitEvent(s2, s->ev_pi[0], 0));
-  gemm<0>(GemmP{H1p, 0, H, 1, dHD, 0, 2 * ad, 0, s->g[4], 0, 2 * ad, H, 2 * ad, n, nullptr, nullptr, nullptr}, 1, s2);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((2 * ad + 31) / 32, 1), 256, 0, s2>>>(dHD, s->g[5], n, 2 * ad, 0);
-  CUDA_TRY(cudaStreamWaitEvent(s2, s->ev_pi[1], 0));
-  gemm<0>(GemmP{H0p, 0, H, 1, dZ1p, 0, H, 0, s->g[2], 0, H, H, H, n, nullptr, nullptr, nullptr}, 1, s2);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 1), 256, 0, s2>>>(dZ1p, s->g[3], n, H, 0);
-  CUDA_TRY(cudaStreamWaitEvent(s2, s->ev_pi[2], 0));
-  gemm<0>(GemmP{Xpi, 0, od, 1, dZ0p, 0, H, 0, s->g[0], 0, H, od, H, n, nullptr, nullptr, nullptr}, 1, s2);
-  MOPO_COUNT_LAUNCH; colsum_kernel<<<dim3((H + 31) / 32, 1), 256, 0, s2>>>(dZ0p, s->g[1], n, H, 0);
-  CUDA_TRY(cudaEventRecord(s->ev_pi[3], s2));
-  CUDA_TRY(cudaStreamWaitEvent(st, s->ev_pi[3], 0));
-  CUDA_TRY(cudaStreamWaitEvent(st, s->ev_join, 0));
-  // the four Adam optimisers in one launch, then the Polyak update (every target_update_interval-th update, mopo.py:839-841)
-  SacAdam ab;
-  size_t biggest = 0;
-  for (int i = 0; i < SAC_TENSORS; ++i) {
-    ab.p[i] = s->param(i); ab.g[i] = s->g[i]; ab.m[i] = s->m[i]; ab.v[i] = s->v[i]; ab.n[i] = (int64_t)s->psize(i);
-    ab.which_lr[i] = (i < 6 || i == 12) ? 0 : 1;
-    if (s->psize(i) > biggest) biggest = s->psize(i);
-  }
-  ab.lr_t = s->lr_t;
-  int gx = (int)((biggest + 1023) / 1024); if (gx > 148) gx = 148;
-  MOPO_COUNT_LAUNCH;
-  sac_adam_kernel<<<dim3(gx, SAC_TENSORS), 256, 0, st>>>(ab);
   const int interval = s->hp.target_update_interval > 0 ? s->hp.target_update_interval : 1;
-  if (s->updates % interval == 0) {
-    SacPolyak pk;
-    for (int l = 0; l < 3; ++l) {
-      pk.targ[2 * l] = s->tW[l]; pk.main[2 * l] = s->qW[l]; pk.n[2 * l] = (int64_t)s->psize(6 + 2 * l);
-      pk.targ[2 * l + 1] = s->tb[l]; pk.main[2 * l + 1] = s->qb[l]; pk.n[2 * l + 1] = (int64_t)s->psize(7 + 2 * l);
-    }
-    pk.tau = s->hp.tau;
-    MOPO_COUNT_LAUNCH;
-    sac_polyak_kernel<<<dim3(gx, 6), 256, 0, st>>>(pk);
+  a.polyak = s->updates % interval == 0;             // every target_update_interval-th update (mopo.py:839-841)
+  for (int l = 0; l < 3; ++l) { a.piW[l] = s->piW[l]; a.pib[l] = s->pib[l]; a.qW[l] = s->qW[l]; a.qb[l] = s->qb[l]; a.tW[l] = s->tW[l]; a.tb[l] = s->tb[l]; }
+  a.log_alpha = s->log_alpha;
+  a.cpref[0] = 0;
+  for (int i = 0; i < SAC_TENSORS; ++i) {
+    a.g[i] = s->g[i]; a.m[i] = s->m[i]; a.v[i] = s->v[i]; a.psize[i] = (int64_t)s->psize(i);
+    a.par[i] = s->param(i);
+    a.targ[i] = (i >= 6 && i < 12) ? ((i & 1) ? s->tb[(i - 6) / 2] : s->tW[(i - 6) / 2]) : nullptr;
+    a.cpref[i + 1] = a.cpref[i] + (a.psize[i] + 3) / 4;
   }
+  a.Xpi = Xpi; a.H0p = s->H0p.as<float>(); a.H1p = s->H1p.as<float>(); a.HD = s->HD.as<float>(); a.eps = s->eps.as<float>();
+  a.logp = s->logp.as<float>(); a.Xq = s->Xq.as<float>(); a.Xt = s->Xt.as<float>(); a.H0q = s->H0q.as<float>(); a.H1q = s->H1q.as<float>();
+  a.Qo = s->Qo.as<float>(); a.T0 = s->T0.as<float>(); a.T1 = s->T1.as<float>(); a.To = s->To.as<float>(); a.dQo = s->dQo.as<float>();
+  a.dZ1q = s->dZ1q.as<float>(); a.dZ0q = s->dZ0q.as<float>(); a.dXa = s->dXa.as<float>(); a.dHD = s->dHD.as<float>();
+  a.dZ1p = s->dZ1p.as<float>(); a.dZ0p = s->dZ0p.as<float>();
+  a.out = s->out;
+  // the program: stages of independent ops (the weight / bias gradients sit beside the next link of the data-gradient chain)
+  {
+    const int ad = s->ad, H = s->H, in_q = od + ad, n2 = 2 * n;
+    const int64_t sH2 = (int64_t)n2 * H, sH1 = (int64_t)n * H;
+    int stage = 0, k = 0;
+    bool full = false;
+    auto push = [&](FOp op) { if (k < SAC_MAX_OPS) a.ops[k++] = op; else full = true; };
+    auto gemm_op = [&](const GemmP& g, int E, int epi) {
+      FOp op; memset(&op, 0, sizeof(op));
+      op.g = g; op.kind = OP_GEMM; op.epi = epi; op.stage = stage;
+      op.tn = (g.N + FT - 1) / FT; op.tmn = op.tn * ((g.M + FT - 1) / FT); op.units = op.tmn * E; op.flags = gemm_flags(g);
+      push(op);
+    };
+    auto colsum_op = [&](const float* dZ, float* db, int rows, int N, int64_t stride, int E) {
+      FOp op; memset(&op, 0, sizeof(op));
+      op.g.A = dZ; op.g.C = db; op.g.M = rows; op.g.N = N; op.g.sA = stride; op.kind = OP_COLSUM; op.stage = stage; op.units = ((N + 31) / 32) * E;
+      push(op);
+    };
+    auto plain_op = [&](int kind, int units) { FOp op; memset(&op, 0, sizeof(op)); op.kind = kind; op.stage = stage; op.units = units; push(op); };
+    if (smp) { plain_op(OP_SAMPLE, 0); ++stage; }
+    // actor on [s; s']
+    gemm_op(GemmP{a.Xpi, 0, od, 0, a.piW[0], 0, H, 0, a.H0p, 0, H, n2, H, od, a.pib[0], nullptr, nullptr}, 1, 4); ++stage;
+    gemm_op(GemmP{a.H0p, 0, H, 0, a.piW[1], 0, H, 0, a.H1p, 0, H, n2, H, H, a.pib[1], nullptr, nullptr}, 1, 4); ++stage;
+    gemm_op(GemmP{a.H1p, 0, H, 0, a.piW[2], 0, 2 * ad, 0, a.HD, 0, 2 * ad, n2, 2 * ad, H, a.pib[2], nullptr, nullptr}, 1, 2); ++stage;
+    plain_op(OP_PI_HEAD, (n2 + FUSED_THREADS / a.adp - 1) / (FUSED_THREADS / a.adp)); ++stage;                 // squash, log-likelihood, critic inputs
+    // twin critics on [(s, a); (s, pi(s))] and the target twins on (s', pi(s')), side by side
+    gemm_op(GemmP{a.Xq, 0, in_q, 0, a.qW[0], (int64_t)in_q * H, H, 0, a.H0q, sH2, H, n2, H, in_q, a.qb[0], nullptr, nullptr}, 2, 4);
+    gemm_op(GemmP{a.Xt, 0, in_q, 0, a.tW[0], (int64_t)in_q * H, H, 0, a.T0, sH1, H, n, H, in_q, a.tb[0], nullptr, nullptr}, 2, 4); ++stage;
+    gemm_op(GemmP{a.H0q, sH2, H, 0, a.qW[1], (int64_t)H * H, H, 0, a.H1q, sH2, H, n2, H, H, a.qb[1], nullptr, nullptr}, 2, 4);
+    gemm_op(GemmP{a.T0, sH1, H, 0, a.tW[1], (int64_t)H * H, H, 0, a.T1, sH1, H, n, H, H, a.tb[1], nullptr, nullptr}, 2, 4); ++stage;
+    gemm_op(GemmP{a.H1q, sH2, H, 0, a.qW[2], (int64_t)H, 1, 0, a.Qo, n2, 1, n2, 1, H, a.qb[2], nullptr, nullptr}, 2, 2);
+    gemm_op(GemmP{a.T1, sH1, H, 0, a.tW[2], (int64_t)H, 1, 0, a.To, n, 1, n, 1, H, a.tb[2], nullptr, nullptr}, 2, 2); ++stage;
+    plain_op(OP_LOSS, 1); ++stage;                                   // targets, losses, dQ
+    // critic backward over all 2n rows (data rows feed the critic gradients, pi rows the action gradient)
+    if (H % 4 == 0) {                                                // K = 1: an elementwise outer product
+      FOp op; memset(&op, 0, sizeof(op));
+      op.g = GemmP{a.dQo, n2, 1, 0, a.qW[2], (int64_t)H, 1, 1, a.dZ1q, sH2, H, n2, H, 2, nullptr, nullptr, a.H1q};
+      op.kind = OP_OUTER; op.stage = stage; op.units = (int)(((int64_t)2 * n2 * (H / 4) + FUSED_THREADS - 1) / FUSED_THREADS);
+      push(op);
+    } else {
+      gemm_op(GemmP{a.dQo, n2, 1, 0, a.qW[2], (int64_t)H, 1, 1, a.dZ1q, sH2, H, n2, H, 1, nullptr, nullptr, a.H1q}, 2, 5);
+    }
+    gemm_op(GemmP{a.H1q, sH2, H, 1, a.dQo, n2, 1, 0, a.g[10], (int64_t)H, 1, H, 1, n, nullptr, nullptr, nullptr}, 2, 0);
+    colsum_op(a.dQo, a.g[11], n, 1, (int64_t)n2, 2); ++stage;
+    gemm_op(GemmP{a.dZ1q, sH2, H, 0, a.qW[1], (int64_t)H * H, H, 1, a.dZ0q, sH2, H, n2, H, H, nullptr, nullptr, a.H0q}, 2, 5);
+    gemm_op(GemmP{a.H0q, sH2, H, 1, a.dZ1q, sH2, H, 0, a.g[8], (int64_t)H * H, H, H, H, n, nullptr, nullptr, nullptr}, 2, 0);
+    colsum_op(a.dZ1q, a.g[9], n, H, sH2, 2); ++stage;
+    gemm_op(GemmP{a.dZ0q + (size_t)n * H, sH2, H, 0, a.qW[0] + (size_t)od * H, (int64_t)in_q * H, H, 1, a.dXa, (int64_t)n * ad, ad, n, ad, H,
+                  nullptr, nullptr, nullptr}, 2, 0);
+    gemm_op(GemmP{a.Xq, 0, in_q, 1, a.dZ0q, sH2, H, 0, a.g[6], (int64_t)in_q * H, H, in_q, H, n, nullptr, nullptr, nullptr}, 2, 0);
+    colsum_op(a.dZ0q, a.g[7], n, H, sH2, 2); ++stage;
+    plain_op(OP_PI_GRAD, (n * ad + FUSED_THREADS - 1) / FUSED_THREADS); ++stage;                  // policy head gradient
+    // actor backward
+    gemm_op(GemmP{a.dHD, 0, 2 * ad, 0, a.piW[2], 0, 2 * ad, 1, a.dZ1p, 0, H, n, H, 2 * ad, nullptr, nullptr, a.H1p}, 1, 5);
+    gemm_op(GemmP{a.H1p, 0, H, 1, a.dHD, 0, 2 * ad, 0, a.g[4], 0, 2 * ad, H, 2 * ad, n, nullptr, nullptr, nullptr}, 1, 0);
+    colsum_op(a.dHD, a.g[5], n, 2 * ad, 0, 1); ++stage;
+    gemm_op(GemmP{a.dZ1p, 0, H, 0, a.piW[1], 0, H, 1, a.dZ0p, 0, H, n, H, H, nullptr, nullptr, a.H0p}, 1, 5);
+    gemm_op(GemmP{a.H0p, 0, H, 1, a.dZ1p, 0, H, 0, a.g[2], 0, H, H, H, n, nullptr, nullptr, nullptr}, 1, 0);
+    colsum_op(a.dZ1p, a.g[3], n, H, 0, 1); ++stage;
+    gemm_op(GemmP{a.Xpi, 0, od, 1, a.dZ0p, 0, H, 0, a.g[0], 0, H, od, H, n, nullptr, nullptr, nullptr}, 1, 0);
+    colsum_op(a.dZ0p, a.g[1], n, H, 0, 1); ++stage;
+    REQUIRE(!full, MOPO_EINVAL, "sac update: program table too small");
+    a.n_ops = k;
+    a.bar = s->bar; a.bar_base = s->bar_count;
+    s->bar_count += (unsigned)stage * (unsigned)s->grid;      // one barrier per stage, every CTA arrives once
+  }
+  static unsigned long long* d_trace = nullptr;
+  if (getenv("MOPO_SAC_TRACE") && !d_trace) cudaMalloc(&d_trace, 64 * 8);
+  a.trace = d_trace;
+  void* args[] = {&a};
+  MOPO_COUNT_LAUNCH;
+  CUDA_TRY(cudaLaunchCooperativeKernel((const void*)sac_fused_kernel, dim3(s->grid), dim3(FUSED_THREADS), args, sizeof(FusedSmem), st));
+  if (d_trace && s->updates == 40) { unsigned long long h[64]; cudaStreamSynchronize(st); cudaMemcpy(h, d_trace, 64 * 8, cudaMemcpyDeviceToHost);
+    for (int i = 1; i < 20; ++i) fprintf(stderr, "stage %d: %.2f us\n", i - 1, (double)(h[i] - h[i - 1]) * 1e-3); }
+  if (losses_out) CUDA_TRY(cudaMemcpyAsync(losses_out, s->out, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st));
   s->updates += 1;
-  CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
 }
 
@@ -539,7 +616,7 @@ MOPO_API int mopo_sac_update(mopo_sac* s, const mopo_sac_batch* b, void* stream)
   REQUIRE(b->obs && b->act && b->rew && b->term && b->next_obs, MOPO_EINVAL, "mopo_sac_update: null batch field");
   REQUIRE(b->n > 0 && b->n <= (1 << 20), MOPO_EINVAL, "mopo_sac_update: n=%lld", (long long)b->n);
   CUDA_TRY(cudaSetDevice(s->device));
-  return sac_update_impl(s, b->obs, b->act, b->rew, b->term, b->next_obs, (int)b->n, b->eps, b->seed, b->losses_out, (cudaStream_t)stream);
+  return sac_update_impl(s, nullptr, b->obs, b->act, b->rew, b->term, b->next_obs, (int)b->n, b->eps, b->seed, b->losses_out, (cudaStream_t)stream);
 }
 
 // n_updates x { _training_batch (mopo.py:801-821): n_env rows of the env pool then n_model rows of the model pool, drawn
@@ -555,70 +632,21 @@ MOPO_API int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, 
   CUDA_TRY(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
   const int n = n_env + n_model, od = s->od, ad = s->ad;
-  TRY(sac_reserve(s, n));
   TRY(s->ba.reserve((size_t)n * ad * sizeof(float)));
   TRY(s->br.reserve((size_t)n * sizeof(float))); TRY(s->bt.reserve((size_t)n));
   TRY(s->bidx.reserve((size_t)n * sizeof(int64_t)));
-  // observations / next observations are sampled straight into the actor's stacked input [s; s']
-  float *bo = s->Xpi.as<float>(), *ba = s->ba.as<float>(), *br = s->br.as<float>(), *bno = s->Xpi.as<float>() + (size_t)n * od;
-  uint8_t* bt = s->bt.as<uint8_t>();
-  int64_t* bidx = s->bidx.as<int64_t>();
   REQUIRE((n_env == 0 || env_pool->size > 0) && (n_model == 0 || model_pool->size > 0), MOPO_ESTATE, "mopo_sac_update_from_pools: pool is empty");
   const mopo_pool* pools[2] = {env_pool, n_model ? model_pool : env_pool};
   SacSample smp;
-  memset(&smp, 0, sizeof(smp));                     // compared bytewise as the graph's key
+  memset(&smp, 0, sizeof(smp));
   for (int w = 0; w < 2; ++w) {
     smp.obs[w] = pools[w]->obs; smp.act[w] = pools[w]->actions; smp.nobs[w] = pools[w]->next_obs; smp.rew[w] = pools[w]->rewards;
     smp.term[w] = pools[w]->terminals; smp.size[w] = pools[w]->size;
   }
   smp.n_env = n_env; smp.n = n; smp.od = od; smp.ad = ad;
-  const int interval = s->hp.target_update_interval > 0 ? s->hp.target_update_interval : 1;
-  // one iteration: tick (update index, lr_t) -> draw env rows, draw model rows (offsets 2u, 2u + 1 read on the device) -> update
-  auto iteration = [&](float* lo) -> int {
-    MOPO_COUNT_LAUNCH;
-    sac_tick_kernel<<<1, 1, 0, st>>>(s->t, s->d_step, s->lr_t, s->hp.policy_lr, s->hp.q_lr);
-    MOPO_COUNT_LAUNCH;
-    sac_sample_kernel<<<(n * (2 * od + ad + 2) + 255) / 256, 256, 0, st>>>(smp, seed, s->d_step, bo, ba, bno, br, bt, bidx);
-    return sac_update_impl(s, bo, ba, br, bt, bno, n, nullptr, seed, lo, st, true);
-  };
-  int k = 0;
-  // ~45 small launches per update: capture the iteration once per call and replay it (needs a capturable stream, no
-  // per-update host-side variation: Polyak every update, no loss read-back)
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (st) CUDA_TRY(cudaStreamIsCapturing(st, &cap));
-  const bool can_graph = st && cap == cudaStreamCaptureStatusNone && !losses_out && interval == 1 && n_updates > 0;
-  const bool key_match = s->graph && s->g_seed == seed && memcmp(&s->g_smp, &smp, sizeof(smp)) == 0;
-  const bool recurring = s->have_last && s->last_seed == seed && memcmp(&s->last_smp, &smp, sizeof(smp)) == 0;
-  s->last_smp = smp; s->last_seed = seed; s->have_last = true;
-  if (can_graph && (key_match || n_updates >= 8 || recurring)) {
-    TRY(sac_reserve(s, n));
-    TRY(s->ba.reserve((size_t)n * ad * sizeof(float)));
-    bool fresh = false;
-    if (!(s->graph && s->g_seed == seed && memcmp(&s->g_smp, &smp, sizeof(smp)) == 0)) {
-      s->drop_graph();
-      cudaGraph_t g = nullptr;
-      const long long before = (long long)mopo_launch_count();
-      CUDA_TRY(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-      int rc = iteration(nullptr);
-      cudaError_t ce = cudaStreamEndCapture(st, &g);
-      s->updates -= 1;                                // the capture enqueued nothing
-      if (rc != MOPO_OK) { if (g) cudaGraphDestroy(g); return rc; }
-      CUDA_TRY(ce);
-      s->g_nodes = (int)((long long)mopo_launch_count() - before);
-      cudaError_t ci = cudaGraphInstantiate(&s->graph, g, 0);
-      cudaGraphDestroy(g);
-      if (ci != cudaSuccess) s->graph = nullptr;
-      CUDA_TRY(ci);
-      s->g_smp = smp; s->g_seed = seed;
-      fresh = true;                                   // the launches counted during the capture stand for the first replay
-    }
-    for (; k < n_updates; ++k) {
-      CUDA_TRY(cudaGraphLaunch(s->graph, st));
-      if (!(fresh && k == 0)) for (int i = 0; i < s->g_nodes; ++i) mopo_count_launch();
-      s->updates += 1;
-    }
-    return MOPO_OK;
-  }
-  for (; k < n_updates; ++k) TRY(iteration(losses_out ? losses_out + 4 * k : nullptr));
+  // observations / next observations are drawn straight into the actor's stacked input [s; s']; the update index and the Adam
+  // step live on the device, so the n_updates launches queue back to back with nothing read back in between
+  for (int k = 0; k < n_updates; ++k)
+    TRY(sac_update_impl(s, &smp, nullptr, nullptr, nullptr, nullptr, nullptr, n, nullptr, seed, losses_out ? losses_out + 4 * k : nullptr, st));
   return MOPO_OK;
 }

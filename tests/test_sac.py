@@ -160,15 +160,14 @@ def test_sac_train_from_pools_equals_explicit_batches_and_exports_actor():
     b = SACUpdate(od, ad, device=0, seed=99)                       # same seed -> same glorot init
     assert a.batch_sizes() == (12, 244)
     K = 10
-    side = torch.cuda.Stream()                                     # a capturable stream: the 10 updates replay one CUDA graph
+    side = torch.cuda.Stream()                                     # a caller-chosen stream: the updates queue on it back to back
     torch.cuda.synchronize()
     with torch.cuda.stream(side):
         a.train_from_pools(env_pool, model_pool, n_updates=K - 2)
     torch.cuda.synchronize()
-    logs = a.train_from_pools(env_pool, model_pool, n_updates=2, return_losses=True)     # direct launches, same sequence
+    logs = a.train_from_pools(env_pool, model_pool, n_updates=2, return_losses=True)     # with the loss read-back, same sequence
     assert all(np.isfinite(v) for v in logs.values())
-    # the per-environment-step pattern (_do_training_repeats, mopo.py:780-799): one update per call; from the second call
-    # with the same pools on, the captured iteration is kept and replayed across calls
+    # the per-environment-step pattern (_do_training_repeats, mopo.py:780-799): one update per call
     with torch.cuda.stream(side):
         for _ in range(5):
             a.train_from_pools(env_pool, model_pool, n_updates=1)
