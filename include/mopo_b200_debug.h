@@ -35,6 +35,10 @@ int mopo_debug_mma_rate(int cta_group, int N, int nacc, int a_tmem, int ksteps, 
  * iterations completed by the leader CTA's warps. */
 int mopo_debug_mma_interference(int N, int a_tmem, int ksteps, int imode, int n_warps, int with_mma, int icol, long long* out_dev, void* stream);   /* icol: first TMEM column of the interferers' groups (the accumulator is [0, N), the A operand [408, 512)) */
 
+/* Stage timeline of the one-kernel SAC update (csrc/sac.cu): once set, every update writes CTA 0's %globaltimer at kernel
+ * start, after each stage's grid barrier and at the kernel's end into buf (device, >= 64 entries); NULL switches it off. */
+int mopo_debug_sac_trace(mopo_sac* s, unsigned long long* buf);
+
 #ifdef __cplusplus
 }
 #endif

@@ -131,6 +131,7 @@ DEBUG_SYMBOLS = {
     'mopo_debug_mma_interference': (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'mopo_debug_pipe_bench': (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_debug_mma_rate': (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    'mopo_debug_sac_trace': (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

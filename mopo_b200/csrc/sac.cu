@@ -45,7 +45,7 @@ struct SacFused {
   float *par[SAC_TENSORS], *targ[SAC_TENSORS]; int64_t cpref[SAC_TENSORS + 1];   // variables, their Polyak targets (or null), 4-element chunk prefix
   float *Xpi, *H0p, *H1p, *HD, *eps, *logp, *Xq, *Xt, *H0q, *H1q, *Qo, *T0, *T1, *To, *dQo, *dZ1q, *dZ0q, *dXa, *dHD, *dZ1p, *dZ0p;
   float* out;
-  unsigned long long* trace;
+  unsigned long long* trace;                   // null, or where CTA 0 records %globaltimer at its start and after every barrier
   unsigned* bar; unsigned bar_base;          // grid barrier counter (only grows) and its value when this launch starts
   int n_ops; FOp ops[SAC_MAX_OPS];
 };
@@ -286,6 +286,7 @@ struct mopo_sac {
   uint64_t* d_step = nullptr;                         // device Philox step id of the policy noise (advanced by the update kernel)
   int grid = 0;                                       // CTAs of sac_fused_kernel: one per SM (cooperative launch)
   unsigned* bar = nullptr; unsigned bar_count = 0;    // its grid barrier counter and the arrivals launched so far
+  unsigned long long* trace = nullptr;                // probe build: device buffer for CTA 0's globaltimer after every stage
   size_t psize(int i) const {                         // elements of tensor i in SacAdam order
     const int in_q = od + ad;
     const size_t s[SAC_TENSORS] = {(size_t)od * H, (size_t)H, (size_t)H * H, (size_t)H, (size_t)H * 2 * ad, (size_t)2 * ad,
@@ -597,14 +598,10 @@ static int sac_update_impl(mopo_sac* s, const SacSample* smp, const float* obs, 
     a.bar = s->bar; a.bar_base = s->bar_count;
     s->bar_count += (unsigned)stage * (unsigned)s->grid;      // one barrier per stage, every CTA arrives once
   }
-  static unsigned long long* d_trace = nullptr;
-  if (getenv("MOPO_SAC_TRACE") && !d_trace) cudaMalloc(&d_trace, 64 * 8);
-  a.trace = d_trace;
+  a.trace = s->trace;
   void* args[] = {&a};
   MOPO_COUNT_LAUNCH;
   CUDA_TRY(cudaLaunchCooperativeKernel((const void*)sac_fused_kernel, dim3(s->grid), dim3(FUSED_THREADS), args, sizeof(FusedSmem), st));
-  if (d_trace && s->updates == 40) { unsigned long long h[64]; cudaStreamSynchronize(st); cudaMemcpy(h, d_trace, 64 * 8, cudaMemcpyDeviceToHost);
-    for (int i = 1; i < 20; ++i) fprintf(stderr, "stage %d: %.2f us\n", i - 1, (double)(h[i] - h[i - 1]) * 1e-3); }
   if (losses_out) CUDA_TRY(cudaMemcpyAsync(losses_out, s->out, 4 * sizeof(float), cudaMemcpyDeviceToDevice, st));
   s->updates += 1;
   return MOPO_OK;
@@ -650,3 +647,13 @@ MOPO_API int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, 
     TRY(sac_update_impl(s, &smp, nullptr, nullptr, nullptr, nullptr, nullptr, n, nullptr, seed, losses_out ? losses_out + 4 * k : nullptr, st));
   return MOPO_OK;
 }
+
+#ifdef MOPO_DEBUG_PROBES
+// Stage timeline of the update kernel: every later update writes CTA 0's %globaltimer at kernel start, after each stage's
+// barrier and at its end into buf (device, >= 64 entries); NULL switches it off.  tools/sac_probe.py --trace prints it.
+MOPO_API int mopo_debug_sac_trace(mopo_sac* s, unsigned long long* buf) {
+  REQUIRE(s, MOPO_EINVAL, "mopo_debug_sac_trace: null handle");
+  s->trace = buf;
+  return MOPO_OK;
+}
+#endif
