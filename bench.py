@@ -340,10 +340,15 @@ def measure(cx, c, steps, warmup, clocks=False, kernel=True, e2e=True):
         h2d = c.h_obs.numel() * 4 + (0 if c.pol else sum(a.numel() * 4 for a in c.h_acts))
         d2h = c.h_rew.numel() * 4
 
+        import time as _t
+        prof = []
+
         def rollout_e2e():
+            _a = _t.perf_counter()
             # pinned host buffers straight into the public call: it uploads the starts + step 0's actions on the compute
             # stream and the later steps' actions on a side stream, overlapped with the earlier steps
             ro._rollout_model(B, start_obs=c.h_obs, actions=None if c.pol else c.h_acts, origin_base=c.origin, quiet=True)
+            _b = _t.perf_counter()
             pool = ro._model_pool                           # read-back: the penalised rewards of the rollout's last step
             n_last = ro._last_steps_added[-1] if ro._last_steps_added else 0
             last = (pool._pointer - n_last) % pool._max_size
@@ -353,10 +358,16 @@ def measure(cx, c, steps, warmup, clocks=False, kernel=True, e2e=True):
                 k = pool._max_size - last
                 c.h_rew[:k].copy_(pool.fields['rewards'][last:], non_blocking=True)
                 c.h_rew[k:n_last].copy_(pool.fields['rewards'][:n_last - k], non_blocking=True)
+            _c = _t.perf_counter()
             torch.cuda.current_stream(cx.dev).synchronize()
+            _d = _t.perf_counter()
+            prof.append((_b - _a, _c - _b, _d - _c))
             return sum(ro._last_steps_added)
 
         ms_e, trans_e, _, _ = timed(cx, rollout_e2e, steps, warmup)
+        if os.environ.get('MOPO_BENCH_PROF'):
+            import numpy as _np
+            sys.stderr.write('e2e cpu profile (ms): enqueue %.3f  readback-enqueue %.3f  sync-wait %.3f\n' % tuple(_np.median(_np.array(prof[-steps:]), 0) * 1e3))
         v, ms_e_max = whole_job(cx, ms_e, trans_e)
         out['e2e'] = {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h, 'ms_per_step': ms_e_max / steps,
                       'result': 'the rollout result (the pool rows) stays in HBM for the SAC sampler, as the reference returns only '

@@ -77,7 +77,8 @@ MOPO_API int mopo_ens_destroy(mopo_ens* h) {
   for (cudaEvent_t e : h->act_ev) cudaEventDestroy(e);
   if (h->ev_start) cudaEventDestroy(h->ev_start);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
-  h->st_obs.release(); h->st_act.release();
+  h->st_obs.release(); h->st_act.release(); h->ready_flags.release();
+  if (h->flag_src) cudaFreeHost(h->flag_src);
   for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
   DevBuf* bufs[] = {&h->sel, &h->selmv, &h->pen2, &h->xn, &h->xtiles, &h->actA, &h->actB, &h->mean, &h->lv, &h->blk_counts, &h->misc,
                     &h->ro_obs[0], &h->ro_obs[1], &h->ro_origin[0], &h->ro_origin[1], &h->ro_counts, &h->ro_act};
@@ -353,7 +354,7 @@ MOPO_API int mopo_ens_predict3d(mopo_ens* h, const float* x, int64_t B, float* m
 static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_kind, int deterministic,
                         const float* obs, const float* act, int64_t B, const int* d_n, const int32_t* model_inds,
                         uint64_t seed, uint64_t step_id, const int32_t* origin, int64_t origin_base,
-                        TailArgs* t, cudaStream_t st, bool tiles_ready = false, bool pdl = false) {
+                        TailArgs* t, cudaStream_t st, bool tiles_ready = false, bool pdl = false, const InputReady* ready = nullptr) {
   const int E = h->E, D1 = h->D1;
   const int path = ens_path(h, precision);
   REQUIRE_PATH(path, precision);
@@ -385,6 +386,7 @@ static int step_forward(mopo_ens* h, int precision, bool want_diag, int penalty_
     // streamed-weights kernel: reads obs / act itself (scaler and hi/lo split inside); only the elite picks come first
     if (fused && !tiles_ready) TRY(tc3_pick(h, q.sel, model_inds, B, d_n, seed, step_id, origin, origin_base, st));
     Tc3In x = {obs, act, h->cfg.obs_dim, h->cfg.act_dim, true};
+    if (ready) x.ready = *ready;
     return tc3_launch(h, path == PATH_TC3 ? 3 : 1, x, B, d_n, o, st);
   }
   TRY(h->xn.reserve(sizeof(float) * B * h->in));
@@ -667,8 +669,15 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
     }
     TRY(step_forward(h, a->precision, false, a->penalty_kind, a->deterministic, obs_cur, act_i, B, d_n,
                      a->model_inds ? a->model_inds[i] : nullptr, a->seed, step_id, origin_cur, a->origin_base, &t, st,
-                     (chain && i > 0) || tiles_done || (compact_tiles && i > 0), (pdl && !a->action_events) || (pdl_pol && tiles_done)));
+                     (chain && i > 0) || tiles_done || (compact_tiles && i > 0), (pdl && !a->action_events) || (pdl_pol && tiles_done),
+                     (h->host_ready_on && streamed && (int)h->host_ready.size() == H) ? &h->host_ready[i] : nullptr));
+    if (i == 0 && h->after_first_forward) {                 // (mopo_rollout_host: the kernel is polling the first chunk's flag by now)
+      int (*hook)(void*) = h->after_first_forward;
+      h->after_first_forward = nullptr;
+      TRY(hook(h->after_first_forward_ctx));
+    }
     t.pdl = (chain && pdl) || (pdl_pol && tiles_done);
+    if (h->host_ready_on && streamed && (int)h->host_ready.size() == H) t.ready = h->host_ready[i];
     if (chain && i + 1 < H) {
       if (!streamed) {
         t.xt_next = h->xtiles.as<uint4>(); t.act_next = a->actions[i + 1]; t.mu = h->mu; t.sigma = h->sigma;
@@ -758,9 +767,86 @@ MOPO_API int mopo_rollout_host(mopo_ens* h, mopo_pool* pool, const mopo_rollout_
   if (h->st_obs.cap < sizeof(float) * B * od || (host_actions && h->st_act.cap < sizeof(float) * B * ad * H)) CUDA_TRY(cudaDeviceSynchronize());
   TRY(h->st_obs.reserve(sizeof(float) * B * od));
   if (host_actions) TRY(h->st_act.reserve(sizeof(float) * B * ad * H));
-  CUDA_TRY(cudaMemcpyAsync(h->st_obs.p, a->start_obs, sizeof(float) * B * od, cudaMemcpyHostToDevice, st));
   std::vector<const float*> d_act(H, nullptr);
   std::vector<void*> evs(H, nullptr);
+  const int path = ens_path(h, a->precision);
+  // Streamed-weights kernel: its forward reads obs / act itself, so the rollout need not wait for the uploads at all -- the
+  // inputs go up in chunks on the copy stream, each followed by a stream-ordered 4-byte copy into its flag; step 0's forward
+  // starts at once, runs its units tile-major (every pair strides through the tiles in upload order) and polls the flag of a
+  // tile's chunk before it touches the rows (first chunks small: the kernel is launched behind the first 0.3 MB, the other chunks
+  // are enqueued while it already runs); the later steps' actions likewise, in fewer chunks.  The step tail, which may start
+  // under the forward (programmatic launch), looks at the flag once and otherwise reads its inputs behind the forward.
+  // (MOPO_NO_INPUT_FLAGS: developer A/B switch back to whole-array uploads behind events.)
+  const bool flagged = host_actions && (path == PATH_TC3 || path == PATH_TC1) && getenv("MOPO_NO_INPUT_FLAGS") == nullptr;
+  h->host_ready_on = false;
+  if (flagged) {
+    if (h->ready_flags.cap < sizeof(uint32_t) * 8 * H) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      TRY(h->ready_flags.reserve(sizeof(uint32_t) * 8 * H));
+      CUDA_TRY(cudaMemset(h->ready_flags.p, 0, h->ready_flags.cap));
+    }
+    if (!h->flag_src) {                                              // pinned constants 0x01010101 b: the sources of the flag writes
+      CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&h->flag_src), 256 * sizeof(uint32_t), cudaHostAllocDefault));
+      for (uint32_t bb = 0; bb < 256; ++bb) h->flag_src[bb] = 0x01010101u * bb;
+    }
+    h->ready_epoch = h->ready_epoch % 255 + 1;                       // 1 .. 255: never the byte the flags hold from the call before
+    const int byte = (int)h->ready_epoch;
+    const int nT = (int)((B + 255) / 256);
+    h->host_ready.assign(H, InputReady());
+    // the copy stream starts behind the previous rollout on `st`, which may still read the staging buffers
+    CUDA_TRY(cudaEventRecord(h->ev_start, st));
+    CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->ev_start, 0));
+    uint32_t* flags = h->ready_flags.as<uint32_t>();
+    for (int i = 0; i < H; ++i) {
+      REQUIRE(a->actions[i], MOPO_EINVAL, "mopo_rollout_host: actions[%d] null", i);
+      d_act[i] = h->st_act.as<float>() + (size_t)i * B * ad;
+      InputReady& r = h->host_ready[i];
+      r.flags = flags + 8 * i; r.value = 0x01010101u * (uint32_t)byte;
+      const int div0[5] = {16, 8, 4, 2, 1}, div1[4] = {8, 4, 2, 1}, div2[2] = {2, 1};   // later steps have had time: fewer chunks
+      const int* dv = i == 0 ? div0 : i == 1 ? div1 : div2;
+      const int n_frac = i == 0 ? 5 : i == 1 ? 4 : 2;
+      r.n = 0;
+      for (int c = 0; c < n_frac; ++c) {
+        const int end = (nT + dv[c] - 1) / dv[c];
+        if (r.n == 0 || end > r.end_tile[r.n - 1]) r.end_tile[r.n++] = end;
+      }
+    }
+    // chunk c of step i: [obs rows,] action rows, then the flag
+    struct Upload {
+      mopo_ens* h; const mopo_rollout_args* a; int64_t B; int od, ad, H, byte; const float* const* d_act; const uint32_t* flag_src;
+      int chunk(int i, int c) const {
+        const InputReady& r = h->host_ready[i];
+        const int64_t row0 = c ? std::min<int64_t>(B, (int64_t)r.end_tile[c - 1] * 256) : 0, row1 = std::min<int64_t>(B, (int64_t)r.end_tile[c] * 256);
+        const int64_t rows = row1 - row0;
+        cudaStream_t cs = h->copy_stream;
+        if (i == 0) CUDA_TRY(cudaMemcpyAsync(h->st_obs.as<float>() + row0 * od, a->start_obs + row0 * od, sizeof(float) * rows * od, cudaMemcpyHostToDevice, cs));
+        CUDA_TRY(cudaMemcpyAsync(const_cast<float*>(d_act[i]) + row0 * ad, a->actions[i] + row0 * ad, sizeof(float) * rows * ad, cudaMemcpyHostToDevice, cs));
+        CUDA_TRY(cudaMemcpyAsync(const_cast<uint32_t*>(r.flags) + c, flag_src + byte, sizeof(uint32_t), cudaMemcpyHostToDevice, cs));   // (a copy-engine write)
+        return MOPO_OK;
+      }
+      int rest() const {
+        for (int i = 0; i < H; ++i)
+          for (int c = i == 0 ? 1 : 0; c < h->host_ready[i].n; ++c) TRY(chunk(i, c));
+        return MOPO_OK;
+      }
+      static int hook(void* self) { return static_cast<const Upload*>(self)->rest(); }
+    } up = {h, a, B, od, ad, H, byte, d_act.data(), h->flag_src};
+    TRY(up.chunk(0, 0));                               // the first 1/16 of step 0's rows; everything else once its forward is launched
+    h->after_first_forward = &Upload::hook; h->after_first_forward_ctx = &up;
+    h->host_ready_on = true;
+    mopo_rollout_args b = *a;
+    b.start_obs = h->st_obs.as<float>();
+    b.actions = d_act.data(); b.action_events = nullptr;
+    int rc = mopo_rollout(h, pool, &b, stream);
+    h->host_ready_on = false;
+    if (h->after_first_forward) {                      // the rollout failed before its first forward: the caller's buffers must still not be left half read
+      h->after_first_forward = nullptr;
+      const int rc2 = up.rest();
+      if (rc == MOPO_OK) rc = rc2;
+    }
+    return rc;
+  }
+  CUDA_TRY(cudaMemcpyAsync(h->st_obs.p, a->start_obs, sizeof(float) * B * od, cudaMemcpyHostToDevice, st));
   if (host_actions) {
     for (int i = 0; i < H; ++i) {
       REQUIRE(a->actions[i], MOPO_EINVAL, "mopo_rollout_host: actions[%d] null", i);

@@ -174,6 +174,8 @@ struct T3Args {
   int E;
   S3 s;
   unsigned long long* trace;   // debug timeline (mopo_debug_tc3_trace, probe build only) or nullptr
+  InputReady ready;            // chunk flags of inputs still in flight over PCIe (units then run tile-major), or flags == nullptr
+  int tile_major;
 };
 
 struct Bars3 {
@@ -291,8 +293,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
   const int pair = blockIdx.x / 2, n_pairs = gridDim.x / 2;
   const int n = __shfl_sync(0xffffffffu, a.d_n ? min(*a.d_n, a.n_max) : a.n_max, 0);
   const int nT = (n + 255) / 256;
-  const int64_t U = (int64_t)a.E * nT;                  // (net, tile) units, net-major
-  const int u0 = (int)(U * pair / n_pairs), u1 = (int)(U * (pair + 1) / n_pairs);
+  const int64_t U = (int64_t)a.E * nT;                  // (net, tile) units: net-major, or tile-major while the inputs arrive
+  const bool tile_major = a.tile_major != 0;
+  auto net_of = [&](int u) { return tile_major ? u % a.E : u / nT; };
+  auto tile_of = [&](int u) { return tile_major ? u / a.E : u % nT; };
+  // a pair's units: a contiguous block [U p / P, U (p + 1) / P), or -- while the inputs arrive tile by tile -- every P-th unit
+  // from p on, so that all pairs move through the tiles in upload order
+  const int ustep = tile_major ? n_pairs : 1;
+  const int u0 = tile_major ? pair : (int)(U * pair / n_pairs), u1 = tile_major ? (int)U : (int)(U * (pair + 1) / n_pairs);
 
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
@@ -336,7 +344,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
       uint32_t li = 0;
       const uint32_t hw_w0 = 2 * (uint32_t)s.head_part();            // offset of the W0 blob inside a [head | W0] stage
       const size_t off_w0 = 0, off_h = 2 * (size_t)s.w0_part() + 3 * (size_t)STAGE;
-      auto img_of = [&](int u) { return a.img + ((size_t)(u / nT) * 2 + rank) * s.img_bytes(); };
+      auto img_of = [&](int u) { return a.img + ((size_t)net_of(u) * 2 + rank) * s.img_bytes(); };
       auto stage_wait = [&](int tag) {
         const uint32_t st = li & 1;
         if (li >= 2) mbar_wait_relaxed(&bars->w_free[st], ((li >> 1) - 1) & 1, 1000 + tag);
@@ -355,7 +363,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         bulk_g2s(sW + st * STAGE + hw_w0, img_of(u0) + off_w0, 2 * (uint32_t)s.w0_part(), &bars->w_full[st]);
         stage_done(st, 0);
       }
-      for (int u = u0; u < u1; ++u) {
+      for (int u = u0; u < u1; u += ustep) {
         const uint8_t* src = img_of(u);
         for (int j = 1; j < 4; ++j) {
           const uint32_t st = stage_wait(j);
@@ -366,10 +374,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
           stage_done(st, j);
         }
         const uint32_t st = stage_wait(4);
-        const bool more = u + 1 < u1;
+        const bool more = u + ustep < u1;
         mbar_expect_tx(&bars->w_full[st], 2 * (uint32_t)s.head_part() + (more ? 2 * (uint32_t)s.w0_part() : 0u));
         bulk_g2s(sW + st * STAGE, src + off_h, 2 * (uint32_t)s.head_part(), &bars->w_full[st]);
-        if (more) bulk_g2s(sW + st * STAGE + hw_w0, img_of(u + 1) + off_w0, 2 * (uint32_t)s.w0_part(), &bars->w_full[st]);
+        if (more) bulk_g2s(sW + st * STAGE + hw_w0, img_of(u + ustep) + off_w0, 2 * (uint32_t)s.w0_part(), &bars->w_full[st]);
         stage_done(st, 4);
       }
     }
@@ -421,7 +429,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         __syncwarp();
         ++li;
       }
-      for (int u = u0; u < u1; ++u) {
+      for (int u = u0; u < u1; u += ustep) {
         for (int j = 1; j < 5; ++j, ++li) {
           const uint32_t st = li & 1;
           const uint32_t wb = wa + st * STAGE;
@@ -453,7 +461,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
             // [head | W0'] stage.  Layer 0 of the NEXT unit goes to the tensor pipe first: it writes buffer 0 (free since
             // layer 3's MMAs were issued) while the epilogue still turns layer 3's accumulator (buffer 1) into the head's
             // A operand, and its own epilogue then runs under the head MMA.
-            if (u + 1 < u1) issue_l0(wb + hw_w0);
+            if (u + ustep < u1) issue_l0(wb + hw_w0);
             // the head MMA overwrites the previous unit's head accumulator: the head warps must have read it
             if (n_h > 0) mbar_wait_cluster_backoff<MOPO_TC3_POLL_NS>(&bars->h_done, (n_h - 1) & 1, 44);
             ++n_h;
@@ -487,7 +495,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     const uint32_t tlane = tbase + ((uint32_t)(q * 32) << 16);
     uint32_t n_d = 0, n_u = 0;                          // hidden layers 1..3 / units consumed (every barrier flips once per layer)
     uint32_t va[16], vb[16];
-    for (int u = u0; u < u1; ++u, ++n_u) {
+    for (int u = u0; u < u1; u += ustep, ++n_u) {
       for (int j = 0; j < 4; ++j) {
         const uint32_t buf = tlane + ((j & 1) ? C_BUF1 : C_BUF0);
         uint64_t* dfull = j == 0 ? bars->d0_full : bars->d_full;
@@ -540,11 +548,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     const int kcs = s.K0 / 8;
     pdl_wait();
     // x block of unit u: this thread's row -> K-panels (hi | lo) of the SS-form A operand of layer 0
+    int ready_tiles = 0;
     auto produce_x = [&](int u) {
-      const int t = u % nT;
+      const int t = tile_of(u);
+      if (a.ready.flags && t >= ready_tiles) {           // this tile's rows may still be on their way: wait for its chunk's flag
+        int c = 0;
+        while (c + 1 < a.ready.n && t >= a.ready.end_tile[c]) ++c;
+        if (lane == 0) {
+          uint32_t v, spins = 0;
+          do {
+            asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(a.ready.flags + c) : "memory");
+            if (v == a.ready.value) break;
+            __nanosleep(500);
+          } while (++spins < (1u << 22));                // (~2 s: a lost upload must not hang the device)
+          __threadfence();                               // the rows are read (ld.global.cg) after the flag
+        }
+        __syncwarp();
+        ready_tiles = a.ready.end_tile[c];               // chunks arrive in order: nothing below this needs another look
+      }
       const int64_t row = 256 * (int64_t)t + (int64_t)rank * 128 + rr;
       const bool ok = row < n;
-      const int64_t src_row = row + (int64_t)(u / nT) * a.net_stride;
+      const int64_t src_row = row + (int64_t)net_of(u) * a.net_stride;
       const float* po = a.obs + src_row * a.od;
       const float* pa = a.act + src_row * a.ad;
       // four K-panels (32 input columns) per pass, all their loads issued before the first use: the first block of a launch
@@ -555,7 +579,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         for (int i = 0; i < 32; ++i) {
           const int k = kc0 * 8 + i;
           raw[i] = 0.0f;
-          if (ok && k < s.in) raw[i] = k < a.od ? po[k] : pa[k - a.od];
+          if (ok && k < s.in) raw[i] = __ldcg(k < a.od ? po + k : pa + (k - a.od));   // L2: the rows may have landed after a neighbour's line was cached
         }
 #pragma unroll
         for (int pnl = 0; pnl < 4; ++pnl) {
@@ -588,12 +612,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     };
     if (u0 < u1) produce_x(u0);
     uint32_t n_h = 0;
-    for (int u = u0; u < u1; ++u, ++n_h) {
-      const int e = u / nT, t = u - e * nT;
-      if (u + 1 < u1) {
+    for (int u = u0; u < u1; u += ustep, ++n_h) {
+      const int e = net_of(u), t = tile_of(u);
+      if (u + ustep < u1) {
         mbar_wait_relaxed(&bars->x_free, n_h & 1, 200);          // layer 0 of unit u has consumed the block
         if (q == 0) TR(4, 150);
-        produce_x(u + 1);
+        produce_x(u + ustep);
         if (q == 0) TR(4, 250);
       }
       const int64_t row = 256 * (int64_t)t + (int64_t)rank * 128 + rr;
@@ -682,6 +706,8 @@ int tc3_launch(mopo_ens* h, int terms, const Tc3In& x, int64_t n_max, const int*
   a.out.sel = o.sel; a.out.selmv = o.selmv; a.out.pen2 = o.pen2; a.out.E = h->E;
   a.n_max = (int)n_max; a.d_n = d_n; a.E = h->E;
   a.trace = reinterpret_cast<unsigned long long*>(h->tc_trace);
+  a.ready = x.ready;
+  a.tile_major = x.ready.flags != nullptr;
   const size_t smem = tc3_smem_bytes(a.s);
   const int n_pairs = h->sm_count / 2;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;

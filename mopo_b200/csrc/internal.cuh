@@ -62,6 +62,10 @@ struct DevBuf {
   template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// Inputs that are still arriving over PCIe while the kernel runs (mopo_rollout_host): chunk c covers the 256-row tiles
+// [end_tile[c-1], end_tile[c]) and is complete once flags[c] == value (a stream-ordered memset behind the chunk's copies).
+struct InputReady { const uint32_t* flags = nullptr; uint32_t value = 0; int n = 0; int end_tile[8] = {}; };
+
 struct mopo_train;   // optimiser state while BNN.train runs (train.cu)
 
 struct mopo_ens {
@@ -99,6 +103,10 @@ struct mopo_ens {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_start = nullptr;
   std::vector<cudaEvent_t> act_ev;
+  // mopo_rollout_host on the streamed-weights kernel: inputs arrive in chunks behind flags the forward polls (ens_tc3.cu)
+  DevBuf ready_flags; uint32_t ready_epoch = 0; std::vector<InputReady> host_ready; bool host_ready_on = false;
+  uint32_t* flag_src = nullptr;
+  int (*after_first_forward)(void*) = nullptr; void* after_first_forward_ctx = nullptr;   // the rest of the uploads, enqueued once step 0's forward is launched
 };
 void mopo_train_release(mopo_ens* h);
 
@@ -145,6 +153,7 @@ struct Tc3In {
   const float *obs, *act; int od, ad;     // x = concat(obs [n, od], act [n, ad]); ad == 0: obs is the whole input row
   bool scale;                             // apply the handle's scaler (false: x is already scaled)
   int64_t net_stride = 0;                 // rows between consecutive nets' inputs (0: every net reads the same rows)
+  InputReady ready;                       // flags == nullptr: the inputs are complete when the kernel starts
 };
 int tc3_pick(mopo_ens* h, int32_t* sel, const int32_t* model_inds, int64_t n_max, const int* d_n, uint64_t seed,
              uint64_t step_id, const int32_t* origin, int64_t origin_base, cudaStream_t st);
@@ -172,6 +181,7 @@ struct TailArgs {
   float *p_act, *p_rew, *p_obs, *p_nobs; uint8_t* p_term; int64_t pool_max, pool_base; const int64_t* d_pool_off;
   // optional compaction bookkeeping
   int* blk_counts;             // [ceil(n_max/TAIL_ROWS)] survivors per block
+  InputReady ready;            // obs / act may still be in flight when a programmatic launch starts this grid (flags == nullptr: no)
 };
 int launch_prep(const float* obs, const float* act, const float* mu, const float* sigma, float* xn,
                 int64_t n_max, const int* d_n, int obs_dim, int act_dim, cudaStream_t st);

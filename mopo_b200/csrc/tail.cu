@@ -217,6 +217,15 @@ __global__ void __launch_bounds__(TAIL_ROWS * TQ, 3) step_tail_fused_kernel(Tail
   // --- part 1: everything that does not depend on the forward kernel's outputs (under a programmatic dependent launch
   // this runs while the forward kernel's last CTA pairs are still busy): input spans -> smem, Philox draws, elite pick
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (a.ready.flags) {                   // obs / act may still be arriving over PCIe (mopo_rollout_host): one look at this block's
+    int c = 0;                           // chunk flag -- not there yet: read the inputs behind the forward, which has waited for them
+    const int tile = (int)((j0 + TAIL_ROWS - 1) / 256);
+    while (c + 1 < a.ready.n && tile >= a.ready.end_tile[c]) ++c;
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(a.ready.flags + c) : "memory");
+    if (!__syncthreads_and(v == a.ready.value)) asm volatile("griddepcontrol.wait;" ::: "memory");
+    else __threadfence();
+  }
   uint32_t orow = 0;
   float z[GMAX][4];
   int32_t pick = 0;

@@ -379,17 +379,18 @@ def test_callback_rollout_matches_fused():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('precision_name', ['bf16', 'fp32'])
-def test_rollout_host_actions_overlapped_upload_equals_device_actions(precision_name):
-    """Pinned host action arrays are uploaded on a side stream behind per-step events (mopo_rollout_args.action_events);
-    the pool must equal the one produced from device-resident actions, bit for bit."""
+@pytest.mark.parametrize('precision_name,B', [('bf16', 3000), ('fp32', 3000), ('fp32', 50000), ('fp32', 300)])
+def test_rollout_host_actions_overlapped_upload_equals_device_actions(precision_name, B):
+    """Pinned host start states / action arrays are uploaded while the rollout runs -- bf16: behind per-step events
+    (mopo_rollout_args.action_events); fp32 (streamed-weights kernel): in chunks behind flags the forward polls, units
+    tile-major -- and the pool must equal the one produced from device-resident inputs, bit for bit."""
     import torch
     from mopo_b200 import _lib
     from mopo_b200.models.fake_env import FakeEnv
     from mopo_b200.replay_pools import SimpleReplayPool
     from mopo_b200.algorithms.mopo import ModelRollout
     import mopo_b200.static as static
-    B, h = 3000, 4
+    h = 4
     p, obs, _ = ens.synthetic_case('halfcheetah', B, seed=61)
     prec = {'bf16': _lib.PREC_BF16, 'fp32': _lib.PREC_FP32}[precision_name]
     m = make_model(p, precision=prec)
