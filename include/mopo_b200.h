@@ -114,6 +114,16 @@ int mopo_ens_set_elites(mopo_ens* h, const int32_t* elites, int32_t n);
 int mopo_ens_predict(mopo_ens* h, const float* x, int64_t B, float* mean, float* var,
                      int precision, void* stream);
 
+/* BNN.predict(x, factored=True) like mopo_ens_predict with MOPO_PREC_FP32_REF (the FFMA kernels), but allocating NOTHING: no
+ * cudaMalloc / cudaFree / allocating library call on any path.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The scratch (scaled inputs, two [E,B,hidden] activation buffers, log-variances) is a static device array of
+ * MOPO_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; a B that needs more is rejected with
+ * MOPO_EINVAL (HalfCheetah shapes: B <= 1422).  x [B,in], mean / var [E,B,D1]: device fp32, caller-owned.  ALL calls share the
+ * one array (it keeps the last call's contents; nothing in it must start at zero): calls that overlap on the GPU race. */
+#define MOPO_NOALLOC_SCRATCH_BYTES (16u << 20)
+int mopo_ens_predict_noalloc(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, void* stream);
+
 /* BNN.predict with 3-D inputs (bnn.py:541-545; fc.py:100-101: net e sees x[e]): x [E,B,in] device fp32 -> mean, var [E,B,D1]. */
 int mopo_ens_predict3d(mopo_ens* h, const float* x, int64_t B, float* mean, float* var,
                        int precision, void* stream);

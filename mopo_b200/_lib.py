@@ -79,6 +79,7 @@ SYMBOLS = {
     'mopo_ens_refresh_images': (C.c_int, [C.c_void_p, C.c_void_p]),
     'mopo_ens_predict': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_predict3d': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    'mopo_ens_predict_noalloc': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     'mopo_ens_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     'mopo_ens_train_begin': (C.c_int, [C.c_void_p, C.c_float, C.POINTER(C.c_float)]),
     'mopo_ens_train_reset': (C.c_int, [C.c_void_p]),

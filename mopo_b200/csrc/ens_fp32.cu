@@ -8,6 +8,7 @@
 // One launch per layer, activations [E,chunk,H] ping-pong through HBM: simple and exact;
 // the tensor-core path in ens_tc.cu is the fast one.
 #include "gemm_fp32.cuh"   // load4, softplus_f, TM / TN
+#include <mutex>
 
 namespace {
 
@@ -124,4 +125,77 @@ int fp32_forward(mopo_ens* h, const float* xn, int64_t n_max, const int* d_n, fl
                                           h->max_lv, h->min_lv, (int)n_max, d_n, h->HO, K, h->D1);
   CUDA_TRY(cudaGetLastError());
   return MOPO_OK;
+}
+
+// ---- mopo_ens_predict_noalloc: BNN.predict(factored=True) on this file's FFMA kernels with NO allocation ----------------------
+// (No counterpart in the reference: added for callers that cannot call cudaMalloc --
+// code under CUDA graph capture, tight serving loops, harnesses that forbid it.)  fp32_forward above keeps its scaled inputs and
+// the [E, B, H] activation ping-pong in DevBufs that grow with cudaMalloc; this variant carves the same buffers out of ONE
+// file-scope device array of MOPO_NOALLOC_SCRATCH_BYTES, which every GPU that loads the library holds until exit.  All calls, on
+// every handle and stream, share the array and it keeps the last call's contents: calls that overlap on the GPU race (serialise
+// them on one stream or with events).  Nothing in it has to start at zero -- every word a call reads (xn, the activations, the
+// log-variances) is written earlier in the same call by its own kernels -- so nothing is cleared.
+namespace {
+
+constexpr size_t NOALLOC_FLOATS = MOPO_NOALLOC_SCRATCH_BYTES / sizeof(float);
+static __device__ __align__(256) float g_noalloc_scratch[NOALLOC_FLOATS];
+
+constexpr int NOALLOC_MAX_DEV = 64;
+float* g_noalloc_ptr[NOALLOC_MAX_DEV] = {};     // device address of the array per device (the symbol itself is a host-side stand-in)
+std::mutex g_noalloc_mu;
+
+// once per device, with that device current
+int noalloc_scratch(int device, float** out) {
+  if (device < 0 || device >= NOALLOC_MAX_DEV) { mopo_set_error("mopo_ens_predict_noalloc: device %d out of range", device); return MOPO_EINVAL; }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    float* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+    g_noalloc_ptr[device] = p;
+  }
+  *out = g_noalloc_ptr[device];
+  return MOPO_OK;
+}
+
+inline size_t round64(size_t n) { return (n + 63) & ~(size_t)63; }      // 256-byte aligned sub-buffers
+
+}  // namespace
+
+MOPO_API int mopo_ens_predict_noalloc(mopo_ens* h, const float* x, int64_t B, float* mean, float* var, void* stream) {
+  REQUIRE(h && (B == 0 || (x && mean && var)), MOPO_EINVAL, "mopo_ens_predict_noalloc: null argument");
+  REQUIRE(B >= 0 && B < (1ll << 31), MOPO_EINVAL, "mopo_ens_predict_noalloc: B=%lld", (long long)B);
+  REQUIRE(h->params_set, MOPO_ESTATE, "mopo_ens_predict_noalloc: parameters not set");
+  if (B == 0) return MOPO_OK;
+  const int E = h->E, H = h->H, D1 = h->D1;
+  // scratch: xn [B, in] | act A [E, B, H] | act B [E, B, H] | logvar [E, B, D1]
+  const size_t n_x = round64((size_t)B * h->in), n_act = round64((size_t)E * B * H), n_lv = round64((size_t)E * B * D1);
+  const size_t need = n_x + (h->L > 0 ? (h->L > 1 ? 2 : 1) : 0) * n_act + n_lv;
+  REQUIRE(need <= NOALLOC_FLOATS, MOPO_EINVAL,
+          "mopo_ens_predict_noalloc: B=%lld rows need %zu bytes of scratch, the static array holds %zu (MOPO_NOALLOC_SCRATCH_BYTES); "
+          "split the batch or use mopo_ens_predict", (long long)B, need * sizeof(float), (size_t)MOPO_NOALLOC_SCRATCH_BYTES);
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(cudaSetDevice(h->cfg.device));
+  float* base = nullptr;
+  TRY(noalloc_scratch(h->cfg.device, &base));
+  float* xn = base;
+  float* bufs[2] = {base + n_x, base + n_x + n_act};
+  float* lv = base + n_x + (h->L > 0 ? (h->L > 1 ? 2 : 1) : 0) * n_act;
+  TRY(launch_prep(x, x, h->mu, h->sigma, xn, B, nullptr, h->in, 0, st));          // x is already concat(obs, act)
+  const int64_t strideAct = B * (int64_t)H;
+  dim3 blk(256);
+  const float* A = xn;
+  int64_t strideA = 0;
+  int lda = h->in, K = h->in;
+  for (int l = 0; l < h->L; ++l) {
+    dim3 grid((H + BN - 1) / BN, (unsigned)((B + BM - 1) / BM), E);
+    float* out = bufs[l & 1];
+    MOPO_COUNT_LAUNCH, ens_layer_fp32<0><<<grid, blk, 0, st>>>(A, strideA, lda, h->W[l], h->b[l], out, strideAct, nullptr, nullptr, 0,
+                                                            nullptr, nullptr, (int)B, nullptr, H, K, 0);
+    A = out; strideA = strideAct; lda = H; K = H;
+  }
+  dim3 grid((h->HO + BN - 1) / BN, (unsigned)((B + BM - 1) / BM), E);
+  MOPO_COUNT_LAUNCH, ens_layer_fp32<1><<<grid, blk, 0, st>>>(A, strideA, lda, h->W[h->L], h->b[h->L], nullptr, 0, mean, lv, B,
+                                                          h->max_lv, h->min_lv, (int)B, nullptr, h->HO, K, D1);
+  CUDA_TRY(cudaGetLastError());
+  return launch_exp(lv, var, (int64_t)E * B * D1, st);
 }
