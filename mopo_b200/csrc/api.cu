@@ -677,6 +677,7 @@ MOPO_API int mopo_rollout(mopo_ens* h, mopo_pool* pool, const mopo_rollout_args*
       TRY(hook(h->after_first_forward_ctx));
     }
     t.pdl = (chain && pdl) || (pdl_pol && tiles_done);
+    t.obs_behind = t.pdl && i > 0;
     if (h->host_ready_on && streamed && (int)h->host_ready.size() == H) t.ready = h->host_ready[i];
     if (chain && i + 1 < H) {
       if (!streamed) {

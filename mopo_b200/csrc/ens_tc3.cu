@@ -556,11 +556,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
         while (c + 1 < a.ready.n && t >= a.ready.end_tile[c]) ++c;
         if (lane == 0) {
           uint32_t v, spins = 0;
-          do {
+          for (;;) {
             asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(a.ready.flags + c) : "memory");
             if (v == a.ready.value) break;
             __nanosleep(500);
-          } while (++spins < (1u << 22));                // (~2 s: a lost upload must not hang the device)
+            if (++spins > (1u << 24)) asm volatile("trap;");   // ~10 s: a lost upload fails the launch instead of computing on garbage
+          }
           __threadfence();                               // the rows are read (ld.global.cg) after the flag
         }
         __syncwarp();

@@ -182,6 +182,7 @@ struct TailArgs {
   // optional compaction bookkeeping
   int* blk_counts;             // [ceil(n_max/TAIL_ROWS)] survivors per block
   InputReady ready;            // obs / act may still be in flight when a programmatic launch starts this grid (flags == nullptr: no)
+  bool obs_behind;             // obs is the previous step's tail output and this grid is launched programmatically: read it behind the wait
 };
 int launch_prep(const float* obs, const float* act, const float* mu, const float* sigma, float* xn,
                 int64_t n_max, const int* d_n, int obs_dim, int act_dim, cudaStream_t st);

@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(TAIL_ROWS * TQ, 3) step_tail_fused_kernel(Tail
   float z[GMAX][4];
   int32_t pick = 0;
   {
-    span_copy<NT>(sObs, a.obs + j0 * od, rows * od, tid);
+    if (!a.obs_behind) span_copy<NT>(sObs, a.obs + j0 * od, rows * od, tid);
     span_copy<NT>(sAct, a.act + j0 * ad, rows * ad, tid);
     if (a.xt_next) {
       span_copy<NT>(sActN, a.act_next + j0 * ad, rows * ad, tid);
@@ -255,6 +255,9 @@ __global__ void __launch_bounds__(TAIL_ROWS * TQ, 3) step_tail_fused_kernel(Tail
   }
   // --- part 2: the forward kernel's outputs
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  // obs written by the PREVIOUS step's tail: that grid is only known to be complete behind this wait (the forward between the
+  // two tails waited for it; this grid may have started before it ended)
+  if (a.obs_behind) span_copy<NT>(sObs, a.obs + j0 * od, rows * od, tid);
   float2 mv[GMAX][4];
   float p2a[MOPO_MAX_E], p2b[MOPO_MAX_E];
   if (ok) {
