@@ -239,14 +239,41 @@ __device__ __forceinline__ void group_store(uint32_t taddr, const uint32_t (&v)[
   // MUFU instructions of the following pairs in the instruction stream: with all 16 swishes first and all 8 splits after
   // them every warp had a ~60-instruction tail without a single MUFU, and the warps of a round run in phase.
   uint32_t o[16];
+  constexpr float sc = TERMS == 3 ? 1.0f / W_SCALE : 1.0f;
+#if !defined(MOPO_TC3_NO_SHARED_RCP)
+  if constexpr (TERMS == 3) {
+    // The sigmoids of FOUR features share ONE reciprocal (batch inversion): with d_i = 1 + 2^min(-x_i log2 e, 30),
+    // r = rcp(d0 d1 d2 d3), 1/d0 = d1 (d2 d3 r), ... -- five MUFU results per four activations instead of eight (the MUFU is this
+    // kernel's busiest pipe) for nine more FMULs.  The clamp keeps the product finite (<= 2^121); below x = -20.8 swish is
+    // < 2e-8 in magnitude either way.  Relative error ~4e-7 (was 3e-7): the path's measured error is unchanged.
 #pragma unroll
-  for (int p = 0; p < 8; ++p) {
-    const float sc = TERMS == 3 ? 1.0f / W_SCALE : 1.0f;
-    float s0 = swish_acc<TERMS>(sc * __uint_as_float(v[2 * p]));
-    const float s1 = swish_acc<TERMS>(sc * __uint_as_float(v[2 * p + 1]));
-    if (p == 4 && ones) s0 = 1.0f;
-    if constexpr (TERMS == 3) split2(s0, s1, o[p], o[8 + p]);
-    else { o[p] = pack_bf16x2(s0, s1); o[8 + p] = 0u; }
+    for (int q = 0; q < 4; ++q) {
+      float x[4], d[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        x[i] = sc * __uint_as_float(v[4 * q + i]);
+        d[i] = 1.0f + ex2_approx(fminf(-1.44269504f * x[i], 30.0f));
+      }
+      const float p01 = d[0] * d[1], p23 = d[2] * d[3];
+      const float r = rcp_approx(p01 * p23);
+      const float r01 = r * p23, r23 = r * p01;
+      float s0 = x[0] * (d[1] * r01);
+      const float s1 = x[1] * (d[0] * r01), s2 = x[2] * (d[3] * r23), s3 = x[3] * (d[2] * r23);
+      if (q == 2 && ones) s0 = 1.0f;                                   // feature 8 of group 12 = column 200: the bias row's constant
+      split2(s0, s1, o[2 * q], o[8 + 2 * q]);
+      split2(s2, s3, o[2 * q + 1], o[8 + 2 * q + 1]);
+    }
+  } else
+#endif
+  {
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      float s0 = swish_acc<TERMS>(sc * __uint_as_float(v[2 * p]));
+      const float s1 = swish_acc<TERMS>(sc * __uint_as_float(v[2 * p + 1]));
+      if (p == 4 && ones) s0 = 1.0f;
+      if constexpr (TERMS == 3) split2(s0, s1, o[p], o[8 + p]);
+      else { o[p] = pack_bf16x2(s0, s1); o[8 + p] = 0u; }
+    }
   }
   tmem_st16(taddr, o);
 }
