@@ -148,7 +148,6 @@ class ModelRollout:
             use_host = False
         if use_host:
             obs, B = obs_h, obs_h.shape[0]
-            self._host_keep = (obs_h, acts_h)            # pinned sources of asynchronous copies stay alive until the next call
         else:
             obs = torch.as_tensor(start_obs).to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
             B = obs.shape[0]
@@ -203,6 +202,14 @@ class ModelRollout:
         model._ensure_handle()
         call = _lib.load().mopo_rollout_host if use_host else _lib.load().mopo_rollout
         _lib.check(call(model._handle, self._model_pool._handle, C.byref(a), _lib.stream_ptr(dev)))
+        if use_host:
+            # the host sources of the asynchronous uploads stay alive until the rollout that consumes them has run (the
+            # caller may drop or reuse its arrays as soon as this returns, and a freed pinned block is recycled at once)
+            done = torch.cuda.Event()
+            done.record(torch.cuda.current_stream(dev))
+            pending = [(e, t) for e, t in getattr(self, '_host_keep', []) if not e.query()]
+            pending.append((done, (obs_h, acts_h)))
+            self._host_keep = pending
         out = [int(steps[i]) for i in range(h)]
         while out and out[-1] == 0:          # the reference breaks out of the loop when nothing survives (mopo.py:754-756)
             out.pop()

@@ -113,3 +113,46 @@ def test_identity_model_type_bypasses_the_model():
         assert np.array_equal(f['next_observations'][:n], f['observations'][:n]) and np.array_equal(f['observations'][:50], obs)
         assert not f['rewards'][:n].any() and f['terminals'][:n].all() == bool(ident_term)
         assert np.array_equal(f['actions'][:50], acts[0])
+
+
+def test_host_rollouts_back_to_back_with_changing_sizes():
+    """mopo_rollout_host on the streamed-weights path keeps per-handle upload state (staging buffers, flag words, a flag
+    epoch that wraps after 255 calls): 300 consecutive host rollouts of changing size, nothing synchronised in between,
+    and the checked ones equal the device-input route bit for bit."""
+    import torch
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    import mopo_b200.static as static
+    h = 2
+    p, obs_all, _ = ens.synthetic_case('halfcheetah', 2000, seed=12)
+    m = _model(p)
+    rng = np.random.RandomState(4)
+    acts_all = [np.tanh(rng.standard_normal((2000, 6))).astype(np.float32) for _ in range(h)]
+
+    def runner():
+        env = FakeEnv(m, static['halfcheetah'], penalty_coeff=1.0, penalty_learned_var=True, seed=3)
+        ro = ModelRollout(env, SimpleReplayPool(17, 6, 10), rollout_batch_size=2000, rollout_schedule=(0, 1, h, h), seed=3)
+        ro._set_rollout_length()
+        return ro
+
+    host, dev = runner(), runner()
+    sizes = [257, 1, 2000, 300, 513, 64]
+    for it in range(300):
+        B = sizes[it % len(sizes)]
+        check = it in (0, 1, 2, 254, 255, 256, 299)
+        host._model_pool = SimpleReplayPool(17, 6, B * h)
+        o = torch.as_tensor(obs_all[:B]).pin_memory()
+        a = [torch.as_tensor(x[:B]).pin_memory() for x in acts_all]
+        rid = host._rollout_count                                   # (the rollout id feeds the Philox step id)
+        host._rollout_model(B, start_obs=o, actions=a, quiet=True)
+        if not check:
+            continue
+        torch.cuda.synchronize()
+        dev._model_pool = SimpleReplayPool(17, 6, B * h)
+        dev._rollout_count = rid
+        dev._rollout_model(B, start_obs=torch.as_tensor(obs_all[:B]).cuda(), actions=[torch.as_tensor(x[:B]).cuda() for x in acts_all], quiet=True)
+        torch.cuda.synchronize()
+        for k, v in host._model_pool.fields.items():
+            assert np.array_equal(v.cpu().numpy(), dev._model_pool.fields[k].cpu().numpy()), (it, B, k)
