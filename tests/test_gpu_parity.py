@@ -413,6 +413,46 @@ def test_rollout_host_actions_overlapped_upload_equals_device_actions(precision_
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize('domain,B', [('hopper', 5000), ('walker2d', 20000)])
+def test_rollout_host_inputs_with_terminating_rows_equal_device_inputs(domain, B):
+    """Terminating environments (compaction between the steps) with pinned HOST inputs: the chunked, flag-guarded uploads of
+    the fp32-accurate path must give the pool of the device-input route bit for bit, rows dying at every step."""
+    import torch
+    from mopo_b200 import _lib
+    from mopo_b200.models.fake_env import FakeEnv
+    from mopo_b200.replay_pools import SimpleReplayPool
+    from mopo_b200.algorithms.mopo import ModelRollout
+    import mopo_b200.static as static
+    h = 4
+    od, ad = SHAPES[domain]
+    p, obs, _ = ens.synthetic_case(domain, B, seed=63)
+    p['max_logvar'][:] = -9.0
+    p['weights'][-1] = p['weights'][-1] * 0.02
+    p['biases'][-1] = p['biases'][-1] * 0.0
+    r0 = np.random.RandomState(7)
+    obs[:, 0] = r0.uniform(0.75, 1.5, B).astype(np.float32)
+    obs[:, 1] = r0.uniform(-0.19, 0.19, B).astype(np.float32)
+    m = make_model(p)
+    rng = np.random.RandomState(3)
+    acts = [np.tanh(rng.standard_normal((B, ad))).astype(np.float32) for _ in range(h)]
+    pools, steps = [], []
+    for mode in ('device', 'host'):
+        env = FakeEnv(m, static[domain], penalty_coeff=1.0, penalty_learned_var=True, seed=5)
+        ro = ModelRollout(env, SimpleReplayPool(od, ad, 10), rollout_batch_size=B, rollout_schedule=(0, 1, h, h), seed=5)
+        ro._set_rollout_length()
+        ro._model_pool = SimpleReplayPool(od, ad, B * h)
+        a = [torch.as_tensor(x).cuda() for x in acts] if mode == 'device' else [torch.as_tensor(x).pin_memory() for x in acts]
+        o = torch.as_tensor(obs).cuda() if mode == 'device' else torch.as_tensor(obs).pin_memory()
+        ro._rollout_model(B, start_obs=o, actions=a, quiet=True)
+        torch.cuda.synchronize()
+        steps.append(list(ro._last_steps_added))
+        pools.append({k: v.cpu().numpy() for k, v in ro._model_pool.fields.items()})
+    assert steps[0] == steps[1] and len(steps[0]) > 1 and 0 < steps[0][1] < steps[0][0]
+    for k in pools[0]:
+        assert np.array_equal(pools[0][k], pools[1][k]), k
+
+
+@pytest.mark.gpu
 def test_offline_pool_restore_contiguous_and_d4rl_dict(tmp_path):
     """loader.py:102-126 / :23-29: the offline dataset lands in the device pool exactly as FlexibleReplayPool.add_samples
     would place it (oracle pool), incl. the f64 -> f32 cast and the bool terminals; random_batch then feeds the rollout."""
