@@ -350,6 +350,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
     const bool sc = a.mu != nullptr && i < s.in;
     sMu[i] = sc ? a.mu[i] : 0.0f;
     sSg[i] = sc ? a.sigma[i] : 1.0f;
+#ifndef MOPO_SCALER_DIVIDE
+    sSg[i] = 1.0f / sSg[i];                            // the input warps multiply (one rounding away from models/utils.py:96's division)
+#endif
   }
   if (warp == W_ISSUE) { tmem_alloc<2>(&bars->tmem_base, 512); tmem_relinquish<2>(); }
   tc_fence_before();
@@ -619,7 +622,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1) ens_tc3
             const int k = kc * 8 + i;
             float x = 0.0f;
             if (ok) {
+#ifdef MOPO_SCALER_DIVIDE
               if (k < s.in) x = (raw[pnl * 8 + i] - sMu[k]) / sSg[k];          // models/utils.py:96
+#else
+              if (k < s.in) x = (raw[pnl * 8 + i] - sMu[k]) * sSg[k];          // models/utils.py:96 (sSg = 1 / sigma)
+#endif
               else if (k == s.in) x = 1.0f;                                    // the bias row's constant
             }
             v[i] = x;

@@ -122,7 +122,18 @@ __device__ __forceinline__ void head_fused(uint32_t tblk, const HeadShape& s, co
   for (int w = 0; w < 2; ++w)
 #pragma unroll
     for (int i = 0; i < P; ++i) {
-      if constexpr (PRECISE) var[w][i] = sC[w * P + i] + 1.0f / (sC[MOPO_MAX_D1 + w * P + i] + expf(-a.acc_scale * __uint_as_float(v[w * 2 * P + P + i])));
+      if constexpr (PRECISE) {
+#ifdef MOPO_HEAD_LIBM
+        var[w][i] = sC[w * P + i] + 1.0f / (sC[MOPO_MAX_D1 + w * P + i] + expf(-a.acc_scale * __uint_as_float(v[w * 2 * P + P + i])));
+#else
+        // MUFU forms (ex2.approx / rcp.approx: ~1e-6 relative for |raw logvar| <= 20) -- in the fp32-accurate kernel the MUFU has
+        // room (37 % busy) and issue slots do not: libm's expf + an IEEE division were ~20 instructions per output
+        float ex, rc;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex) : "f"((-1.44269504f * a.acc_scale) * __uint_as_float(v[w * 2 * P + P + i])));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(sC[MOPO_MAX_D1 + w * P + i] + ex));
+        var[w][i] = sC[w * P + i] + rc;
+#endif
+      }
       else var[w][i] = sC[w * P + i] + rcp_fma(sC[MOPO_MAX_D1 + w * P + i] + exp2_fma(-1.44269504f * __uint_as_float(v[w * 2 * P + P + i])));
       pen[w] += var[w][i];
     }
