@@ -778,7 +778,11 @@ MOPO_API int mopo_rollout_host(mopo_ens* h, mopo_pool* pool, const mopo_rollout_
   // are enqueued while it already runs); the later steps' actions likewise, in fewer chunks.  The step tail, which may start
   // under the forward (programmatic launch), looks at the flag once and otherwise reads its inputs behind the forward.
   // (MOPO_NO_INPUT_FLAGS: developer A/B switch back to whole-array uploads behind events.)
-  const bool flagged = host_actions && (path == PATH_TC3 || path == PATH_TC1) && getenv("MOPO_NO_INPUT_FLAGS") == nullptr;
+  // (not under stream capture: a graph would hold the kernel and the copies it polls for as unordered branches)
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  CUDA_TRY(cudaStreamIsCapturing(st, &cap));
+  const bool flagged = host_actions && (path == PATH_TC3 || path == PATH_TC1) && cap == cudaStreamCaptureStatusNone &&
+                       getenv("MOPO_NO_INPUT_FLAGS") == nullptr;
   h->host_ready_on = false;
   if (flagged) {
     if (h->ready_flags.cap < sizeof(uint32_t) * 8 * H) {

@@ -46,7 +46,7 @@ struct SacFused {
   float *Xpi, *H0p, *H1p, *HD, *eps, *logp, *Xq, *Xt, *H0q, *H1q, *Qo, *T0, *T1, *To, *dQo, *dZ1q, *dZ0q, *dXa, *dHD, *dZ1p, *dZ0p;
   float* out;
   unsigned long long* trace;                   // null, or where CTA 0 records %globaltimer at its start and after every barrier
-  unsigned* bar; unsigned bar_base;          // grid barrier counter (only grows) and its value when this launch starts
+  unsigned long long* bar;                     // grid barrier counter, device-only state (gemm_fp32.cuh grid_bar)
   int n_ops; FOp ops[SAC_MAX_OPS];
 };
 
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) sac_fused_kernel(const __gri
     const double c = sqrt(1.0 - pow((double)ADAM_B2, (double)k_adam)) / (1.0 - pow((double)ADAM_B1, (double)k_adam));
     s_lr[0] = (float)((double)a.lr_pi * c); s_lr[1] = (float)((double)a.lr_q * c);
   }
-  unsigned bar_target = a.bar_base;
+  unsigned long long bar_target = grid_bar_begin(a.bar);
   int tr_i = 0;
   auto TRC = [&]() { if (a.trace && blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); a.trace[tr_i] = t; } ++tr_i; };
   TRC();
@@ -214,7 +214,6 @@ __global__ void __launch_bounds__(FUSED_THREADS, 1) sac_fused_kernel(const __gri
         default: break;
       }
     }
-    bar_target += gridDim.x;
     grid_bar(a.bar, bar_target); TRC();
     if (stage == 0 && blockIdx.x == 0 && threadIdx.x == 0) { *a.t = k_adam; *a.d_step = step; a.lr_t[0] = s_lr[0]; a.lr_t[1] = s_lr[1]; }
   }
@@ -285,7 +284,7 @@ struct mopo_sac {
   DevBuf Xpi, H0p, H1p, HD, eps, logp, Xq, Xt, H0q, H1q, Qo, T0, T1, To, dQo, dZ1q, dZ0q, dXa, dHD, dZ1p, dZ0p;
   uint64_t* d_step = nullptr;                         // device Philox step id of the policy noise (advanced by the update kernel)
   int grid = 0;                                       // CTAs of sac_fused_kernel: one per SM (cooperative launch)
-  unsigned* bar = nullptr; unsigned bar_count = 0;    // its grid barrier counter and the arrivals launched so far
+  unsigned long long* bar = nullptr;                  // its grid barrier counter (device-only state)
   unsigned long long* trace = nullptr;                // probe build: device buffer for CTA 0's globaltimer after every stage
   size_t psize(int i) const {                         // elements of tensor i in SacAdam order
     const int in_q = od + ad;
@@ -330,7 +329,7 @@ MOPO_API int mopo_sac_create(int32_t obs_dim, int32_t act_dim, int32_t hidden, i
   int per_sm = 0, sms = 0;
   CUDA_TRY(cudaFuncSetAttribute(sac_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FusedSmem)));
   CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sac_fused_kernel, FUSED_THREADS, sizeof(FusedSmem)));
-  CUDA_TRY(cudaMalloc(&s->bar, sizeof(unsigned))); CUDA_TRY(cudaMemset(s->bar, 0, sizeof(unsigned)));
+  CUDA_TRY(cudaMalloc(&s->bar, sizeof(unsigned long long))); CUDA_TRY(cudaMemset(s->bar, 0, sizeof(unsigned long long)));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   REQUIRE(per_sm > 0 && sms > 0, MOPO_ECUDA, "mopo_sac_create: the update kernel does not fit on an SM");
   s->grid = sms;
@@ -595,8 +594,7 @@ static int sac_update_impl(mopo_sac* s, const SacSample* smp, const float* obs, 
     colsum_op(a.dZ0p, a.g[1], n, H, 0, 1); ++stage;
     REQUIRE(!full, MOPO_EINVAL, "sac update: program table too small");
     a.n_ops = k;
-    a.bar = s->bar; a.bar_base = s->bar_count;
-    s->bar_count += (unsigned)stage * (unsigned)s->grid;      // one barrier per stage, every CTA arrives once
+    a.bar = s->bar;
   }
   a.trace = s->trace;
   void* args[] = {&a};
