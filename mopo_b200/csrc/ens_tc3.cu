@@ -201,17 +201,9 @@ __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.
 // (Measured and rejected, profiles/r02_tc3_timeline_v2_newton.txt: taking every second reciprocal on the FMA pipe -- magic
 // seed + 3 Newton steps -- to balance MUFU against issue slots made the epilogue 1.6x SLOWER: with two epilogue warps per
 // SM sub-partition the dependent FMA chains are not hidden, as round 1 found for the bf16 kernel.)  TERMS == 1: tanh form.
-template <int TERMS, bool NEWTON = false> __device__ __forceinline__ float swish_acc(float x) {
+template <int TERMS> __device__ __forceinline__ float swish_acc(float x) {
   if constexpr (TERMS == 1) { const float xh = 0.5f * x; return fmaf(xh, tanh_fast(xh), xh); }
-  else if constexpr (!NEWTON) return x * rcp_approx(1.0f + ex2_approx(-1.44269504f * x));
-  else {
-    // reciprocal on the FMA pipe: magic-constant seed (12 %) + 3 Newton steps (4e-8); d in [1, 2^100] keeps the seed finite
-    const float d = 1.0f + ex2_approx(fminf(-1.44269504f * x, 100.0f));
-    float r = __int_as_float(0x7EF311C7 - __float_as_int(d));
-#pragma unroll
-    for (int it = 0; it < 3; ++it) r = fmaf(r, fmaf(-d, r, 1.0f), r);
-    return x * r;
-  }
+  else return x * rcp_approx(1.0f + ex2_approx(-1.44269504f * x));
 }
 
 // operand formats: TERMS == 3 -> fp16 pairs, TERMS == 1 -> bf16
