@@ -21,6 +21,8 @@ __device__ __forceinline__ uint32_t op(uint32_t x) {
     asm volatile("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
     y = __float_as_uint(f * r);
   } else if (KIND == 8) asm volatile("cvt.rn.satfinite.f16x2.f32 %0, %1, %1;" : "=r"(y) : "r"(x));
+  else if (KIND == 10) asm volatile("ex2.approx.f16x2 %0, %1;" : "=r"(y) : "r"(x));
+  else if (KIND == 11) asm volatile("ex2.approx.ftz.bf16x2 %0, %1;" : "=r"(y) : "r"(x));
   else {                        // KIND 9: f16 -> f32 unpack + subtract (the lo part of the split)
     float f;
     asm volatile("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %1;\n\tcvt.f32.f16 %0, l;\n\t}" : "=f"(f) : "r"(x));
@@ -67,6 +69,8 @@ int mopo_debug_pipe_bench(int kind, int iters, long long* cycles_dev, int n_bloc
     case 7: MOPO_COUNT_LAUNCH, mufu_bench_kernel<7><<<n_blocks, 512, 0, st>>>(iters, 1u, cycles_dev, sink); break;
     case 8: MOPO_COUNT_LAUNCH, mufu_bench_kernel<8><<<n_blocks, 512, 0, st>>>(iters, 1u, cycles_dev, sink); break;
     case 9: MOPO_COUNT_LAUNCH, mufu_bench_kernel<9><<<n_blocks, 512, 0, st>>>(iters, 1u, cycles_dev, sink); break;
+    case 10: MOPO_COUNT_LAUNCH, mufu_bench_kernel<10><<<n_blocks, 512, 0, st>>>(iters, 1u, cycles_dev, sink); break;
+    case 11: MOPO_COUNT_LAUNCH, mufu_bench_kernel<11><<<n_blocks, 512, 0, st>>>(iters, 1u, cycles_dev, sink); break;
     default: mopo_set_error("mopo_debug_pipe_bench: kind=%d", kind); return MOPO_EINVAL;
   }
   CUDA_TRY(cudaGetLastError());

@@ -16,8 +16,8 @@ lib = _lib.load_probes()
 dev = torch.device('cuda', 0)
 st = torch.cuda.current_stream(dev)
 
-names = {0: 'tanh.f32', 1: 'tanh.bf16x2', 2: 'ex2.f32', 3: 'tanh.f16x2', 4: 'fma.bf16x2', 5: 'fma.f32', 6: 'rcp.f32', 7: 'swish(ex2+rcp)', 8: 'cvt.f16x2.f32', 9: 'cvt.f32.f16+sub'}
-for kind in (range(10) if os.environ.get('TL_PIPES', '1') == '1' else ()):
+names = {0: 'tanh.f32', 1: 'tanh.bf16x2', 2: 'ex2.f32', 3: 'tanh.f16x2', 4: 'fma.bf16x2', 5: 'fma.f32', 6: 'rcp.f32', 7: 'swish(ex2+rcp)', 8: 'cvt.f16x2.f32', 9: 'cvt.f32.f16+sub', 10: 'ex2.f16x2', 11: 'ex2.bf16x2'}
+for kind in (range(12) if os.environ.get('TL_PIPES', '1') == '1' else ()):
     nb, iters = 148, 2000
     cyc = torch.zeros(nb + 1, dtype=torch.int64, device=dev)
     for _ in range(2):
