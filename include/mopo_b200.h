@@ -289,6 +289,14 @@ int mopo_sac_update_from_pools(mopo_sac* s, const mopo_pool* env_pool, const mop
                                int32_t n_model, uint64_t seed, int32_t n_updates, float* losses_out, void* stream);
 /* Copy the actor (scope main/pi) into a rollout policy handle, device to device (rebuilds its tensor-core image). */
 int mopo_sac_export_policy(mopo_sac* s, mopo_policy* p, void* stream);
+/* Optimiser state for checkpoint / resume (the reference checkpoints its TF session, which holds the four Adam optimisers'
+ * slots, mopo.py:417-441): the 13 tensors in the order pi {W0 b0 W1 b1 Whead bhead}, q {W0 b0 W1 b1 W2 b2} (twins stacked),
+ * log_alpha, with Whead / bhead the fused [mu | log_std] head.  sizes: element counts; m / v: HOST arrays of those sizes;
+ * t: Adam step; draw: update index that keys the minibatch draws and the policy noise. */
+#define MOPO_SAC_TENSORS 13
+int mopo_sac_opt_sizes(mopo_sac* s, int64_t* sizes);
+int mopo_sac_get_opt_state(mopo_sac* s, float* const* m, float* const* v, int64_t* t, uint64_t* draw, void* stream);
+int mopo_sac_set_opt_state(mopo_sac* s, const float* const* m, const float* const* v, int64_t t, uint64_t draw, void* stream);
 
 /* ---- MOPO._rollout_model ------------------------------------------------------------------ */
 typedef struct {

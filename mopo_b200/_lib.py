@@ -118,6 +118,9 @@ SYMBOLS = {
     'mopo_sac_update_from_pools': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint64, C.c_int32,
                                              C.c_void_p, C.c_void_p]),
     'mopo_sac_export_policy': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    'mopo_sac_opt_sizes': (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    'mopo_sac_get_opt_state': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_uint64), C.c_void_p]),
+    'mopo_sac_set_opt_state': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int64, C.c_uint64, C.c_void_p]),
     'mopo_policy_create': (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     'mopo_policy_destroy': (C.c_int, [C.c_void_p]),
     'mopo_policy_set_params': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_void_p]),

@@ -94,15 +94,49 @@ class SACUpdate:
         out['log_alpha'] = float(la.value)
         return out
 
+    def _opt_sizes(self):
+        sizes = (C.c_int64 * 13)()
+        _lib.check(_lib.load().mopo_sac_opt_sizes(self._handle, sizes))
+        return [int(x) for x in sizes]
+
+    def get_opt_state(self):
+        """Adam slots of the 13 variables (C-ABI order), the Adam step and the update index that keys the random draws."""
+        sizes = self._opt_sizes()
+        m = [np.empty(n, np.float32) for n in sizes]
+        v = [np.empty(n, np.float32) for n in sizes]
+        t, draw = C.c_int64(), C.c_uint64()
+        _lib.check(_lib.load().mopo_sac_get_opt_state(self._handle, (C.c_void_p * 13)(*[a.ctypes.data for a in m]),
+                                                      (C.c_void_p * 13)(*[a.ctypes.data for a in v]), C.byref(t), C.byref(draw),
+                                                      _lib.stream_ptr(self.device)))
+        return {'m': m, 'v': v, 't': int(t.value), 'draw': int(draw.value)}
+
+    def set_opt_state(self, state):
+        sizes = self._opt_sizes()
+        m = [np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1)) for a in state['m']]
+        v = [np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1)) for a in state['v']]
+        if [a.size for a in m] != sizes or [a.size for a in v] != sizes:
+            raise ValueError('SACUpdate.set_opt_state: slot sizes %r, expected %r' % ([a.size for a in m], sizes))
+        _lib.check(_lib.load().mopo_sac_set_opt_state(self._handle, (C.c_void_p * 13)(*[a.ctypes.data for a in m]),
+                                                      (C.c_void_p * 13)(*[a.ctypes.data for a in v]), int(state['t']), int(state['draw']),
+                                                      _lib.stream_ptr(self.device)))
+        self._num_train_steps = int(state['t'])
+
     def save(self, path):
-        """Checkpoint of every variable (main + target networks, log_alpha) as one .npz (the reference checkpoints the TF
-        session; the optimiser moments are not part of it and restart from zero on load, like a fresh AdamOptimizer)."""
+        """Checkpoint as one .npz: every variable (main + target networks, log_alpha) and the optimiser state (Adam slots, Adam
+        step, the update index behind the minibatch draws and the policy noise) -- what the reference's TF-session checkpoint
+        holds, so that a resumed run continues the same sequence instead of replaying it from update 0."""
         p = self.get_params()
         flat = {'log_alpha': np.float32(p['log_alpha'])}
         for name in ('pi', 'q1', 'q2', 'q1_targ', 'q2_targ'):
             for k in ('W', 'b'):
                 for i, a in enumerate(p[name][k]):
                     flat['%s/%s%d' % (name, k, i)] = a
+        o = self.get_opt_state()
+        for i in range(13):
+            flat['opt/m%d' % i] = o['m'][i]
+            flat['opt/v%d' % i] = o['v'][i]
+        flat['opt/t'] = np.int64(o['t'])
+        flat['opt/draw'] = np.uint64(o['draw'])
         np.savez(path, **flat)
 
     def load(self, path):
@@ -110,8 +144,11 @@ class SACUpdate:
         get = lambda name, k, n: [d['%s/%s%d' % (name, k, i)] for i in range(n)]
         self.set_params(get('pi', 'W', 4), get('pi', 'b', 4), get('q1', 'W', 3), get('q1', 'b', 3), get('q2', 'W', 3), get('q2', 'b', 3),
                         float(d['log_alpha']))
-        # set_params runs target_init; a checkpoint taken mid-training carries its own targets
+        # set_params runs target_init and resets the optimisers; a checkpoint taken mid-training carries its own targets and slots
         self._set_targets(get('q1_targ', 'W', 3), get('q1_targ', 'b', 3), get('q2_targ', 'W', 3), get('q2_targ', 'b', 3))
+        if 'opt/t' in d.files:                      # (checkpoints written before the optimiser state was saved: variables only)
+            self.set_opt_state({'m': [d['opt/m%d' % i] for i in range(13)], 'v': [d['opt/v%d' % i] for i in range(13)],
+                                't': int(d['opt/t']), 'draw': int(d['opt/draw'])})
 
     def _set_targets(self, q1t_W, q1t_b, q2t_W, q2t_b):
         keep = []

@@ -477,6 +477,47 @@ MOPO_API int mopo_sac_export_policy(mopo_sac* s, mopo_policy* p, void* stream) {
   return mopo_policy_set_params(p, W, b, 1, stream);
 }
 
+MOPO_API int mopo_sac_opt_sizes(mopo_sac* s, int64_t* sizes) {
+  REQUIRE(s && sizes, MOPO_EINVAL, "mopo_sac_opt_sizes: null argument");
+  static_assert(SAC_TENSORS == MOPO_SAC_TENSORS, "header and kernel disagree on the tensor count");
+  for (int i = 0; i < SAC_TENSORS; ++i) sizes[i] = (int64_t)s->psize(i);
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_sac_get_opt_state(mopo_sac* s, float* const* m, float* const* v, int64_t* t, uint64_t* draw, void* stream) {
+  REQUIRE(s && m && v && t && draw, MOPO_EINVAL, "mopo_sac_get_opt_state: null argument");
+  REQUIRE(s->params_set, MOPO_ESTATE, "mopo_sac_get_opt_state: parameters not set");
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int i = 0; i < SAC_TENSORS; ++i) {
+    REQUIRE(m[i] && v[i], MOPO_EINVAL, "mopo_sac_get_opt_state: tensor %d null", i);
+    TRY(sac_copy(m[i], s->m[i], s->psize(i), cudaMemcpyDeviceToHost, st));
+    TRY(sac_copy(v[i], s->v[i], s->psize(i), cudaMemcpyDeviceToHost, st));
+  }
+  CUDA_TRY(cudaMemcpyAsync(t, s->t, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(draw, s->d_step, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  return MOPO_OK;
+}
+
+MOPO_API int mopo_sac_set_opt_state(mopo_sac* s, const float* const* m, const float* const* v, int64_t t, uint64_t draw, void* stream) {
+  REQUIRE(s && m && v, MOPO_EINVAL, "mopo_sac_set_opt_state: null argument");
+  REQUIRE(s->params_set, MOPO_ESTATE, "mopo_sac_set_opt_state: parameters not set");
+  REQUIRE(t >= 0, MOPO_EINVAL, "mopo_sac_set_opt_state: t=%lld", (long long)t);
+  CUDA_TRY(cudaSetDevice(s->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int i = 0; i < SAC_TENSORS; ++i) {
+    REQUIRE(m[i] && v[i], MOPO_EINVAL, "mopo_sac_set_opt_state: tensor %d null", i);
+    TRY(sac_copy(s->m[i], m[i], s->psize(i), cudaMemcpyHostToDevice, st));
+    TRY(sac_copy(s->v[i], v[i], s->psize(i), cudaMemcpyHostToDevice, st));
+  }
+  CUDA_TRY(cudaMemcpyAsync(s->t, &t, sizeof(int64_t), cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaMemcpyAsync(s->d_step, &draw, sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  s->updates = t;                                  // (the Polyak interval counts updates, mopo.py:839-841)
+  return MOPO_OK;
+}
+
 static int sac_reserve(mopo_sac* s, int n) {
   const int od = s->od, ad = s->ad, H = s->H, in_q = od + ad;
   const size_t N = (size_t)n;

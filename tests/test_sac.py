@@ -298,3 +298,39 @@ def test_sac_real_ratio_one_uses_only_the_env_pool():
     empty = SimpleReplayPool(od, ad, 10)
     with pytest.raises(RuntimeError):                     # sampling an empty pool (np.random.randint(0, 0) raises in the reference)
         a.train_from_pools(empty, None, n_updates=1)
+
+
+@pytest.mark.gpu
+def test_checkpoint_resume_continues_the_same_sequence(tmp_path):
+    """save() / load() carry the Adam slots, the Adam step and the update index behind the random draws: 4 + 3 updates with a
+    checkpoint in between equal 7 uninterrupted updates bit for bit (a resumed run that restarted its optimisers or replayed
+    its draws from update 0 would not)."""
+    from mopo_b200.algorithms.sac import SACUpdate
+    from mopo_b200.replay_pools import SimpleReplayPool
+    od, ad = 11, 3
+    rng = np.random.RandomState(8)
+    env_pool, model_pool = SimpleReplayPool(od, ad, 2000), SimpleReplayPool(od, ad, 9000)
+    env_pool.add_samples(_batch(rng, 2000, od, ad))
+    model_pool.add_samples(_batch(rng, 9000, od, ad))
+    a = SACUpdate(od, ad, device=0, seed=5)
+    b = SACUpdate(od, ad, device=0, seed=5)
+    a.train_from_pools(env_pool, model_pool, n_updates=7)
+    b.train_from_pools(env_pool, model_pool, n_updates=4)
+    path = str(tmp_path / 'sac.npz')
+    b.save(path)
+    c = SACUpdate(od, ad, device=0, seed=5)
+    c.load(path)
+    st = c.get_opt_state()
+    assert st['t'] == 4 and st['draw'] == 4 and any(np.abs(m).max() > 0 for m in st['m'])
+    c.train_from_pools(env_pool, model_pool, n_updates=3)
+    pa, pc = a.get_params(), c.get_params()
+    for name in ('pi', 'q1', 'q2', 'q1_targ', 'q2_targ'):
+        for k in ('W', 'b'):
+            for x, y in zip(pa[name][k], pc[name][k]):
+                assert np.array_equal(x, y), (name, k)
+    assert pa['log_alpha'] == pc['log_alpha']
+    oa, oc = a.get_opt_state(), c.get_opt_state()
+    assert oa['t'] == oc['t'] == 7 and oa['draw'] == oc['draw']
+    for x, y in zip(oa['m'] + oa['v'], oc['m'] + oc['v']):
+        assert np.array_equal(x, y)
+
