@@ -21,8 +21,10 @@
  *   mopo_rollout, mopo_rollout_host        <- MOPO._rollout_model, mopo/algorithms/mopo.py:723-765 (device / host inputs)
  *   mopo_sac_*                             <- the SAC update (actor, twin critics, alpha, Polyak targets): graph mopo.py:271-457,
  *                                             MOPO._do_training / _training_batch, mopo.py:801-843
+ *   mopo_sac_get/set_opt_state             <- the Adam slots + step inside the reference's TF-session checkpoint (mopo.py:417-441)
  *   mopo_policy_*                          <- the SAC actor graph (mlp_gaussian_policy + apply_squashing_func,
  *                                             mopo.py:292-312) and MOPO.get_action_meta, mopo.py:468-485
+ *   mopo_ens_predict_noalloc               <- no counterpart in the reference
  */
 #ifndef MOPO_B200_H
 #define MOPO_B200_H
